@@ -1,0 +1,202 @@
+/*
+ * salp_b200.h -- C ABI of the B200-native batched SALP swimmer environment step.
+ *
+ * This is the drop-in boundary for ONE hot path of SungRoboticsGroup/UNDERWATER-SWIMMER_RL:
+ * SalpSnakeEnv.reset / SalpSnakeEnv.step over the legacy SalpRobotEnv integrator
+ *   R = scripts/utilities/salp_robot.py                 (reference tree)
+ *   S = src/salp/environments/salp_snake_env.py
+ * The reference has no FFI (it is pure Python); each entry point below names the Python
+ * method(s) it replaces.  A Python host binds this with ctypes (INTEGRATION.md shows the
+ * stub); the in-repo host is underwater_swimmer_rl_b200/vector_env.py.
+ *
+ * Conventions
+ *   - Every function returns 0 on success, a negative SALP_E* code on failure; the
+ *     message is available from salp_last_error() (thread-local).  No exceptions cross
+ *     the ABI; CUDA errors are returned, never aborted on.
+ *   - All DEVICE buffers are allocated and owned by the caller (PyTorch's caching
+ *     allocator in the in-repo host).  The library never allocates, frees or copies
+ *     tensor memory in the async API; a handle owns only its parameter block (and, for
+ *     the optional *_host entry points, private staging buffers and streams).
+ *   - salp_reset / salp_step are asynchronous on the caller-supplied CUDA stream and
+ *     never synchronise.  One handle per GPU per process; a handle is not thread-safe,
+ *     different handles are independent.
+ *   - There is no CPU fallback: without a CUDA device every compute entry point fails
+ *     with SALP_ECUDA.
+ */
+#ifndef SALP_B200_H_
+#define SALP_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SALP_ABI_VERSION 1
+
+enum { SALP_OK = 0, SALP_EINVAL = -1, SALP_ECUDA = -2, SALP_EUNBOUND = -3, SALP_EUNSUPPORTED = -4 };
+
+/* arithmetic type of the integrator ("dtype" of the build, not a precision claim) */
+enum { SALP_F32 = 0, /* throughput build: float state/actions/reward                      */
+       SALP_F64 = 1  /* validation build: double, reference operation order, no FMA fusion */ };
+
+enum { SALP_MAX_FOOD = 32, SALP_MAX_OBSERVED_FOOD = 8 };
+
+/* flags for SalpParams.flags */
+enum { SALP_AUTORESET = 1 /* done lanes are reset inside the step (gymnasium 0.29 vector semantics) */ };
+
+/* event bits written to SalpBuffers.events */
+enum { SALP_EV_TERMINATED = 1, SALP_EV_TRUNCATED = 2, SALP_EV_COLLISION = 4, SALP_EV_FOOD = 8 };
+
+/*
+ * Task parameters == the keyword arguments of SalpSnakeEnv.__init__ (S:29-33) plus the
+ * tank size of SalpRobotEnv.__init__ (R:28).  The robot constants of R:34-53 and the
+ * food constants of S:53-54 are fixed in the kernel, as they are in the reference.
+ */
+typedef struct SalpParams {
+    double width, height;             /* R:28            default 800 x 600           */
+    int32_t num_food_items;           /* S:30,36         base_num_food_items, 0..32  */
+    int32_t max_observed_food;        /* S:32,44         1..8, default 3             */
+    int32_t forced_breathing;         /* S:31,43,66      1: action = [nozzle]; 0: [inhale, nozzle] */
+    int32_t random_food_count;        /* S:32,37,144-146                             */
+    int32_t respawn_food;             /* S:32,38,179                                 */
+    int32_t max_steps_without_food;   /* S:33,46,185                                 */
+    double food_reward;               /* S:30,39                                     */
+    double collision_penalty;         /* S:30,40                                     */
+    double time_penalty;              /* S:31,41                                     */
+    double efficiency_bonus;          /* S:31,42,287-290                             */
+    double proximity_reward_weight;   /* S:33,45,297-322                             */
+    int32_t flags;                    /* SALP_AUTORESET                              */
+    int32_t reserved_;
+} SalpParams;
+
+/* Sizes the caller needs to allocate SalpBuffers; filled by salp_query_layout(). */
+typedef struct SalpLayout {
+    int32_t real_bytes;      /* 4 (SALP_F32) or 8 (SALP_F64)                                   */
+    int32_t obs_dim;         /* 10 + 4*max_observed_food + 2   (S:79-80)                       */
+    int32_t act_dim;         /* 1 forced breathing, 2 manual   (S:69-74)                       */
+    int32_t food_slots;      /* F: food records per env kept in HBM (>= num_food_items)        */
+    int32_t body_reals;      /* 8  reals per env: [2][N] records of 4                          */
+    int32_t ctrl_ints;       /* 8  int32 per env: [2][N] records of 4                          */
+    int32_t stats_len;       /* 8  doubles                                                     */
+    int32_t reserved_;
+} SalpLayout;
+
+/*
+ * Device buffers.  N = num_envs of the handle.  "real" = float or double per dtype.
+ * State lives in HBM as structure-of-arrays of 128-bit (f32) / 256-bit (f64) records so
+ * that every per-env load/store is one vector access and a warp touches 512 contiguous bytes:
+ *   body      real [2][N][4]   rec0 = (pos.x, pos.y, vel.x, vel.y)          R:61-62
+ *                              rec1 = (angle, angular_vel, nozzle, water)    R:63-67,77
+ *   ctrl      i32  [2][N][4]   rec0 = (fsm, steps_since_food, food_collected, food_mask)
+ *                              rec1 = (food_cursor, jitter_cursor, episode_len, n_food)
+ *             fsm bits: [0:2) breathing phase 0 rest/1 inhaling/2 exhaling (R:71)
+ *                       [2:10) breathing_timer (R:72)   [10:18) current_exhale_duration (R:223)
+ *                       [18:20) body-shape source 0 reset(30,30)/1 rest/2 inhale/3 exhale
+ *                       [20:28) timer value the ellipse axes were last computed from
+ *             (ellipse_a/b of R:74-75 are recomputed from the shape fields, never stored)
+ *   ep_return real [N]         running episode return
+ *   food      real [F][N][2]   food_positions (S:52); liveness is ctrl.food_mask
+ *   actions   real [K][N][act_dim]      read by salp_step
+ *   obs       f32  [K][N][obs_dim]      written by salp_step (and [N][obs_dim] by salp_reset)
+ *   reward    real [K][N]
+ *   terminated, truncated  u8 [K][N]    (torch.bool compatible)
+ *   events    u8   [K][N]  SALP_EV_* bits, may be NULL
+ *   final_obs f32  [K][N][obs_dim]  terminal observation, written ONLY for lanes that
+ *             finished at that substep in SALP_AUTORESET mode; may be NULL
+ *   final_info real [K][N][4]  (episode return, episode length, food_collected,
+ *             steps_since_food) of the episode that just ended (the reference's terminal
+ *             `info`, S:195-200), written ONLY for lanes that finished; may be NULL
+ *   stats     f64  [8]  accumulated: episodes, sum return, sum length, sum food, collisions,
+ *             truncations, non-finite lanes, env-steps; may be NULL
+ *   food_words / jit_words  u32 [rows][len]  host-seeded MT19937 output streams the
+ *             reference would draw from `random` (S:101-104,239-242) and `np.random`
+ *             (R:311); env e (local index) reads row e % table_rows at its cursor (mod len).
+ *             The host fills row r from seed (seed0 + env_id0 + r), so with
+ *             table_rows == N results do not depend on how envs are sharded over GPUs.
+ */
+typedef struct SalpBuffers {
+    void *body;
+    int32_t *ctrl;
+    void *ep_return;
+    void *food;
+    const void *actions;
+    float *obs;
+    void *reward;
+    uint8_t *terminated;
+    uint8_t *truncated;
+    uint8_t *events;
+    float *final_obs;
+    void *final_info;
+    double *stats;
+    const uint32_t *food_words;
+    const uint32_t *jit_words;
+    int64_t table_rows;
+    int64_t food_len; /* words per row, power of two */
+    int64_t jit_len;  /* words per row, power of two, >= 2 */
+    int32_t max_substeps; /* K the actions/obs/reward/... buffers were sized for */
+    int32_t reserved_;
+} SalpBuffers;
+
+typedef struct SalpHandle SalpHandle;
+
+int salp_abi_version(void);
+
+/* Thread-local message of the last failing call ("" if none). */
+const char *salp_last_error(void);
+
+/* Validate params and report buffer geometry.  Pure host code. */
+int salp_query_layout(const SalpParams *params, int dtype, SalpLayout *out);
+
+/*
+ * Replaces SalpSnakeEnv.__init__ (S:29-90) for a slab of `num_envs` independent
+ * environments with global ids env_id0 .. env_id0+num_envs-1 on CUDA device `device`.
+ */
+int salp_create(const SalpParams *params, int64_t num_envs, int64_t env_id0, int device, int dtype,
+                SalpHandle **out);
+int salp_destroy(SalpHandle *h);
+
+/* Attach caller-owned device buffers (raw pointers, e.g. torch.Tensor.data_ptr()). */
+int salp_bind(SalpHandle *h, const SalpBuffers *buffers);
+
+/*
+ * Replaces SalpSnakeEnv.reset (S:133-155 over R:95-117) for every env whose byte in the
+ * DEVICE array `mask` is non-zero (all envs when mask is NULL).  Writes the reset
+ * observation to obs[0][e][:].  RNG cursors are NOT rewound (the reference keeps
+ * consuming its global streams across episodes); pass rewind_rng != 0 to restart them.
+ */
+int salp_reset(SalpHandle *h, const uint8_t *mask, int rewind_rng, void *cuda_stream);
+
+/*
+ * Replaces K consecutive SalpSnakeEnv.step calls (S:157-202 over R:119-156) per env in ONE
+ * kernel launch: state is read once, kept in registers for the K substeps, written once.
+ * 1 <= K <= buffers.max_substeps.
+ */
+int salp_step(SalpHandle *h, int K, void *cuda_stream);
+
+/*
+ * Host-buffer convenience path (what a caller holding numpy arrays uses): copies
+ * actions host->device, runs one step (K=1), copies obs/reward/terminated/truncated
+ * device->host, chunked over internal streams so the copies overlap the kernel, and
+ * returns after the results are in host memory.  Host pointers should be page-locked.
+ * Any output pointer may be NULL.
+ */
+int salp_step_host(SalpHandle *h, const void *actions_host, float *obs_host, void *reward_host,
+                   uint8_t *terminated_host, uint8_t *truncated_host);
+
+/*
+ * Fill `rows` rows of `len` raw MT19937 outputs into HOST memory dst[rows][len]:
+ *   kind 0: the stream of Python's random.seed(seed0 + first_row + r)     (init_by_array)
+ *   kind 1: the stream of numpy.random.seed(seed0 + first_row + r)        (init_genrand)
+ * Pure host code (multi-threaded); seeds must be < 2^32.
+ */
+int salp_fill_rng_words(uint32_t *dst, int64_t rows, int64_t len, uint64_t seed0, int64_t first_row,
+                        int kind, int num_threads);
+
+/* Number of kernels this library has launched on behalf of `h` (bench "gpu_launches"). */
+int64_t salp_launch_count(const SalpHandle *h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SALP_B200_H_ */

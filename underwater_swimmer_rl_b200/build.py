@@ -1,0 +1,77 @@
+"""Build libsalp_b200.so (the C-ABI shared library) in-tree with nvcc for sm_100a.
+
+    python -m underwater_swimmer_rl_b200.build [--force] [--verbose]
+
+Three translation units, compiled in parallel:
+  salp_kernels.cu  -DSALP_BUILD_F64=0               float   kernels (throughput build)
+  salp_kernels.cu  -DSALP_BUILD_F64=1 -fmad=false   double  kernels (validation build: no FMA
+                                                    contraction, reference operation order)
+  salp_capi.cu                                      extern "C" boundary (include/salp_b200.h)
+nvcc cross-compiles without a GPU; the built .so is git-ignored but travels with gpurun.
+"""
+from __future__ import annotations
+
+import os
+import subprocess
+import sys
+from concurrent.futures import ThreadPoolExecutor
+
+PKG = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(PKG, "csrc")
+OBJ = os.path.join(PKG, "_build")
+LIB = os.path.join(PKG, "libsalp_b200.so")
+NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
+COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC"] + ARCH
+
+
+def _sources():
+    hdrs = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".h", ".cuh"))]
+    hdrs.append(os.path.join(os.path.dirname(PKG), "include", "salp_b200.h"))
+    return hdrs
+
+
+def _stale(target: str, deps) -> bool:
+    if not os.path.exists(target):
+        return True
+    t = os.path.getmtime(target)
+    return any(os.path.getmtime(d) > t for d in deps)
+
+
+def build(force: bool = False, verbose: bool = False) -> str:
+    os.makedirs(OBJ, exist_ok=True)
+    hdrs = _sources()
+    kern = os.path.join(CSRC, "salp_kernels.cu")
+    capi = os.path.join(CSRC, "salp_capi.cu")
+    vflag = ["-Xptxas", "-v"] if verbose else []
+    jobs = [
+        (os.path.join(OBJ, "salp_kernels_f32.o"), [NVCC, "-c", kern, "-DSALP_BUILD_F64=0"] + COMMON + vflag, [kern] + hdrs),
+        (os.path.join(OBJ, "salp_kernels_f64.o"), [NVCC, "-c", kern, "-DSALP_BUILD_F64=1", "-fmad=false"] + COMMON + vflag, [kern] + hdrs),
+        (os.path.join(OBJ, "salp_capi.o"), [NVCC, "-c", capi] + COMMON, [capi] + hdrs),
+    ]
+    todo = [(o, c + ["-o", o]) for o, c, d in jobs if force or _stale(o, d)]
+
+    def run(job):
+        o, cmd = job
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        if r.returncode != 0:
+            raise RuntimeError(f"nvcc failed for {o}:\n{r.stdout}\n{r.stderr}")
+        return o, r.stderr
+
+    if todo:
+        with ThreadPoolExecutor(max_workers=3) as ex:
+            for o, log in ex.map(run, todo):
+                if verbose and log:
+                    print(f"---- {os.path.basename(o)}\n{log}")
+    objs = [o for o, _, _ in jobs]
+    if todo or force or _stale(LIB, objs):
+        cmd = [NVCC, "-shared", "-o", LIB] + objs + ARCH + ["-Xcompiler", "-fPIC", "-lcudart_static", "-lpthread", "-ldl", "-lrt"]
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        if r.returncode != 0:
+            raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")
+    return LIB
+
+
+if __name__ == "__main__":
+    path = build(force="--force" in sys.argv, verbose="--verbose" in sys.argv)
+    print(path)

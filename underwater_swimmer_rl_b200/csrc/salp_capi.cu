@@ -1,0 +1,353 @@
+// salp_capi.cu -- the extern "C" boundary declared in include/salp_b200.h.
+// Host-side only: parameter validation, buffer binding, kernel dispatch, the host-buffer
+// (pinned memory) step path, and the MT19937 word-table generator that reproduces the
+// reference's two global random streams.  No CPU implementation of the env step exists here:
+// without a CUDA device every compute entry point returns SALP_ECUDA.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <thread>
+#include <vector>
+
+#include "../../include/salp_b200.h"
+#include "salp_internal.h"
+
+namespace {
+
+thread_local char g_err[512] = "";
+
+int fail(int code, const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+int cuda_fail(cudaError_t e, const char *what) {
+    return fail(SALP_ECUDA, "%s: %s (%s)", what, cudaGetErrorName(e), cudaGetErrorString(e));
+}
+
+#define SALP_CUDA(expr)                                   \
+    do {                                                  \
+        cudaError_t err__ = (expr);                       \
+        if (err__ != cudaSuccess) return cuda_fail(err__, #expr); \
+    } while (0)
+
+constexpr int kHostChunks = 4;
+
+int pick_food_slots(int n) {
+    const int opts[] = {1, 4, 8, 12, 16, 32};
+    for (int o : opts)
+        if (n <= o) return o;
+    return -1;
+}
+
+bool is_pow2(int64_t v) { return v > 0 && (v & (v - 1)) == 0; }
+
+}  // namespace
+
+struct SalpHandle {
+    SalpParams params;
+    SalpLayout layout;
+    SalpBuffers buf;
+    salp::KernelArgs base;  // everything except per-launch fields
+    int64_t num_envs, env_id0;
+    int device, dtype;
+    bool bound;
+    int64_t launches;
+    cudaStream_t host_streams[kHostChunks];
+    bool host_streams_ready;
+};
+
+extern "C" {
+
+int salp_abi_version(void) { return SALP_ABI_VERSION; }
+
+const char *salp_last_error(void) { return g_err; }
+
+int salp_query_layout(const SalpParams *p, int dtype, SalpLayout *out) {
+    if (!p || !out) return fail(SALP_EINVAL, "null argument");
+    if (dtype != SALP_F32 && dtype != SALP_F64) return fail(SALP_EINVAL, "dtype must be SALP_F32 or SALP_F64");
+    if (!(p->width > 0) || !(p->height > 0)) return fail(SALP_EINVAL, "width/height must be positive");
+    if (p->num_food_items < 0 || p->num_food_items > SALP_MAX_FOOD)
+        return fail(SALP_EUNSUPPORTED, "num_food_items=%d outside 0..%d", p->num_food_items, SALP_MAX_FOOD);
+    if (p->max_observed_food < 0 || p->max_observed_food > SALP_MAX_OBSERVED_FOOD)
+        return fail(SALP_EUNSUPPORTED, "max_observed_food=%d outside 0..%d", p->max_observed_food, SALP_MAX_OBSERVED_FOOD);
+    if (p->max_steps_without_food < 0) return fail(SALP_EINVAL, "max_steps_without_food must be >= 0");
+    memset(out, 0, sizeof(*out));
+    out->real_bytes = dtype == SALP_F64 ? 8 : 4;
+    out->obs_dim = 10 + 4 * p->max_observed_food + 2;
+    out->act_dim = p->forced_breathing ? 1 : 2;
+    out->food_slots = pick_food_slots(std::max(1, p->num_food_items));
+    out->body_reals = 8;
+    out->ctrl_ints = 8;
+    out->stats_len = salp::kStatsLen;
+    return SALP_OK;
+}
+
+int salp_create(const SalpParams *p, int64_t num_envs, int64_t env_id0, int device, int dtype, SalpHandle **out) {
+    if (!out) return fail(SALP_EINVAL, "null out pointer");
+    *out = nullptr;
+    SalpLayout lay;
+    int rc = salp_query_layout(p, dtype, &lay);
+    if (rc != SALP_OK) return rc;
+    if (num_envs <= 0 || num_envs > (int64_t)1 << 30) return fail(SALP_EINVAL, "num_envs=%lld outside 1..2^30", (long long)num_envs);
+    if (env_id0 < 0) return fail(SALP_EINVAL, "env_id0 must be >= 0");
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0)
+        return fail(SALP_ECUDA, "no CUDA device available (%s); this library has no CPU fallback",
+                    e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e));
+    if (device < 0 || device >= ndev) return fail(SALP_EINVAL, "device %d outside 0..%d", device, ndev - 1);
+    cudaDeviceProp prop;
+    SALP_CUDA(cudaGetDeviceProperties(&prop, device));
+    if (prop.major < 10)
+        return fail(SALP_EUNSUPPORTED, "device %d is sm_%d%d; this library is built for sm_100a only", device, prop.major, prop.minor);
+
+    SalpHandle *h = new SalpHandle();
+    memset(h, 0, sizeof(*h));
+    h->params = *p;
+    h->layout = lay;
+    h->num_envs = num_envs;
+    h->env_id0 = env_id0;
+    h->device = device;
+    h->dtype = dtype;
+    salp::KernelArgs &a = h->base;
+    a.N = num_envs;
+    a.first = 0;
+    a.count = num_envs;
+    a.K = 1;
+    a.obs_dim = lay.obs_dim;
+    a.observed = p->max_observed_food;
+    a.act_dim = lay.act_dim;
+    a.forced = p->forced_breathing ? 1 : 0;
+    a.random_food_count = p->random_food_count ? 1 : 0;
+    a.respawn = p->respawn_food ? 1 : 0;
+    a.autoreset = (p->flags & SALP_AUTORESET) ? 1 : 0;
+    a.max_steps = p->max_steps_without_food;
+    a.num_food = p->num_food_items;
+    a.W = p->width;
+    a.H = p->height;
+    a.food_reward = p->food_reward;
+    a.collision_penalty = p->collision_penalty;
+    a.time_penalty = p->time_penalty;
+    a.efficiency_bonus = p->efficiency_bonus;
+    a.proximity_w = p->proximity_reward_weight;
+    for (int t = 0; t < 128; ++t) {  // R:223 int(self.exhale_duration * max(self.water_volume, 0.3)), wv = t/120
+        const double wv = (double)std::min(t, 120) / 120.0;
+        a.exhale_lut[t] = (uint8_t)(int)(150.0 * std::max(wv, 0.3));
+    }
+    *out = h;
+    return SALP_OK;
+}
+
+int salp_destroy(SalpHandle *h) {
+    if (!h) return SALP_OK;
+    if (h->host_streams_ready) {
+        cudaSetDevice(h->device);
+        for (auto &s : h->host_streams) cudaStreamDestroy(s);
+    }
+    delete h;
+    return SALP_OK;
+}
+
+int salp_bind(SalpHandle *h, const SalpBuffers *b) {
+    if (!h || !b) return fail(SALP_EINVAL, "null argument");
+    if (!b->body || !b->ctrl || !b->ep_return || !b->food || !b->obs || !b->reward || !b->terminated || !b->truncated)
+        return fail(SALP_EINVAL, "body/ctrl/ep_return/food/obs/reward/terminated/truncated must be non-null");
+    if (!b->food_words || !b->jit_words) return fail(SALP_EINVAL, "RNG word tables must be non-null");
+    if (b->table_rows <= 0 || b->table_rows > h->num_envs) return fail(SALP_EINVAL, "table_rows must be in 1..num_envs");
+    if (!is_pow2(b->food_len) || !is_pow2(b->jit_len) || b->jit_len < 2 || b->food_len < 2)
+        return fail(SALP_EINVAL, "food_len/jit_len must be powers of two >= 2");
+    if (b->food_len > ((int64_t)1 << 30) || b->jit_len > ((int64_t)1 << 30)) return fail(SALP_EINVAL, "table rows too long");
+    if (b->max_substeps < 1) return fail(SALP_EINVAL, "max_substeps must be >= 1");
+    const uintptr_t align16[] = {(uintptr_t)b->body, (uintptr_t)b->ctrl, (uintptr_t)b->food, (uintptr_t)b->obs,
+                                 (uintptr_t)b->final_obs, (uintptr_t)b->actions, (uintptr_t)b->jit_words};
+    for (uintptr_t p : align16)
+        if (p % 32 != 0) return fail(SALP_EINVAL, "device buffers must be 32-byte aligned");
+    h->buf = *b;
+    salp::KernelArgs &a = h->base;
+    a.body = b->body;
+    a.ctrl = reinterpret_cast<int4 *>(b->ctrl);
+    a.ep_return = b->ep_return;
+    a.food = b->food;
+    a.actions = b->actions;
+    a.obs = b->obs;
+    a.reward = b->reward;
+    a.terminated = b->terminated;
+    a.truncated = b->truncated;
+    a.events = b->events;
+    a.final_obs = b->final_obs;
+    a.final_info = b->final_info;
+    a.stats = b->stats;
+    a.food_words = b->food_words;
+    a.jit_words = b->jit_words;
+    a.rows = (unsigned)b->table_rows;
+    a.food_len = (unsigned)b->food_len;
+    a.jit_len = (unsigned)b->jit_len;
+    a.food_len_mask = (unsigned)b->food_len - 1;
+    a.jit_len_mask = (unsigned)b->jit_len - 1;
+    h->bound = true;
+    return SALP_OK;
+}
+
+static int launch_step(SalpHandle *h, const salp::KernelArgs &a, cudaStream_t s) {
+    cudaError_t e = h->dtype == SALP_F64 ? salp::launch_step_f64(a, h->layout.food_slots, s)
+                                         : salp::launch_step_f32(a, h->layout.food_slots, s);
+    if (e != cudaSuccess) return cuda_fail(e, "salp_step kernel launch");
+    ++h->launches;
+    return SALP_OK;
+}
+
+int salp_reset(SalpHandle *h, const uint8_t *mask, int rewind_rng, void *stream) {
+    if (!h) return fail(SALP_EINVAL, "null handle");
+    if (!h->bound) return fail(SALP_EUNBOUND, "salp_bind has not been called");
+    SALP_CUDA(cudaSetDevice(h->device));
+    salp::KernelArgs a = h->base;
+    a.reset_mask = mask;
+    a.rewind_rng = rewind_rng ? 1 : 0;
+    cudaError_t e = h->dtype == SALP_F64 ? salp::launch_reset_f64(a, h->layout.food_slots, (cudaStream_t)stream)
+                                         : salp::launch_reset_f32(a, h->layout.food_slots, (cudaStream_t)stream);
+    if (e != cudaSuccess) return cuda_fail(e, "salp_reset kernel launch");
+    ++h->launches;
+    return SALP_OK;
+}
+
+int salp_step(SalpHandle *h, int K, void *stream) {
+    if (!h) return fail(SALP_EINVAL, "null handle");
+    if (!h->bound) return fail(SALP_EUNBOUND, "salp_bind has not been called");
+    if (!h->buf.actions) return fail(SALP_EUNBOUND, "actions buffer is null");
+    if (K < 1 || K > h->buf.max_substeps) return fail(SALP_EINVAL, "K=%d outside 1..max_substeps=%d", K, h->buf.max_substeps);
+    SALP_CUDA(cudaSetDevice(h->device));
+    salp::KernelArgs a = h->base;
+    a.K = K;
+    return launch_step(h, a, (cudaStream_t)stream);
+}
+
+int salp_step_host(SalpHandle *h, const void *actions_host, float *obs_host, void *reward_host,
+                   uint8_t *terminated_host, uint8_t *truncated_host) {
+    if (!h) return fail(SALP_EINVAL, "null handle");
+    if (!h->bound) return fail(SALP_EUNBOUND, "salp_bind has not been called");
+    if (!h->buf.actions || !actions_host) return fail(SALP_EINVAL, "actions (device and host) must be non-null");
+    SALP_CUDA(cudaSetDevice(h->device));
+    if (!h->host_streams_ready) {
+        // blocking streams: ordered after earlier work on the legacy default stream
+        for (auto &s : h->host_streams) SALP_CUDA(cudaStreamCreate(&s));
+        h->host_streams_ready = true;
+    }
+    const int64_t N = h->num_envs;
+    const size_t rb = (size_t)h->layout.real_bytes, ad = (size_t)h->layout.act_dim, od = (size_t)h->layout.obs_dim;
+    // chunk boundaries on CTA granularity so every chunk but the last is a whole number of tiles
+    const int64_t tiles = (N + salp::kBlockThreads - 1) / salp::kBlockThreads;
+    const int chunks = (int)std::min<int64_t>(kHostChunks, tiles);
+    int rc = SALP_OK;
+    for (int c = 0; c < chunks && rc == SALP_OK; ++c) {
+        const int64_t t0 = tiles * c / chunks, t1 = tiles * (c + 1) / chunks;
+        const int64_t lo = t0 * salp::kBlockThreads, hi = std::min<int64_t>(N, t1 * salp::kBlockThreads);
+        const size_t n = (size_t)(hi - lo);
+        cudaStream_t s = h->host_streams[c];
+        SALP_CUDA(cudaMemcpyAsync((char *)h->buf.actions + lo * ad * rb, (const char *)actions_host + lo * ad * rb,
+                                  n * ad * rb, cudaMemcpyHostToDevice, s));
+        salp::KernelArgs a = h->base;
+        a.K = 1;
+        a.first = lo;
+        a.count = hi - lo;
+        rc = launch_step(h, a, s);
+        if (rc != SALP_OK) break;
+        if (obs_host)
+            SALP_CUDA(cudaMemcpyAsync(obs_host + lo * od, h->buf.obs + lo * od, n * od * sizeof(float), cudaMemcpyDeviceToHost, s));
+        if (reward_host)
+            SALP_CUDA(cudaMemcpyAsync((char *)reward_host + lo * rb, (char *)h->buf.reward + lo * rb, n * rb, cudaMemcpyDeviceToHost, s));
+        if (terminated_host)
+            SALP_CUDA(cudaMemcpyAsync(terminated_host + lo, h->buf.terminated + lo, n, cudaMemcpyDeviceToHost, s));
+        if (truncated_host)
+            SALP_CUDA(cudaMemcpyAsync(truncated_host + lo, h->buf.truncated + lo, n, cudaMemcpyDeviceToHost, s));
+    }
+    for (int c = 0; c < chunks; ++c) {
+        cudaError_t e = cudaStreamSynchronize(h->host_streams[c]);
+        if (e != cudaSuccess && rc == SALP_OK) rc = cuda_fail(e, "salp_step_host synchronize");
+    }
+    return rc;
+}
+
+int64_t salp_launch_count(const SalpHandle *h) { return h ? h->launches : 0; }
+
+// ---------------------------------------------------------------------------------------------
+// MT19937 word streams (host).  Reproduces CPython's random.seed(int) and numpy's legacy
+// np.random.seed(int) so the tables hold exactly the words the reference would consume.
+// ---------------------------------------------------------------------------------------------
+namespace {
+struct MT {
+    uint32_t mt[624];
+    int idx;
+    void init_genrand(uint32_t s) {
+        mt[0] = s;
+        for (int i = 1; i < 624; ++i) mt[i] = 1812433253u * (mt[i - 1] ^ (mt[i - 1] >> 30)) + (uint32_t)i;
+        idx = 624;
+    }
+    void init_by_array(const uint32_t *key, int len) {
+        init_genrand(19650218u);
+        int i = 1, j = 0;
+        for (int k = std::max(624, len); k; --k) {
+            mt[i] = (mt[i] ^ ((mt[i - 1] ^ (mt[i - 1] >> 30)) * 1664525u)) + key[j] + (uint32_t)j;
+            if (++i >= 624) { mt[0] = mt[623]; i = 1; }
+            if (++j >= len) j = 0;
+        }
+        for (int k = 623; k; --k) {
+            mt[i] = (mt[i] ^ ((mt[i - 1] ^ (mt[i - 1] >> 30)) * 1566083941u)) - (uint32_t)i;
+            if (++i >= 624) { mt[0] = mt[623]; i = 1; }
+        }
+        mt[0] = 0x80000000u;
+        idx = 624;
+    }
+    void twist() {
+        for (int k = 0; k < 624; ++k) {
+            const uint32_t y = (mt[k] & 0x80000000u) | (mt[(k + 1) % 624] & 0x7fffffffu);
+            mt[k] = mt[(k + 397) % 624] ^ (y >> 1) ^ ((y & 1u) ? 0x9908b0dfu : 0u);
+        }
+        idx = 0;
+    }
+    uint32_t next() {
+        if (idx >= 624) twist();
+        uint32_t y = mt[idx++];
+        y ^= y >> 11;
+        y ^= (y << 7) & 0x9d2c5680u;
+        y ^= (y << 15) & 0xefc60000u;
+        y ^= y >> 18;
+        return y;
+    }
+};
+}  // namespace
+
+int salp_fill_rng_words(uint32_t *dst, int64_t rows, int64_t len, uint64_t seed0, int64_t first_row, int kind,
+                        int num_threads) {
+    if (!dst || rows < 0 || len <= 0 || first_row < 0) return fail(SALP_EINVAL, "bad arguments");
+    if (kind != 0 && kind != 1) return fail(SALP_EINVAL, "kind must be 0 (python random) or 1 (numpy legacy)");
+    if (seed0 + (uint64_t)first_row + (uint64_t)rows > 0xffffffffull) return fail(SALP_EINVAL, "seeds must stay below 2^32");
+    int nt = num_threads > 0 ? num_threads : (int)std::thread::hardware_concurrency();
+    nt = (int)std::max<int64_t>(1, std::min<int64_t>(nt, rows));
+    auto work = [=](int t) {
+        MT g;
+        for (int64_t r = rows * t / nt; r < rows * (t + 1) / nt; ++r) {
+            const uint32_t s = (uint32_t)(seed0 + (uint64_t)first_row + (uint64_t)r);
+            if (kind == 0) g.init_by_array(&s, 1);
+            else g.init_genrand(s);
+            uint32_t *out = dst + r * len;
+            for (int64_t i = 0; i < len; ++i) out[i] = g.next();
+        }
+    };
+    if (nt == 1) work(0);
+    else {
+        std::vector<std::thread> th;
+        for (int t = 0; t < nt; ++t) th.emplace_back(work, t);
+        for (auto &t : th) t.join();
+    }
+    return SALP_OK;
+}
+
+}  // extern "C"

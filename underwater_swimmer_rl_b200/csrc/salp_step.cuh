@@ -1,0 +1,634 @@
+// salp_step.cuh -- the SALP env-step kernel for sm_100a (one thread per environment).
+//
+// What it replaces (reference tree, Python):
+//   R = scripts/utilities/salp_robot.py             SalpRobotEnv.step            R:119-156
+//   S = src/salp/environments/salp_snake_env.py     SalpSnakeEnv.step / reset    S:133-202
+// K consecutive env steps per launch: the per-env state is read ONCE with 128-bit (f32) /
+// 256-bit (f64) vector loads from structure-of-arrays records, lives in registers across the
+// K substeps and is written back ONCE; per substep only action is read and only
+// obs / reward / terminated / truncated are written.  The observation tile of a CTA
+// (256 envs x obs_dim floats, contiguous in HBM) is staged in shared memory and written with
+// one TMA bulk store (cp.async.bulk.global.shared::cta) per substep, double-buffered so the
+// store of substep k overlaps the arithmetic of substep k+1.  Rare, divergent work (food
+// respawn, episode reset: rejection sampling from the RNG word tables) lives in __noinline__
+// slow paths that talk to global memory directly so it costs no registers on the hot path.
+// Episode statistics are reduced with warp shuffles and one atomic per warp, only in warps
+// where an episode actually ended.
+//
+// Arithmetic: templated on the real type.  The double instantiation is compiled with
+// -fmad=false and keeps the reference's operation order so that discrete events match the
+// reference bit-for-bit; the float instantiation is the throughput build.
+#pragma once
+#include <math_constants.h>
+
+#include "salp_internal.h"
+#include "salp_sortnets.cuh"
+
+namespace salp {
+
+template <typename T> struct alignas(4 * sizeof(T)) Vec4 { T x, y, z, w; };
+template <typename T> struct alignas(2 * sizeof(T)) Vec2 { T x, y; };
+
+// Model constants, evaluated in double exactly as the Python expressions are (R:34-53, S:53-54).
+namespace kc {
+constexpr double PI = 3.141592653589793;   // math.pi
+constexpr double TWO_PI = 2 * PI;
+constexpr double MAX_NOZZLE = PI / 3;      // R:47
+constexpr double HALF_PI = PI / 2;         // R:301
+constexpr double TANK_MARGIN = 50.0, BASE_R = 30.0, FOOD_R = 15.0, MIN_FOOD_DIST = 80.0;
+constexpr double A_REST = BASE_R * 1.3, B_REST = BASE_R * 0.8;  // R:190-191
+constexpr double A_FULL = BASE_R * 1.1, B_FULL = BASE_R * 1.1;  // R:209-210
+constexpr double NOZZLE_RATE = 0.05;       // R:48
+constexpr int INHALE_DUR = 120;            // R:51
+}  // namespace kc
+
+template <typename T> struct is_f64 { static constexpr bool value = false; };
+template <> struct is_f64<double> { static constexpr bool value = true; };
+
+template <typename T> __device__ __forceinline__ T rsqrt_(T x);
+__device__ __forceinline__ float sqrt_(float x) { return sqrtf(x); }
+__device__ __forceinline__ double sqrt_(double x) { return sqrt(x); }
+__device__ __forceinline__ float sin_(float x) { return sinf(x); }
+__device__ __forceinline__ double sin_(double x) { return sin(x); }
+__device__ __forceinline__ float cos_(float x) { return cosf(x); }
+__device__ __forceinline__ double cos_(double x) { return cos(x); }
+__device__ __forceinline__ void sincos_(float x, float *s, float *c) { sincosf(x, s, c); }
+__device__ __forceinline__ void sincos_(double x, double *s, double *c) { sincos(x, s, c); }
+__device__ __forceinline__ float atan2_(float y, float x) { return atan2f(y, x); }
+__device__ __forceinline__ double atan2_(double y, double x) { return atan2(y, x); }
+__device__ __forceinline__ float abs_(float x) { return fabsf(x); }
+__device__ __forceinline__ double abs_(double x) { return fabs(x); }
+
+// Python's max(x, y) / min(x, y): keep the first argument unless the second is strictly better.
+template <typename T> __device__ __forceinline__ T pymax(T x, T y) { return (y > x) ? y : x; }
+template <typename T> __device__ __forceinline__ T pymin(T x, T y) { return (y < x) ? y : x; }
+
+// x / c with c a compile-time constant: true division in the validation build, multiply by the
+// folded reciprocal in the throughput build (<= 1 ulp(f32) apart; tolerance is 1e-3).
+template <typename T> __device__ __forceinline__ T divc(T x, double c) {
+    if constexpr (is_f64<T>::value) return x / c;
+    else return x * (float)(1.0 / c);
+}
+
+template <typename T> __device__ __forceinline__ T wrap_pi(T x) {  // R:329-332, S:311-314, S:403-406
+    while (x > (T)kc::PI) x -= (T)kc::TWO_PI;
+    while (x < (T)(-kc::PI)) x += (T)kc::TWO_PI;
+    return x;
+}
+
+// ---------------------------------------------------------------------------------------------
+// RNG word tables (see include/salp_b200.h): genrand_res53 from two consecutive MT19937 outputs
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ double res53(uint32_t w0, uint32_t w1) {
+    return ((double)(w0 >> 5) * 67108864.0 + (double)(w1 >> 6)) * (1.0 / 9007199254740992.0);
+}
+__device__ __forceinline__ uint32_t food_word(const KernelArgs &a, unsigned row, unsigned &cur) {
+    const uint32_t w = a.food_words[(size_t)row * a.food_len + (cur & a.food_len_mask)];
+    ++cur;
+    return w;
+}
+template <typename T> __device__ __forceinline__ T food_uniform(const KernelArgs &a, unsigned row, unsigned &cur, T lo, T hi) {
+    const uint32_t w0 = food_word(a, row, cur), w1 = food_word(a, row, cur);
+    return lo + (hi - lo) * (T)res53(w0, w1);  // random.uniform: a + (b-a)*random()
+}
+
+// ---------------------------------------------------------------------------------------------
+// Slow paths: __noinline__, operate on global memory, executed by a handful of lanes per step
+// ---------------------------------------------------------------------------------------------
+
+// S:232-276 _respawn_food.  Live foods are read from HBM (food records only ever change here
+// and in reset_slow, so HBM is always current).  Returns the refilled slot and its position.
+template <typename T>
+__device__ __noinline__ void respawn_slow(const KernelArgs &a, long long e, T px, T py, unsigned &mask, int n_food,
+                                          unsigned &cur, int &slot, T &nx, T &ny) {
+    const unsigned row = (unsigned)e % a.rows;
+    Vec2<T> *food = reinterpret_cast<Vec2<T> *>(a.food);
+    const T xlo = (T)(kc::TANK_MARGIN + kc::FOOD_R), xhi = (T)a.W - (T)kc::TANK_MARGIN - (T)kc::FOOD_R;
+    const T ylo = xlo, yhi = (T)a.H - (T)kc::TANK_MARGIN - (T)kc::FOOD_R;
+    int attempts = 0;
+    T x, y;
+    bool found = false;
+    while (attempts < 50) {
+        x = food_uniform<T>(a, row, cur, xlo, xhi);
+        y = food_uniform<T>(a, row, cur, ylo, yhi);
+        const T rx = x - px, ry = y - py;
+        if (sqrt_(rx * rx + ry * ry) < (T)kc::MIN_FOOD_DIST) { ++attempts; continue; }
+        bool valid = true;
+        for (int j = 0; j < n_food; ++j)
+            if ((mask >> j) & 1u) {
+                const Vec2<T> f = food[(size_t)j * a.N + e];
+                const T dx = x - f.x, dy = y - f.y;
+                if (sqrt_(dx * dx + dy * dy) < (T)kc::MIN_FOOD_DIST) { valid = false; break; }
+            }
+        if (valid) { found = true; break; }
+        ++attempts;
+    }
+    if (!found) {
+        x = food_uniform<T>(a, row, cur, xlo, xhi);
+        y = food_uniform<T>(a, row, cur, ylo, yhi);
+    }
+    slot = -1;
+    for (int j = 0; j < n_food; ++j)
+        if (!((mask >> j) & 1u)) { slot = j; break; }
+    if (slot >= 0) {
+        food[(size_t)slot * a.N + e] = Vec2<T>{x, y};
+        mask |= 1u << slot;
+    }
+    nx = x; ny = y;
+}
+
+// S:133-155 reset (food part: S:92-131 _generate_food_positions, S:144-148 food count) and the
+// reset observation (S:366-428 with the robot at the tank centre, R:95-117).
+template <typename T>
+__device__ __noinline__ void reset_slow(const KernelArgs &a, long long e, unsigned &cur, int &n_food_out,
+                                        unsigned &mask_out, float *obs_row) {
+    const unsigned row = (unsigned)e % a.rows;
+    Vec2<T> *food = reinterpret_cast<Vec2<T> *>(a.food);
+    int n_food = a.num_food;
+    if (a.random_food_count) {  // random.randint(1, max(1, base)) == 1 + _randbelow(n)
+        const uint32_t n = (uint32_t)(a.num_food > 1 ? a.num_food : 1);
+        const int kbits = 32 - __clz(n);
+        uint32_t r;
+        do { r = food_word(a, row, cur) >> (32 - kbits); } while (r >= n);
+        n_food = 1 + (int)r;
+    }
+    const T xlo = (T)(kc::TANK_MARGIN + kc::FOOD_R), xhi = (T)a.W - (T)kc::TANK_MARGIN - (T)kc::FOOD_R;
+    const T ylo = xlo, yhi = (T)a.H - (T)kc::TANK_MARGIN - (T)kc::FOOD_R;
+    const T cx = (T)a.W / 2, cy = (T)a.H / 2;
+    T dist[kMaxFood];
+    int idx[kMaxFood];
+    for (int i = 0; i < n_food; ++i) {
+        int attempts = 0;
+        T x = 0, y = 0;
+        while (attempts < 100) {
+            x = food_uniform<T>(a, row, cur, xlo, xhi);
+            y = food_uniform<T>(a, row, cur, ylo, yhi);
+            bool valid = true;
+            for (int j = 0; j < i; ++j) {
+                const Vec2<T> f = food[(size_t)j * a.N + e];
+                const T dx = x - f.x, dy = y - f.y;
+                if (sqrt_(dx * dx + dy * dy) < (T)kc::MIN_FOOD_DIST) { valid = false; break; }
+            }
+            const T rx = x - cx, ry = y - cy;
+            if (sqrt_(rx * rx + ry * ry) < (T)kc::MIN_FOOD_DIST) valid = false;
+            if (valid) break;
+            ++attempts;
+        }
+        if (attempts >= 100) {
+            x = food_uniform<T>(a, row, cur, xlo, xhi);
+            y = food_uniform<T>(a, row, cur, ylo, yhi);
+        }
+        food[(size_t)i * a.N + e] = Vec2<T>{x, y};
+        const T rx = x - cx, ry = y - cy;
+        dist[i] = sqrt_(rx * rx + ry * ry);
+        idx[i] = i;
+    }
+    n_food_out = n_food;
+    mask_out = n_food >= 32 ? 0xffffffffu : ((1u << n_food) - 1u);
+    if (obs_row == nullptr) return;
+    // observation of the freshly reset env: robot at the centre, all zeros, body radius 30
+    obs_row[0] = (float)(cx / (T)a.W); obs_row[1] = (float)(cy / (T)a.H);
+    obs_row[2] = 0.f; obs_row[3] = 0.f; obs_row[4] = 0.f; obs_row[5] = 0.f;
+    obs_row[6] = (float)((T)kc::BASE_R / (T)kc::BASE_R);
+    obs_row[7] = 0.f; obs_row[8] = 0.f; obs_row[9] = 0.f;
+    for (int i = 1; i < n_food; ++i) {  // stable insertion sort by distance
+        const T d = dist[i];
+        const int k = idx[i];
+        int j = i - 1;
+        while (j >= 0 && dist[j] > d) { dist[j + 1] = dist[j]; idx[j + 1] = idx[j]; --j; }
+        dist[j + 1] = d; idx[j + 1] = k;
+    }
+    const T diag = sqrt_((T)a.W * (T)a.W + (T)a.H * (T)a.H);
+    float *fo = obs_row + 10;
+    for (int i = 0; i < a.observed; ++i) {
+        if (i < n_food) {
+            const Vec2<T> f = food[(size_t)idx[i] * a.N + e];
+            const T dx = f.x - cx, dy = f.y - cy;
+            const T rel = wrap_pi<T>(atan2_(dy, dx) - (T)0);
+            fo[0] = (float)(dx / (T)a.W); fo[1] = (float)(dy / (T)a.H);
+            fo[2] = (float)(dist[i] / diag); fo[3] = (float)(rel / (T)kc::PI);
+        } else { fo[0] = 0.f; fo[1] = 0.f; fo[2] = 1.f; fo[3] = 0.f; }
+        fo += 4;
+    }
+    fo[0] = (float)pymin<T>((T)n_food / (T)10.0, (T)1.0);
+    if (n_food > 0) {
+        T s = 0;
+        for (int i = 0; i < n_food; ++i) s = s + dist[i];
+        fo[1] = (float)((s / (T)n_food) / diag);
+    } else fo[1] = 1.f;
+}
+
+// ---------------------------------------------------------------------------------------------
+// TMA bulk store helpers (1-D, no tensor map): shared::cta -> global
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void bulk_store_commit(void *gdst, const void *ssrc, uint32_t bytes) {
+    const uint32_t s = (uint32_t)__cvta_generic_to_shared(ssrc);
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(s), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+template <int kPending> __device__ __forceinline__ void bulk_wait_read() {
+    asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(kPending) : "memory");
+}
+
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// ---------------------------------------------------------------------------------------------
+// The step kernel
+//   T  : float | double      F : food records per env (1,4,8,12,16,32)
+//   MT : compile-time bound on max_observed_food (3 -> the reference default, 8 -> generic)
+// ---------------------------------------------------------------------------------------------
+template <typename T, int F, int MT>
+__global__ void __launch_bounds__(kBlockThreads) salp_step_kernel(const __grid_constant__ KernelArgs a) {
+    extern __shared__ __align__(128) float s_tile[];  // [nbuf][256][obs_dim]
+    const int tid = threadIdx.x;
+    const long long blk0 = a.first + (long long)blockIdx.x * kBlockThreads;
+    const long long e = blk0 + tid;
+    const long long end = a.first + a.count;
+    const bool valid = e < end;
+    const int n_rows = (int)((end - blk0) < kBlockThreads ? (end - blk0) : kBlockThreads);
+    const int OBS = a.obs_dim;
+    const long long N = a.N;
+
+    Vec4<T> *g_body = reinterpret_cast<Vec4<T> *>(a.body);
+    T *g_epret = reinterpret_cast<T *>(a.ep_return);
+    const Vec2<T> *g_food = reinterpret_cast<const Vec2<T> *>(a.food);
+    T *g_reward = reinterpret_cast<T *>(a.reward);
+    const T *g_act = reinterpret_cast<const T *>(a.actions);
+
+    // ---- load state: 4 x 128-bit records + ep_return + F food records, all independent loads
+    Vec4<T> b0{0, 0, 0, 0}, b1{0, 0, 0, 0};
+    int4 c0 = make_int4(0, 0, 0, 0), c1 = make_int4(0, 0, 0, 0);
+    T ep_ret = 0;
+    T fx[F], fy[F];
+#pragma unroll
+    for (int f = 0; f < F; ++f) { fx[f] = 0; fy[f] = 0; }
+    if (valid) {
+        b0 = g_body[e];
+        b1 = g_body[N + e];
+        c0 = a.ctrl[e];
+        c1 = a.ctrl[N + e];
+        ep_ret = g_epret[e];
+#pragma unroll
+        for (int f = 0; f < F; ++f) {
+            const Vec2<T> v = g_food[(size_t)f * N + e];
+            fx[f] = v.x; fy[f] = v.y;
+        }
+    }
+    T px = b0.x, py = b0.y, vx = b0.z, vy = b0.w;
+    T angle = b1.x, omega = b1.y, nozzle = b1.z, wv = b1.w;
+    int phase = c0.x & 3, timer = (c0.x >> 2) & 0xff, exd = (c0.x >> 10) & 0xff;
+    int skind = (c0.x >> 18) & 3, stimer = (c0.x >> 20) & 0xff;
+    int steps_since_food = c0.y, food_collected = c0.z;
+    unsigned mask = (unsigned)c0.w;
+    unsigned cur_food = (unsigned)c1.x, cur_jit = (unsigned)c1.y;
+    int ep_len = c1.z, n_food = c1.w;
+
+    const T W = (T)a.W, H = (T)a.H;
+    const T diag = sqrt_(W * W + H * H);  // S:396 (exact for the integer tank sizes)
+    T invW = 0, invH = 0, invDiag = 0;
+    if constexpr (!is_f64<T>::value) { invW = 1.0f / W; invH = 1.0f / H; invDiag = 1.0f / diag; }
+
+    for (int k = 0; k < a.K; ++k) {
+        float *s_buf = s_tile + (size_t)(k & 1) * kBlockThreads * OBS;
+        float *s_row = s_buf + (size_t)tid * OBS;
+        if (k >= 2) {  // the bulk store issued two substeps ago must have finished reading s_buf
+            if (tid == 0) bulk_wait_read<1>();
+            __syncthreads();
+        }
+        // ---- action (R:121-135)
+        T act0 = 0, act1 = 0;
+        if (valid) {
+            if (a.act_dim == 1) act0 = g_act[(size_t)k * N + e];
+            else {
+                const Vec2<T> v = reinterpret_cast<const Vec2<T> *>(g_act)[(size_t)k * N + e];
+                act0 = v.x; act1 = v.y;
+            }
+        }
+        bool inhaling;
+        T dir;
+        if (a.forced) {  // R:158-167: (timer % 330) < 120; timer <= 151 so the modulo is the identity
+            dir = act0;
+            inhaling = timer < kc::INHALE_DUR;
+        } else {
+            inhaling = act0 > (T)0.5;
+            dir = act1;
+        }
+        // ---- nozzle slew (R:169-182)
+        {
+            const T target = dir * (T)kc::MAX_NOZZLE;
+            const T diff = target - nozzle;
+            if (abs_(diff) > (T)kc::NOZZLE_RATE) nozzle = (diff > 0) ? nozzle + (T)kc::NOZZLE_RATE : nozzle - (T)kc::NOZZLE_RATE;
+            else nozzle = target;
+            nozzle = pymax<T>((T)(-kc::MAX_NOZZLE), pymin<T>((T)kc::MAX_NOZZLE, nozzle));
+        }
+        // ---- breathing FSM on integers (R:184-259); thresholds 0.1<=t/D<=0.5 and t/D<=1 are
+        //      exact integer compares (margins >= 1/(10*150) >> ulp), see tests/test_fsm_invariants.py
+        bool thrust = false;
+        int wv_mode = 0;  // 0 keep, 1 wv=p, 2 wv=max(0,wv*(1-p)), 3 wv=0
+        if (phase == kPhaseRest) {
+            skind = kShapeRest;
+            if (inhaling) { phase = kPhaseInhale; timer = 0; }
+        } else if (phase == kPhaseInhale) {
+            if (inhaling && timer < kc::INHALE_DUR) {
+                ++timer; skind = kShapeInhale; stimer = timer; wv_mode = 1;
+            } else if (wv > (T)0.05) {
+                exd = a.exhale_lut[timer];
+                phase = kPhaseExhale; timer = 0;
+            } else { phase = kPhaseRest; timer = 0; wv_mode = 3; }
+        } else {
+            ++timer;
+            if (timer <= exd) {
+                skind = kShapeExhale; stimer = timer; wv_mode = 2;
+                thrust = (10 * timer >= exd) && (2 * timer <= exd);
+            } else { phase = kPhaseRest; timer = 0; wv_mode = 3; }
+        }
+        // ---- ellipse axes from the shape fields (R:190-191, 207-213, 240-246)
+        T ea, eb, prog = 0;
+        if (skind == kShapeReset) { ea = (T)kc::BASE_R; eb = (T)kc::BASE_R; }
+        else if (skind == kShapeRest) { ea = (T)kc::A_REST; eb = (T)kc::B_REST; }
+        else {
+            const bool inh = (skind == kShapeInhale);
+            prog = (T)stimer / (T)(inh ? kc::INHALE_DUR : exd);
+            const T sa = inh ? (T)kc::A_REST : (T)kc::A_FULL, sb = inh ? (T)kc::B_REST : (T)kc::B_FULL;
+            const T da = inh ? (T)(kc::A_FULL - kc::A_REST) : (T)(kc::A_REST - kc::A_FULL);
+            const T db = inh ? (T)(kc::B_FULL - kc::B_REST) : (T)(kc::B_REST - kc::B_FULL);
+            ea = sa + da * prog; eb = sb + db * prog;
+        }
+        const T radius = pymax<T>(ea, eb);
+        if (wv_mode == 1) wv = prog;
+        // ---- jet thrust through the steerable nozzle (R:261-314)
+        if (thrust) {
+            const T Tm = (T)100.0 * wv * (T)0.4;
+            const T th = angle - nozzle;
+            T s0, c0_;
+            sincos_(th, &s0, &c0_);
+            vx += (c0_ * Tm) * (T)0.012;
+            vy += (s0 * Tm) * (T)0.012;
+            const T primary = -nozzle * Tm * (T)0.0002;
+            const T arm = radius * (T)0.7;
+            const T perp = Tm * sin_(-nozzle);
+            const T moment = perp * arm * (T)0.00005;
+            const T shape = -nozzle * Tm * wv * (T)0.00003;
+            omega += primary + moment + shape;
+            const T sm = Tm * abs_(nozzle) * (T)0.3;
+            T s1, c1_;
+            if constexpr (is_f64<T>::value) sincos_(th + (T)kc::HALF_PI, &s1, &c1_);
+            else { s1 = c0_; c1_ = -s0; }  // cos(x+pi/2) = -sin x, sin(x+pi/2) = cos x
+            vx += (c1_ * sm) * (T)0.008;
+            vy += (s1 * sm) * (T)0.008;
+            const unsigned row = (unsigned)e % a.rows;
+            const uint2 w = *reinterpret_cast<const uint2 *>(a.jit_words + (size_t)row * a.jit_len + (cur_jit & a.jit_len_mask));
+            cur_jit += 2;
+            const T u = (T)res53(w.x, w.y);  // np.random.random(), R:311
+            const T na = th + (u - (T)0.5) * (T)0.05;
+            const T nf = Tm * (T)0.04;
+            T s2, c2;
+            sincos_(na, &s2, &c2);
+            vx += c2 * nf * (T)0.002;
+            vy += s2 * nf * (T)0.002;
+        }
+        if (wv_mode == 2) { const T w2 = wv * ((T)1.0 - prog); wv = (w2 > 0) ? w2 : (T)0; }
+        else if (wv_mode == 3) wv = 0;
+        // ---- drag, integrate, wrap, wall bounce (R:316-352)
+        vx *= (T)0.98; vy *= (T)0.98; omega *= (T)0.95;
+        px += vx; py += vy;
+        angle = wrap_pi<T>(angle + omega);
+        {
+            const T margin = (T)kc::TANK_MARGIN + radius;
+            if (px < margin) { px = margin; vx = abs_(vx) * (T)0.4; omega *= (T)0.7; }
+            else if (px > W - margin) { px = W - margin; vx = -abs_(vx) * (T)0.4; omega *= (T)0.7; }
+            if (py < margin) { py = margin; vy = abs_(vy) * (T)0.4; omega *= (T)0.7; }
+            else if (py > H - margin) { py = H - margin; vy = -abs_(vy) * (T)0.4; omega *= (T)0.7; }
+        }
+        // ---- food distances (shared by hit test S:204-217, reward S:350-364 and obs S:375-379)
+        T dx[F], dy[F], dd[F];
+#pragma unroll
+        for (int f = 0; f < F; ++f) {
+            dx[f] = fx[f] - px; dy[f] = fy[f] - py;
+            dd[f] = sqrt_(dx[f] * dx[f] + dy[f] * dy[f]);
+        }
+        bool hit = false;
+        {
+            const T reach = radius + (T)kc::FOOD_R;
+#pragma unroll
+            for (int f = 0; f < F; ++f)
+                if (!hit && ((mask >> f) & 1u) && dd[f] < reach) { hit = true; mask &= ~(1u << f); }
+        }
+        // ---- wall contact (S:219-230), rounding-critical: same operands/order as the reference
+        const bool collision = (px - radius <= (T)kc::TANK_MARGIN) || (px + radius >= W - (T)kc::TANK_MARGIN) ||
+                               (py - radius <= (T)kc::TANK_MARGIN) || (py + radius >= H - (T)kc::TANK_MARGIN);
+        // ---- reward (S:278-327)
+        T reward = 0;
+        if (hit) {
+            reward += (T)a.food_reward;
+            if (a.efficiency_bonus > 0) reward += (T)a.efficiency_bonus * (T)(a.max_steps - steps_since_food);
+        }
+        if (collision) reward += (T)a.collision_penalty;
+        if (a.proximity_w > 0) {
+            bool any = false;
+            T bd = 0, bx = 0, by = 0;
+#pragma unroll
+            for (int f = 0; f < F; ++f)
+                if (((mask >> f) & 1u) && (!any || dd[f] < bd)) { any = true; bd = dd[f]; bx = dx[f]; by = dy[f]; }
+            if (any) reward += (T)a.proximity_w * cos_(wrap_pi<T>(atan2_(by, bx) - angle));
+        }
+        reward += (T)a.time_penalty;
+        // ---- counters, respawn (S:171-180)
+        ++steps_since_food;
+        if (hit) {
+            ++food_collected;
+            steps_since_food = 0;
+            if (a.respawn) {
+                int slot; T nx, ny;
+                respawn_slow<T>(a, e, px, py, mask, n_food, cur_food, slot, nx, ny);
+#pragma unroll
+                for (int f = 0; f < F; ++f)
+                    if (f == slot) {
+                        fx[f] = nx; fy[f] = ny;
+                        dx[f] = nx - px; dy[f] = ny - py;
+                        dd[f] = sqrt_(dx[f] * dx[f] + dy[f] * dy[f]);
+                    }
+            }
+        }
+        // ---- termination (S:182-189): collision > timeout > all collected
+        bool terminated = false, truncated = false;
+        if (collision) terminated = true;
+        else if (steps_since_food > a.max_steps) truncated = true;
+        else if (!a.respawn && mask == 0u) terminated = true;
+        if (!valid) { terminated = false; truncated = false; }
+        ep_ret += reward;
+        ++ep_len;
+
+        // ---- observation (R:377-388 + S:366-428) -> shared-memory row
+        float o[12 + 4 * MT];
+        if constexpr (is_f64<T>::value) {
+            o[0] = (float)(px / W); o[1] = (float)(py / H);
+        } else { o[0] = px * invW; o[1] = py * invH; }
+        o[2] = (float)divc<T>(vx, 5.0); o[3] = (float)divc<T>(vy, 5.0);
+        o[4] = (float)divc<T>(angle, kc::PI); o[5] = (float)divc<T>(omega, 0.1);
+        o[6] = (float)divc<T>(radius, kc::BASE_R);
+        o[7] = (float)((T)phase / (T)2.0);
+        o[8] = (float)wv;
+        o[9] = (float)divc<T>(nozzle, kc::MAX_NOZZLE);
+        {
+            int id[F];
+#pragma unroll
+            for (int f = 0; f < F; ++f) {
+                id[f] = f;
+                if (!((mask >> f) & 1u)) dd[f] = is_f64<T>::value ? (T)CUDART_INF : (T)CUDART_INF_F;
+            }
+#define SALP_CE(i, j)                                                                          \
+    {                                                                                          \
+        const bool sw = (dd[j] < dd[i]) || (dd[j] == dd[i] && id[j] < id[i]);                  \
+        const T t0 = sw ? dd[j] : dd[i], t1 = sw ? dd[i] : dd[j];                              \
+        const int u0 = sw ? id[j] : id[i], u1 = sw ? id[i] : id[j];                            \
+        dd[i] = t0; dd[j] = t1; id[i] = u0; id[j] = u1;                                        \
+    }
+            if constexpr (F == 2) { SALP_SORTNET_2(SALP_CE) }
+            else if constexpr (F == 4) { SALP_SORTNET_4(SALP_CE) }
+            else if constexpr (F == 8) { SALP_SORTNET_8(SALP_CE) }
+            else if constexpr (F == 12) { SALP_SORTNET_12(SALP_CE) }
+            else if constexpr (F == 16) { SALP_SORTNET_16(SALP_CE) }
+            else if constexpr (F == 32) { SALP_SORTNET_32(SALP_CE) }
+#undef SALP_CE
+            const int n_live = __popc(mask);
+            constexpr int MU = (MT < F) ? MT : F;  // entries that can ever be real
+#pragma unroll
+            for (int i = 0; i < MT; ++i) {
+                float q0 = 0.f, q1 = 0.f, q2 = 1.f, q3 = 0.f;  // S:412 padding [0,0,1,0]
+                if (i < MU) {
+                    if (i < n_live) {
+                        T sx = 0, sy = 0;
+#pragma unroll
+                        for (int f = 0; f < F; ++f)
+                            if (id[i] == f) { sx = dx[f]; sy = dy[f]; }
+                        const T rel = wrap_pi<T>(atan2_(sy, sx) - angle);
+                        if constexpr (is_f64<T>::value) {
+                            q0 = (float)(sx / W); q1 = (float)(sy / H); q2 = (float)(dd[i] / diag);
+                        } else { q0 = sx * invW; q1 = sy * invH; q2 = dd[i] * invDiag; }
+                        q3 = (float)divc<T>(rel, kc::PI);
+                    }
+                }
+                o[10 + 4 * i] = q0; o[11 + 4 * i] = q1; o[12 + 4 * i] = q2; o[13 + 4 * i] = q3;
+            }
+            float cnt, avg = 1.f;
+            cnt = (float)pymin<T>((T)n_live / (T)10.0, (T)1.0);
+            if (n_live > 0) {
+                T s = 0;
+#pragma unroll
+                for (int f = 0; f < F; ++f)
+                    if (f < n_live) s = s + dd[f];
+                const T mean = s / (T)n_live;
+                if constexpr (is_f64<T>::value) avg = (float)(mean / diag);
+                else avg = mean * invDiag;
+            }
+            // summary pair sits right after the `observed` food entries (runtime <= MT)
+#pragma unroll
+            for (int i = 0; i <= MT; ++i)
+                if (i == a.observed) { o[10 + 4 * i] = cnt; o[11 + 4 * i] = avg; }
+        }
+#pragma unroll
+        for (int j = 0; j < (12 + 4 * MT) / 4; ++j)
+            if (4 * j < OBS) *reinterpret_cast<float4 *>(s_row + 4 * j) = make_float4(o[4 * j], o[4 * j + 1], o[4 * j + 2], o[4 * j + 3]);
+
+        // ---- per-step outputs
+        const bool done = terminated || truncated;
+        if (valid) {
+            const size_t oi = (size_t)k * N + e;
+            g_reward[oi] = reward;
+            a.terminated[oi] = terminated ? 1 : 0;
+            a.truncated[oi] = truncated ? 1 : 0;
+            if (a.events) a.events[oi] = (uint8_t)((terminated ? 1 : 0) | (truncated ? 2 : 0) | (collision ? 4 : 0) | (hit ? 8 : 0));
+        }
+        // ---- episode statistics: warp-shuffle reduction, only in warps where an episode ended
+        const unsigned done_mask = __ballot_sync(0xffffffffu, done);
+        if (done_mask != 0u) {
+            if (a.stats) {
+                const double r = warp_sum(done ? (double)ep_ret : 0.0);
+                const double l = warp_sum(done ? (double)ep_len : 0.0);
+                const double fc = warp_sum(done ? (double)food_collected : 0.0);
+                const unsigned coll_mask = __ballot_sync(0xffffffffu, done && collision);
+                const unsigned trunc_mask = __ballot_sync(0xffffffffu, done && truncated);
+                const unsigned bad_mask = __ballot_sync(0xffffffffu, done && !(isfinite((double)px) && isfinite((double)py)));
+                if ((tid & 31) == 0) {
+                    atomicAdd(a.stats + 0, (double)__popc(done_mask));
+                    atomicAdd(a.stats + 1, r);
+                    atomicAdd(a.stats + 2, l);
+                    atomicAdd(a.stats + 3, fc);
+                    if (coll_mask) atomicAdd(a.stats + 4, (double)__popc(coll_mask));
+                    if (trunc_mask) atomicAdd(a.stats + 5, (double)__popc(trunc_mask));
+                    if (bad_mask) atomicAdd(a.stats + 6, (double)__popc(bad_mask));
+                }
+            }
+            if (done && a.final_info)
+                reinterpret_cast<Vec4<T> *>(a.final_info)[(size_t)k * N + e] =
+                    Vec4<T>{ep_ret, (T)ep_len, (T)food_collected, (T)steps_since_food};
+            if (done && a.autoreset) {
+                if (a.final_obs) {  // terminal observation (gymnasium "final_observation")
+                    float4 *dst = reinterpret_cast<float4 *>(a.final_obs + ((size_t)k * N + e) * OBS);
+                    for (int j = 0; j < OBS / 4; ++j) dst[j] = *reinterpret_cast<const float4 *>(s_row + 4 * j);
+                }
+                reset_slow<T>(a, e, cur_food, n_food, mask, s_row);
+                // R:95-117 deterministic robot reset, S:139-141 counters
+                px = W / 2; py = H / 2; vx = 0; vy = 0; angle = 0; omega = 0; nozzle = 0; wv = 0;
+                phase = kPhaseRest; timer = 0; skind = kShapeReset; stimer = 0;
+                steps_since_food = 0; food_collected = 0; ep_ret = 0; ep_len = 0;
+#pragma unroll
+                for (int f = 0; f < F; ++f) {
+                    if (f < n_food) {
+                        const Vec2<T> v = g_food[(size_t)f * N + e];
+                        fx[f] = v.x; fy[f] = v.y;
+                    }
+                }
+            }
+        }
+        // ---- publish the CTA's observation tile with one TMA bulk store
+        fence_proxy_async_smem();
+        __syncthreads();
+        if (tid == 0)
+            bulk_store_commit(a.obs + ((size_t)k * N + blk0) * OBS, s_buf, (uint32_t)(n_rows * OBS * sizeof(float)));
+    }
+
+    // ---- write state back once (food records are only written by the slow paths)
+    if (valid) {
+        g_body[e] = Vec4<T>{px, py, vx, vy};
+        g_body[N + e] = Vec4<T>{angle, omega, nozzle, wv};
+        const int fsm = phase | (timer << 2) | (exd << 10) | (skind << 18) | (stimer << 20);
+        a.ctrl[e] = make_int4(fsm, steps_since_food, food_collected, (int)mask);
+        a.ctrl[N + e] = make_int4((int)cur_food, (int)cur_jit, ep_len, n_food);
+        g_epret[e] = ep_ret;
+    }
+    if (blockIdx.x == 0 && tid == 0 && a.stats) atomicAdd(a.stats + 7, (double)a.count * (double)a.K);
+    if (tid == 0) bulk_wait_read<0>();  // smem must stay allocated until the last bulk store has read it
+}
+
+// ---------------------------------------------------------------------------------------------
+// Reset kernel: SalpSnakeEnv.reset for masked envs (S:133-155); writes obs[0][e][:]
+// ---------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(kBlockThreads) salp_reset_kernel(const __grid_constant__ KernelArgs a) {
+    const long long e = a.first + (long long)blockIdx.x * kBlockThreads + threadIdx.x;
+    if (e >= a.first + a.count) return;
+    if (a.reset_mask && a.reset_mask[e] == 0) return;
+    const long long N = a.N;
+    Vec4<T> *g_body = reinterpret_cast<Vec4<T> *>(a.body);
+    int4 c1 = a.ctrl[N + e];
+    unsigned cur_food = a.rewind_rng ? 0u : (unsigned)c1.x;
+    const unsigned cur_jit = a.rewind_rng ? 0u : (unsigned)c1.y;
+    int n_food;
+    unsigned mask;
+    reset_slow<T>(a, e, cur_food, n_food, mask, a.obs ? a.obs + (size_t)e * a.obs_dim : nullptr);
+    g_body[e] = Vec4<T>{(T)a.W / 2, (T)a.H / 2, 0, 0};
+    g_body[N + e] = Vec4<T>{0, 0, 0, 0};
+    const int fsm = kPhaseRest | (kShapeReset << 18);
+    a.ctrl[e] = make_int4(fsm, 0, 0, (int)mask);
+    a.ctrl[N + e] = make_int4((int)cur_food, (int)cur_jit, 0, n_food);
+    reinterpret_cast<T *>(a.ep_return)[e] = 0;
+}
+
+}  // namespace salp
