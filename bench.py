@@ -1,0 +1,320 @@
+#!/usr/bin/env python
+"""bench.py -- SALP env-steps/s on N B200s (one process per GPU), roofline, CPU baseline.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload NAME] [--impl ours|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
+        --master-port P bench.py --gpus N --steps K --warmup W
+
+A "step" is ONE launch of the env-step kernel over this rank's slab of environments (one env
+step for every env).  Workloads (BASELINE.json configs; per-GPU slab, weak scaling -- envs never
+interact, so ranks share nothing on the data path):
+    single_food_1m   configs/single_food.yaml, 1,048,576 envs / GPU, fp32          [default]
+    long_horizon_64k configs/single_food_long_horizon.yaml, 65,536 envs / GPU, fp32 (configs[2])
+    defaults_1m      configs/defaults.yaml (12 food), 1,048,576 envs / GPU, fp32   (configs[3])
+    parity_4k        configs/single_food.yaml, 4,096 envs, fp64 validation build   (configs[1])
+Prints ONE JSON line (rank 0).  See DESIGN.md section "Measurement" for every field.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+SINGLE_FOOD = dict(num_food_items=1, food_reward=1000.0, collision_penalty=-10.0, time_penalty=-0.1,
+                   proximity_reward_weight=5.0, respawn_food=True, forced_breathing=True,
+                   max_steps_without_food=1500, efficiency_bonus=0.0)
+LONG_HORIZON = dict(num_food_items=1, food_reward=1000.0, collision_penalty=-500.0, time_penalty=-0.5,
+                    proximity_reward_weight=3.0, respawn_food=True, forced_breathing=True,
+                    max_steps_without_food=2000, efficiency_bonus=0.0)
+DEFAULTS = dict(num_food_items=12, food_reward=15.0, collision_penalty=-30.0, time_penalty=-0.05,
+                efficiency_bonus=2.0, forced_breathing=True)
+WORKLOADS = {
+    "single_food_1m": dict(yaml="configs/single_food.yaml", params=SINGLE_FOOD, envs=1 << 20, dtype="float32"),
+    "long_horizon_64k": dict(yaml="configs/single_food_long_horizon.yaml", params=LONG_HORIZON, envs=1 << 16, dtype="float32"),
+    "defaults_1m": dict(yaml="configs/defaults.yaml", params=DEFAULTS, envs=1 << 20, dtype="float32"),
+    "parity_4k": dict(yaml="configs/single_food.yaml", params=SINGLE_FOOD, envs=1 << 12, dtype="float64"),
+}
+METRIC = "salp_env_steps_per_sec"
+UNIT = "env-steps/s"
+
+
+def algorithmic_bytes_per_env_step(n_food: int, real_bytes: int, k_fused: int = 1, act_dim: int = 1, obs_dim: int = 24) -> float:
+    """B(K) = A + O + R + D + (S_in + S_out)/K,
+    S = 8 reals + 4 (fsm) + 8 (counters) + 8 (cursors) + (real + 4) (ep return, len) + 2F reals + 4 (mask)."""
+    A, O, R, D = real_bytes * act_dim, 4 * obs_dim, real_bytes, 2
+    S = 8 * real_bytes + 4 + 8 + 8 + (real_bytes + 4) + 2 * n_food * real_bytes + 4
+    return A + O + R + D + 2.0 * S / k_fused
+
+
+def measured_peak_gbs():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.idx, self.rows, self.proc = gpu_index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.idx)], stdout=subprocess.PIPE, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self) -> dict:
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[1]))
+                mx = float(r[2])
+                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[4:8]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+            except Exception:
+                continue
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def cpu_oracle_throughput(params: dict, budget_s: float, threads: int, n_envs: int, T: int):
+    """Time the CPU restatement (oracle/salp_oracle.c, OpenMP over envs) on a bounded sample of the
+    same workload.  Returns (env-steps/s, seconds, description)."""
+    import numpy as np
+
+    from oracle import salp_oracle
+    from underwater_swimmer_rl_b200 import rng_tables
+    os.environ["OMP_NUM_THREADS"] = str(threads)
+    salp_oracle.build()
+    fw = rng_tables.fill_words(n_envs, 128, 10_000, 0, rng_tables.FOOD_STREAM)
+    jw = rng_tables.fill_words(n_envs, 512, 10_000, 0, rng_tables.JITTER_STREAM)
+    g = np.random.default_rng(1234)
+    acts = g.uniform(-1, 1, (T, n_envs, 1)).astype(np.float32)
+    orc = salp_oracle.Oracle(n_envs, fw, jw, **params)
+    orc.reset()
+    orc.rollout(acts[: max(1, T // 10)], autoreset=True, record=False)  # warm-up
+    done_steps, t0 = 0, time.perf_counter()
+    reps = 0
+    while True:
+        orc.rollout(acts, autoreset=True, record=False)
+        done_steps += n_envs * T
+        reps += 1
+        el = time.perf_counter() - t0
+        if el >= budget_s or reps >= 64:
+            break
+    return done_steps / el, el, f"{n_envs} envs x {T * reps} steps, auto-reset, uniform(-1,1) actions, no output recording"
+
+
+def run_reference_arm(args, wl):
+    """--impl reference: the reference's CPU implementation of the path on the host cores.
+    The reference is pure Python and cannot travel to the GPU box, so this is its C restatement
+    (oracle/, bit-exact against the Python reference -- DESIGN.md) with all host threads."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import numpy as np
+
+    from oracle import salp_oracle
+    from underwater_swimmer_rl_b200 import rng_tables
+    threads = os.cpu_count() or 1
+    os.environ["OMP_NUM_THREADS"] = str(threads)
+    salp_oracle.build()
+    n = min(wl["envs"], 1 << 16)
+    fw = rng_tables.fill_words(n, 128, 10_000, 0, rng_tables.FOOD_STREAM)
+    jw = rng_tables.fill_words(n, 512, 10_000, 0, rng_tables.JITTER_STREAM)
+    acts = np.random.default_rng(1234).uniform(-1, 1, (args.warmup + args.steps, n, 1)).astype(np.float32)
+    orc = salp_oracle.Oracle(n, fw, jw, **wl["params"])
+    orc.reset()
+    if args.warmup:
+        orc.rollout(acts[: args.warmup], autoreset=True, record=False)
+    t0 = time.perf_counter()
+    orc.rollout(acts[args.warmup:], autoreset=True, record=False)
+    el = time.perf_counter() - t0
+    value = n * args.steps / el
+    sample = f"{n} envs x {args.steps} steps per run (bounded sample of {wl['envs']} envs/GPU), auto-reset"
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * el / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": args.workload, "reference_yaml": wl["yaml"], "envs_per_step": n,
+                   "note": "C restatement of the Python reference (bit-exact, oracle/), OpenMP over envs"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="single_food_1m", choices=sorted(WORKLOADS))
+    ap.add_argument("--envs-per-gpu", type=int, default=0)
+    ap.add_argument("--substeps", type=int, default=1, help="K env steps fused per launch (open-loop actions)")
+    ap.add_argument("--e2e-steps", type=int, default=20)
+    ap.add_argument("--cpu-seconds", type=float, default=12.0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+    wl = dict(WORKLOADS[args.workload])
+    if args.envs_per_gpu:
+        wl["envs"] = args.envs_per_gpu
+    if args.impl == "reference":
+        return run_reference_arm(args, wl)
+
+    import torch
+    import torch.distributed as dist
+
+    from underwater_swimmer_rl_b200 import SalpVectorEnv
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (there is no CPU fallback for the product path)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    N, K = wl["envs"], args.substeps
+    real = torch.float64 if wl["dtype"] == "float64" else torch.float32
+    env = SalpVectorEnv(N, device=dev, dtype=wl["dtype"], seed=10_000, env_id0=rank * N, food_table_len=128,
+                        jitter_table_len=512, max_substeps=K, autoreset=True, **wl["params"])
+    env.reset()
+    # synthetic actions, resident in HBM before the timed region: a pool of 32 [K, N, 1] tensors
+    gen = torch.Generator(device=dev)
+    gen.manual_seed(1234 + rank)
+    pool = [torch.rand(K, N, env.act_dim, device=dev, dtype=real, generator=gen) * 2 - 1 for _ in range(32)]
+
+    def one_step(i):
+        if K == 1:
+            env.step(pool[i % 32][0])
+        else:
+            env.step_many(pool[i % 32], K)
+
+    for i in range(args.warmup):
+        one_step(i)
+    sampler = ClockSampler(local)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    if rank == 0:
+        sampler.start()
+    launches0 = env.launch_count
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for i in range(args.steps):
+        one_step(args.warmup + i)
+    ev1.record()
+    torch.cuda.synchronize()
+    ms = ev0.elapsed_time(ev1)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    clocks = sampler.stop() if rank == 0 else None
+    launches = env.launch_count - launches0
+    t = torch.tensor([ms], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_max = float(t.item())
+    value = world * N * K * args.steps / (ms_max * 1e-3)
+
+    # ---- e2e: the reference-facing call with HOST buffers (H2D actions, step, D2H results) ----
+    a_h = (torch.rand(N, env.act_dim, dtype=real) * 2 - 1).pin_memory()
+    o_h = torch.empty(N, env.obs_dim, dtype=torch.float32).pin_memory()
+    r_h = torch.empty(N, dtype=real).pin_memory()
+    te_h = torch.empty(N, dtype=torch.bool).pin_memory()
+    tr_h = torch.empty(N, dtype=torch.bool).pin_memory()
+    for _ in range(3):
+        env.step_host(a_h, o_h, r_h, te_h, tr_h)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.e2e_steps):
+        env.step_host(a_h, o_h, r_h, te_h, tr_h)
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    t = torch.tensor([e2e_s], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_value = world * N * args.e2e_steps / float(t.item())
+    rb = 8 if real == torch.float64 else 4
+    h2d = N * env.act_dim * rb
+    d2h = N * (env.obs_dim * 4 + rb + 2)
+
+    stats = env.episode_stats()  # NCCL all-reduce (SUM) of the 8-double stats vector when world > 1
+
+    if rank == 0:
+        peak, peak_src = measured_peak_gbs()
+        nf = wl["params"]["num_food_items"]
+        bpe = algorithmic_bytes_per_env_step(nf, rb, K, env.act_dim, env.obs_dim)
+        kernel_ms = ms_max / args.steps  # the timed region is nothing but back-to-back launches of this kernel
+        achieved = bpe * N * K / (kernel_ms * 1e-3) / 1e9
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64" if real == torch.float64 else "f32", "data": "synthetic",
+            "config": {"workload": args.workload, "reference_yaml": wl["yaml"], "envs_per_gpu": N, "global_envs": world * N,
+                       "substeps_per_launch": K, "obs_dim": env.obs_dim, "act_dim": env.act_dim, "autoreset": True,
+                       "l2": f"per-step footprint {bpe * N / 1e6:.0f} MB vs 126 MB L2"
+                             + (" (inputs larger than L2, no flush needed)" if bpe * N > 126e6 else " (L2-resident working set)"),
+                       "parallelism": f"env-slab x{world} (no data-path collective; NCCL all-reduce of episode stats only)"},
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": None, "kernel": "salp_step_kernel", "kernel_ms": kernel_ms,
+                         "algorithmic_bytes_per_env_step": bpe, "peak_source": peak_src},
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "steps": args.e2e_steps, "api": "SalpVectorEnv.step_host -> salp_step_host (pinned host buffers)"},
+            "gpu_launches": launches, "clocks": clocks,
+            "episode_stats": {k: stats[k] for k in ("episodes", "mean_return", "mean_length", "collisions", "truncations", "env_steps")},
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            threads = os.cpu_count() or 1
+            v, secs, sample = cpu_oracle_throughput(wl["params"], args.cpu_seconds, threads, 4096 * max(1, min(threads, 16)), 250)
+            line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample,
+                                    "seconds": secs, "note": "C restatement of the Python reference (oracle/), OpenMP; "
+                                    "the unmodified Python reference measured ~2.0e4 env-steps/s/core in the build container"}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

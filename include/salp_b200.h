@@ -97,7 +97,6 @@ typedef struct SalpLayout {
  *             (ellipse_a/b of R:74-75 are recomputed from the shape fields, never stored)
  *   ep_return real [N]         running episode return
  *   food      real [F][N][2]   food_positions (S:52); liveness is ctrl.food_mask
- *   actions   real [K][N][act_dim]      read by salp_step
  *   obs       f32  [K][N][obs_dim]      written by salp_step (and [N][obs_dim] by salp_reset)
  *   reward    real [K][N]
  *   terminated, truncated  u8 [K][N]    (torch.bool compatible)
@@ -120,7 +119,6 @@ typedef struct SalpBuffers {
     int32_t *ctrl;
     void *ep_return;
     void *food;
-    const void *actions;
     float *obs;
     void *reward;
     uint8_t *terminated;
@@ -134,7 +132,7 @@ typedef struct SalpBuffers {
     int64_t table_rows;
     int64_t food_len; /* words per row, power of two */
     int64_t jit_len;  /* words per row, power of two, >= 2 */
-    int32_t max_substeps; /* K the actions/obs/reward/... buffers were sized for */
+    int32_t max_substeps; /* K the obs/reward/... buffers were sized for */
     int32_t reserved_;
 } SalpBuffers;
 
@@ -170,19 +168,22 @@ int salp_reset(SalpHandle *h, const uint8_t *mask, int rewind_rng, void *cuda_st
 /*
  * Replaces K consecutive SalpSnakeEnv.step calls (S:157-202 over R:119-156) per env in ONE
  * kernel launch: state is read once, kept in registers for the K substeps, written once.
+ * `actions` is a DEVICE pointer to real [K][N][act_dim] (any caller-owned memory, e.g. the
+ * policy's output tensor -- no staging copy); it must stay valid until the launch has run.
  * 1 <= K <= buffers.max_substeps.
  */
-int salp_step(SalpHandle *h, int K, void *cuda_stream);
+int salp_step(SalpHandle *h, int K, const void *actions, void *cuda_stream);
 
 /*
  * Host-buffer convenience path (what a caller holding numpy arrays uses): copies
- * actions host->device, runs one step (K=1), copies obs/reward/terminated/truncated
+ * actions host->device (into the caller-owned DEVICE staging buffer `actions_staging`,
+ * real [N][act_dim]), runs one step (K=1), copies obs/reward/terminated/truncated
  * device->host, chunked over internal streams so the copies overlap the kernel, and
  * returns after the results are in host memory.  Host pointers should be page-locked.
  * Any output pointer may be NULL.
  */
-int salp_step_host(SalpHandle *h, const void *actions_host, float *obs_host, void *reward_host,
-                   uint8_t *terminated_host, uint8_t *truncated_host);
+int salp_step_host(SalpHandle *h, void *actions_staging, const void *actions_host, float *obs_host,
+                   void *reward_host, uint8_t *terminated_host, uint8_t *truncated_host);
 
 /*
  * Fill `rows` rows of `len` raw MT19937 outputs into HOST memory dst[rows][len]:

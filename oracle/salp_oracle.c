@@ -61,7 +61,10 @@ typedef struct {
     int32_t phase, timer, exhale_dur;          /* R:71-72,223  phase: 0 rest 1 inhaling 2 exhaling */
     int32_t is_inhaling;                       /* R:76 */
     int32_t food_collected, steps_since_food;  /* S:58-59 */
-    int32_t pad_;
+    /* bookkeeping for the tests only (never read by the model): which expression last wrote
+     * ellipse_a/b -- 0 reset R:112-113, 1 rest R:190-191, 2 inhale R:212-213, 3 exhale R:245-246 --
+     * and the breathing_timer value it used.  Mirrors the kernel's packed "shape" fields. */
+    int32_t shape_kind, shape_timer, pad_;
     uint64_t cur_food, cur_jit;                /* words consumed from the two streams */
 } OracleEnv;
 
@@ -178,7 +181,7 @@ static void env_reset(const OracleParams *p, OracleEnv *e, const OracleTables *t
     e->vx = 0.0; e->vy = 0.0; e->angle = 0.0; e->omega = 0.0;
     e->nozzle = 0.0; e->target_nozzle = 0.0;
     e->phase = 0; e->timer = 0;
-    e->a = BASE_RADIUS; e->b = BASE_RADIUS;
+    e->a = BASE_RADIUS; e->b = BASE_RADIUS; e->shape_kind = 0; e->shape_timer = 0;
     e->is_inhaling = 0; e->wv = 0.0;
     e->score = 0.0; e->food_collected = 0; e->steps_since_food = 0;
     if (p->random_food_count) { /* S:144-146 random.randint(1, max(1, base)) */
@@ -235,7 +238,7 @@ static void robot_step(const OracleParams *p, OracleEnv *e, const double *action
     e->nozzle = pymax(-maxn, pymin(maxn, e->nozzle));
     /* R:184-259 _update_breathing_cycle */
     if (e->phase == 0) {
-        e->a = BASE_RADIUS * 1.3; e->b = BASE_RADIUS * 0.8;
+        e->a = BASE_RADIUS * 1.3; e->b = BASE_RADIUS * 0.8; e->shape_kind = 1;
         if (e->is_inhaling) { e->phase = 1; e->timer = 0; }
     } else if (e->phase == 1) {
         if (e->is_inhaling && e->timer < INHALE_DUR) {
@@ -243,6 +246,7 @@ static void robot_step(const OracleParams *p, OracleEnv *e, const double *action
             const double pr = (double)e->timer / (double)INHALE_DUR;
             const double sa = BASE_RADIUS * 1.3, sb = BASE_RADIUS * 0.8, ea = BASE_RADIUS * 1.1, eb = BASE_RADIUS * 1.1;
             e->a = sa + (ea - sa) * pr; e->b = sb + (eb - sb) * pr;
+            e->shape_kind = 2; e->shape_timer = e->timer;
             e->wv = pr;
         } else if (e->wv > 0.05) {
             e->phase = 2; e->timer = 0;
@@ -254,6 +258,7 @@ static void robot_step(const OracleParams *p, OracleEnv *e, const double *action
         if (pr <= 1.0) {
             const double sa = BASE_RADIUS * 1.1, sb = BASE_RADIUS * 1.1, ea = BASE_RADIUS * 1.3, eb = BASE_RADIUS * 0.8;
             e->a = sa + (ea - sa) * pr; e->b = sb + (eb - sb) * pr;
+            e->shape_kind = 3; e->shape_timer = e->timer;
             if (0.1 <= pr && pr <= 0.5) jet_thrust(e, t, row);
             const double w = e->wv * (1.0 - pr);
             e->wv = (w > 0) ? w : 0.0; /* max(0, w) */

@@ -45,7 +45,8 @@ class OracleEnv(C.Structure):
         ("food", (C.c_double * 2) * MAX_FOOD), ("alive", C.c_int32 * MAX_FOOD),
         ("n_food", C.c_int32), ("phase", C.c_int32), ("timer", C.c_int32),
         ("exhale_dur", C.c_int32), ("is_inhaling", C.c_int32),
-        ("food_collected", C.c_int32), ("steps_since_food", C.c_int32), ("pad_", C.c_int32),
+        ("food_collected", C.c_int32), ("steps_since_food", C.c_int32),
+        ("shape_kind", C.c_int32), ("shape_timer", C.c_int32), ("pad_", C.c_int32),
         ("cur_food", C.c_uint64), ("cur_jit", C.c_uint64),
     ]
 
@@ -59,7 +60,7 @@ class OracleTables(C.Structure):
 
 ENV_DTYPE = np.dtype(dict(
     names=[f[0] for f in OracleEnv._fields_],
-    formats=["f8"] * 12 + [("f8", (MAX_FOOD, 2)), ("i4", (MAX_FOOD,))] + ["i4"] * 8 + ["u8", "u8"],
+    formats=["f8"] * 12 + [("f8", (MAX_FOOD, 2)), ("i4", (MAX_FOOD,))] + ["i4"] * 10 + ["u8", "u8"],
     offsets=[getattr(OracleEnv, f[0]).offset for f in OracleEnv._fields_],
     itemsize=C.sizeof(OracleEnv),
 ))

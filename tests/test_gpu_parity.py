@@ -1,0 +1,258 @@
+"""GPU parity tests: the CUDA path (through the C ABI, via SalpVectorEnv) against
+ (1) the committed reference trajectories (tests/golden/), and
+ (2) the C oracle on the same seeded inputs, at BASELINE.json configs[1] size (4096 envs, 1000 steps).
+
+Bars (BASELINE.json north_star):
+  fp64 validation build: discrete state (flags, breathing phase/timer, counters, food liveness,
+      RNG cursors) BIT-EXACT; continuous state within 1e-9 abs (stated bar: 1e-5) -- the only
+      source of difference is CUDA libdevice vs glibc sin/cos/atan2 (<= 2 ulp) and pow(x,2) vs x*x.
+  observations (f32): |err| <= 2e-6 (one f32 rounding of near-identical doubles).
+  fp32 throughput build: per-step error from synced states <= 1e-3 (normalised obs units).
+"""
+import numpy as np
+import pytest
+import torch
+
+from helpers import CONFIGS, bits_equal, golden_cases, load_golden, py_tables, synth_actions
+
+pytestmark = pytest.mark.gpu
+
+OBS_ATOL_F64 = 2e-6
+STATE_ATOL_F64 = 1e-9
+
+
+def _env(n, params, dtype="float64", **kw):
+    from underwater_swimmer_rl_b200 import SalpVectorEnv
+    return SalpVectorEnv(n, device="cuda:0", dtype=dtype, **kw, **params)
+
+
+def _unpack_state(env):
+    body = env.body.cpu().numpy()
+    ctrl = env.ctrl.cpu().numpy()
+    a, b = env.ellipse_axes()
+    return dict(px=body[0, :, 0], py=body[0, :, 1], vx=body[0, :, 2], vy=body[0, :, 3], angle=body[1, :, 0],
+                omega=body[1, :, 1], nozzle=body[1, :, 2], wv=body[1, :, 3], a=a.cpu().numpy(), b=b.cpu().numpy(),
+                phase=ctrl[0, :, 0] & 3, timer=(ctrl[0, :, 0] >> 2) & 0xFF, steps_since_food=ctrl[0, :, 1],
+                food_collected=ctrl[0, :, 2], mask=ctrl[0, :, 3].astype(np.uint32), cur_food=ctrl[1, :, 0],
+                cur_jit=ctrl[1, :, 1], n_food=ctrl[1, :, 3])
+
+
+@pytest.mark.parametrize("case", golden_cases())
+def test_fp64_kernel_reproduces_reference_trajectory(case):
+    g = load_golden(case)
+    T, N = g["actions"].shape[:2]
+    fw, jw = py_tables(g["seeds"], 2048, 2048)
+    env = _env(N, g["params"], autoreset=True)
+    env.set_rng_tables(fw, jw)
+    obs0, _ = env.reset()
+    np.testing.assert_allclose(obs0.cpu().numpy(), g["reset_obs0"], atol=OBS_ATOL_F64, rtol=0)
+    F = g["alive"].shape[2]
+    sub = {int(s): i for i, s in enumerate(g["sub_steps"])}
+    acts = torch.from_numpy(g["actions"].astype(np.float64)).cuda()
+    worst_obs = worst_state = 0.0
+    for t in range(T):
+        obs, rew, term, trunc, info = env.step(acts[t])
+        ev = info["events"].cpu().numpy()
+        assert ((ev & 7) == g["flags"][t]).all(), f"{case}: flags differ at step {t}"
+        assert (term.cpu().numpy() == (g["flags"][t] & 1)).all() and (trunc.cpu().numpy() == ((g["flags"][t] >> 1) & 1)).all()
+        done = (g["flags"][t] & 3) != 0
+        o = obs.cpu().numpy()
+        fo = info["final_observation"].cpu().numpy()
+        term_obs = np.where(done[:, None], fo, o)
+        worst_obs = max(worst_obs, float(np.abs(term_obs - g["obs"][t]).max()))
+        if done.any():
+            worst_obs = max(worst_obs, float(np.abs(o[done] - g["reset_obs"][t][done]).max()))
+        np.testing.assert_allclose(rew.cpu().numpy(), g["reward"][t], atol=1e-9, rtol=1e-12)
+        if t in sub or t == T - 1:
+            st = _unpack_state(env)
+            nd = ~done  # auto-reset lanes hold the NEW episode's state
+            assert (st["phase"][nd] == g["phase"][t][nd]).all() and (st["timer"][nd] == g["timer"][t][nd]).all()
+            assert (st["steps_since_food"][nd] == g["steps_since_food"][t][nd]).all()
+            assert (st["food_collected"][nd] == g["food_collected"][t][nd]).all()
+            assert (st["n_food"][nd] == g["n_food"][t][nd]).all()
+            alive = (st["mask"][:, None] >> np.arange(F)[None, :]) & 1
+            assert (alive[nd] == g["alive"][t][nd]).all()
+            if t in sub:
+                i = sub[t]
+                for c, k in enumerate(("px", "py", "vx", "vy", "angle", "omega", "nozzle", "wv", "a", "b")):
+                    worst_state = max(worst_state, float(np.abs(st[k][nd] - g["sub_state"][i, :, c][nd]).max()))
+                food = env.food.cpu().numpy().transpose(1, 0, 2)[:, :F]
+                al = g["alive"][t][..., None] * nd[:, None, None]
+                assert bits_equal(g["sub_food"][i] * al, food * al).all(), "food positions must be bit-exact"
+    st = _unpack_state(env)
+    assert (st["cur_food"] == g["cur_food"]).all() and (st["cur_jit"] == g["cur_jit"]).all(), "RNG consumption"
+    assert worst_obs <= OBS_ATOL_F64, worst_obs
+    assert worst_state <= STATE_ATOL_F64, worst_state
+
+
+def _oracle_rollout(oracle_lib, params, fw, jw, acts):
+    orc = oracle_lib.Oracle(acts.shape[1], fw, jw, **params)
+    o0 = orc.reset()
+    out = orc.rollout(acts, autoreset=True)
+    return orc, o0, out
+
+
+@pytest.mark.parametrize("cfg,forced", [("single_food", True), ("defaults", True), ("single_food", False)])
+def test_fp64_4096_envs_1000_steps_vs_oracle(cfg, forced, oracle_lib, salp_lib):
+    """BASELINE.json configs[1]: 4096 envs, fp64 parity build, 1000 steps, K-fused launches."""
+    from underwater_swimmer_rl_b200 import rng_tables
+    N, T, K = 4096, 1000, 50
+    params = dict(CONFIGS[cfg], forced_breathing=forced)
+    acts = synth_actions(T, N, 1 if forced else 2, seed=99)
+    fw = rng_tables.fill_words(N, 512, 10_000, 0, 0)
+    jw = rng_tables.fill_words(N, 1024, 10_000, 0, 1)
+    orc, o0, ref = _oracle_rollout(oracle_lib, params, fw, jw, acts)
+    env = _env(N, params, autoreset=True, max_substeps=K)
+    env.set_rng_tables(fw, jw)
+    obs0, _ = env.reset()
+    np.testing.assert_allclose(obs0.cpu().numpy(), o0, atol=OBS_ATOL_F64, rtol=0)
+    a_dev = torch.from_numpy(acts.astype(np.float64)).cuda()
+    worst_obs = worst_rew = 0.0
+    n_done = 0
+    for t0 in range(0, T, K):
+        obs, rew, term, trunc, info = env.step_many(a_dev[t0:t0 + K])
+        ev = info["events"].cpu().numpy()
+        rf = ref["flags"][t0:t0 + K]
+        assert (ev == rf).all(), f"discrete events differ in steps {t0}..{t0 + K}: {int((ev != rf).sum())} lanes"
+        done = (rf & 3) != 0
+        n_done += int(done.sum())
+        o = obs.cpu().numpy()
+        fo = info["final_observation"].cpu().numpy()
+        term_obs = np.where(done[..., None], fo, o)
+        worst_obs = max(worst_obs, float(np.abs(term_obs - ref["obs"][t0:t0 + K]).max()))
+        if done.any():
+            worst_obs = max(worst_obs, float(np.abs(o[done] - ref["reset_obs"][t0:t0 + K][done]).max()))
+        worst_rew = max(worst_rew, float(np.abs(rew.cpu().numpy() - ref["reward"][t0:t0 + K]).max()))
+    st = _unpack_state(env)
+    e = orc.envs
+    for k in ("phase", "timer", "steps_since_food", "food_collected", "n_food"):
+        assert (st[k] == e[k]).all(), k
+    assert (st["cur_food"] == e["cur_food"].astype(np.int64)).all() and (st["cur_jit"] == e["cur_jit"].astype(np.int64)).all()
+    F = env.food_slots
+    alive = (st["mask"][:, None] >> np.arange(F)[None, :]) & 1
+    assert (alive == e["alive"][:, :F]).all()
+    food = env.food.cpu().numpy().transpose(1, 0, 2)
+    assert bits_equal(e["food"][:, :F] * alive[..., None], food * alive[..., None]).all()
+    worst_state = max(float(np.abs(st[k] - e[k]).max()) for k in ("px", "py", "vx", "vy", "angle", "omega", "nozzle", "wv", "a", "b"))
+    assert n_done > 1000, "the action sequence must actually end episodes"
+    assert worst_obs <= OBS_ATOL_F64 and worst_rew <= 1e-8 and worst_state <= STATE_ATOL_F64, (worst_obs, worst_rew, worst_state)
+    # episode statistics accumulated on the device == the oracle's
+    s = env.episode_stats()
+    assert s["episodes"] == ref["stats"][0] and s["collisions"] == ref["stats"][2] and s["truncations"] == ref["stats"][3]
+    assert s["env_steps"] == N * T and s["nonfinite"] == 0
+    assert abs(s["return_sum"] - float(ref["reward"].sum() - _open_episode_returns(env))) <= 1e-6 * max(1.0, abs(s["return_sum"]))
+
+
+def _open_episode_returns(env):
+    return float(env.ep_return.sum().item())
+
+
+def test_k_fusion_is_bitwise_identical_to_single_steps(salp_lib):
+    """K fused substeps in one launch == K launches of one step (same arithmetic, f32 build)."""
+    from underwater_swimmer_rl_b200 import rng_tables
+    N, T, K = 3000, 240, 8  # N not a multiple of the CTA size on purpose
+    params = CONFIGS["defaults"]
+    acts = torch.from_numpy(synth_actions(T, N, 1, seed=5)).cuda()
+    outs = []
+    for k in (1, K):
+        env = _env(N, params, dtype="float32", max_substeps=k, seed=77)
+        env.reset()
+        rec = []
+        for t0 in range(0, T, k):
+            obs, rew, term, trunc, info = env.step_many(acts[t0:t0 + k])
+            rec.append((obs.clone(), rew.clone(), info["events"].clone(), info["final_observation"].clone()))
+        outs.append([torch.cat([r[i] for r in rec]) for i in range(4)] + [env.body.clone(), env.ctrl.clone(), env.food.clone()])
+    ev = outs[0][2]
+    done = (ev & 3) != 0
+    for i, (x, y) in enumerate(zip(*outs)):
+        if i == 3:  # final_obs rows are only defined where an episode ended
+            x, y = x[done], y[done]
+        assert torch.equal(x, y), i
+
+
+def test_autoreset_off_keeps_stepping_like_the_reference(oracle_lib, salp_lib):
+    """autoreset=False: done lanes are NOT reset; the next step continues from the terminal state
+    exactly as the reference does when its caller ignores `done`."""
+    N, T = 64, 1300
+    params = CONFIGS["single_food"]
+    acts = synth_actions(T, N, 1, seed=3)
+    fw, jw = py_tables(range(500, 500 + N), 256, 1024)
+    orc = oracle_lib.Oracle(N, fw, jw, **params)
+    orc.reset()
+    ref = orc.rollout(acts, autoreset=False)
+    env = _env(N, params, autoreset=False)
+    env.set_rng_tables(fw, jw)
+    env.reset()
+    a = torch.from_numpy(acts.astype(np.float64)).cuda()
+    for t in range(T):
+        obs, rew, term, trunc, info = env.step(a[t])
+        assert (info["events"].cpu().numpy() == ref["flags"][t]).all(), t
+        assert float(np.abs(obs.cpu().numpy() - ref["obs"][t]).max()) <= OBS_ATOL_F64
+    assert ((ref["flags"] & 3) != 0).sum() > 0
+
+
+def test_fp32_per_step_error_from_synced_states(oracle_lib, salp_lib):
+    """fp32 throughput build: load the oracle's fp64 state every step, advance one step on the GPU,
+    compare -> single-step rounding error only.  Bar: 1e-3 (north_star); measured ~1e-6."""
+    N, T = 512, 600
+    params = CONFIGS["defaults"]
+    acts = synth_actions(T, N, 1, seed=11)
+    fw, jw = py_tables(range(9000, 9000 + N), 512, 1024)
+    orc = oracle_lib.Oracle(N, fw, jw, **params)
+    orc.reset()
+    env = _env(N, params, dtype="float32", autoreset=False)
+    env.set_rng_tables(fw, jw)
+    env.reset()
+    F = env.food_slots
+    worst = 0.0
+    flips = 0
+    for t in range(T):
+        e = orc.envs
+        body = np.stack([np.stack([e["px"], e["py"], e["vx"], e["vy"]], 1),
+                         np.stack([e["angle"], e["omega"], e["nozzle"], e["wv"]], 1)])
+        env.body.copy_(torch.from_numpy(body.astype(np.float32)))
+        ctrl = env.ctrl.cpu().numpy()
+        fsm = e["phase"] | (e["timer"] << 2) | (e["exhale_dur"] << 10) | (e["shape_kind"] << 18) | (e["shape_timer"] << 20)
+        ctrl[0, :, 0] = fsm
+        ctrl[0, :, 1] = e["steps_since_food"]
+        ctrl[0, :, 2] = e["food_collected"]
+        mask = (e["alive"][:, :F].astype(np.int64) << np.arange(F)).sum(1)
+        ctrl[0, :, 3] = np.where(mask >= 2 ** 31, mask - 2 ** 32, mask)
+        ctrl[1, :, 0] = e["cur_food"]
+        ctrl[1, :, 1] = e["cur_jit"]
+        ctrl[1, :, 3] = e["n_food"]
+        env.ctrl.copy_(torch.from_numpy(ctrl))
+        env.food.copy_(torch.from_numpy(e["food"][:, :F].transpose(1, 0, 2).astype(np.float32)))
+        obs_ref, rew_ref, flags_ref = orc.step(acts[t].astype(np.float64))
+        obs, rew, term, trunc, info = env.step(torch.from_numpy(acts[t]).cuda())
+        same = info["events"].cpu().numpy() == flags_ref
+        flips += int((~same).sum())
+        err = np.abs(obs.cpu().numpy() - obs_ref)[same]
+        worst = max(worst, float(err.max()))
+        for i in np.nonzero(flags_ref & 3)[0]:
+            orc.reset_one(int(i))
+    assert worst <= 1e-3, worst
+    assert flips <= 2, f"{flips} discrete flips in {N * T} fp32 steps from synced states"
+
+
+def test_step_host_equals_device_path(salp_lib):
+    """salp_step_host (pinned host buffers, chunked copy/compute overlap) == the device path."""
+    N, T = 5000, 40
+    params = CONFIGS["single_food"]
+    acts = synth_actions(T, N, 1, seed=21)
+    env_d = _env(N, params, dtype="float32", seed=5)
+    env_h = _env(N, params, dtype="float32", seed=5)
+    env_d.reset()
+    env_h.reset()
+    a_h = torch.empty(N, 1, dtype=torch.float32).pin_memory()
+    o_h = torch.empty(N, env_h.obs_dim, dtype=torch.float32).pin_memory()
+    r_h = torch.empty(N, dtype=torch.float32).pin_memory()
+    te_h = torch.empty(N, dtype=torch.bool).pin_memory()
+    tr_h = torch.empty(N, dtype=torch.bool).pin_memory()
+    for t in range(T):
+        a_h.copy_(torch.from_numpy(acts[t]))
+        env_h.step_host(a_h, o_h, r_h, te_h, tr_h)
+        obs, rew, term, trunc, _ = env_d.step(torch.from_numpy(acts[t]).cuda())
+        assert torch.equal(o_h, obs.cpu()) and torch.equal(r_h, rew.cpu())
+        assert torch.equal(te_h, term.cpu()) and torch.equal(tr_h, trunc.cpu())
+    assert torch.equal(env_d.body, env_h.body) and torch.equal(env_d.ctrl, env_h.ctrl)

@@ -44,7 +44,7 @@ class SalpLayout(C.Structure):
 class SalpBuffers(C.Structure):
     _fields_ = [
         ("body", C.c_void_p), ("ctrl", C.c_void_p), ("ep_return", C.c_void_p), ("food", C.c_void_p),
-        ("actions", C.c_void_p), ("obs", C.c_void_p), ("reward", C.c_void_p),
+        ("obs", C.c_void_p), ("reward", C.c_void_p),
         ("terminated", C.c_void_p), ("truncated", C.c_void_p), ("events", C.c_void_p),
         ("final_obs", C.c_void_p), ("final_info", C.c_void_p), ("stats", C.c_void_p),
         ("food_words", C.c_void_p), ("jit_words", C.c_void_p),
@@ -81,8 +81,8 @@ def load():
     L.salp_destroy.argtypes = [C.c_void_p]
     L.salp_bind.argtypes = [C.c_void_p, C.POINTER(SalpBuffers)]
     L.salp_reset.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
-    L.salp_step.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
-    L.salp_step_host.argtypes = [C.c_void_p] + [C.c_void_p] * 5
+    L.salp_step.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
+    L.salp_step_host.argtypes = [C.c_void_p] + [C.c_void_p] * 6
     L.salp_fill_rng_words.argtypes = [C.c_void_p, C.c_int64, C.c_int64, C.c_uint64, C.c_int64, C.c_int, C.c_int]
     L.salp_launch_count.argtypes = [C.c_void_p]
     L.salp_launch_count.restype = C.c_int64

@@ -167,7 +167,7 @@ int salp_bind(SalpHandle *h, const SalpBuffers *b) {
     if (b->food_len > ((int64_t)1 << 30) || b->jit_len > ((int64_t)1 << 30)) return fail(SALP_EINVAL, "table rows too long");
     if (b->max_substeps < 1) return fail(SALP_EINVAL, "max_substeps must be >= 1");
     const uintptr_t align16[] = {(uintptr_t)b->body, (uintptr_t)b->ctrl, (uintptr_t)b->food, (uintptr_t)b->obs,
-                                 (uintptr_t)b->final_obs, (uintptr_t)b->actions, (uintptr_t)b->jit_words};
+                                 (uintptr_t)b->final_obs, (uintptr_t)b->final_info, (uintptr_t)b->jit_words};
     for (uintptr_t p : align16)
         if (p % 32 != 0) return fail(SALP_EINVAL, "device buffers must be 32-byte aligned");
     h->buf = *b;
@@ -176,7 +176,6 @@ int salp_bind(SalpHandle *h, const SalpBuffers *b) {
     a.ctrl = reinterpret_cast<int4 *>(b->ctrl);
     a.ep_return = b->ep_return;
     a.food = b->food;
-    a.actions = b->actions;
     a.obs = b->obs;
     a.reward = b->reward;
     a.terminated = b->terminated;
@@ -218,22 +217,25 @@ int salp_reset(SalpHandle *h, const uint8_t *mask, int rewind_rng, void *stream)
     return SALP_OK;
 }
 
-int salp_step(SalpHandle *h, int K, void *stream) {
+int salp_step(SalpHandle *h, int K, const void *actions, void *stream) {
     if (!h) return fail(SALP_EINVAL, "null handle");
     if (!h->bound) return fail(SALP_EUNBOUND, "salp_bind has not been called");
-    if (!h->buf.actions) return fail(SALP_EUNBOUND, "actions buffer is null");
+    if (!actions) return fail(SALP_EINVAL, "actions pointer is null");
+    if ((uintptr_t)actions % (size_t)(h->layout.real_bytes * h->layout.act_dim) != 0)
+        return fail(SALP_EINVAL, "actions pointer is not aligned to one action record");
     if (K < 1 || K > h->buf.max_substeps) return fail(SALP_EINVAL, "K=%d outside 1..max_substeps=%d", K, h->buf.max_substeps);
     SALP_CUDA(cudaSetDevice(h->device));
     salp::KernelArgs a = h->base;
     a.K = K;
+    a.actions = actions;
     return launch_step(h, a, (cudaStream_t)stream);
 }
 
-int salp_step_host(SalpHandle *h, const void *actions_host, float *obs_host, void *reward_host,
-                   uint8_t *terminated_host, uint8_t *truncated_host) {
+int salp_step_host(SalpHandle *h, void *actions_staging, const void *actions_host, float *obs_host,
+                   void *reward_host, uint8_t *terminated_host, uint8_t *truncated_host) {
     if (!h) return fail(SALP_EINVAL, "null handle");
     if (!h->bound) return fail(SALP_EUNBOUND, "salp_bind has not been called");
-    if (!h->buf.actions || !actions_host) return fail(SALP_EINVAL, "actions (device and host) must be non-null");
+    if (!actions_staging || !actions_host) return fail(SALP_EINVAL, "actions (device staging and host) must be non-null");
     SALP_CUDA(cudaSetDevice(h->device));
     if (!h->host_streams_ready) {
         // blocking streams: ordered after earlier work on the legacy default stream
@@ -251,10 +253,11 @@ int salp_step_host(SalpHandle *h, const void *actions_host, float *obs_host, voi
         const int64_t lo = t0 * salp::kBlockThreads, hi = std::min<int64_t>(N, t1 * salp::kBlockThreads);
         const size_t n = (size_t)(hi - lo);
         cudaStream_t s = h->host_streams[c];
-        SALP_CUDA(cudaMemcpyAsync((char *)h->buf.actions + lo * ad * rb, (const char *)actions_host + lo * ad * rb,
+        SALP_CUDA(cudaMemcpyAsync((char *)actions_staging + lo * ad * rb, (const char *)actions_host + lo * ad * rb,
                                   n * ad * rb, cudaMemcpyHostToDevice, s));
         salp::KernelArgs a = h->base;
         a.K = 1;
+        a.actions = actions_staging;
         a.first = lo;
         a.count = hi - lo;
         rc = launch_step(h, a, s);

@@ -165,7 +165,7 @@ class SalpVectorEnv(VectorEnv):
 
     def _bind(self) -> None:
         b = _capi.SalpBuffers()
-        for name in ("body", "ctrl", "ep_return", "food", "actions", "obs", "reward", "terminated", "truncated",
+        for name in ("body", "ctrl", "ep_return", "food", "obs", "reward", "terminated", "truncated",
                      "events", "final_obs", "final_info", "stats", "food_words", "jit_words"):
             setattr(b, name, getattr(self, name).data_ptr())
         b.table_rows, b.food_len, b.jit_len = self.table_rows, self.food_table_len, self.jitter_table_len
@@ -199,25 +199,31 @@ class SalpVectorEnv(VectorEnv):
         self._needs_reset = False
         return self.obs[0], {}
 
-    def _stage_actions(self, actions, k_steps: int) -> None:
+    def _stage_actions(self, actions, k_steps: int) -> torch.Tensor:
+        """Return a contiguous device tensor [k, N, act_dim] of this build's real type.  A CUDA
+        tensor that already has that form is used IN PLACE (its pointer goes to the kernel);
+        anything else is copied into the env's own staging buffer."""
+        shape = (k_steps, self.num_envs, self.act_dim)
+        if (isinstance(actions, torch.Tensor) and actions.device == self.device and actions.dtype == self.real
+                and actions.is_contiguous() and actions.numel() == k_steps * self.num_envs * self.act_dim):
+            return actions
         buf = self.actions[:k_steps]
         if isinstance(actions, torch.Tensor):
-            if actions.data_ptr() == buf.data_ptr():
-                return  # the policy wrote straight into the bound buffer
-            buf.copy_(actions.reshape(buf.shape), non_blocking=True)
+            buf.copy_(actions.reshape(shape), non_blocking=True)
         else:
-            a = torch.as_tensor(np.asarray(actions), dtype=self.real).reshape(buf.shape)
-            buf.copy_(a, non_blocking=True)
+            buf.copy_(torch.as_tensor(np.asarray(actions)).reshape(shape), non_blocking=True)
+        return buf
 
     def step(self, actions):
-        """One env step for all N envs.  ``actions``: [N, act_dim] tensor on this device (zero copy
-        when it is ``self.action_buffer``), or anything array-like (copied host->device).
+        """One env step for all N envs.  ``actions``: a contiguous [N, act_dim] tensor of this
+        build's dtype on this device is consumed in place (zero copy: its pointer is passed to
+        the kernel); anything else (numpy, other dtype/device) is staged through a copy.
         Returns views of the bound output buffers (overwritten by the next step)."""
         if self._needs_reset:
             raise RuntimeError("call reset() before step()")
-        self._stage_actions(actions, 1)
+        a = self._stage_actions(actions, 1)
         with torch.cuda.device(self.device):
-            _capi.check(self._L.salp_step(self._handle, 1, self._stream()))
+            _capi.check(self._L.salp_step(self._handle, 1, a.data_ptr(), self._stream()))
         return self.obs[0], self.reward[0], self.terminated[0], self.truncated[0], StepInfos(self, 0)
 
     def step_many(self, actions, k_steps: Optional[int] = None):
@@ -228,9 +234,9 @@ class SalpVectorEnv(VectorEnv):
             raise ValueError(f"k_steps={k_steps} outside 1..max_substeps={self.max_substeps}")
         if self._needs_reset:
             raise RuntimeError("call reset() before step()")
-        self._stage_actions(actions, k_steps)
+        a = self._stage_actions(actions, k_steps)
         with torch.cuda.device(self.device):
-            _capi.check(self._L.salp_step(self._handle, k_steps, self._stream()))
+            _capi.check(self._L.salp_step(self._handle, k_steps, a.data_ptr(), self._stream()))
         return (self.obs[:k_steps], self.reward[:k_steps], self.terminated[:k_steps], self.truncated[:k_steps],
                 {"events": self.events[:k_steps], "final_observation": self.final_obs[:k_steps],
                  "final_info": self.final_info[:k_steps]})
@@ -245,7 +251,7 @@ class SalpVectorEnv(VectorEnv):
         for t in (actions_host, obs_host, reward_host, terminated_host, truncated_host):
             assert t.device.type == "cpu" and t.is_contiguous()
         assert actions_host.dtype == self.real and reward_host.dtype == self.real and obs_host.dtype == torch.float32
-        _capi.check(self._L.salp_step_host(self._handle, actions_host.data_ptr(), obs_host.data_ptr(),
+        _capi.check(self._L.salp_step_host(self._handle, self.actions.data_ptr(), actions_host.data_ptr(), obs_host.data_ptr(),
                                            reward_host.data_ptr(), terminated_host.data_ptr(),
                                            truncated_host.data_ptr()))
 
