@@ -189,6 +189,9 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=20)
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--prime-steps", type=int, default=2048,
+                    help="untimed env steps before warm-up so episodes have ended and envs are de-synchronised "
+                         "(steady state: resets, respawns and divergent breathing phases inside the timed region)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     wl = dict(WORKLOADS[args.workload])
@@ -228,6 +231,8 @@ def main():
         else:
             env.step_many(pool[i % 32], K)
 
+    for i in range((args.prime_steps + K - 1) // K):
+        one_step(i)
     for i in range(args.warmup):
         one_step(i)
     sampler = ClockSampler(local)
@@ -293,7 +298,7 @@ def main():
             "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f64" if real == torch.float64 else "f32", "data": "synthetic",
             "config": {"workload": args.workload, "reference_yaml": wl["yaml"], "envs_per_gpu": N, "global_envs": world * N,
-                       "substeps_per_launch": K, "obs_dim": env.obs_dim, "act_dim": env.act_dim, "autoreset": True,
+                       "substeps_per_launch": K, "prime_steps": args.prime_steps, "obs_dim": env.obs_dim, "act_dim": env.act_dim, "autoreset": True,
                        "l2": f"per-step footprint {bpe * N / 1e6:.0f} MB vs 126 MB L2"
                              + (" (inputs larger than L2, no flush needed)" if bpe * N > 126e6 else " (L2-resident working set)"),
                        "parallelism": f"env-slab x{world} (no data-path collective; NCCL all-reduce of episode stats only)"},
