@@ -245,12 +245,12 @@ int salp_step_host(SalpHandle *h, void *actions_staging, const void *actions_hos
     const int64_t N = h->num_envs;
     const size_t rb = (size_t)h->layout.real_bytes, ad = (size_t)h->layout.act_dim, od = (size_t)h->layout.obs_dim;
     // chunk boundaries on CTA granularity so every chunk but the last is a whole number of tiles
-    const int64_t tiles = (N + salp::kBlockThreads - 1) / salp::kBlockThreads;
+    const int64_t tiles = (N + salp::kHostChunkAlign - 1) / salp::kHostChunkAlign;
     const int chunks = (int)std::min<int64_t>(kHostChunks, tiles);
     int rc = SALP_OK;
     for (int c = 0; c < chunks && rc == SALP_OK; ++c) {
         const int64_t t0 = tiles * c / chunks, t1 = tiles * (c + 1) / chunks;
-        const int64_t lo = t0 * salp::kBlockThreads, hi = std::min<int64_t>(N, t1 * salp::kBlockThreads);
+        const int64_t lo = t0 * salp::kHostChunkAlign, hi = std::min<int64_t>(N, t1 * salp::kHostChunkAlign);
         const size_t n = (size_t)(hi - lo);
         cudaStream_t s = h->host_streams[c];
         SALP_CUDA(cudaMemcpyAsync((char *)actions_staging + lo * ad * rb, (const char *)actions_host + lo * ad * rb,

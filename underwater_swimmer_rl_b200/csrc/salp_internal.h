@@ -6,7 +6,7 @@
 
 namespace salp {
 
-constexpr int kBlockThreads = 256;  // one thread per env; 8 warps per CTA
+constexpr int kHostChunkAlign = 256;  // host-path chunks start on multiples of this many envs (covers every CTA size)
 constexpr int kStatsLen = 8;
 constexpr int kMaxFood = 32;
 constexpr int kMaxObserved = 8;

@@ -2,7 +2,17 @@
 // Compiled twice by build.py:
 //   -DSALP_BUILD_F64=0                 -> launch_step_f32 / launch_reset_f32   (throughput build)
 //   -DSALP_BUILD_F64=1 -fmad=false     -> launch_step_f64 / launch_reset_f64   (validation build)
-#include "salp_step.cuh"
+// SALP_STORE / SALP_BLOCK pick the observation-store mode and CTA size that tools/kernel_lab.cu
+// measured fastest on B200 (see DESIGN.md "kernel variants").
+#include "salp_launch.cuh"
+
+#ifndef SALP_STORE
+#define SALP_STORE kStoreWarp
+#endif
+#ifndef SALP_BLOCK
+#define SALP_BLOCK 128
+#endif
+
 
 namespace salp {
 
@@ -16,25 +26,17 @@ using real_t = float;
 #define SALP_LAUNCH_RESET launch_reset_f32
 #endif
 
-template <int F, int MT>
-static cudaError_t launch_step_t(const KernelArgs &a, cudaStream_t s) {
-    auto kern = salp_step_kernel<real_t, F, MT>;
-    const int nbuf = a.K > 1 ? 2 : 1;
-    const size_t smem = (size_t)nbuf * kBlockThreads * a.obs_dim * sizeof(float);
-    static size_t smem_set = 0;  // per instantiation
-    if (smem > 48 * 1024 && smem > smem_set) {
-        cudaError_t err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (err != cudaSuccess) return err;
-        smem_set = smem;
-    }
-    const unsigned grid = (unsigned)((a.count + kBlockThreads - 1) / kBlockThreads);
-    kern<<<grid, kBlockThreads, smem, s>>>(a);
-    return cudaGetLastError();
+// CTAs/SM the register allocator must leave room for (registers per thread <= 65536/(MINB*BLOCK)).
+// Tuned with tools/kernel_lab.cu; the double build and the wide sorting networks need more registers.
+template <int F> constexpr int min_blocks() {
+    constexpr int f32 = F <= 4 ? 8 : (F <= 8 ? 6 : (F <= 12 ? 4 : (F <= 16 ? 3 : 2)));
+    return (SALP_BUILD_F64 ? (f32 + 1) / 2 : f32) * 128 / SALP_BLOCK > 0 ? (SALP_BUILD_F64 ? (f32 + 1) / 2 : f32) * 128 / SALP_BLOCK : 1;
 }
 
 template <int F>
 static cudaError_t launch_step_f(const KernelArgs &a, cudaStream_t s) {
-    return a.observed <= 3 ? launch_step_t<F, 3>(a, s) : launch_step_t<F, 8>(a, s);
+    return a.observed == 3 ? launch_step_variant<real_t, F, 3, SALP_STORE, SALP_BLOCK, min_blocks<F>()>(a, s)
+                           : launch_step_variant<real_t, F, 8, SALP_STORE, SALP_BLOCK, min_blocks<F>()>(a, s);
 }
 
 cudaError_t SALP_LAUNCH_STEP(const KernelArgs &a, int food_slots, cudaStream_t s) {
@@ -52,8 +54,8 @@ cudaError_t SALP_LAUNCH_STEP(const KernelArgs &a, int food_slots, cudaStream_t s
 
 cudaError_t SALP_LAUNCH_RESET(const KernelArgs &a, int /*food_slots*/, cudaStream_t s) {
     if (a.count <= 0) return cudaSuccess;
-    const unsigned grid = (unsigned)((a.count + kBlockThreads - 1) / kBlockThreads);
-    salp_reset_kernel<real_t><<<grid, kBlockThreads, 0, s>>>(a);
+    const unsigned grid = (unsigned)((a.count + 255) / 256);
+    salp_reset_kernel<real_t><<<grid, 256, 0, s>>>(a);
     return cudaGetLastError();
 }
 

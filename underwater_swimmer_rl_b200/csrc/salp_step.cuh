@@ -45,7 +45,6 @@ constexpr int INHALE_DUR = 120;            // R:51
 template <typename T> struct is_f64 { static constexpr bool value = false; };
 template <> struct is_f64<double> { static constexpr bool value = true; };
 
-template <typename T> __device__ __forceinline__ T rsqrt_(T x);
 __device__ __forceinline__ float sqrt_(float x) { return sqrtf(x); }
 __device__ __forceinline__ double sqrt_(double x) { return sqrt(x); }
 __device__ __forceinline__ float sin_(float x) { return sinf(x); }
@@ -93,20 +92,23 @@ template <typename T> __device__ __forceinline__ T food_uniform(const KernelArgs
 }
 
 // ---------------------------------------------------------------------------------------------
-// Slow paths: __noinline__, operate on global memory, executed by a handful of lanes per step
+// Slow paths: __noinline__, arguments and results BY VALUE (so no hot-path variable ever has its
+// address taken), operate on global memory, executed by a handful of lanes per step
 // ---------------------------------------------------------------------------------------------
+template <typename T> struct RespawnResult { T x, y; unsigned cur, mask; int slot; };
+struct ResetResult { unsigned cur, mask; int n_food; };
 
 // S:232-276 _respawn_food.  Live foods are read from HBM (food records only ever change here
 // and in reset_slow, so HBM is always current).  Returns the refilled slot and its position.
 template <typename T>
-__device__ __noinline__ void respawn_slow(const KernelArgs &a, long long e, T px, T py, unsigned &mask, int n_food,
-                                          unsigned &cur, int &slot, T &nx, T &ny) {
+__device__ __noinline__ RespawnResult<T> respawn_slow(const KernelArgs &a, long long e, T px, T py, unsigned mask,
+                                                      int n_food, unsigned cur) {
     const unsigned row = (unsigned)e % a.rows;
     Vec2<T> *food = reinterpret_cast<Vec2<T> *>(a.food);
     const T xlo = (T)(kc::TANK_MARGIN + kc::FOOD_R), xhi = (T)a.W - (T)kc::TANK_MARGIN - (T)kc::FOOD_R;
     const T ylo = xlo, yhi = (T)a.H - (T)kc::TANK_MARGIN - (T)kc::FOOD_R;
     int attempts = 0;
-    T x, y;
+    T x = 0, y = 0;
     bool found = false;
     while (attempts < 50) {
         x = food_uniform<T>(a, row, cur, xlo, xhi);
@@ -127,21 +129,20 @@ __device__ __noinline__ void respawn_slow(const KernelArgs &a, long long e, T px
         x = food_uniform<T>(a, row, cur, xlo, xhi);
         y = food_uniform<T>(a, row, cur, ylo, yhi);
     }
-    slot = -1;
+    int slot = -1;
     for (int j = 0; j < n_food; ++j)
         if (!((mask >> j) & 1u)) { slot = j; break; }
     if (slot >= 0) {
         food[(size_t)slot * a.N + e] = Vec2<T>{x, y};
         mask |= 1u << slot;
     }
-    nx = x; ny = y;
+    return RespawnResult<T>{x, y, cur, mask, slot};
 }
 
 // S:133-155 reset (food part: S:92-131 _generate_food_positions, S:144-148 food count) and the
-// reset observation (S:366-428 with the robot at the tank centre, R:95-117).
+// reset observation (S:366-428 with the robot at the tank centre, R:95-117) written to obs_row.
 template <typename T>
-__device__ __noinline__ void reset_slow(const KernelArgs &a, long long e, unsigned &cur, int &n_food_out,
-                                        unsigned &mask_out, float *obs_row) {
+__device__ __noinline__ ResetResult reset_slow(const KernelArgs &a, long long e, unsigned cur, float *obs_row) {
     const unsigned row = (unsigned)e % a.rows;
     Vec2<T> *food = reinterpret_cast<Vec2<T> *>(a.food);
     int n_food = a.num_food;
@@ -183,39 +184,40 @@ __device__ __noinline__ void reset_slow(const KernelArgs &a, long long e, unsign
         dist[i] = sqrt_(rx * rx + ry * ry);
         idx[i] = i;
     }
-    n_food_out = n_food;
-    mask_out = n_food >= 32 ? 0xffffffffu : ((1u << n_food) - 1u);
-    if (obs_row == nullptr) return;
-    // observation of the freshly reset env: robot at the centre, all zeros, body radius 30
-    obs_row[0] = (float)(cx / (T)a.W); obs_row[1] = (float)(cy / (T)a.H);
-    obs_row[2] = 0.f; obs_row[3] = 0.f; obs_row[4] = 0.f; obs_row[5] = 0.f;
-    obs_row[6] = (float)((T)kc::BASE_R / (T)kc::BASE_R);
-    obs_row[7] = 0.f; obs_row[8] = 0.f; obs_row[9] = 0.f;
-    for (int i = 1; i < n_food; ++i) {  // stable insertion sort by distance
-        const T d = dist[i];
-        const int k = idx[i];
-        int j = i - 1;
-        while (j >= 0 && dist[j] > d) { dist[j + 1] = dist[j]; idx[j + 1] = idx[j]; --j; }
-        dist[j + 1] = d; idx[j + 1] = k;
+    const unsigned mask = n_food >= 32 ? 0xffffffffu : ((1u << n_food) - 1u);
+    if (obs_row != nullptr) {
+        // observation of the freshly reset env: robot at the centre, all zeros, body radius 30
+        obs_row[0] = (float)(cx / (T)a.W); obs_row[1] = (float)(cy / (T)a.H);
+        obs_row[2] = 0.f; obs_row[3] = 0.f; obs_row[4] = 0.f; obs_row[5] = 0.f;
+        obs_row[6] = (float)((T)kc::BASE_R / (T)kc::BASE_R);
+        obs_row[7] = 0.f; obs_row[8] = 0.f; obs_row[9] = 0.f;
+        for (int i = 1; i < n_food; ++i) {  // stable insertion sort by distance
+            const T d = dist[i];
+            const int k = idx[i];
+            int j = i - 1;
+            while (j >= 0 && dist[j] > d) { dist[j + 1] = dist[j]; idx[j + 1] = idx[j]; --j; }
+            dist[j + 1] = d; idx[j + 1] = k;
+        }
+        const T diag = sqrt_((T)a.W * (T)a.W + (T)a.H * (T)a.H);
+        float *fo = obs_row + 10;
+        for (int i = 0; i < a.observed; ++i) {
+            if (i < n_food) {
+                const Vec2<T> f = food[(size_t)idx[i] * a.N + e];
+                const T dx = f.x - cx, dy = f.y - cy;
+                const T rel = wrap_pi<T>(atan2_(dy, dx) - (T)0);
+                fo[0] = (float)(dx / (T)a.W); fo[1] = (float)(dy / (T)a.H);
+                fo[2] = (float)(dist[i] / diag); fo[3] = (float)(rel / (T)kc::PI);
+            } else { fo[0] = 0.f; fo[1] = 0.f; fo[2] = 1.f; fo[3] = 0.f; }
+            fo += 4;
+        }
+        fo[0] = (float)pymin<T>((T)n_food / (T)10.0, (T)1.0);
+        if (n_food > 0) {
+            T s = 0;
+            for (int i = 0; i < n_food; ++i) s = s + dist[i];
+            fo[1] = (float)((s / (T)n_food) / diag);
+        } else fo[1] = 1.f;
     }
-    const T diag = sqrt_((T)a.W * (T)a.W + (T)a.H * (T)a.H);
-    float *fo = obs_row + 10;
-    for (int i = 0; i < a.observed; ++i) {
-        if (i < n_food) {
-            const Vec2<T> f = food[(size_t)idx[i] * a.N + e];
-            const T dx = f.x - cx, dy = f.y - cy;
-            const T rel = wrap_pi<T>(atan2_(dy, dx) - (T)0);
-            fo[0] = (float)(dx / (T)a.W); fo[1] = (float)(dy / (T)a.H);
-            fo[2] = (float)(dist[i] / diag); fo[3] = (float)(rel / (T)kc::PI);
-        } else { fo[0] = 0.f; fo[1] = 0.f; fo[2] = 1.f; fo[3] = 0.f; }
-        fo += 4;
-    }
-    fo[0] = (float)pymin<T>((T)n_food / (T)10.0, (T)1.0);
-    if (n_food > 0) {
-        T s = 0;
-        for (int i = 0; i < n_food; ++i) s = s + dist[i];
-        fo[1] = (float)((s / (T)n_food) / diag);
-    } else fo[1] = 1.f;
+    return ResetResult{cur, mask, n_food};
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -237,22 +239,34 @@ __device__ __forceinline__ double warp_sum(double v) {
     return v;
 }
 
+// How the observation tile leaves the SM (A/B-measured in tools/kernel_lab.cu):
+//   kStoreWarp     each warp stages its 32 rows (32*obs_dim floats, contiguous in HBM) in shared
+//                  memory and writes them with fully coalesced 128-bit stores; no CTA barrier
+//   kStoreTmaWarp  same staging, one TMA bulk store (cp.async.bulk) per warp per substep
+//   kStoreTmaBlock whole-CTA tile, one TMA bulk store per CTA per substep (needs __syncthreads)
+//   kStoreDirect   no staging: each thread writes its own row (6 x 128-bit, 96-byte stride)
+enum : int { kStoreWarp = 0, kStoreTmaWarp = 1, kStoreTmaBlock = 2, kStoreDirect = 3 };
+
 // ---------------------------------------------------------------------------------------------
 // The step kernel
-//   T  : float | double      F : food records per env (1,4,8,12,16,32)
-//   MT : compile-time bound on max_observed_food (3 -> the reference default, 8 -> generic)
+//   T     : float | double          F : food records per env (1,4,8,12,16,32)
+//   MT    : 3 -> max_observed_food == 3 (reference default; vectorised row assembly)
+//           8 -> any max_observed_food in 0..8 (generic scalar row assembly)
+//   STORE : see above               BLOCK : threads per CTA (multiple of 32)
+//   MINB  : CTAs per SM the register allocation must allow (__launch_bounds__)
 // ---------------------------------------------------------------------------------------------
-template <typename T, int F, int MT>
-__global__ void __launch_bounds__(kBlockThreads) salp_step_kernel(const __grid_constant__ KernelArgs a) {
-    extern __shared__ __align__(128) float s_tile[];  // [nbuf][256][obs_dim]
+template <typename T, int F, int MT, int STORE, int BLOCK, int MINB>
+__global__ void __launch_bounds__(BLOCK, MINB) salp_step_kernel(const __grid_constant__ KernelArgs a) {
+    extern __shared__ __align__(128) float s_tile[];  // [nbuf][BLOCK][obs_dim] (unused for kStoreDirect)
     const int tid = threadIdx.x;
-    const long long blk0 = a.first + (long long)blockIdx.x * kBlockThreads;
+    const int lane = tid & 31;
+    const long long blk0 = a.first + (long long)blockIdx.x * BLOCK;
     const long long e = blk0 + tid;
     const long long end = a.first + a.count;
     const bool valid = e < end;
-    const int n_rows = (int)((end - blk0) < kBlockThreads ? (end - blk0) : kBlockThreads);
     const int OBS = a.obs_dim;
     const long long N = a.N;
+    constexpr bool kTma = (STORE == kStoreTmaWarp || STORE == kStoreTmaBlock);
 
     Vec4<T> *g_body = reinterpret_cast<Vec4<T> *>(a.body);
     T *g_epret = reinterpret_cast<T *>(a.ep_return);
@@ -268,10 +282,10 @@ __global__ void __launch_bounds__(kBlockThreads) salp_step_kernel(const __grid_c
 #pragma unroll
     for (int f = 0; f < F; ++f) { fx[f] = 0; fy[f] = 0; }
     if (valid) {
-        b0 = g_body[e];
-        b1 = g_body[N + e];
         c0 = a.ctrl[e];
         c1 = a.ctrl[N + e];
+        b0 = g_body[e];
+        b1 = g_body[N + e];
         ep_ret = g_epret[e];
 #pragma unroll
         for (int f = 0; f < F; ++f) {
@@ -292,14 +306,35 @@ __global__ void __launch_bounds__(kBlockThreads) salp_step_kernel(const __grid_c
     const T diag = sqrt_(W * W + H * H);  // S:396 (exact for the integer tank sizes)
     T invW = 0, invH = 0, invDiag = 0;
     if constexpr (!is_f64<T>::value) { invW = 1.0f / W; invH = 1.0f / H; invDiag = 1.0f / diag; }
+    const uint32_t *jit_row = a.jit_words + (size_t)((unsigned)e % a.rows) * a.jit_len;
 
     for (int k = 0; k < a.K; ++k) {
-        float *s_buf = s_tile + (size_t)(k & 1) * kBlockThreads * OBS;
-        float *s_row = s_buf + (size_t)tid * OBS;
-        if (k >= 2) {  // the bulk store issued two substeps ago must have finished reading s_buf
-            if (tid == 0) bulk_wait_read<1>();
-            __syncthreads();
+        // ---- where this thread's observation row goes
+        float *s_buf = nullptr;   // tile base (block or warp) in shared memory
+        float *row;
+        if constexpr (STORE == kStoreDirect) {
+            row = a.obs + ((size_t)k * N + (valid ? e : a.first)) * OBS;
+        } else if constexpr (STORE == kStoreTmaBlock) {
+            s_buf = s_tile + (size_t)(k & 1) * BLOCK * OBS;
+            row = s_buf + (size_t)tid * OBS;
+            if (k >= 2) {  // the bulk store issued two substeps ago must have finished reading s_buf
+                if (tid == 0) bulk_wait_read<1>();
+                __syncthreads();
+            }
+        } else {
+            const int nbuf = (STORE == kStoreTmaWarp) ? 2 : 1;
+            s_buf = s_tile + ((size_t)(tid >> 5) * nbuf + (STORE == kStoreTmaWarp ? (k & 1) : 0)) * 32 * OBS;
+            row = s_buf + (size_t)lane * OBS;
+            if constexpr (STORE == kStoreTmaWarp) {
+                if (k >= 2) { if (lane == 0) bulk_wait_read<1>(); __syncwarp(); }
+            } else if (k >= 1) __syncwarp();  // previous substep's cooperative copy has read the tile
         }
+        // ---- does this step fire the jet?  (exhaling, and 0.1 <= (timer+1)/D <= 0.5, R:231-250.)
+        //      Known before anything else is computed, so the jitter word load is issued first.
+        const int t1 = timer + 1;
+        const bool thrust = (phase == kPhaseExhale) && (t1 <= exd) && (10 * t1 >= exd) && (2 * t1 <= exd);
+        uint2 jw = make_uint2(0u, 0u);
+        if (thrust) jw = *reinterpret_cast<const uint2 *>(jit_row + (cur_jit & a.jit_len_mask));
         // ---- action (R:121-135)
         T act0 = 0, act1 = 0;
         if (valid) {
@@ -328,7 +363,6 @@ __global__ void __launch_bounds__(kBlockThreads) salp_step_kernel(const __grid_c
         }
         // ---- breathing FSM on integers (R:184-259); thresholds 0.1<=t/D<=0.5 and t/D<=1 are
         //      exact integer compares (margins >= 1/(10*150) >> ulp), see tests/test_fsm_invariants.py
-        bool thrust = false;
         int wv_mode = 0;  // 0 keep, 1 wv=p, 2 wv=max(0,wv*(1-p)), 3 wv=0
         if (phase == kPhaseRest) {
             skind = kShapeRest;
@@ -342,10 +376,8 @@ __global__ void __launch_bounds__(kBlockThreads) salp_step_kernel(const __grid_c
             } else { phase = kPhaseRest; timer = 0; wv_mode = 3; }
         } else {
             ++timer;
-            if (timer <= exd) {
-                skind = kShapeExhale; stimer = timer; wv_mode = 2;
-                thrust = (10 * timer >= exd) && (2 * timer <= exd);
-            } else { phase = kPhaseRest; timer = 0; wv_mode = 3; }
+            if (timer <= exd) { skind = kShapeExhale; stimer = timer; wv_mode = 2; }
+            else { phase = kPhaseRest; timer = 0; wv_mode = 3; }
         }
         // ---- ellipse axes from the shape fields (R:190-191, 207-213, 240-246)
         T ea, eb, prog = 0;
@@ -381,10 +413,8 @@ __global__ void __launch_bounds__(kBlockThreads) salp_step_kernel(const __grid_c
             else { s1 = c0_; c1_ = -s0; }  // cos(x+pi/2) = -sin x, sin(x+pi/2) = cos x
             vx += (c1_ * sm) * (T)0.008;
             vy += (s1 * sm) * (T)0.008;
-            const unsigned row = (unsigned)e % a.rows;
-            const uint2 w = *reinterpret_cast<const uint2 *>(a.jit_words + (size_t)row * a.jit_len + (cur_jit & a.jit_len_mask));
             cur_jit += 2;
-            const T u = (T)res53(w.x, w.y);  // np.random.random(), R:311
+            const T u = (T)res53(jw.x, jw.y);  // np.random.random(), R:311
             const T na = th + (u - (T)0.5) * (T)0.05;
             const T nf = Tm * (T)0.04;
             T s2, c2;
@@ -444,13 +474,13 @@ __global__ void __launch_bounds__(kBlockThreads) salp_step_kernel(const __grid_c
             ++food_collected;
             steps_since_food = 0;
             if (a.respawn) {
-                int slot; T nx, ny;
-                respawn_slow<T>(a, e, px, py, mask, n_food, cur_food, slot, nx, ny);
+                const RespawnResult<T> r = respawn_slow<T>(a, e, px, py, mask, n_food, cur_food);
+                mask = r.mask; cur_food = r.cur;
 #pragma unroll
                 for (int f = 0; f < F; ++f)
-                    if (f == slot) {
-                        fx[f] = nx; fy[f] = ny;
-                        dx[f] = nx - px; dy[f] = ny - py;
+                    if (f == r.slot) {
+                        fx[f] = r.x; fy[f] = r.y;
+                        dx[f] = r.x - px; dy[f] = r.y - py;
                         dd[f] = sqrt_(dx[f] * dx[f] + dy[f] * dy[f]);
                     }
             }
@@ -464,77 +494,89 @@ __global__ void __launch_bounds__(kBlockThreads) salp_step_kernel(const __grid_c
         ep_ret += reward;
         ++ep_len;
 
-        // ---- observation (R:377-388 + S:366-428) -> shared-memory row
-        float o[12 + 4 * MT];
-        if constexpr (is_f64<T>::value) {
-            o[0] = (float)(px / W); o[1] = (float)(py / H);
-        } else { o[0] = px * invW; o[1] = py * invH; }
-        o[2] = (float)divc<T>(vx, 5.0); o[3] = (float)divc<T>(vy, 5.0);
-        o[4] = (float)divc<T>(angle, kc::PI); o[5] = (float)divc<T>(omega, 0.1);
-        o[6] = (float)divc<T>(radius, kc::BASE_R);
-        o[7] = (float)((T)phase / (T)2.0);
-        o[8] = (float)wv;
-        o[9] = (float)divc<T>(nozzle, kc::MAX_NOZZLE);
-        {
-            int id[F];
+        // ---- observation (R:377-388 + S:366-428), assembled in registers, written as 128-bit rows
+        float4 v0, v1;
+        float o8, o9;
+        if constexpr (is_f64<T>::value) { v0.x = (float)(px / W); v0.y = (float)(py / H); }
+        else { v0.x = px * invW; v0.y = py * invH; }
+        v0.z = (float)divc<T>(vx, 5.0); v0.w = (float)divc<T>(vy, 5.0);
+        v1.x = (float)divc<T>(angle, kc::PI); v1.y = (float)divc<T>(omega, 0.1);
+        v1.z = (float)divc<T>(radius, kc::BASE_R);
+        v1.w = (float)((T)phase / (T)2.0);
+        o8 = (float)wv;
+        o9 = (float)divc<T>(nozzle, kc::MAX_NOZZLE);
+        int id[F];
 #pragma unroll
-            for (int f = 0; f < F; ++f) {
-                id[f] = f;
-                if (!((mask >> f) & 1u)) dd[f] = is_f64<T>::value ? (T)CUDART_INF : (T)CUDART_INF_F;
-            }
+        for (int f = 0; f < F; ++f) {
+            id[f] = f;
+            if (!((mask >> f) & 1u)) dd[f] = is_f64<T>::value ? (T)CUDART_INF : (T)CUDART_INF_F;
+        }
 #define SALP_CE(i, j)                                                                          \
     {                                                                                          \
         const bool sw = (dd[j] < dd[i]) || (dd[j] == dd[i] && id[j] < id[i]);                  \
-        const T t0 = sw ? dd[j] : dd[i], t1 = sw ? dd[i] : dd[j];                              \
+        const T t0 = sw ? dd[j] : dd[i], t1_ = sw ? dd[i] : dd[j];                             \
         const int u0 = sw ? id[j] : id[i], u1 = sw ? id[i] : id[j];                            \
-        dd[i] = t0; dd[j] = t1; id[i] = u0; id[j] = u1;                                        \
+        dd[i] = t0; dd[j] = t1_; id[i] = u0; id[j] = u1;                                       \
     }
-            if constexpr (F == 2) { SALP_SORTNET_2(SALP_CE) }
-            else if constexpr (F == 4) { SALP_SORTNET_4(SALP_CE) }
-            else if constexpr (F == 8) { SALP_SORTNET_8(SALP_CE) }
-            else if constexpr (F == 12) { SALP_SORTNET_12(SALP_CE) }
-            else if constexpr (F == 16) { SALP_SORTNET_16(SALP_CE) }
-            else if constexpr (F == 32) { SALP_SORTNET_32(SALP_CE) }
+        if constexpr (F == 2) { SALP_SORTNET_2(SALP_CE) }
+        else if constexpr (F == 4) { SALP_SORTNET_4(SALP_CE) }
+        else if constexpr (F == 8) { SALP_SORTNET_8(SALP_CE) }
+        else if constexpr (F == 12) { SALP_SORTNET_12(SALP_CE) }
+        else if constexpr (F == 16) { SALP_SORTNET_16(SALP_CE) }
+        else if constexpr (F == 32) { SALP_SORTNET_32(SALP_CE) }
 #undef SALP_CE
-            const int n_live = __popc(mask);
-            constexpr int MU = (MT < F) ? MT : F;  // entries that can ever be real
+        const int n_live = __popc(mask);
+        // i-th nearest live food -> [dx/W, dy/H, d/diag, wrap(atan2(dy,dx) - angle)/pi]; S:412 padding [0,0,1,0]
+        auto food_entry = [&](int i) -> float4 {
+            float4 q = make_float4(0.f, 0.f, 1.f, 0.f);
+            if (i < F && i < n_live) {
+                T sx = 0, sy = 0, sd = 0;
 #pragma unroll
-            for (int i = 0; i < MT; ++i) {
-                float q0 = 0.f, q1 = 0.f, q2 = 1.f, q3 = 0.f;  // S:412 padding [0,0,1,0]
-                if (i < MU) {
-                    if (i < n_live) {
-                        T sx = 0, sy = 0;
-#pragma unroll
-                        for (int f = 0; f < F; ++f)
-                            if (id[i] == f) { sx = dx[f]; sy = dy[f]; }
-                        const T rel = wrap_pi<T>(atan2_(sy, sx) - angle);
-                        if constexpr (is_f64<T>::value) {
-                            q0 = (float)(sx / W); q1 = (float)(sy / H); q2 = (float)(dd[i] / diag);
-                        } else { q0 = sx * invW; q1 = sy * invH; q2 = dd[i] * invDiag; }
-                        q3 = (float)divc<T>(rel, kc::PI);
-                    }
+                for (int f = 0; f < F; ++f) {
+                    if (id[i < F ? i : 0] == f) { sx = dx[f]; sy = dy[f]; }
                 }
-                o[10 + 4 * i] = q0; o[11 + 4 * i] = q1; o[12 + 4 * i] = q2; o[13 + 4 * i] = q3;
+                sd = dd[i < F ? i : 0];
+                const T rel = wrap_pi<T>(atan2_(sy, sx) - angle);
+                if constexpr (is_f64<T>::value) { q.x = (float)(sx / W); q.y = (float)(sy / H); q.z = (float)(sd / diag); }
+                else { q.x = sx * invW; q.y = sy * invH; q.z = sd * invDiag; }
+                q.w = (float)divc<T>(rel, kc::PI);
             }
-            float cnt, avg = 1.f;
-            cnt = (float)pymin<T>((T)n_live / (T)10.0, (T)1.0);
-            if (n_live > 0) {
-                T s = 0;
+            return q;
+        };
+        float cnt, avg = 1.f;
+        cnt = (float)pymin<T>((T)n_live / (T)10.0, (T)1.0);
+        if (n_live > 0) {
+            T s = 0;
 #pragma unroll
-                for (int f = 0; f < F; ++f)
-                    if (f < n_live) s = s + dd[f];
-                const T mean = s / (T)n_live;
-                if constexpr (is_f64<T>::value) avg = (float)(mean / diag);
-                else avg = mean * invDiag;
-            }
-            // summary pair sits right after the `observed` food entries (runtime <= MT)
-#pragma unroll
-            for (int i = 0; i <= MT; ++i)
-                if (i == a.observed) { o[10 + 4 * i] = cnt; o[11 + 4 * i] = avg; }
+            for (int f = 0; f < F; ++f)
+                if (f < n_live) s = s + dd[f];
+            const T mean = s / (T)n_live;
+            if constexpr (is_f64<T>::value) avg = (float)(mean / diag);
+            else avg = mean * invDiag;
         }
+        const bool write_row = (STORE != kStoreDirect) || valid;
+        if (write_row) {
+            float4 *r4 = reinterpret_cast<float4 *>(row);
+            r4[0] = v0; r4[1] = v1;
+            if constexpr (MT == 3) {
+                const float4 e0 = food_entry(0), e1 = food_entry(1), e2 = food_entry(2);
+                r4[2] = make_float4(o8, o9, e0.x, e0.y);
+                r4[3] = make_float4(e0.z, e0.w, e1.x, e1.y);
+                r4[4] = make_float4(e1.z, e1.w, e2.x, e2.y);
+                r4[5] = make_float4(e2.z, e2.w, cnt, avg);
+            } else {
+                float2 *r2 = reinterpret_cast<float2 *>(row);
+                r2[4] = make_float2(o8, o9);
 #pragma unroll
-        for (int j = 0; j < (12 + 4 * MT) / 4; ++j)
-            if (4 * j < OBS) *reinterpret_cast<float4 *>(s_row + 4 * j) = make_float4(o[4 * j], o[4 * j + 1], o[4 * j + 2], o[4 * j + 3]);
+                for (int i = 0; i < MT; ++i)
+                    if (i < a.observed) {
+                        const float4 q = food_entry(i);
+                        r2[5 + 2 * i] = make_float2(q.x, q.y);
+                        r2[6 + 2 * i] = make_float2(q.z, q.w);
+                    }
+                r2[5 + 2 * a.observed] = make_float2(cnt, avg);
+            }
+        }
 
         // ---- per-step outputs
         const bool done = terminated || truncated;
@@ -555,7 +597,7 @@ __global__ void __launch_bounds__(kBlockThreads) salp_step_kernel(const __grid_c
                 const unsigned coll_mask = __ballot_sync(0xffffffffu, done && collision);
                 const unsigned trunc_mask = __ballot_sync(0xffffffffu, done && truncated);
                 const unsigned bad_mask = __ballot_sync(0xffffffffu, done && !(isfinite((double)px) && isfinite((double)py)));
-                if ((tid & 31) == 0) {
+                if (lane == 0) {
                     atomicAdd(a.stats + 0, (double)__popc(done_mask));
                     atomicAdd(a.stats + 1, r);
                     atomicAdd(a.stats + 2, l);
@@ -571,9 +613,10 @@ __global__ void __launch_bounds__(kBlockThreads) salp_step_kernel(const __grid_c
             if (done && a.autoreset) {
                 if (a.final_obs) {  // terminal observation (gymnasium "final_observation")
                     float4 *dst = reinterpret_cast<float4 *>(a.final_obs + ((size_t)k * N + e) * OBS);
-                    for (int j = 0; j < OBS / 4; ++j) dst[j] = *reinterpret_cast<const float4 *>(s_row + 4 * j);
+                    for (int j = 0; j < OBS / 4; ++j) dst[j] = *reinterpret_cast<const float4 *>(row + 4 * j);
                 }
-                reset_slow<T>(a, e, cur_food, n_food, mask, s_row);
+                const ResetResult rr = reset_slow<T>(a, e, cur_food, row);
+                cur_food = rr.cur; mask = rr.mask; n_food = rr.n_food;
                 // R:95-117 deterministic robot reset, S:139-141 counters
                 px = W / 2; py = H / 2; vx = 0; vy = 0; angle = 0; omega = 0; nozzle = 0; wv = 0;
                 phase = kPhaseRest; timer = 0; skind = kShapeReset; stimer = 0;
@@ -587,11 +630,29 @@ __global__ void __launch_bounds__(kBlockThreads) salp_step_kernel(const __grid_c
                 }
             }
         }
-        // ---- publish the CTA's observation tile with one TMA bulk store
-        fence_proxy_async_smem();
-        __syncthreads();
-        if (tid == 0)
-            bulk_store_commit(a.obs + ((size_t)k * N + blk0) * OBS, s_buf, (uint32_t)(n_rows * OBS * sizeof(float)));
+        // ---- publish the observation tile
+        if constexpr (STORE == kStoreTmaBlock) {
+            fence_proxy_async_smem();
+            __syncthreads();
+            const int n_rows = (int)((end - blk0) < BLOCK ? (end - blk0) : BLOCK);
+            if (tid == 0) bulk_store_commit(a.obs + ((size_t)k * N + blk0) * OBS, s_buf, (uint32_t)(n_rows * OBS * sizeof(float)));
+        } else if constexpr (STORE != kStoreDirect) {
+            const long long w0 = blk0 + (tid & ~31);           // first env of this warp
+            const long long left = end - w0;
+            const int w_rows = left >= 32 ? 32 : (left > 0 ? (int)left : 0);
+            float *g_tile = a.obs + ((size_t)k * N + w0) * OBS;
+            if constexpr (STORE == kStoreTmaWarp) {
+                fence_proxy_async_smem();
+                __syncwarp();
+                if (lane == 0 && w_rows > 0) bulk_store_commit(g_tile, s_buf, (uint32_t)(w_rows * OBS * sizeof(float)));
+            } else {
+                __syncwarp();
+                const int chunks = w_rows * (OBS / 4);  // 16-byte chunks, contiguous in HBM
+                const float4 *src = reinterpret_cast<const float4 *>(s_buf);
+                float4 *dst = reinterpret_cast<float4 *>(g_tile);
+                for (int c = lane; c < chunks; c += 32) dst[c] = src[c];
+            }
+        }
     }
 
     // ---- write state back once (food records are only written by the slow paths)
@@ -604,30 +665,30 @@ __global__ void __launch_bounds__(kBlockThreads) salp_step_kernel(const __grid_c
         g_epret[e] = ep_ret;
     }
     if (blockIdx.x == 0 && tid == 0 && a.stats) atomicAdd(a.stats + 7, (double)a.count * (double)a.K);
-    if (tid == 0) bulk_wait_read<0>();  // smem must stay allocated until the last bulk store has read it
+    if constexpr (kTma) {  // smem must stay allocated until the last bulk store has read it
+        if (STORE == kStoreTmaBlock ? (tid == 0) : (lane == 0)) bulk_wait_read<0>();
+    }
 }
 
 // ---------------------------------------------------------------------------------------------
 // Reset kernel: SalpSnakeEnv.reset for masked envs (S:133-155); writes obs[0][e][:]
 // ---------------------------------------------------------------------------------------------
 template <typename T>
-__global__ void __launch_bounds__(kBlockThreads) salp_reset_kernel(const __grid_constant__ KernelArgs a) {
-    const long long e = a.first + (long long)blockIdx.x * kBlockThreads + threadIdx.x;
+__global__ void __launch_bounds__(256) salp_reset_kernel(const __grid_constant__ KernelArgs a) {
+    const long long e = a.first + (long long)blockIdx.x * 256 + threadIdx.x;
     if (e >= a.first + a.count) return;
     if (a.reset_mask && a.reset_mask[e] == 0) return;
     const long long N = a.N;
     Vec4<T> *g_body = reinterpret_cast<Vec4<T> *>(a.body);
-    int4 c1 = a.ctrl[N + e];
-    unsigned cur_food = a.rewind_rng ? 0u : (unsigned)c1.x;
+    const int4 c1 = a.ctrl[N + e];
+    const unsigned cur_food = a.rewind_rng ? 0u : (unsigned)c1.x;
     const unsigned cur_jit = a.rewind_rng ? 0u : (unsigned)c1.y;
-    int n_food;
-    unsigned mask;
-    reset_slow<T>(a, e, cur_food, n_food, mask, a.obs ? a.obs + (size_t)e * a.obs_dim : nullptr);
+    const ResetResult rr = reset_slow<T>(a, e, cur_food, a.obs ? a.obs + (size_t)e * a.obs_dim : nullptr);
     g_body[e] = Vec4<T>{(T)a.W / 2, (T)a.H / 2, 0, 0};
     g_body[N + e] = Vec4<T>{0, 0, 0, 0};
     const int fsm = kPhaseRest | (kShapeReset << 18);
-    a.ctrl[e] = make_int4(fsm, 0, 0, (int)mask);
-    a.ctrl[N + e] = make_int4((int)cur_food, (int)cur_jit, 0, n_food);
+    a.ctrl[e] = make_int4(fsm, 0, 0, (int)rr.mask);
+    a.ctrl[N + e] = make_int4((int)rr.cur, (int)cur_jit, 0, rr.n_food);
     reinterpret_cast<T *>(a.ep_return)[e] = 0;
 }
 
