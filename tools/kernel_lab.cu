@@ -49,7 +49,7 @@ int main(int argc, char **argv) {
     a.N = N; a.first = 0; a.count = N; a.rows = (unsigned)N; a.food_len = FL; a.jit_len = JL;
     a.food_len_mask = FL - 1; a.jit_len_mask = JL - 1;
     a.K = 1; a.obs_dim = OBS; a.observed = 3; a.act_dim = 1; a.forced = 1; a.respawn = 1; a.autoreset = 1;
-    a.W = 800; a.H = 600;
+    a.W = 800; a.H = 600; a.diag = 1000.0; a.inv_w = 1.0 / 800; a.inv_h = 1.0 / 600; a.inv_diag = 1e-3;
     if (F == 1) { a.max_steps = 1500; a.num_food = 1; a.food_reward = 1000; a.collision_penalty = -10; a.time_penalty = -0.1; a.proximity_w = 5.0; }
     else { a.max_steps = 1500; a.num_food = 12; a.food_reward = 15; a.collision_penalty = -30; a.time_penalty = -0.05; a.efficiency_bonus = 2.0; }
     for (int t = 0; t < 128; ++t) { double wv = (t < 120 ? t : 120) / 120.0; a.exhale_lut[t] = (uint8_t)(int)(150.0 * (wv > 0.3 ? wv : 0.3)); }
@@ -75,15 +75,21 @@ int main(int argc, char **argv) {
         V(kStoreWarp, 128, 4), V(kStoreWarp, 128, 8), V(kStoreWarp, 128, 10), V(kStoreWarp, 128, 12),
         V(kStoreWarp, 256, 4), V(kStoreWarp, 256, 5), V(kStoreWarp, 256, 6),
         V(kStoreTmaWarp, 128, 8), V(kStoreTmaWarp, 128, 10), V(kStoreTmaWarp, 256, 4),
-        V(kStoreTmaBlock, 128, 8), V(kStoreTmaBlock, 256, 4), V(kStoreTmaBlock, 64, 16),
+        V(kStoreTmaBlock, 128, 8), V(kStoreTmaBlock, 256, 4), V(kStoreTmaBlock, 64, 16), V(kStoreTmaBlock, 32, 32), V(kStoreTmaBlock, 64, 14), V(kStoreWarp, 32, 32),
         V(kStoreDirect, 64, 16), V(kStoreDirect, 128, 8), V(kStoreDirect, 128, 10), V(kStoreDirect, 128, 12), V(kStoreDirect, 256, 4), V(kStoreDirect, 256, 6),
 #else
-        V(kStoreWarp, 64, 8), V(kStoreWarp, 64, 10), V(kStoreWarp, 64, 12), V(kStoreWarp, 64, 16),
-        V(kStoreWarp, 128, 2), V(kStoreWarp, 128, 4), V(kStoreWarp, 128, 5), V(kStoreWarp, 128, 6), V(kStoreWarp, 128, 8),
-        V(kStoreWarp, 256, 2), V(kStoreWarp, 256, 3), V(kStoreWarp, 256, 4),
-        V(kStoreDirect, 128, 4), V(kStoreDirect, 128, 6), V(kStoreDirect, 128, 8), V(kStoreTmaBlock, 256, 3),
+        V(kStoreWarp, 64, 8), V(kStoreWarp, 64, 10), V(kStoreWarp, 64, 12),
+        V(kStoreWarp, 128, 4), V(kStoreWarp, 128, 5), V(kStoreWarp, 128, 6),
+        V(kStoreWarp, 256, 3),
+        V(kStoreDirect, 64, 8), V(kStoreDirect, 64, 10), V(kStoreDirect, 64, 12), V(kStoreDirect, 128, 4), V(kStoreDirect, 128, 5), V(kStoreDirect, 128, 6),
+        V(kStoreTmaBlock, 64, 8), V(kStoreTmaBlock, 64, 10), V(kStoreTmaBlock, 64, 12), V(kStoreTmaBlock, 128, 5),
 #endif
     };
+    if (argc > 4) {  // keep only variants whose name contains argv[4]
+        std::vector<Variant> keep;
+        for (auto &v : vs) if (strstr(v.name, argv[4])) keep.push_back(v);
+        vs = keep;
+    }
     const double bpe = F == 1 ? 250.0 : 426.0;
     cudaEvent_t e0, e1;
     CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));

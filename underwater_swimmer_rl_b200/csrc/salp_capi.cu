@@ -7,6 +7,7 @@
 
 #include <algorithm>
 #include <atomic>
+#include <cmath>
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
@@ -133,6 +134,10 @@ int salp_create(const SalpParams *p, int64_t num_envs, int64_t env_id0, int devi
     a.num_food = p->num_food_items;
     a.W = p->width;
     a.H = p->height;
+    a.diag = std::sqrt(p->width * p->width + p->height * p->height);  // S:396
+    a.inv_w = 1.0 / a.W;
+    a.inv_h = 1.0 / a.H;
+    a.inv_diag = 1.0 / a.diag;
     a.food_reward = p->food_reward;
     a.collision_penalty = p->collision_penalty;
     a.time_penalty = p->time_penalty;

@@ -36,6 +36,7 @@ struct KernelArgs {
     int K, obs_dim, observed, act_dim;
     int forced, random_food_count, respawn, autoreset, max_steps, num_food, rewind_rng;
     double W, H, food_reward, collision_penalty, time_penalty, efficiency_bonus, proximity_w;
+    double diag, inv_w, inv_h, inv_diag;  // sqrt(W^2+H^2) and reciprocals, computed once on the host
     uint8_t exhale_lut[128];  // int(150 * max(t/120, 0.3)) for inhale timer t (R:223)
 };
 

@@ -2,17 +2,7 @@
 // Compiled twice by build.py:
 //   -DSALP_BUILD_F64=0                 -> launch_step_f32 / launch_reset_f32   (throughput build)
 //   -DSALP_BUILD_F64=1 -fmad=false     -> launch_step_f64 / launch_reset_f64   (validation build)
-// SALP_STORE / SALP_BLOCK pick the observation-store mode and CTA size that tools/kernel_lab.cu
-// measured fastest on B200 (see DESIGN.md "kernel variants").
 #include "salp_launch.cuh"
-
-#ifndef SALP_STORE
-#define SALP_STORE kStoreWarp
-#endif
-#ifndef SALP_BLOCK
-#define SALP_BLOCK 128
-#endif
-
 
 namespace salp {
 
@@ -26,17 +16,23 @@ using real_t = float;
 #define SALP_LAUNCH_RESET launch_reset_f32
 #endif
 
-// CTAs/SM the register allocator must leave room for (registers per thread <= 65536/(MINB*BLOCK)).
-// Tuned with tools/kernel_lab.cu; the double build and the wide sorting networks need more registers.
-template <int F> constexpr int min_blocks() {
-    constexpr int f32 = F <= 4 ? 8 : (F <= 8 ? 6 : (F <= 12 ? 4 : (F <= 16 ? 3 : 2)));
-    return (SALP_BUILD_F64 ? (f32 + 1) / 2 : f32) * 128 / SALP_BLOCK > 0 ? (SALP_BUILD_F64 ? (f32 + 1) / 2 : f32) * 128 / SALP_BLOCK : 1;
-}
+// Launch configuration per food-slot count, chosen from tools/kernel_lab.cu timings on B200
+// (1,048,576 envs, steady state; DESIGN.md "kernel variants"):
+//   STORE  how the observation tile leaves the SM      BLOCK  threads per CTA
+//   REGS   register budget per thread (f32 build); MINB = 65536 / (REGS * BLOCK) CTAs per SM
+template <int F> struct StepCfg {
+    static constexpr int store = (F <= 4) ? kStoreTmaBlock : kStoreWarp;
+    static constexpr int block = 64;
+    static constexpr int regs_f32 = F <= 4 ? 64 : (F <= 8 ? 80 : (F <= 12 ? 102 : (F <= 16 ? 128 : 255)));
+    static constexpr int regs = SALP_BUILD_F64 ? (2 * regs_f32 > 255 ? 255 : 2 * regs_f32) : regs_f32;
+    static constexpr int minb = (65536 / (regs * block)) > 32 ? 32 : (65536 / (regs * block) < 1 ? 1 : 65536 / (regs * block));
+};
 
 template <int F>
 static cudaError_t launch_step_f(const KernelArgs &a, cudaStream_t s) {
-    return a.observed == 3 ? launch_step_variant<real_t, F, 3, SALP_STORE, SALP_BLOCK, min_blocks<F>()>(a, s)
-                           : launch_step_variant<real_t, F, 8, SALP_STORE, SALP_BLOCK, min_blocks<F>()>(a, s);
+    using C = StepCfg<F>;
+    return a.observed == 3 ? launch_step_variant<real_t, F, 3, C::store, C::block, C::minb>(a, s)
+                           : launch_step_variant<real_t, F, 8, C::store, C::block, C::minb>(a, s);
 }
 
 cudaError_t SALP_LAUNCH_STEP(const KernelArgs &a, int food_slots, cudaStream_t s) {

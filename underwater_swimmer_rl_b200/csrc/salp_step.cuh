@@ -69,9 +69,17 @@ template <typename T> __device__ __forceinline__ T divc(T x, double c) {
     else return x * (float)(1.0 / c);
 }
 
-template <typename T> __device__ __forceinline__ T wrap_pi(T x) {  // R:329-332, S:311-314, S:403-406
-    while (x > (T)kc::PI) x -= (T)kc::TWO_PI;
-    while (x < (T)(-kc::PI)) x += (T)kc::TWO_PI;
+// R:329-332, S:311-314, S:403-406:  while x > pi: x -= 2pi;  while x < -pi: x += 2pi.
+// One predicated correction per direction reproduces the loops' first iterations (same operations,
+// same order, bit-identical) and is all that ever runs for values the model itself produces
+// (|angle| <= pi, |omega| << pi, |atan2| <= pi); the loops remain as the tail for poked-in states.
+template <typename T> __device__ __forceinline__ T wrap_pi(T x) {
+    x = (x > (T)kc::PI) ? x - (T)kc::TWO_PI : x;
+    x = (x < (T)(-kc::PI)) ? x + (T)kc::TWO_PI : x;
+    if (abs_(x) > (T)kc::PI) {
+        while (x > (T)kc::PI) x -= (T)kc::TWO_PI;
+        while (x < (T)(-kc::PI)) x += (T)kc::TWO_PI;
+    }
     return x;
 }
 
@@ -260,12 +268,13 @@ __global__ void __launch_bounds__(BLOCK, MINB) salp_step_kernel(const __grid_con
     extern __shared__ __align__(128) float s_tile[];  // [nbuf][BLOCK][obs_dim] (unused for kStoreDirect)
     const int tid = threadIdx.x;
     const int lane = tid & 31;
-    const long long blk0 = a.first + (long long)blockIdx.x * BLOCK;
-    const long long e = blk0 + tid;
-    const long long end = a.first + a.count;
+    // env indices fit 32 bits (salp_create caps num_envs at 2^30): cheap IMAD.WIDE addressing
+    const unsigned blk0 = (unsigned)a.first + blockIdx.x * BLOCK;
+    const unsigned e = blk0 + tid;
+    const unsigned end = (unsigned)a.first + (unsigned)a.count;
     const bool valid = e < end;
     const int OBS = a.obs_dim;
-    const long long N = a.N;
+    const unsigned N = (unsigned)a.N;
     constexpr bool kTma = (STORE == kStoreTmaWarp || STORE == kStoreTmaBlock);
 
     Vec4<T> *g_body = reinterpret_cast<Vec4<T> *>(a.body);
@@ -283,9 +292,9 @@ __global__ void __launch_bounds__(BLOCK, MINB) salp_step_kernel(const __grid_con
     for (int f = 0; f < F; ++f) { fx[f] = 0; fy[f] = 0; }
     if (valid) {
         c0 = a.ctrl[e];
-        c1 = a.ctrl[N + e];
+        c1 = a.ctrl[(size_t)N + e];
         b0 = g_body[e];
-        b1 = g_body[N + e];
+        b1 = g_body[(size_t)N + e];
         ep_ret = g_epret[e];
 #pragma unroll
         for (int f = 0; f < F; ++f) {
@@ -303,17 +312,17 @@ __global__ void __launch_bounds__(BLOCK, MINB) salp_step_kernel(const __grid_con
     int ep_len = c1.z, n_food = c1.w;
 
     const T W = (T)a.W, H = (T)a.H;
-    const T diag = sqrt_(W * W + H * H);  // S:396 (exact for the integer tank sizes)
-    T invW = 0, invH = 0, invDiag = 0;
-    if constexpr (!is_f64<T>::value) { invW = 1.0f / W; invH = 1.0f / H; invDiag = 1.0f / diag; }
-    const uint32_t *jit_row = a.jit_words + (size_t)((unsigned)e % a.rows) * a.jit_len;
+    const T diag = (T)a.diag;  // sqrt(W^2 + H^2), S:396, computed on the host in double
+    const T invW = (T)a.inv_w, invH = (T)a.inv_h, invDiag = (T)a.inv_diag;  // used by the f32 build only
+    const unsigned trow = (a.rows == N) ? e : e % a.rows;
+    const uint32_t *jit_row = a.jit_words + (size_t)trow * a.jit_len;
 
     for (int k = 0; k < a.K; ++k) {
         // ---- where this thread's observation row goes
         float *s_buf = nullptr;   // tile base (block or warp) in shared memory
         float *row;
         if constexpr (STORE == kStoreDirect) {
-            row = a.obs + ((size_t)k * N + (valid ? e : a.first)) * OBS;
+            row = a.obs + ((size_t)k * N + (valid ? e : (unsigned)a.first)) * OBS;
         } else if constexpr (STORE == kStoreTmaBlock) {
             s_buf = s_tile + (size_t)(k & 1) * BLOCK * OBS;
             row = s_buf + (size_t)tid * OBS;
@@ -415,10 +424,17 @@ __global__ void __launch_bounds__(BLOCK, MINB) salp_step_kernel(const __grid_con
             vy += (s1 * sm) * (T)0.008;
             cur_jit += 2;
             const T u = (T)res53(jw.x, jw.y);  // np.random.random(), R:311
-            const T na = th + (u - (T)0.5) * (T)0.05;
+            const T dn = (u - (T)0.5) * (T)0.05;
             const T nf = Tm * (T)0.04;
             T s2, c2;
-            sincos_(na, &s2, &c2);
+            if constexpr (is_f64<T>::value) sincos_(th + dn, &s2, &c2);
+            else {  // sin/cos(th + dn) by angle addition; |dn| <= 0.025 so the series error is < 1e-13
+                const T d2 = dn * dn;
+                const T sd = dn * ((T)1.0 - d2 * ((T)(1.0 / 6.0) - d2 * (T)(1.0 / 120.0)));
+                const T cd = (T)1.0 - d2 * ((T)0.5 - d2 * (T)(1.0 / 24.0));
+                s2 = s0 * cd + c0_ * sd;
+                c2 = c0_ * cd - s0 * sd;
+            }
             vx += c2 * nf * (T)0.002;
             vy += s2 * nf * (T)0.002;
         }
@@ -459,14 +475,15 @@ __global__ void __launch_bounds__(BLOCK, MINB) salp_step_kernel(const __grid_con
             if (a.efficiency_bonus > 0) reward += (T)a.efficiency_bonus * (T)(a.max_steps - steps_since_food);
         }
         if (collision) reward += (T)a.collision_penalty;
-        if (a.proximity_w > 0) {
-            bool any = false;
-            T bd = 0, bx = 0, by = 0;
+        // nearest live food (strict <, first index wins: S:350-364).  Its bearing is used by the
+        // alignment reward AND, when no food was eaten this step, is the first observation entry.
+        bool any_food = false;
+        T near_d = 0, near_x = 0, near_y = 0, near_rel = 0;
 #pragma unroll
-            for (int f = 0; f < F; ++f)
-                if (((mask >> f) & 1u) && (!any || dd[f] < bd)) { any = true; bd = dd[f]; bx = dx[f]; by = dy[f]; }
-            if (any) reward += (T)a.proximity_w * cos_(wrap_pi<T>(atan2_(by, bx) - angle));
-        }
+        for (int f = 0; f < F; ++f)
+            if (((mask >> f) & 1u) && (!any_food || dd[f] < near_d)) { any_food = true; near_d = dd[f]; near_x = dx[f]; near_y = dy[f]; }
+        if (any_food && (a.proximity_w > 0 || a.observed > 0)) near_rel = wrap_pi<T>(atan2_(near_y, near_x) - angle);
+        if (a.proximity_w > 0 && any_food) reward += (T)a.proximity_w * cos_(near_rel);
         reward += (T)a.time_penalty;
         // ---- counters, respawn (S:171-180)
         ++steps_since_food;
@@ -505,12 +522,24 @@ __global__ void __launch_bounds__(BLOCK, MINB) salp_step_kernel(const __grid_con
         v1.w = (float)((T)phase / (T)2.0);
         o8 = (float)wv;
         o9 = (float)divc<T>(nozzle, kc::MAX_NOZZLE);
-        int id[F];
+        const int n_live = __popc(mask);
+        // The MU nearest live foods in order (stable: equal distances keep slot order, S:382) and the
+        // mean distance (S:419).
+        constexpr int MU = (MT < F) ? MT : F;  // entries that can ever be real
+        T top_d[MU], top_x[MU], top_y[MU];
+        T dist_sum = 0;
+        if constexpr (F == 1) {
+            top_d[0] = dd[0]; top_x[0] = dx[0]; top_y[0] = dy[0];
+            dist_sum = dd[0];
+        } else if constexpr (is_f64<T>::value) {
+            // validation build: full sorting network on (distance, slot) so that the mean is summed
+            // in sorted order exactly like sum() over the sorted list
+            int id[F];
 #pragma unroll
-        for (int f = 0; f < F; ++f) {
-            id[f] = f;
-            if (!((mask >> f) & 1u)) dd[f] = is_f64<T>::value ? (T)CUDART_INF : (T)CUDART_INF_F;
-        }
+            for (int f = 0; f < F; ++f) {
+                id[f] = f;
+                if (!((mask >> f) & 1u)) dd[f] = (T)CUDART_INF;
+            }
 #define SALP_CE(i, j)                                                                          \
     {                                                                                          \
         const bool sw = (dd[j] < dd[i]) || (dd[j] == dd[i] && id[j] < id[i]);                  \
@@ -518,25 +547,67 @@ __global__ void __launch_bounds__(BLOCK, MINB) salp_step_kernel(const __grid_con
         const int u0 = sw ? id[j] : id[i], u1 = sw ? id[i] : id[j];                            \
         dd[i] = t0; dd[j] = t1_; id[i] = u0; id[j] = u1;                                       \
     }
-        if constexpr (F == 2) { SALP_SORTNET_2(SALP_CE) }
-        else if constexpr (F == 4) { SALP_SORTNET_4(SALP_CE) }
-        else if constexpr (F == 8) { SALP_SORTNET_8(SALP_CE) }
-        else if constexpr (F == 12) { SALP_SORTNET_12(SALP_CE) }
-        else if constexpr (F == 16) { SALP_SORTNET_16(SALP_CE) }
-        else if constexpr (F == 32) { SALP_SORTNET_32(SALP_CE) }
+            if constexpr (F == 2) { SALP_SORTNET_2(SALP_CE) }
+            else if constexpr (F == 4) { SALP_SORTNET_4(SALP_CE) }
+            else if constexpr (F == 8) { SALP_SORTNET_8(SALP_CE) }
+            else if constexpr (F == 12) { SALP_SORTNET_12(SALP_CE) }
+            else if constexpr (F == 16) { SALP_SORTNET_16(SALP_CE) }
+            else if constexpr (F == 32) { SALP_SORTNET_32(SALP_CE) }
 #undef SALP_CE
-        const int n_live = __popc(mask);
+#pragma unroll
+            for (int f = 0; f < F; ++f)
+                if (f < n_live) dist_sum = dist_sum + dd[f];
+#pragma unroll
+            for (int i = 0; i < MU; ++i) {
+                T sx = 0, sy = 0;
+#pragma unroll
+                for (int f = 0; f < F; ++f)
+                    if (id[i] == f) { sx = dx[f]; sy = dy[f]; }
+                top_d[i] = dd[i]; top_x[i] = sx; top_y[i] = sy;
+            }
+        } else {
+            // throughput build: only the MU nearest are needed -> insertion of every food into a
+            // sorted MU-list of (distance, slot).  Strict < keeps equal distances in slot order
+            // (foods arrive in slot order), i.e. the stable order of list.sort(); the mean is summed
+            // in slot order (differs from the sorted-order sum by rounding only).
+            T kd[MU];
+            int ki[MU];
+#pragma unroll
+            for (int i = 0; i < MU; ++i) { kd[i] = (T)CUDART_INF_F; ki[i] = F; }
+#pragma unroll
+            for (int f = 0; f < F; ++f) {
+                const bool alive = (mask >> f) & 1u;
+                if (alive) dist_sum += dd[f];
+                T cd = alive ? dd[f] : (T)CUDART_INF_F;
+                int ci = alive ? f : F;
+#pragma unroll
+                for (int i = 0; i < MU; ++i) {
+                    const bool lt = cd < kd[i];
+                    const T lo_d = lt ? cd : kd[i], hi_d = lt ? kd[i] : cd;
+                    const int lo_i = lt ? ci : ki[i], hi_i = lt ? ki[i] : ci;
+                    kd[i] = lo_d; ki[i] = lo_i; cd = hi_d; ci = hi_i;
+                }
+            }
+#pragma unroll
+            for (int i = 0; i < MU; ++i) {
+                T sx = 0, sy = 0;
+#pragma unroll
+                for (int f = 0; f < F; ++f)
+                    if (ki[i] == f) { sx = dx[f]; sy = dy[f]; }
+                top_d[i] = kd[i]; top_x[i] = sx; top_y[i] = sy;
+            }
+        }
         // i-th nearest live food -> [dx/W, dy/H, d/diag, wrap(atan2(dy,dx) - angle)/pi]; S:412 padding [0,0,1,0]
         auto food_entry = [&](int i) -> float4 {
             float4 q = make_float4(0.f, 0.f, 1.f, 0.f);
-            if (i < F && i < n_live) {
-                T sx = 0, sy = 0, sd = 0;
-#pragma unroll
-                for (int f = 0; f < F; ++f) {
-                    if (id[i < F ? i : 0] == f) { sx = dx[f]; sy = dy[f]; }
-                }
-                sd = dd[i < F ? i : 0];
-                const T rel = wrap_pi<T>(atan2_(sy, sx) - angle);
+            if (i < MU && i < n_live) {
+                const int j = i < MU ? i : 0;
+                const T sx = top_x[j], sy = top_y[j], sd = top_d[j];
+                // entry 0 is the nearest food: its bearing was already computed for the reward unless
+                // a food was eaten (and possibly respawned) after that
+                T rel;
+                if (i == 0) rel = hit ? wrap_pi<T>(atan2_(sy, sx) - angle) : near_rel;
+                else rel = wrap_pi<T>(atan2_(sy, sx) - angle);
                 if constexpr (is_f64<T>::value) { q.x = (float)(sx / W); q.y = (float)(sy / H); q.z = (float)(sd / diag); }
                 else { q.x = sx * invW; q.y = sy * invH; q.z = sd * invDiag; }
                 q.w = (float)divc<T>(rel, kc::PI);
@@ -546,11 +617,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) salp_step_kernel(const __grid_con
         float cnt, avg = 1.f;
         cnt = (float)pymin<T>((T)n_live / (T)10.0, (T)1.0);
         if (n_live > 0) {
-            T s = 0;
-#pragma unroll
-            for (int f = 0; f < F; ++f)
-                if (f < n_live) s = s + dd[f];
-            const T mean = s / (T)n_live;
+            const T mean = dist_sum / (T)n_live;
             if constexpr (is_f64<T>::value) avg = (float)(mean / diag);
             else avg = mean * invDiag;
         }
@@ -634,12 +701,11 @@ __global__ void __launch_bounds__(BLOCK, MINB) salp_step_kernel(const __grid_con
         if constexpr (STORE == kStoreTmaBlock) {
             fence_proxy_async_smem();
             __syncthreads();
-            const int n_rows = (int)((end - blk0) < BLOCK ? (end - blk0) : BLOCK);
+            const int n_rows = (int)((end - blk0) < (unsigned)BLOCK ? (end - blk0) : (unsigned)BLOCK);
             if (tid == 0) bulk_store_commit(a.obs + ((size_t)k * N + blk0) * OBS, s_buf, (uint32_t)(n_rows * OBS * sizeof(float)));
         } else if constexpr (STORE != kStoreDirect) {
-            const long long w0 = blk0 + (tid & ~31);           // first env of this warp
-            const long long left = end - w0;
-            const int w_rows = left >= 32 ? 32 : (left > 0 ? (int)left : 0);
+            const unsigned w0 = blk0 + (tid & ~31);            // first env of this warp
+            const int w_rows = w0 >= end ? 0 : (end - w0 >= 32u ? 32 : (int)(end - w0));
             float *g_tile = a.obs + ((size_t)k * N + w0) * OBS;
             if constexpr (STORE == kStoreTmaWarp) {
                 fence_proxy_async_smem();
@@ -658,10 +724,10 @@ __global__ void __launch_bounds__(BLOCK, MINB) salp_step_kernel(const __grid_con
     // ---- write state back once (food records are only written by the slow paths)
     if (valid) {
         g_body[e] = Vec4<T>{px, py, vx, vy};
-        g_body[N + e] = Vec4<T>{angle, omega, nozzle, wv};
+        g_body[(size_t)N + e] = Vec4<T>{angle, omega, nozzle, wv};
         const int fsm = phase | (timer << 2) | (exd << 10) | (skind << 18) | (stimer << 20);
         a.ctrl[e] = make_int4(fsm, steps_since_food, food_collected, (int)mask);
-        a.ctrl[N + e] = make_int4((int)cur_food, (int)cur_jit, ep_len, n_food);
+        a.ctrl[(size_t)N + e] = make_int4((int)cur_food, (int)cur_jit, ep_len, n_food);
         g_epret[e] = ep_ret;
     }
     if (blockIdx.x == 0 && tid == 0 && a.stats) atomicAdd(a.stats + 7, (double)a.count * (double)a.K);
