@@ -22,7 +22,8 @@ static uint64_t sm64(uint64_t &s) { uint64_t z = (s += 0x9e3779b97f4a7c15ull); z
 
 struct Variant { const char *name; cudaError_t (*fn)(const KernelArgs &, cudaStream_t); };
 
-#define V(STORE, BLOCK, MINB) {#STORE "/b" #BLOCK "/minb" #MINB, &launch_step_variant<float, LAB_F, 3, STORE, BLOCK, MINB>}
+#define V(STORE, BLOCK, MINB) {#STORE "/b" #BLOCK "/minb" #MINB, &launch_step_variant<float, LAB_F, 3, STORE, BLOCK, MINB, 0>}
+#define P(STORE, BLOCK, MINB) {#STORE "/b" #BLOCK "/minb" #MINB "/PF", &launch_step_variant<float, LAB_F, 3, STORE, BLOCK, MINB, 1>}
 
 int main(int argc, char **argv) {
     const long long N = argc > 1 ? atoll(argv[1]) : (1 << 20);
@@ -48,7 +49,7 @@ int main(int argc, char **argv) {
     a.food_words = fw; a.jit_words = jw;
     a.N = N; a.first = 0; a.count = N; a.rows = (unsigned)N; a.food_len = FL; a.jit_len = JL;
     a.food_len_mask = FL - 1; a.jit_len_mask = JL - 1;
-    a.K = 1; a.obs_dim = OBS; a.observed = 3; a.act_dim = 1; a.forced = 1; a.respawn = 1; a.autoreset = 1;
+    a.K = 1; a.obs_dim = OBS; a.observed = 3; a.act_dim = 1; a.forced = 1; a.respawn = 1; a.autoreset = argc > 5 ? atoi(argv[5]) : 1; a.stats = (argc > 6 && atoi(argv[6]) == 0) ? nullptr : a.stats; if (argc > 7 && atoi(argv[7]) == 0) { a.events = nullptr; a.final_obs = nullptr; a.final_info = nullptr; }
     a.W = 800; a.H = 600; a.diag = 1000.0; a.inv_w = 1.0 / 800; a.inv_h = 1.0 / 600; a.inv_diag = 1e-3;
     if (F == 1) { a.max_steps = 1500; a.num_food = 1; a.food_reward = 1000; a.collision_penalty = -10; a.time_penalty = -0.1; a.proximity_w = 5.0; }
     else { a.max_steps = 1500; a.num_food = 12; a.food_reward = 15; a.collision_penalty = -30; a.time_penalty = -0.05; a.efficiency_bonus = 2.0; }
@@ -61,7 +62,7 @@ int main(int argc, char **argv) {
         CK(cudaMemcpy(acts[i], ha.data(), N * 4, cudaMemcpyHostToDevice));
     }
     CK(launch_reset_f32(a, F, 0));
-    Variant base = V(kStoreWarp, 128, 4);
+    Variant base = V(kStoreWarp, 128, 8);
     for (int i = 0; i < PRIME; ++i) { a.actions = acts[i % NACT]; CK(base.fn(a, 0)); }
     CK(cudaDeviceSynchronize());
     void *snap_body, *snap_ctrl, *snap_ep, *snap_food;
@@ -71,18 +72,13 @@ int main(int argc, char **argv) {
 
     std::vector<Variant> vs = {
 #if LAB_F == 1
-        V(kStoreWarp, 64, 16), V(kStoreWarp, 64, 20), V(kStoreWarp, 64, 24),
-        V(kStoreWarp, 128, 4), V(kStoreWarp, 128, 8), V(kStoreWarp, 128, 10), V(kStoreWarp, 128, 12),
-        V(kStoreWarp, 256, 4), V(kStoreWarp, 256, 5), V(kStoreWarp, 256, 6),
-        V(kStoreTmaWarp, 128, 8), V(kStoreTmaWarp, 128, 10), V(kStoreTmaWarp, 256, 4),
-        V(kStoreTmaBlock, 128, 8), V(kStoreTmaBlock, 256, 4), V(kStoreTmaBlock, 64, 16), V(kStoreTmaBlock, 32, 32), V(kStoreTmaBlock, 64, 14), V(kStoreWarp, 32, 32),
-        V(kStoreDirect, 64, 16), V(kStoreDirect, 128, 8), V(kStoreDirect, 128, 10), V(kStoreDirect, 128, 12), V(kStoreDirect, 256, 4), V(kStoreDirect, 256, 6),
+        V(kStoreWarp, 64, 16), V(kStoreWarp, 128, 8), V(kStoreTmaBlock, 64, 16), V(kStoreTmaBlock, 32, 32),
+        P(kStoreWarp, 64, 16), P(kStoreWarp, 128, 8), P(kStoreWarp, 256, 4), P(kStoreWarp, 64, 12), P(kStoreWarp, 128, 6),
+        P(kStoreTmaBlock, 64, 16), P(kStoreTmaBlock, 128, 8), P(kStoreTmaBlock, 256, 4), P(kStoreTmaBlock, 64, 12), P(kStoreTmaBlock, 32, 32),
+        P(kStoreDirect, 64, 16), P(kStoreDirect, 128, 8), P(kStoreDirect, 64, 12),
 #else
-        V(kStoreWarp, 64, 8), V(kStoreWarp, 64, 10), V(kStoreWarp, 64, 12),
-        V(kStoreWarp, 128, 4), V(kStoreWarp, 128, 5), V(kStoreWarp, 128, 6),
-        V(kStoreWarp, 256, 3),
-        V(kStoreDirect, 64, 8), V(kStoreDirect, 64, 10), V(kStoreDirect, 64, 12), V(kStoreDirect, 128, 4), V(kStoreDirect, 128, 5), V(kStoreDirect, 128, 6),
-        V(kStoreTmaBlock, 64, 8), V(kStoreTmaBlock, 64, 10), V(kStoreTmaBlock, 64, 12), V(kStoreTmaBlock, 128, 5),
+        V(kStoreWarp, 128, 5), V(kStoreDirect, 64, 10), V(kStoreDirect, 128, 5), V(kStoreTmaBlock, 64, 10),
+        P(kStoreDirect, 64, 10), P(kStoreDirect, 128, 5), P(kStoreDirect, 64, 8), P(kStoreWarp, 64, 10), P(kStoreTmaBlock, 64, 10), P(kStoreDirect, 128, 4),
 #endif
     };
     if (argc > 4) {  // keep only variants whose name contains argv[4]
@@ -107,7 +103,16 @@ int main(int argc, char **argv) {
             float ms;
             CK(cudaEventElapsedTime(&ms, e0, e1));
             const double us = 1e3 * ms / STEPS;
-            printf("rep%d %-28s %8.2f us/step  %7.1f GB/s(alg)  %6.2f Gsteps/s\n", rep, v.name, us, bpe * N / us / 1e3, N / us / 1e3);
+            // all variants run the same arithmetic from the same snapshot: state/obs hashes must agree
+            static std::vector<uint32_t> hb;
+            uint64_t h = 1469598103934665603ull;
+            auto mix = [&](const void *dptr, size_t bytes) {
+                hb.resize(bytes / 4);
+                CK(cudaMemcpy(hb.data(), dptr, bytes, cudaMemcpyDeviceToHost));
+                for (uint32_t w : hb) { h ^= w; h *= 1099511628211ull; }
+            };
+            mix(a.body, body_b); mix(a.ctrl, ctrl_b); mix(a.obs, (size_t)N * OBS * 4); mix(a.reward, (size_t)N * 4);
+            printf("rep%d %-32s %8.2f us/step  %7.1f GB/s(alg)  %6.2f Gsteps/s  hash %016llx\n", rep, v.name, us, bpe * N / us / 1e3, N / us / 1e3, (unsigned long long)h);
             fflush(stdout);
         }
     return 0;

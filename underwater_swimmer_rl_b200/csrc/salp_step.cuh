@@ -45,7 +45,24 @@ constexpr int INHALE_DUR = 120;            // R:51
 template <typename T> struct is_f64 { static constexpr bool value = false; };
 template <> struct is_f64<double> { static constexpr bool value = true; };
 
-__device__ __forceinline__ float sqrt_(float x) { return sqrtf(x); }
+#ifdef SALP_LAB_NOMATH  // tools/kernel_lab.cu only: how much of the step is transcendental math?
+__device__ __forceinline__ float sqrt_(float x) { return x * 0.5f; }
+__device__ __forceinline__ float sin_(float x) { return x * 0.25f; }
+__device__ __forceinline__ float cos_(float x) { return 1.0f - x * 0.125f; }
+__device__ __forceinline__ void sincos_(float x, float *s, float *c) { *s = x * 0.25f; *c = 1.0f - x * 0.125f; }
+__device__ __forceinline__ float atan2_(float y, float x) { return y * 0.001f + x * 0.002f; }
+#else
+// f32 throughput build: sqrt.approx.f32 (one MUFU op, max relative error 2^-23 per the PTX ISA) instead
+// of the IEEE sequence with its special-case branch -- the 12-food configs take 12 of these per step.
+__device__ __forceinline__ float sqrt_(float x) {
+#ifdef SALP_LAB_IEEE_SQRT
+    return sqrtf(x);
+#else
+    float r;
+    asm("sqrt.approx.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+#endif
+}
 __device__ __forceinline__ double sqrt_(double x) { return sqrt(x); }
 __device__ __forceinline__ float sin_(float x) { return sinf(x); }
 __device__ __forceinline__ double sin_(double x) { return sin(x); }
@@ -54,6 +71,7 @@ __device__ __forceinline__ double cos_(double x) { return cos(x); }
 __device__ __forceinline__ void sincos_(float x, float *s, float *c) { sincosf(x, s, c); }
 __device__ __forceinline__ void sincos_(double x, double *s, double *c) { sincos(x, s, c); }
 __device__ __forceinline__ float atan2_(float y, float x) { return atan2f(y, x); }
+#endif
 __device__ __forceinline__ double atan2_(double y, double x) { return atan2(y, x); }
 __device__ __forceinline__ float abs_(float x) { return fabsf(x); }
 __device__ __forceinline__ double abs_(double x) { return fabs(x); }
@@ -247,6 +265,22 @@ __device__ __forceinline__ double warp_sum(double v) {
     return v;
 }
 
+// cp.async (LDGSTS): global -> shared without a register round trip; 4/8/16-byte forms, larger
+// records as several 16-byte copies.
+template <int BYTES> __device__ __forceinline__ void cp_async(void *sdst, const void *gsrc) {
+    const uint32_t s = (uint32_t)__cvta_generic_to_shared(sdst);
+    if constexpr (BYTES == 4 || BYTES == 8 || BYTES == 16) {
+        asm volatile("cp.async.ca.shared.global [%0], [%1], %2;" ::"r"(s), "l"(gsrc), "n"(BYTES) : "memory");
+    } else {
+        static_assert(BYTES % 16 == 0, "record size");
+#pragma unroll
+        for (int o = 0; o < BYTES; o += 16)
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(s + o), "l"((const char *)gsrc + o) : "memory");
+    }
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
 // How the observation tile leaves the SM (A/B-measured in tools/kernel_lab.cu):
 //   kStoreWarp     each warp stages its 32 rows (32*obs_dim floats, contiguous in HBM) in shared
 //                  memory and writes them with fully coalesced 128-bit stores; no CTA barrier
@@ -255,6 +289,17 @@ __device__ __forceinline__ double warp_sum(double v) {
 //   kStoreDirect   no staging: each thread writes its own row (6 x 128-bit, 96-byte stride)
 enum : int { kStoreWarp = 0, kStoreTmaWarp = 1, kStoreTmaBlock = 2, kStoreDirect = 3 };
 
+// shared-memory bytes the observation tiles take (the PF stage starts after them, 128-byte aligned)
+template <int STORE, int BLOCK> __host__ __device__ constexpr unsigned obs_tile_buffers() {
+    return STORE == kStoreDirect ? 0u : (STORE == kStoreWarp ? 1u : 2u);
+}
+template <int STORE, int BLOCK> __host__ __device__ inline unsigned stage_offset_bytes(int obs_dim) {
+    return (obs_tile_buffers<STORE, BLOCK>() * BLOCK * (unsigned)obs_dim * 4u + 127u) & ~127u;
+}
+template <typename T, int F, int BLOCK> __host__ __device__ constexpr unsigned stage_bytes() {
+    return 2u * (32u * BLOCK + 2u * (unsigned)sizeof(T) * 4u * BLOCK + (unsigned)sizeof(T) * 2u * F * BLOCK + 3u * (unsigned)sizeof(T) * BLOCK);
+}
+
 // ---------------------------------------------------------------------------------------------
 // The step kernel
 //   T     : float | double          F : food records per env (1,4,8,12,16,32)
@@ -262,19 +307,19 @@ enum : int { kStoreWarp = 0, kStoreTmaWarp = 1, kStoreTmaBlock = 2, kStoreDirect
 //           8 -> any max_observed_food in 0..8 (generic scalar row assembly)
 //   STORE : see above               BLOCK : threads per CTA (multiple of 32)
 //   MINB  : CTAs per SM the register allocation must allow (__launch_bounds__)
+//   PF    : 0 one tile per CTA, state loaded straight into registers
+//           1 persistent CTAs, next tile's state prefetched into shared memory with cp.async
 // ---------------------------------------------------------------------------------------------
-template <typename T, int F, int MT, int STORE, int BLOCK, int MINB>
+template <typename T, int F, int MT, int STORE, int BLOCK, int MINB, int PF>
 __global__ void __launch_bounds__(BLOCK, MINB) salp_step_kernel(const __grid_constant__ KernelArgs a) {
-    extern __shared__ __align__(128) float s_tile[];  // [nbuf][BLOCK][obs_dim] (unused for kStoreDirect)
+    extern __shared__ __align__(128) float s_tile[];  // obs tiles [nbuf][BLOCK][obs_dim], then the PF stage
     const int tid = threadIdx.x;
     const int lane = tid & 31;
-    // env indices fit 32 bits (salp_create caps num_envs at 2^30): cheap IMAD.WIDE addressing
-    const unsigned blk0 = (unsigned)a.first + blockIdx.x * BLOCK;
-    const unsigned e = blk0 + tid;
-    const unsigned end = (unsigned)a.first + (unsigned)a.count;
-    const bool valid = e < end;
     const int OBS = a.obs_dim;
     const unsigned N = (unsigned)a.N;
+    // env indices fit 32 bits (salp_create caps num_envs at 2^30): cheap IMAD.WIDE addressing
+    const unsigned end = (unsigned)a.first + (unsigned)a.count;
+    const unsigned ntiles = ((unsigned)a.count + BLOCK - 1) / BLOCK;
     constexpr bool kTma = (STORE == kStoreTmaWarp || STORE == kStoreTmaBlock);
 
     Vec4<T> *g_body = reinterpret_cast<Vec4<T> *>(a.body);
@@ -282,454 +327,527 @@ __global__ void __launch_bounds__(BLOCK, MINB) salp_step_kernel(const __grid_con
     const Vec2<T> *g_food = reinterpret_cast<const Vec2<T> *>(a.food);
     T *g_reward = reinterpret_cast<T *>(a.reward);
     const T *g_act = reinterpret_cast<const T *>(a.actions);
-
-    // ---- load state: 4 x 128-bit records + ep_return + F food records, all independent loads
-    Vec4<T> b0{0, 0, 0, 0}, b1{0, 0, 0, 0};
-    int4 c0 = make_int4(0, 0, 0, 0), c1 = make_int4(0, 0, 0, 0);
-    T ep_ret = 0;
-    T fx[F], fy[F];
-#pragma unroll
-    for (int f = 0; f < F; ++f) { fx[f] = 0; fy[f] = 0; }
-    if (valid) {
-        c0 = a.ctrl[e];
-        c1 = a.ctrl[(size_t)N + e];
-        b0 = g_body[e];
-        b1 = g_body[(size_t)N + e];
-        ep_ret = g_epret[e];
-#pragma unroll
-        for (int f = 0; f < F; ++f) {
-            const Vec2<T> v = g_food[(size_t)f * N + e];
-            fx[f] = v.x; fy[f] = v.y;
-        }
-    }
-    T px = b0.x, py = b0.y, vx = b0.z, vy = b0.w;
-    T angle = b1.x, omega = b1.y, nozzle = b1.z, wv = b1.w;
-    int phase = c0.x & 3, timer = (c0.x >> 2) & 0xff, exd = (c0.x >> 10) & 0xff;
-    int skind = (c0.x >> 18) & 3, stimer = (c0.x >> 20) & 0xff;
-    int steps_since_food = c0.y, food_collected = c0.z;
-    unsigned mask = (unsigned)c0.w;
-    unsigned cur_food = (unsigned)c1.x, cur_jit = (unsigned)c1.y;
-    int ep_len = c1.z, n_food = c1.w;
-
     const T W = (T)a.W, H = (T)a.H;
     const T diag = (T)a.diag;  // sqrt(W^2 + H^2), S:396, computed on the host in double
     const T invW = (T)a.inv_w, invH = (T)a.inv_h, invDiag = (T)a.inv_diag;  // used by the f32 build only
-    const unsigned trow = (a.rows == N) ? e : e % a.rows;
-    const uint32_t *jit_row = a.jit_words + (size_t)trow * a.jit_len;
 
-    for (int k = 0; k < a.K; ++k) {
-        // ---- where this thread's observation row goes
-        float *s_buf = nullptr;   // tile base (block or warp) in shared memory
-        float *row;
-        if constexpr (STORE == kStoreDirect) {
-            row = a.obs + ((size_t)k * N + (valid ? e : (unsigned)a.first)) * OBS;
-        } else if constexpr (STORE == kStoreTmaBlock) {
-            s_buf = s_tile + (size_t)(k & 1) * BLOCK * OBS;
-            row = s_buf + (size_t)tid * OBS;
-            if (k >= 2) {  // the bulk store issued two substeps ago must have finished reading s_buf
-                if (tid == 0) bulk_wait_read<1>();
-                __syncthreads();
-            }
-        } else {
-            const int nbuf = (STORE == kStoreTmaWarp) ? 2 : 1;
-            s_buf = s_tile + ((size_t)(tid >> 5) * nbuf + (STORE == kStoreTmaWarp ? (k & 1) : 0)) * 32 * OBS;
-            row = s_buf + (size_t)lane * OBS;
-            if constexpr (STORE == kStoreTmaWarp) {
-                if (k >= 2) { if (lane == 0) bulk_wait_read<1>(); __syncwarp(); }
-            } else if (k >= 1) __syncwarp();  // previous substep's cooperative copy has read the tile
-        }
-        // ---- does this step fire the jet?  (exhaling, and 0.1 <= (timer+1)/D <= 0.5, R:231-250.)
-        //      Known before anything else is computed, so the jitter word load is issued first.
-        const int t1 = timer + 1;
-        const bool thrust = (phase == kPhaseExhale) && (t1 <= exd) && (10 * t1 >= exd) && (2 * t1 <= exd);
-        uint2 jw = make_uint2(0u, 0u);
-        if (thrust) jw = *reinterpret_cast<const uint2 *>(jit_row + (cur_jit & a.jit_len_mask));
-        // ---- action (R:121-135)
-        T act0 = 0, act1 = 0;
-        if (valid) {
-            if (a.act_dim == 1) act0 = g_act[(size_t)k * N + e];
-            else {
-                const Vec2<T> v = reinterpret_cast<const Vec2<T> *>(g_act)[(size_t)k * N + e];
-                act0 = v.x; act1 = v.y;
-            }
-        }
-        bool inhaling;
-        T dir;
-        if (a.forced) {  // R:158-167: (timer % 330) < 120; timer <= 151 so the modulo is the identity
-            dir = act0;
-            inhaling = timer < kc::INHALE_DUR;
-        } else {
-            inhaling = act0 > (T)0.5;
-            dir = act1;
-        }
-        // ---- nozzle slew (R:169-182)
-        {
-            const T target = dir * (T)kc::MAX_NOZZLE;
-            const T diff = target - nozzle;
-            if (abs_(diff) > (T)kc::NOZZLE_RATE) nozzle = (diff > 0) ? nozzle + (T)kc::NOZZLE_RATE : nozzle - (T)kc::NOZZLE_RATE;
-            else nozzle = target;
-            nozzle = pymax<T>((T)(-kc::MAX_NOZZLE), pymin<T>((T)kc::MAX_NOZZLE, nozzle));
-        }
-        // ---- breathing FSM on integers (R:184-259); thresholds 0.1<=t/D<=0.5 and t/D<=1 are
-        //      exact integer compares (margins >= 1/(10*150) >> ulp), see tests/test_fsm_invariants.py
-        int wv_mode = 0;  // 0 keep, 1 wv=p, 2 wv=max(0,wv*(1-p)), 3 wv=0
-        if (phase == kPhaseRest) {
-            skind = kShapeRest;
-            if (inhaling) { phase = kPhaseInhale; timer = 0; }
-        } else if (phase == kPhaseInhale) {
-            if (inhaling && timer < kc::INHALE_DUR) {
-                ++timer; skind = kShapeInhale; stimer = timer; wv_mode = 1;
-            } else if (wv > (T)0.05) {
-                exd = a.exhale_lut[timer];
-                phase = kPhaseExhale; timer = 0;
-            } else { phase = kPhaseRest; timer = 0; wv_mode = 3; }
-        } else {
-            ++timer;
-            if (timer <= exd) { skind = kShapeExhale; stimer = timer; wv_mode = 2; }
-            else { phase = kPhaseRest; timer = 0; wv_mode = 3; }
-        }
-        // ---- ellipse axes from the shape fields (R:190-191, 207-213, 240-246)
-        T ea, eb, prog = 0;
-        if (skind == kShapeReset) { ea = (T)kc::BASE_R; eb = (T)kc::BASE_R; }
-        else if (skind == kShapeRest) { ea = (T)kc::A_REST; eb = (T)kc::B_REST; }
-        else {
-            const bool inh = (skind == kShapeInhale);
-            prog = (T)stimer / (T)(inh ? kc::INHALE_DUR : exd);
-            const T sa = inh ? (T)kc::A_REST : (T)kc::A_FULL, sb = inh ? (T)kc::B_REST : (T)kc::B_FULL;
-            const T da = inh ? (T)(kc::A_FULL - kc::A_REST) : (T)(kc::A_REST - kc::A_FULL);
-            const T db = inh ? (T)(kc::B_FULL - kc::B_REST) : (T)(kc::B_REST - kc::B_FULL);
-            ea = sa + da * prog; eb = sb + db * prog;
-        }
-        const T radius = pymax<T>(ea, eb);
-        if (wv_mode == 1) wv = prog;
-        // ---- jet thrust through the steerable nozzle (R:261-314)
-        if (thrust) {
-            const T Tm = (T)100.0 * wv * (T)0.4;
-            const T th = angle - nozzle;
-            T s0, c0_;
-            sincos_(th, &s0, &c0_);
-            vx += (c0_ * Tm) * (T)0.012;
-            vy += (s0 * Tm) * (T)0.012;
-            const T primary = -nozzle * Tm * (T)0.0002;
-            const T arm = radius * (T)0.7;
-            const T perp = Tm * sin_(-nozzle);
-            const T moment = perp * arm * (T)0.00005;
-            const T shape = -nozzle * Tm * wv * (T)0.00003;
-            omega += primary + moment + shape;
-            const T sm = Tm * abs_(nozzle) * (T)0.3;
-            T s1, c1_;
-            if constexpr (is_f64<T>::value) sincos_(th + (T)kc::HALF_PI, &s1, &c1_);
-            else { s1 = c0_; c1_ = -s0; }  // cos(x+pi/2) = -sin x, sin(x+pi/2) = cos x
-            vx += (c1_ * sm) * (T)0.008;
-            vy += (s1 * sm) * (T)0.008;
-            cur_jit += 2;
-            const T u = (T)res53(jw.x, jw.y);  // np.random.random(), R:311
-            const T dn = (u - (T)0.5) * (T)0.05;
-            const T nf = Tm * (T)0.04;
-            T s2, c2;
-            if constexpr (is_f64<T>::value) sincos_(th + dn, &s2, &c2);
-            else {  // sin/cos(th + dn) by angle addition; |dn| <= 0.025 so the series error is < 1e-13
-                const T d2 = dn * dn;
-                const T sd = dn * ((T)1.0 - d2 * ((T)(1.0 / 6.0) - d2 * (T)(1.0 / 120.0)));
-                const T cd = (T)1.0 - d2 * ((T)0.5 - d2 * (T)(1.0 / 24.0));
-                s2 = s0 * cd + c0_ * sd;
-                c2 = c0_ * cd - s0 * sd;
-            }
-            vx += c2 * nf * (T)0.002;
-            vy += s2 * nf * (T)0.002;
-        }
-        if (wv_mode == 2) { const T w2 = wv * ((T)1.0 - prog); wv = (w2 > 0) ? w2 : (T)0; }
-        else if (wv_mode == 3) wv = 0;
-        // ---- drag, integrate, wrap, wall bounce (R:316-352)
-        vx *= (T)0.98; vy *= (T)0.98; omega *= (T)0.95;
-        px += vx; py += vy;
-        angle = wrap_pi<T>(angle + omega);
-        {
-            const T margin = (T)kc::TANK_MARGIN + radius;
-            if (px < margin) { px = margin; vx = abs_(vx) * (T)0.4; omega *= (T)0.7; }
-            else if (px > W - margin) { px = W - margin; vx = -abs_(vx) * (T)0.4; omega *= (T)0.7; }
-            if (py < margin) { py = margin; vy = abs_(vy) * (T)0.4; omega *= (T)0.7; }
-            else if (py > H - margin) { py = H - margin; vy = -abs_(vy) * (T)0.4; omega *= (T)0.7; }
-        }
-        // ---- food distances (shared by hit test S:204-217, reward S:350-364 and obs S:375-379)
-        T dx[F], dy[F], dd[F];
-#pragma unroll
-        for (int f = 0; f < F; ++f) {
-            dx[f] = fx[f] - px; dy[f] = fy[f] - py;
-            dd[f] = sqrt_(dx[f] * dx[f] + dy[f] * dy[f]);
-        }
-        bool hit = false;
-        {
-            const T reach = radius + (T)kc::FOOD_R;
-#pragma unroll
-            for (int f = 0; f < F; ++f)
-                if (!hit && ((mask >> f) & 1u) && dd[f] < reach) { hit = true; mask &= ~(1u << f); }
-        }
-        // ---- wall contact (S:219-230), rounding-critical: same operands/order as the reference
-        const bool collision = (px - radius <= (T)kc::TANK_MARGIN) || (px + radius >= W - (T)kc::TANK_MARGIN) ||
-                               (py - radius <= (T)kc::TANK_MARGIN) || (py + radius >= H - (T)kc::TANK_MARGIN);
-        // ---- reward (S:278-327)
-        T reward = 0;
-        if (hit) {
-            reward += (T)a.food_reward;
-            if (a.efficiency_bonus > 0) reward += (T)a.efficiency_bonus * (T)(a.max_steps - steps_since_food);
-        }
-        if (collision) reward += (T)a.collision_penalty;
-        // nearest live food (strict <, first index wins: S:350-364).  Its bearing is used by the
-        // alignment reward AND, when no food was eaten this step, is the first observation entry.
-        bool any_food = false;
-        T near_d = 0, near_x = 0, near_y = 0, near_rel = 0;
+    // ---- PF: persistent CTAs; the state records of the CTA's next tile are copied global->shared
+    //      with cp.async (each thread fetches exactly the records it will read itself, so no CTA
+    //      barrier is needed) while the current tile is being integrated.
+    constexpr unsigned kOffC0 = 0, kOffC1 = kOffC0 + 16 * BLOCK, kOffB0 = kOffC1 + 16 * BLOCK;
+    constexpr unsigned kOffB1 = kOffB0 + sizeof(Vec4<T>) * BLOCK, kOffFood = kOffB1 + sizeof(Vec4<T>) * BLOCK;
+    constexpr unsigned kOffEp = kOffFood + sizeof(Vec2<T>) * F * BLOCK, kOffAct = kOffEp + sizeof(T) * BLOCK;
+    constexpr unsigned kStageBytes = kOffAct + 2 * sizeof(T) * BLOCK;
+    unsigned char *s_stage = reinterpret_cast<unsigned char *>(s_tile) + stage_offset_bytes<STORE, BLOCK>(OBS);
+    auto stage_issue = [&](unsigned t, int buf) {
+        const unsigned pe = (unsigned)a.first + t * BLOCK + tid;
+        if (pe >= end) return;
+        unsigned char *sb = s_stage + (size_t)buf * kStageBytes;
+        cp_async<16>(sb + kOffC0 + 16 * tid, a.ctrl + pe);
+        cp_async<16>(sb + kOffC1 + 16 * tid, a.ctrl + (size_t)N + pe);
+        cp_async<sizeof(Vec4<T>)>(sb + kOffB0 + sizeof(Vec4<T>) * tid, g_body + pe);
+        cp_async<sizeof(Vec4<T>)>(sb + kOffB1 + sizeof(Vec4<T>) * tid, g_body + (size_t)N + pe);
 #pragma unroll
         for (int f = 0; f < F; ++f)
-            if (((mask >> f) & 1u) && (!any_food || dd[f] < near_d)) { any_food = true; near_d = dd[f]; near_x = dx[f]; near_y = dy[f]; }
-        if (any_food && (a.proximity_w > 0 || a.observed > 0)) near_rel = wrap_pi<T>(atan2_(near_y, near_x) - angle);
-        if (a.proximity_w > 0 && any_food) reward += (T)a.proximity_w * cos_(near_rel);
-        reward += (T)a.time_penalty;
-        // ---- counters, respawn (S:171-180)
-        ++steps_since_food;
-        if (hit) {
-            ++food_collected;
-            steps_since_food = 0;
-            if (a.respawn) {
-                const RespawnResult<T> r = respawn_slow<T>(a, e, px, py, mask, n_food, cur_food);
-                mask = r.mask; cur_food = r.cur;
-#pragma unroll
-                for (int f = 0; f < F; ++f)
-                    if (f == r.slot) {
-                        fx[f] = r.x; fy[f] = r.y;
-                        dx[f] = r.x - px; dy[f] = r.y - py;
-                        dd[f] = sqrt_(dx[f] * dx[f] + dy[f] * dy[f]);
-                    }
-            }
-        }
-        // ---- termination (S:182-189): collision > timeout > all collected
-        bool terminated = false, truncated = false;
-        if (collision) terminated = true;
-        else if (steps_since_food > a.max_steps) truncated = true;
-        else if (!a.respawn && mask == 0u) terminated = true;
-        if (!valid) { terminated = false; truncated = false; }
-        ep_ret += reward;
-        ++ep_len;
-
-        // ---- observation (R:377-388 + S:366-428), assembled in registers, written as 128-bit rows
-        float4 v0, v1;
-        float o8, o9;
-        if constexpr (is_f64<T>::value) { v0.x = (float)(px / W); v0.y = (float)(py / H); }
-        else { v0.x = px * invW; v0.y = py * invH; }
-        v0.z = (float)divc<T>(vx, 5.0); v0.w = (float)divc<T>(vy, 5.0);
-        v1.x = (float)divc<T>(angle, kc::PI); v1.y = (float)divc<T>(omega, 0.1);
-        v1.z = (float)divc<T>(radius, kc::BASE_R);
-        v1.w = (float)((T)phase / (T)2.0);
-        o8 = (float)wv;
-        o9 = (float)divc<T>(nozzle, kc::MAX_NOZZLE);
-        const int n_live = __popc(mask);
-        // The MU nearest live foods in order (stable: equal distances keep slot order, S:382) and the
-        // mean distance (S:419).
-        constexpr int MU = (MT < F) ? MT : F;  // entries that can ever be real
-        T top_d[MU], top_x[MU], top_y[MU];
-        T dist_sum = 0;
-        if constexpr (F == 1) {
-            top_d[0] = dd[0]; top_x[0] = dx[0]; top_y[0] = dy[0];
-            dist_sum = dd[0];
-        } else if constexpr (is_f64<T>::value) {
-            // validation build: full sorting network on (distance, slot) so that the mean is summed
-            // in sorted order exactly like sum() over the sorted list
-            int id[F];
-#pragma unroll
-            for (int f = 0; f < F; ++f) {
-                id[f] = f;
-                if (!((mask >> f) & 1u)) dd[f] = (T)CUDART_INF;
-            }
-#define SALP_CE(i, j)                                                                          \
-    {                                                                                          \
-        const bool sw = (dd[j] < dd[i]) || (dd[j] == dd[i] && id[j] < id[i]);                  \
-        const T t0 = sw ? dd[j] : dd[i], t1_ = sw ? dd[i] : dd[j];                             \
-        const int u0 = sw ? id[j] : id[i], u1 = sw ? id[i] : id[j];                            \
-        dd[i] = t0; dd[j] = t1_; id[i] = u0; id[j] = u1;                                       \
+            cp_async<sizeof(Vec2<T>)>(sb + kOffFood + sizeof(Vec2<T>) * (f * BLOCK + tid), g_food + (size_t)f * N + pe);
+        cp_async<sizeof(T)>(sb + kOffEp + sizeof(T) * tid, g_epret + pe);
+        if (a.act_dim == 1) cp_async<sizeof(T)>(sb + kOffAct + sizeof(T) * tid, g_act + pe);
+        else cp_async<2 * sizeof(T)>(sb + kOffAct + 2 * sizeof(T) * tid, g_act + 2 * (size_t)pe);
+    };
+    if constexpr (PF) {
+        if (blockIdx.x < ntiles) { stage_issue(blockIdx.x, 0); cp_async_commit(); }
     }
-            if constexpr (F == 2) { SALP_SORTNET_2(SALP_CE) }
-            else if constexpr (F == 4) { SALP_SORTNET_4(SALP_CE) }
-            else if constexpr (F == 8) { SALP_SORTNET_8(SALP_CE) }
-            else if constexpr (F == 12) { SALP_SORTNET_12(SALP_CE) }
-            else if constexpr (F == 16) { SALP_SORTNET_16(SALP_CE) }
-            else if constexpr (F == 32) { SALP_SORTNET_32(SALP_CE) }
-#undef SALP_CE
-#pragma unroll
-            for (int f = 0; f < F; ++f)
-                if (f < n_live) dist_sum = dist_sum + dd[f];
-#pragma unroll
-            for (int i = 0; i < MU; ++i) {
-                T sx = 0, sy = 0;
-#pragma unroll
-                for (int f = 0; f < F; ++f)
-                    if (id[i] == f) { sx = dx[f]; sy = dy[f]; }
-                top_d[i] = dd[i]; top_x[i] = sx; top_y[i] = sy;
-            }
-        } else {
-            // throughput build: only the MU nearest are needed -> insertion of every food into a
-            // sorted MU-list of (distance, slot).  Strict < keeps equal distances in slot order
-            // (foods arrive in slot order), i.e. the stable order of list.sort(); the mean is summed
-            // in slot order (differs from the sorted-order sum by rounding only).
-            T kd[MU];
-            int ki[MU];
-#pragma unroll
-            for (int i = 0; i < MU; ++i) { kd[i] = (T)CUDART_INF_F; ki[i] = F; }
-#pragma unroll
-            for (int f = 0; f < F; ++f) {
-                const bool alive = (mask >> f) & 1u;
-                if (alive) dist_sum += dd[f];
-                T cd = alive ? dd[f] : (T)CUDART_INF_F;
-                int ci = alive ? f : F;
-#pragma unroll
-                for (int i = 0; i < MU; ++i) {
-                    const bool lt = cd < kd[i];
-                    const T lo_d = lt ? cd : kd[i], hi_d = lt ? kd[i] : cd;
-                    const int lo_i = lt ? ci : ki[i], hi_i = lt ? ki[i] : ci;
-                    kd[i] = lo_d; ki[i] = lo_i; cd = hi_d; ci = hi_i;
-                }
-            }
-#pragma unroll
-            for (int i = 0; i < MU; ++i) {
-                T sx = 0, sy = 0;
-#pragma unroll
-                for (int f = 0; f < F; ++f)
-                    if (ki[i] == f) { sx = dx[f]; sy = dy[f]; }
-                top_d[i] = kd[i]; top_x[i] = sx; top_y[i] = sy;
-            }
-        }
-        // i-th nearest live food -> [dx/W, dy/H, d/diag, wrap(atan2(dy,dx) - angle)/pi]; S:412 padding [0,0,1,0]
-        auto food_entry = [&](int i) -> float4 {
-            float4 q = make_float4(0.f, 0.f, 1.f, 0.f);
-            if (i < MU && i < n_live) {
-                const int j = i < MU ? i : 0;
-                const T sx = top_x[j], sy = top_y[j], sd = top_d[j];
-                // entry 0 is the nearest food: its bearing was already computed for the reward unless
-                // a food was eaten (and possibly respawned) after that
-                T rel;
-                if (i == 0) rel = hit ? wrap_pi<T>(atan2_(sy, sx) - angle) : near_rel;
-                else rel = wrap_pi<T>(atan2_(sy, sx) - angle);
-                if constexpr (is_f64<T>::value) { q.x = (float)(sx / W); q.y = (float)(sy / H); q.z = (float)(sd / diag); }
-                else { q.x = sx * invW; q.y = sy * invH; q.z = sd * invDiag; }
-                q.w = (float)divc<T>(rel, kc::PI);
-            }
-            return q;
-        };
-        float cnt, avg = 1.f;
-        cnt = (float)pymin<T>((T)n_live / (T)10.0, (T)1.0);
-        if (n_live > 0) {
-            const T mean = dist_sum / (T)n_live;
-            if constexpr (is_f64<T>::value) avg = (float)(mean / diag);
-            else avg = mean * invDiag;
-        }
-        const bool write_row = (STORE != kStoreDirect) || valid;
-        if (write_row) {
-            float4 *r4 = reinterpret_cast<float4 *>(row);
-            r4[0] = v0; r4[1] = v1;
-            if constexpr (MT == 3) {
-                const float4 e0 = food_entry(0), e1 = food_entry(1), e2 = food_entry(2);
-                r4[2] = make_float4(o8, o9, e0.x, e0.y);
-                r4[3] = make_float4(e0.z, e0.w, e1.x, e1.y);
-                r4[4] = make_float4(e1.z, e1.w, e2.x, e2.y);
-                r4[5] = make_float4(e2.z, e2.w, cnt, avg);
-            } else {
-                float2 *r2 = reinterpret_cast<float2 *>(row);
-                r2[4] = make_float2(o8, o9);
-#pragma unroll
-                for (int i = 0; i < MT; ++i)
-                    if (i < a.observed) {
-                        const float4 q = food_entry(i);
-                        r2[5 + 2 * i] = make_float2(q.x, q.y);
-                        r2[6 + 2 * i] = make_float2(q.z, q.w);
-                    }
-                r2[5 + 2 * a.observed] = make_float2(cnt, avg);
-            }
-        }
 
-        // ---- per-step outputs
-        const bool done = terminated || truncated;
-        if (valid) {
-            const size_t oi = (size_t)k * N + e;
-            g_reward[oi] = reward;
-            a.terminated[oi] = terminated ? 1 : 0;
-            a.truncated[oi] = truncated ? 1 : 0;
-            if (a.events) a.events[oi] = (uint8_t)((terminated ? 1 : 0) | (truncated ? 2 : 0) | (collision ? 4 : 0) | (hit ? 8 : 0));
-        }
-        // ---- episode statistics: warp-shuffle reduction, only in warps where an episode ended
-        const unsigned done_mask = __ballot_sync(0xffffffffu, done);
-        if (done_mask != 0u) {
-            if (a.stats) {
-                const double r = warp_sum(done ? (double)ep_ret : 0.0);
-                const double l = warp_sum(done ? (double)ep_len : 0.0);
-                const double fc = warp_sum(done ? (double)food_collected : 0.0);
-                const unsigned coll_mask = __ballot_sync(0xffffffffu, done && collision);
-                const unsigned trunc_mask = __ballot_sync(0xffffffffu, done && truncated);
-                const unsigned bad_mask = __ballot_sync(0xffffffffu, done && !(isfinite((double)px) && isfinite((double)py)));
-                if (lane == 0) {
-                    atomicAdd(a.stats + 0, (double)__popc(done_mask));
-                    atomicAdd(a.stats + 1, r);
-                    atomicAdd(a.stats + 2, l);
-                    atomicAdd(a.stats + 3, fc);
-                    if (coll_mask) atomicAdd(a.stats + 4, (double)__popc(coll_mask));
-                    if (trunc_mask) atomicAdd(a.stats + 5, (double)__popc(trunc_mask));
-                    if (bad_mask) atomicAdd(a.stats + 6, (double)__popc(bad_mask));
-                }
-            }
-            if (done && a.final_info)
-                reinterpret_cast<Vec4<T> *>(a.final_info)[(size_t)k * N + e] =
-                    Vec4<T>{ep_ret, (T)ep_len, (T)food_collected, (T)steps_since_food};
-            if (done && a.autoreset) {
-                if (a.final_obs) {  // terminal observation (gymnasium "final_observation")
-                    float4 *dst = reinterpret_cast<float4 *>(a.final_obs + ((size_t)k * N + e) * OBS);
-                    for (int j = 0; j < OBS / 4; ++j) dst[j] = *reinterpret_cast<const float4 *>(row + 4 * j);
-                }
-                const ResetResult rr = reset_slow<T>(a, e, cur_food, row);
-                cur_food = rr.cur; mask = rr.mask; n_food = rr.n_food;
-                // R:95-117 deterministic robot reset, S:139-141 counters
-                px = W / 2; py = H / 2; vx = 0; vy = 0; angle = 0; omega = 0; nozzle = 0; wv = 0;
-                phase = kPhaseRest; timer = 0; skind = kShapeReset; stimer = 0;
-                steps_since_food = 0; food_collected = 0; ep_ret = 0; ep_len = 0;
-#pragma unroll
+    unsigned gk = 0;  // substeps this CTA has published so far (obs tile double-buffer parity)
+    unsigned it = 0;
+    for (unsigned tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+        const unsigned blk0 = (unsigned)a.first + tile * BLOCK;
+        const unsigned e = blk0 + tid;
+        const bool valid = e < end;
+
+        // ---- load state: 4 x 128-bit records + ep_return + F food records, all independent loads
+        Vec4<T> b0{0, 0, 0, 0}, b1{0, 0, 0, 0};
+        int4 c0 = make_int4(0, 0, 0, 0), c1 = make_int4(0, 0, 0, 0);
+        T ep_ret = 0;
+        T fx[F], fy[F];
+    #pragma unroll
+        for (int f = 0; f < F; ++f) { fx[f] = 0; fy[f] = 0; }
+        if constexpr (PF) {
+            // prefetch the NEXT tile of this CTA while this one is computed, then wait for this one
+            const unsigned nxt = tile + gridDim.x;
+            if (nxt < ntiles) { stage_issue(nxt, (it + 1) & 1); cp_async_commit(); cp_async_wait<1>(); }
+            else cp_async_wait<0>();
+            const unsigned char *sb = s_stage + (size_t)(it & 1) * kStageBytes;
+            if (valid) {
+                c0 = reinterpret_cast<const int4 *>(sb + kOffC0)[tid];
+                c1 = reinterpret_cast<const int4 *>(sb + kOffC1)[tid];
+                b0 = reinterpret_cast<const Vec4<T> *>(sb + kOffB0)[tid];
+                b1 = reinterpret_cast<const Vec4<T> *>(sb + kOffB1)[tid];
+                ep_ret = reinterpret_cast<const T *>(sb + kOffEp)[tid];
+    #pragma unroll
                 for (int f = 0; f < F; ++f) {
-                    if (f < n_food) {
-                        const Vec2<T> v = g_food[(size_t)f * N + e];
-                        fx[f] = v.x; fy[f] = v.y;
+                    const Vec2<T> v = reinterpret_cast<const Vec2<T> *>(sb + kOffFood)[f * BLOCK + tid];
+                    fx[f] = v.x; fy[f] = v.y;
+                }
+            }
+        } else if (valid) {
+            c0 = a.ctrl[e];
+            c1 = a.ctrl[(size_t)N + e];
+            b0 = g_body[e];
+            b1 = g_body[(size_t)N + e];
+            ep_ret = g_epret[e];
+    #pragma unroll
+            for (int f = 0; f < F; ++f) {
+                const Vec2<T> v = g_food[(size_t)f * N + e];
+                fx[f] = v.x; fy[f] = v.y;
+            }
+        }
+        T px = b0.x, py = b0.y, vx = b0.z, vy = b0.w;
+        T angle = b1.x, omega = b1.y, nozzle = b1.z, wv = b1.w;
+        int phase = c0.x & 3, timer = (c0.x >> 2) & 0xff, exd = (c0.x >> 10) & 0xff;
+        int skind = (c0.x >> 18) & 3, stimer = (c0.x >> 20) & 0xff;
+        int steps_since_food = c0.y, food_collected = c0.z;
+        unsigned mask = (unsigned)c0.w;
+        unsigned cur_food = (unsigned)c1.x, cur_jit = (unsigned)c1.y;
+        int ep_len = c1.z, n_food = c1.w;
+
+        const unsigned trow = (a.rows == N) ? e : e % a.rows;
+        const uint32_t *jit_row = a.jit_words + (size_t)trow * a.jit_len;
+
+        for (int k = 0; k < a.K; ++k, ++gk) {
+            // ---- where this thread's observation row goes
+            float *s_buf = nullptr;   // tile base (block or warp) in shared memory
+            float *row;
+            if constexpr (STORE == kStoreDirect) {
+                row = a.obs + ((size_t)k * N + (valid ? e : (unsigned)a.first)) * OBS;
+            } else if constexpr (STORE == kStoreTmaBlock) {
+                s_buf = s_tile + (size_t)(gk & 1) * BLOCK * OBS;
+                row = s_buf + (size_t)tid * OBS;
+                if (gk >= 2) {  // the bulk store issued two substeps ago must have finished reading s_buf
+                    if (tid == 0) bulk_wait_read<1>();
+                    __syncthreads();
+                }
+            } else {
+                const int nbuf = (STORE == kStoreTmaWarp) ? 2 : 1;
+                s_buf = s_tile + ((size_t)(tid >> 5) * nbuf + (STORE == kStoreTmaWarp ? (gk & 1) : 0)) * 32 * OBS;
+                row = s_buf + (size_t)lane * OBS;
+                if constexpr (STORE == kStoreTmaWarp) {
+                    if (gk >= 2) { if (lane == 0) bulk_wait_read<1>(); __syncwarp(); }
+                } else if (gk >= 1) __syncwarp();  // previous substep's cooperative copy has read the tile
+            }
+            // ---- does this step fire the jet?  (exhaling, and 0.1 <= (timer+1)/D <= 0.5, R:231-250.)
+            //      Known before anything else is computed, so the jitter word load is issued first.
+            const int t1 = timer + 1;
+            const bool thrust = (phase == kPhaseExhale) && (t1 <= exd) && (10 * t1 >= exd) && (2 * t1 <= exd);
+            uint2 jw = make_uint2(0u, 0u);
+#ifndef SALP_LAB_NOJIT
+            if (thrust) jw = *reinterpret_cast<const uint2 *>(jit_row + (cur_jit & a.jit_len_mask));
+#endif
+            // ---- action (R:121-135)
+            T act0 = 0, act1 = 0;
+            if (PF && k == 0) {
+                const T *sa = reinterpret_cast<const T *>(s_stage + (size_t)(it & 1) * kStageBytes + kOffAct);
+                if (valid) {
+                    if (a.act_dim == 1) act0 = sa[tid];
+                    else { act0 = sa[2 * tid]; act1 = sa[2 * tid + 1]; }
+                }
+            } else if (valid) {
+                if (a.act_dim == 1) act0 = g_act[(size_t)k * N + e];
+                else {
+                    const Vec2<T> v = reinterpret_cast<const Vec2<T> *>(g_act)[(size_t)k * N + e];
+                    act0 = v.x; act1 = v.y;
+                }
+            }
+#ifdef SALP_LAB_SKELETON  // tools/kernel_lab.cu only: memory skeleton of the step (no model arithmetic)
+            const T radius = (T)30; const bool hit = false, collision = false; const T near_rel = 0;
+            const bool terminated = false, truncated = false;
+            px += act0 * (T)0.001 + (T)jw.x * (T)1e-12; T reward = act0 + act1;
+            T dx[F], dy[F], dd[F];
+#pragma unroll
+            for (int f = 0; f < F; ++f) { dx[f] = fx[f] - px; dy[f] = fy[f] - py; dd[f] = dx[f] + dy[f]; }
+#else
+            bool inhaling;
+            T dir;
+            if (a.forced) {  // R:158-167: (timer % 330) < 120; timer <= 151 so the modulo is the identity
+                dir = act0;
+                inhaling = timer < kc::INHALE_DUR;
+            } else {
+                inhaling = act0 > (T)0.5;
+                dir = act1;
+            }
+            // ---- nozzle slew (R:169-182)
+            {
+                const T target = dir * (T)kc::MAX_NOZZLE;
+                const T diff = target - nozzle;
+                if (abs_(diff) > (T)kc::NOZZLE_RATE) nozzle = (diff > 0) ? nozzle + (T)kc::NOZZLE_RATE : nozzle - (T)kc::NOZZLE_RATE;
+                else nozzle = target;
+                nozzle = pymax<T>((T)(-kc::MAX_NOZZLE), pymin<T>((T)kc::MAX_NOZZLE, nozzle));
+            }
+            // ---- breathing FSM on integers (R:184-259); thresholds 0.1<=t/D<=0.5 and t/D<=1 are
+            //      exact integer compares (margins >= 1/(10*150) >> ulp), see tests/test_fsm_invariants.py
+            int wv_mode = 0;  // 0 keep, 1 wv=p, 2 wv=max(0,wv*(1-p)), 3 wv=0
+            if (phase == kPhaseRest) {
+                skind = kShapeRest;
+                if (inhaling) { phase = kPhaseInhale; timer = 0; }
+            } else if (phase == kPhaseInhale) {
+                if (inhaling && timer < kc::INHALE_DUR) {
+                    ++timer; skind = kShapeInhale; stimer = timer; wv_mode = 1;
+                } else if (wv > (T)0.05) {
+                    exd = a.exhale_lut[timer];
+                    phase = kPhaseExhale; timer = 0;
+                } else { phase = kPhaseRest; timer = 0; wv_mode = 3; }
+            } else {
+                ++timer;
+                if (timer <= exd) { skind = kShapeExhale; stimer = timer; wv_mode = 2; }
+                else { phase = kPhaseRest; timer = 0; wv_mode = 3; }
+            }
+            // ---- ellipse axes from the shape fields (R:190-191, 207-213, 240-246)
+            T ea, eb, prog = 0;
+            if (skind == kShapeReset) { ea = (T)kc::BASE_R; eb = (T)kc::BASE_R; }
+            else if (skind == kShapeRest) { ea = (T)kc::A_REST; eb = (T)kc::B_REST; }
+            else {
+                const bool inh = (skind == kShapeInhale);
+                prog = (T)stimer / (T)(inh ? kc::INHALE_DUR : exd);
+                const T sa = inh ? (T)kc::A_REST : (T)kc::A_FULL, sb = inh ? (T)kc::B_REST : (T)kc::B_FULL;
+                const T da = inh ? (T)(kc::A_FULL - kc::A_REST) : (T)(kc::A_REST - kc::A_FULL);
+                const T db = inh ? (T)(kc::B_FULL - kc::B_REST) : (T)(kc::B_REST - kc::B_FULL);
+                ea = sa + da * prog; eb = sb + db * prog;
+            }
+            const T radius = pymax<T>(ea, eb);
+            if (wv_mode == 1) wv = prog;
+            // ---- jet thrust through the steerable nozzle (R:261-314)
+            if (thrust) {
+                const T Tm = (T)100.0 * wv * (T)0.4;
+                const T th = angle - nozzle;
+                T s0, c0_;
+                sincos_(th, &s0, &c0_);
+                vx += (c0_ * Tm) * (T)0.012;
+                vy += (s0 * Tm) * (T)0.012;
+                const T primary = -nozzle * Tm * (T)0.0002;
+                const T arm = radius * (T)0.7;
+                const T perp = Tm * sin_(-nozzle);
+                const T moment = perp * arm * (T)0.00005;
+                const T shape = -nozzle * Tm * wv * (T)0.00003;
+                omega += primary + moment + shape;
+                const T sm = Tm * abs_(nozzle) * (T)0.3;
+                T s1, c1_;
+                if constexpr (is_f64<T>::value) sincos_(th + (T)kc::HALF_PI, &s1, &c1_);
+                else { s1 = c0_; c1_ = -s0; }  // cos(x+pi/2) = -sin x, sin(x+pi/2) = cos x
+                vx += (c1_ * sm) * (T)0.008;
+                vy += (s1 * sm) * (T)0.008;
+                cur_jit += 2;
+                const T u = (T)res53(jw.x, jw.y);  // np.random.random(), R:311
+                const T dn = (u - (T)0.5) * (T)0.05;
+                const T nf = Tm * (T)0.04;
+                T s2, c2;
+                if constexpr (is_f64<T>::value) sincos_(th + dn, &s2, &c2);
+                else {  // sin/cos(th + dn) by angle addition; |dn| <= 0.025 so the series error is < 1e-13
+                    const T d2 = dn * dn;
+                    const T sd = dn * ((T)1.0 - d2 * ((T)(1.0 / 6.0) - d2 * (T)(1.0 / 120.0)));
+                    const T cd = (T)1.0 - d2 * ((T)0.5 - d2 * (T)(1.0 / 24.0));
+                    s2 = s0 * cd + c0_ * sd;
+                    c2 = c0_ * cd - s0 * sd;
+                }
+                vx += c2 * nf * (T)0.002;
+                vy += s2 * nf * (T)0.002;
+            }
+            if (wv_mode == 2) { const T w2 = wv * ((T)1.0 - prog); wv = (w2 > 0) ? w2 : (T)0; }
+            else if (wv_mode == 3) wv = 0;
+            // ---- drag, integrate, wrap, wall bounce (R:316-352)
+            vx *= (T)0.98; vy *= (T)0.98; omega *= (T)0.95;
+            px += vx; py += vy;
+            angle = wrap_pi<T>(angle + omega);
+            {
+                const T margin = (T)kc::TANK_MARGIN + radius;
+                if (px < margin) { px = margin; vx = abs_(vx) * (T)0.4; omega *= (T)0.7; }
+                else if (px > W - margin) { px = W - margin; vx = -abs_(vx) * (T)0.4; omega *= (T)0.7; }
+                if (py < margin) { py = margin; vy = abs_(vy) * (T)0.4; omega *= (T)0.7; }
+                else if (py > H - margin) { py = H - margin; vy = -abs_(vy) * (T)0.4; omega *= (T)0.7; }
+            }
+            // ---- food distances (shared by hit test S:204-217, reward S:350-364 and obs S:375-379)
+            T dx[F], dy[F], dd[F];
+    #pragma unroll
+            for (int f = 0; f < F; ++f) {
+                dx[f] = fx[f] - px; dy[f] = fy[f] - py;
+                dd[f] = sqrt_(dx[f] * dx[f] + dy[f] * dy[f]);
+            }
+            bool hit = false;
+            {
+                const T reach = radius + (T)kc::FOOD_R;
+    #pragma unroll
+                for (int f = 0; f < F; ++f)
+                    if (!hit && ((mask >> f) & 1u) && dd[f] < reach) { hit = true; mask &= ~(1u << f); }
+            }
+            // ---- wall contact (S:219-230), rounding-critical: same operands/order as the reference
+            const bool collision = (px - radius <= (T)kc::TANK_MARGIN) || (px + radius >= W - (T)kc::TANK_MARGIN) ||
+                                   (py - radius <= (T)kc::TANK_MARGIN) || (py + radius >= H - (T)kc::TANK_MARGIN);
+            // ---- reward (S:278-327)
+            T reward = 0;
+            if (hit) {
+                reward += (T)a.food_reward;
+                if (a.efficiency_bonus > 0) reward += (T)a.efficiency_bonus * (T)(a.max_steps - steps_since_food);
+            }
+            if (collision) reward += (T)a.collision_penalty;
+            // nearest live food (strict <, first index wins: S:350-364).  Its bearing is used by the
+            // alignment reward AND, when no food was eaten this step, is the first observation entry.
+            bool any_food = false;
+            T near_d = 0, near_x = 0, near_y = 0, near_rel = 0;
+    #pragma unroll
+            for (int f = 0; f < F; ++f)
+                if (((mask >> f) & 1u) && (!any_food || dd[f] < near_d)) { any_food = true; near_d = dd[f]; near_x = dx[f]; near_y = dy[f]; }
+            if (any_food && (a.proximity_w > 0 || a.observed > 0)) near_rel = wrap_pi<T>(atan2_(near_y, near_x) - angle);
+            if (a.proximity_w > 0 && any_food) reward += (T)a.proximity_w * cos_(near_rel);
+            reward += (T)a.time_penalty;
+            // ---- counters, respawn (S:171-180)
+            ++steps_since_food;
+            if (hit) {
+                ++food_collected;
+                steps_since_food = 0;
+                if (a.respawn) {
+                    const RespawnResult<T> r = respawn_slow<T>(a, e, px, py, mask, n_food, cur_food);
+                    mask = r.mask; cur_food = r.cur;
+    #pragma unroll
+                    for (int f = 0; f < F; ++f)
+                        if (f == r.slot) {
+                            fx[f] = r.x; fy[f] = r.y;
+                            dx[f] = r.x - px; dy[f] = r.y - py;
+                            dd[f] = sqrt_(dx[f] * dx[f] + dy[f] * dy[f]);
+                        }
+                }
+            }
+            // ---- termination (S:182-189): collision > timeout > all collected
+            bool terminated = false, truncated = false;
+            if (collision) terminated = true;
+            else if (steps_since_food > a.max_steps) truncated = true;
+            else if (!a.respawn && mask == 0u) terminated = true;
+            if (!valid) { terminated = false; truncated = false; }
+#endif
+            ep_ret += reward;
+            ++ep_len;
+
+            // ---- observation (R:377-388 + S:366-428), assembled in registers, written as 128-bit rows
+            float4 v0, v1;
+            float o8, o9;
+            if constexpr (is_f64<T>::value) { v0.x = (float)(px / W); v0.y = (float)(py / H); }
+            else { v0.x = px * invW; v0.y = py * invH; }
+            v0.z = (float)divc<T>(vx, 5.0); v0.w = (float)divc<T>(vy, 5.0);
+            v1.x = (float)divc<T>(angle, kc::PI); v1.y = (float)divc<T>(omega, 0.1);
+            v1.z = (float)divc<T>(radius, kc::BASE_R);
+            v1.w = (float)((T)phase / (T)2.0);
+            o8 = (float)wv;
+            o9 = (float)divc<T>(nozzle, kc::MAX_NOZZLE);
+            const int n_live = __popc(mask);
+            // The MU nearest live foods in order (stable: equal distances keep slot order, S:382) and the
+            // mean distance (S:419).
+            constexpr int MU = (MT < F) ? MT : F;  // entries that can ever be real
+            T top_d[MU], top_x[MU], top_y[MU];
+            T dist_sum = 0;
+            if constexpr (F == 1) {
+                top_d[0] = dd[0]; top_x[0] = dx[0]; top_y[0] = dy[0];
+                dist_sum = dd[0];
+            } else if constexpr (is_f64<T>::value) {
+                // validation build: full sorting network on (distance, slot) so that the mean is summed
+                // in sorted order exactly like sum() over the sorted list
+                int id[F];
+    #pragma unroll
+                for (int f = 0; f < F; ++f) {
+                    id[f] = f;
+                    if (!((mask >> f) & 1u)) dd[f] = (T)CUDART_INF;
+                }
+    #define SALP_CE(i, j)                                                                          \
+        {                                                                                          \
+            const bool sw = (dd[j] < dd[i]) || (dd[j] == dd[i] && id[j] < id[i]);                  \
+            const T t0 = sw ? dd[j] : dd[i], t1_ = sw ? dd[i] : dd[j];                             \
+            const int u0 = sw ? id[j] : id[i], u1 = sw ? id[i] : id[j];                            \
+            dd[i] = t0; dd[j] = t1_; id[i] = u0; id[j] = u1;                                       \
+        }
+                if constexpr (F == 2) { SALP_SORTNET_2(SALP_CE) }
+                else if constexpr (F == 4) { SALP_SORTNET_4(SALP_CE) }
+                else if constexpr (F == 8) { SALP_SORTNET_8(SALP_CE) }
+                else if constexpr (F == 12) { SALP_SORTNET_12(SALP_CE) }
+                else if constexpr (F == 16) { SALP_SORTNET_16(SALP_CE) }
+                else if constexpr (F == 32) { SALP_SORTNET_32(SALP_CE) }
+    #undef SALP_CE
+    #pragma unroll
+                for (int f = 0; f < F; ++f)
+                    if (f < n_live) dist_sum = dist_sum + dd[f];
+    #pragma unroll
+                for (int i = 0; i < MU; ++i) {
+                    T sx = 0, sy = 0;
+    #pragma unroll
+                    for (int f = 0; f < F; ++f)
+                        if (id[i] == f) { sx = dx[f]; sy = dy[f]; }
+                    top_d[i] = dd[i]; top_x[i] = sx; top_y[i] = sy;
+                }
+            } else {
+                // throughput build: only the MU nearest are needed -> insertion of every food into a
+                // sorted MU-list of (distance, slot).  Strict < keeps equal distances in slot order
+                // (foods arrive in slot order), i.e. the stable order of list.sort(); the mean is summed
+                // in slot order (differs from the sorted-order sum by rounding only).
+                T kd[MU];
+                int ki[MU];
+    #pragma unroll
+                for (int i = 0; i < MU; ++i) { kd[i] = (T)CUDART_INF_F; ki[i] = F; }
+    #pragma unroll
+                for (int f = 0; f < F; ++f) {
+                    const bool alive = (mask >> f) & 1u;
+                    if (alive) dist_sum += dd[f];
+                    T cd = alive ? dd[f] : (T)CUDART_INF_F;
+                    int ci = alive ? f : F;
+    #pragma unroll
+                    for (int i = 0; i < MU; ++i) {
+                        const bool lt = cd < kd[i];
+                        const T lo_d = lt ? cd : kd[i], hi_d = lt ? kd[i] : cd;
+                        const int lo_i = lt ? ci : ki[i], hi_i = lt ? ki[i] : ci;
+                        kd[i] = lo_d; ki[i] = lo_i; cd = hi_d; ci = hi_i;
+                    }
+                }
+    #pragma unroll
+                for (int i = 0; i < MU; ++i) {
+                    T sx = 0, sy = 0;
+    #pragma unroll
+                    for (int f = 0; f < F; ++f)
+                        if (ki[i] == f) { sx = dx[f]; sy = dy[f]; }
+                    top_d[i] = kd[i]; top_x[i] = sx; top_y[i] = sy;
+                }
+            }
+            // i-th nearest live food -> [dx/W, dy/H, d/diag, wrap(atan2(dy,dx) - angle)/pi]; S:412 padding [0,0,1,0]
+            auto food_entry = [&](int i) -> float4 {
+                float4 q = make_float4(0.f, 0.f, 1.f, 0.f);
+                if (i < MU && i < n_live) {
+                    const int j = i < MU ? i : 0;
+                    const T sx = top_x[j], sy = top_y[j], sd = top_d[j];
+                    // entry 0 is the nearest food: its bearing was already computed for the reward unless
+                    // a food was eaten (and possibly respawned) after that
+                    T rel;
+                    if (i == 0) rel = hit ? wrap_pi<T>(atan2_(sy, sx) - angle) : near_rel;
+                    else rel = wrap_pi<T>(atan2_(sy, sx) - angle);
+                    if constexpr (is_f64<T>::value) { q.x = (float)(sx / W); q.y = (float)(sy / H); q.z = (float)(sd / diag); }
+                    else { q.x = sx * invW; q.y = sy * invH; q.z = sd * invDiag; }
+                    q.w = (float)divc<T>(rel, kc::PI);
+                }
+                return q;
+            };
+            float cnt, avg = 1.f;
+            cnt = (float)pymin<T>((T)n_live / (T)10.0, (T)1.0);
+            if (n_live > 0) {
+                const T mean = dist_sum / (T)n_live;
+                if constexpr (is_f64<T>::value) avg = (float)(mean / diag);
+                else avg = mean * invDiag;
+            }
+            const bool write_row = (STORE != kStoreDirect) || valid;
+            if (write_row) {
+                float4 *r4 = reinterpret_cast<float4 *>(row);
+                r4[0] = v0; r4[1] = v1;
+                if constexpr (MT == 3) {
+                    const float4 e0 = food_entry(0), e1 = food_entry(1), e2 = food_entry(2);
+                    r4[2] = make_float4(o8, o9, e0.x, e0.y);
+                    r4[3] = make_float4(e0.z, e0.w, e1.x, e1.y);
+                    r4[4] = make_float4(e1.z, e1.w, e2.x, e2.y);
+                    r4[5] = make_float4(e2.z, e2.w, cnt, avg);
+                } else {
+                    float2 *r2 = reinterpret_cast<float2 *>(row);
+                    r2[4] = make_float2(o8, o9);
+    #pragma unroll
+                    for (int i = 0; i < MT; ++i)
+                        if (i < a.observed) {
+                            const float4 q = food_entry(i);
+                            r2[5 + 2 * i] = make_float2(q.x, q.y);
+                            r2[6 + 2 * i] = make_float2(q.z, q.w);
+                        }
+                    r2[5 + 2 * a.observed] = make_float2(cnt, avg);
+                }
+            }
+
+            // ---- per-step outputs
+            const bool done = terminated || truncated;
+            if (valid) {
+                const size_t oi = (size_t)k * N + e;
+                g_reward[oi] = reward;
+                a.terminated[oi] = terminated ? 1 : 0;
+                a.truncated[oi] = truncated ? 1 : 0;
+                if (a.events) a.events[oi] = (uint8_t)((terminated ? 1 : 0) | (truncated ? 2 : 0) | (collision ? 4 : 0) | (hit ? 8 : 0));
+            }
+            // ---- episode statistics: warp-shuffle reduction, only in warps where an episode ended
+            const unsigned done_mask = __ballot_sync(0xffffffffu, done);
+            if (done_mask != 0u) {
+                if (a.stats) {
+                    const double r = warp_sum(done ? (double)ep_ret : 0.0);
+                    const double l = warp_sum(done ? (double)ep_len : 0.0);
+                    const double fc = warp_sum(done ? (double)food_collected : 0.0);
+                    const unsigned coll_mask = __ballot_sync(0xffffffffu, done && collision);
+                    const unsigned trunc_mask = __ballot_sync(0xffffffffu, done && truncated);
+                    const unsigned bad_mask = __ballot_sync(0xffffffffu, done && !(isfinite((double)px) && isfinite((double)py)));
+                    if (lane == 0) {
+                        atomicAdd(a.stats + 0, (double)__popc(done_mask));
+                        atomicAdd(a.stats + 1, r);
+                        atomicAdd(a.stats + 2, l);
+                        atomicAdd(a.stats + 3, fc);
+                        if (coll_mask) atomicAdd(a.stats + 4, (double)__popc(coll_mask));
+                        if (trunc_mask) atomicAdd(a.stats + 5, (double)__popc(trunc_mask));
+                        if (bad_mask) atomicAdd(a.stats + 6, (double)__popc(bad_mask));
+                    }
+                }
+                if (done && a.final_info)
+                    reinterpret_cast<Vec4<T> *>(a.final_info)[(size_t)k * N + e] =
+                        Vec4<T>{ep_ret, (T)ep_len, (T)food_collected, (T)steps_since_food};
+                if (done && a.autoreset) {
+                    if (a.final_obs) {  // terminal observation (gymnasium "final_observation")
+                        float4 *dst = reinterpret_cast<float4 *>(a.final_obs + ((size_t)k * N + e) * OBS);
+                        for (int j = 0; j < OBS / 4; ++j) dst[j] = *reinterpret_cast<const float4 *>(row + 4 * j);
+                    }
+                    const ResetResult rr = reset_slow<T>(a, e, cur_food, row);
+                    cur_food = rr.cur; mask = rr.mask; n_food = rr.n_food;
+                    // R:95-117 deterministic robot reset, S:139-141 counters
+                    px = W / 2; py = H / 2; vx = 0; vy = 0; angle = 0; omega = 0; nozzle = 0; wv = 0;
+                    phase = kPhaseRest; timer = 0; skind = kShapeReset; stimer = 0;
+                    steps_since_food = 0; food_collected = 0; ep_ret = 0; ep_len = 0;
+    #pragma unroll
+                    for (int f = 0; f < F; ++f) {
+                        if (f < n_food) {
+                            const Vec2<T> v = g_food[(size_t)f * N + e];
+                            fx[f] = v.x; fy[f] = v.y;
+                        }
                     }
                 }
             }
-        }
-        // ---- publish the observation tile
-        if constexpr (STORE == kStoreTmaBlock) {
-            fence_proxy_async_smem();
-            __syncthreads();
-            const int n_rows = (int)((end - blk0) < (unsigned)BLOCK ? (end - blk0) : (unsigned)BLOCK);
-            if (tid == 0) bulk_store_commit(a.obs + ((size_t)k * N + blk0) * OBS, s_buf, (uint32_t)(n_rows * OBS * sizeof(float)));
-        } else if constexpr (STORE != kStoreDirect) {
-            const unsigned w0 = blk0 + (tid & ~31);            // first env of this warp
-            const int w_rows = w0 >= end ? 0 : (end - w0 >= 32u ? 32 : (int)(end - w0));
-            float *g_tile = a.obs + ((size_t)k * N + w0) * OBS;
-            if constexpr (STORE == kStoreTmaWarp) {
+            // ---- publish the observation tile
+#ifndef SALP_LAB_NOOBS
+            if constexpr (STORE == kStoreTmaBlock) {
                 fence_proxy_async_smem();
-                __syncwarp();
-                if (lane == 0 && w_rows > 0) bulk_store_commit(g_tile, s_buf, (uint32_t)(w_rows * OBS * sizeof(float)));
-            } else {
-                __syncwarp();
-                const int chunks = w_rows * (OBS / 4);  // 16-byte chunks, contiguous in HBM
-                const float4 *src = reinterpret_cast<const float4 *>(s_buf);
-                float4 *dst = reinterpret_cast<float4 *>(g_tile);
-                for (int c = lane; c < chunks; c += 32) dst[c] = src[c];
+                __syncthreads();
+                const int n_rows = (int)((end - blk0) < (unsigned)BLOCK ? (end - blk0) : (unsigned)BLOCK);
+                if (tid == 0) bulk_store_commit(a.obs + ((size_t)k * N + blk0) * OBS, s_buf, (uint32_t)(n_rows * OBS * sizeof(float)));
+            } else if constexpr (STORE != kStoreDirect) {
+                const unsigned w0 = blk0 + (tid & ~31);            // first env of this warp
+                const int w_rows = w0 >= end ? 0 : (end - w0 >= 32u ? 32 : (int)(end - w0));
+                float *g_tile = a.obs + ((size_t)k * N + w0) * OBS;
+                if constexpr (STORE == kStoreTmaWarp) {
+                    fence_proxy_async_smem();
+                    __syncwarp();
+                    if (lane == 0 && w_rows > 0) bulk_store_commit(g_tile, s_buf, (uint32_t)(w_rows * OBS * sizeof(float)));
+                } else {
+                    __syncwarp();
+                    const int chunks = w_rows * (OBS / 4);  // 16-byte chunks, contiguous in HBM
+                    const float4 *src = reinterpret_cast<const float4 *>(s_buf);
+                    float4 *dst = reinterpret_cast<float4 *>(g_tile);
+                    for (int c = lane; c < chunks; c += 32) dst[c] = src[c];
+                }
             }
+#endif
         }
-    }
 
-    // ---- write state back once (food records are only written by the slow paths)
-    if (valid) {
-        g_body[e] = Vec4<T>{px, py, vx, vy};
-        g_body[(size_t)N + e] = Vec4<T>{angle, omega, nozzle, wv};
-        const int fsm = phase | (timer << 2) | (exd << 10) | (skind << 18) | (stimer << 20);
-        a.ctrl[e] = make_int4(fsm, steps_since_food, food_collected, (int)mask);
-        a.ctrl[(size_t)N + e] = make_int4((int)cur_food, (int)cur_jit, ep_len, n_food);
-        g_epret[e] = ep_ret;
-    }
+        // ---- write state back once (food records are only written by the slow paths)
+        if (valid) {
+            g_body[e] = Vec4<T>{px, py, vx, vy};
+            g_body[(size_t)N + e] = Vec4<T>{angle, omega, nozzle, wv};
+            const int fsm = phase | (timer << 2) | (exd << 10) | (skind << 18) | (stimer << 20);
+            a.ctrl[e] = make_int4(fsm, steps_since_food, food_collected, (int)mask);
+            a.ctrl[(size_t)N + e] = make_int4((int)cur_food, (int)cur_jit, ep_len, n_food);
+            g_epret[e] = ep_ret;
+        }
+
+    }  // tiles
     if (blockIdx.x == 0 && tid == 0 && a.stats) atomicAdd(a.stats + 7, (double)a.count * (double)a.K);
     if constexpr (kTma) {  // smem must stay allocated until the last bulk store has read it
         if (STORE == kStoreTmaBlock ? (tid == 0) : (lane == 0)) bulk_wait_read<0>();
