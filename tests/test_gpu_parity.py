@@ -260,3 +260,32 @@ def test_step_host_equals_device_path(salp_lib):
         assert torch.equal(o_h, obs.cpu()) and torch.equal(r_h, rew.cpu())
         assert torch.equal(te_h, term.cpu()) and torch.equal(tr_h, trunc.cpu())
     assert torch.equal(env_d.body, env_h.body) and torch.equal(env_d.ctrl, env_h.ctrl)
+
+
+def test_slab_sharding_is_rank_invariant(salp_lib):
+    """RNG streams are indexed by GLOBAL env id (seed + env_id0 + e), so an env's
+    trajectory does not depend on which rank's slab it lives in: one 2048-env slab == two
+    1024-env slabs with env_id0 = 0 / 1024, bit for bit (f32 throughput build, auto-reset on)."""
+    N, T = 2048, 1400  # long enough for wall collisions, resets and food-table draws
+    params = CONFIGS["single_food"]
+    acts = torch.from_numpy(synth_actions(T, N, 1, seed=9)).cuda()
+    whole = _env(N, params, dtype="float32", seed=4242)
+    halves = [_env(N // 2, params, dtype="float32", seed=4242, env_id0=r * (N // 2)) for r in range(2)]
+    o_w, _ = whole.reset()
+    o_h = torch.cat([h.reset()[0] for h in halves])
+    assert torch.equal(o_w, o_h)
+    n_done = 0
+    for t in range(T):
+        ow, rw, tw, uw, _ = whole.step(acts[t])
+        parts = [h.step(acts[t, r * (N // 2):(r + 1) * (N // 2)].contiguous()) for r, h in enumerate(halves)]
+        assert torch.equal(ow, torch.cat([p[0] for p in parts])), t
+        assert torch.equal(rw, torch.cat([p[1] for p in parts])), t
+        assert torch.equal(tw, torch.cat([p[2] for p in parts])), t
+        n_done += int((tw | uw).sum().item())
+    assert n_done > N // 4  # episodes did end (and were reset from the tables) inside the window
+    assert torch.equal(whole.body, torch.cat([h.body for h in halves], dim=1))
+    assert torch.equal(whole.ctrl, torch.cat([h.ctrl for h in halves], dim=1))
+    s = sum(h.stats for h in halves)
+    idx = torch.tensor([0, 2, 3, 4, 5], device=s.device)  # integer-valued sums are exact in f64
+    assert torch.equal(whole.stats[idx], s[idx])
+    assert torch.allclose(whole.stats[1], s[1], rtol=1e-12)  # return sum: atomic order differs
