@@ -259,6 +259,21 @@ template <int kPending> __device__ __forceinline__ void bulk_wait_read() {
     asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(kPending) : "memory");
 }
 
+// 64-bit load that asks L2 to keep the line (evict_last): an env draws its jitter words sequentially, so
+// the 32-byte sector serves four consecutive jet steps if it survives the ~230 MB that stream through L2
+// per launch; 1 M envs x 32 B = 32 MB of such sectors fit the 126 MB L2.
+__device__ __forceinline__ uint2 ld_evict_last_u2(const uint32_t *p) {
+    uint2 v;
+#ifdef SALP_LAB_NO_EVICT_LAST
+    v = *reinterpret_cast<const uint2 *>(p);
+#else
+    uint64_t pol;
+    asm("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+    asm volatile("ld.global.L2::cache_hint.v2.u32 {%0, %1}, [%2], %3;" : "=r"(v.x), "=r"(v.y) : "l"(p), "l"(pol));
+#endif
+    return v;
+}
+
 __device__ __forceinline__ double warp_sum(double v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -441,7 +456,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) salp_step_kernel(const __grid_con
             const bool thrust = (phase == kPhaseExhale) && (t1 <= exd) && (10 * t1 >= exd) && (2 * t1 <= exd);
             uint2 jw = make_uint2(0u, 0u);
 #ifndef SALP_LAB_NOJIT
-            if (thrust) jw = *reinterpret_cast<const uint2 *>(jit_row + (cur_jit & a.jit_len_mask));
+            if (thrust) jw = ld_evict_last_u2(jit_row + (cur_jit & a.jit_len_mask));
 #endif
             // ---- action (R:121-135)
             T act0 = 0, act1 = 0;
