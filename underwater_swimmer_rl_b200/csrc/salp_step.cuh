@@ -246,6 +246,73 @@ __device__ __noinline__ ResetResult reset_slow(const KernelArgs &a, long long e,
     return ResetResult{cur, mask, n_food};
 }
 
+// Warp-cooperative S:92-131 _generate_food_positions (+ S:144-148 food count) for ONE env, run by all
+// 32 lanes of a converged warp (e, cur warp-uniform).  The reference draws candidates one at a time and
+// tests each against the tank centre and the foods placed so far; here lane L materialises candidate L
+// of a 32-candidate window of the env's `random` stream (4 words each) and keeps a running verdict
+// `ok` that is updated once per newly placed food, so placing a food is a ballot + ffs instead of a
+// serial rejection loop with dependent HBM reads.  Candidate order, the 100-attempt cap and its
+// unconditional 101st draw, and the words consumed are exactly the reference's.
+// Returns food j's position in lane j (j < n_food), plus the new cursor and n_food in every lane.
+template <typename T> struct LayoutResult { T x, y; unsigned cur; int n_food; };
+
+template <typename T>
+__device__ __noinline__ LayoutResult<T> layout_warp(const KernelArgs &a, unsigned e, unsigned cur, int lane) {
+    constexpr unsigned kFull = 0xffffffffu;
+    const unsigned row = (a.rows == (unsigned)a.N) ? e : e % a.rows;
+    const uint32_t *words = a.food_words + (size_t)row * a.food_len;
+    int n_food = a.num_food;
+    if (a.random_food_count) {  // random.randint(1, max(1, base)) == 1 + _randbelow(n); same words in every lane
+        const uint32_t n = (uint32_t)(a.num_food > 1 ? a.num_food : 1);
+        const int kbits = 32 - __clz(n);
+        uint32_t r;
+        do { r = words[cur & a.food_len_mask] >> (32 - kbits); ++cur; } while (r >= n);
+        n_food = 1 + (int)r;
+    }
+    const T xlo = (T)(kc::TANK_MARGIN + kc::FOOD_R), xhi = (T)a.W - (T)kc::TANK_MARGIN - (T)kc::FOOD_R;
+    const T ylo = xlo, yhi = (T)a.H - (T)kc::TANK_MARGIN - (T)kc::FOOD_R;
+    const T cx = (T)a.W / 2, cy = (T)a.H / 2;
+    T myx = 0, myy = 0;       // position of food `lane`
+    T candx = 0, candy = 0;   // candidate `lane` of the current window
+    bool ok = false;          // candidate is >= 80 px from the centre and from every food placed so far
+    int ptr = 32;             // next untested candidate of the window (32 = window exhausted / not loaded)
+    unsigned base = cur;      // stream position of candidate 0 of the next window
+    for (int i = 0; i < n_food; ++i) {
+        int attempts = 0, chosen;
+        for (;;) {
+            if (ptr == 32) {
+                const unsigned w = base + 4u * (unsigned)lane;
+                const uint32_t w0 = words[w & a.food_len_mask], w1 = words[(w + 1) & a.food_len_mask];
+                const uint32_t w2 = words[(w + 2) & a.food_len_mask], w3 = words[(w + 3) & a.food_len_mask];
+                candx = xlo + (xhi - xlo) * (T)res53(w0, w1);  // random.uniform: a + (b-a)*random()
+                candy = ylo + (yhi - ylo) * (T)res53(w2, w3);
+                const T rx = candx - cx, ry = candy - cy;
+                ok = !(sqrt_(rx * rx + ry * ry) < (T)kc::MIN_FOOD_DIST);
+                for (int j = 0; j < i; ++j) {
+                    const T dx = candx - __shfl_sync(kFull, myx, j), dy = candy - __shfl_sync(kFull, myy, j);
+                    if (sqrt_(dx * dx + dy * dy) < (T)kc::MIN_FOOD_DIST) ok = false;
+                }
+                base += 128u;
+                ptr = 0;
+            }
+            const unsigned m = __ballot_sync(kFull, ok) & (kFull << ptr);
+            const int first = m ? __ffs((int)m) - 1 : 32;
+            const int limit = ptr + (100 - attempts);  // after 100 rejects the next draw is taken unconditionally
+            const int c = first < limit ? first : limit;
+            if (c < 32) { chosen = c; break; }
+            attempts += 32 - ptr;
+            ptr = 32;
+        }
+        const T x = __shfl_sync(kFull, candx, chosen), y = __shfl_sync(kFull, candy, chosen);
+        if (lane == i) { myx = x; myy = y; }
+        ptr = chosen + 1;
+        const T dx = candx - x, dy = candy - y;
+        if (sqrt_(dx * dx + dy * dy) < (T)kc::MIN_FOOD_DIST) ok = false;
+    }
+    if (n_food > 0) cur = base - 128u + 4u * (unsigned)ptr;
+    return LayoutResult<T>{myx, myy, cur, n_food};
+}
+
 // ---------------------------------------------------------------------------------------------
 // TMA bulk store helpers (1-D, no tensor map): shared::cta -> global
 // ---------------------------------------------------------------------------------------------
@@ -336,6 +403,14 @@ __global__ void __launch_bounds__(BLOCK, MINB) salp_step_kernel(const __grid_con
     const unsigned end = (unsigned)a.first + (unsigned)a.count;
     const unsigned ntiles = ((unsigned)a.count + BLOCK - 1) / BLOCK;
     constexpr bool kTma = (STORE == kStoreTmaWarp || STORE == kStoreTmaBlock);
+    // many foods: episode resets are laid out by the whole warp (layout_warp) and the reset observation
+    // comes from a second trip through the observation code; few foods: in-thread reset_slow
+    constexpr bool kCoopReset = (F >= 8);
+    // throughput build with several foods: the MU nearest live foods are selected on packed integer keys
+    // (distance bits | slot) with min/max, and their offsets fetched from a shared-memory scratch by slot
+    constexpr bool kFastSel = (!is_f64<T>::value) && (F > 1);
+    constexpr int MU = (MT < F) ? MT : F;  // observation entries that can ever be real
+    __shared__ float2 s_sel[kFastSel ? F * BLOCK : 1];  // [slot][thread] (dx, dy) of this substep
 
     Vec4<T> *g_body = reinterpret_cast<Vec4<T> *>(a.body);
     T *g_epret = reinterpret_cast<T *>(a.ep_return);
@@ -474,12 +549,20 @@ __global__ void __launch_bounds__(BLOCK, MINB) salp_step_kernel(const __grid_con
                 }
             }
 #ifdef SALP_LAB_SKELETON  // tools/kernel_lab.cu only: memory skeleton of the step (no model arithmetic)
-            const T radius = (T)30; const bool hit = false, collision = false; const T near_rel = 0;
+            T radius = (T)30; bool hit = false; const bool collision = false; const T near_rel = 0;
             const bool terminated = false, truncated = false;
             px += act0 * (T)0.001 + (T)jw.x * (T)1e-12; T reward = act0 + act1;
             T dx[F], dy[F], dd[F];
 #pragma unroll
             for (int f = 0; f < F; ++f) { dx[f] = fx[f] - px; dy[f] = fy[f] - py; dd[f] = dx[f] + dy[f]; }
+            unsigned key[MU]; T dist_sum = 0;
+    #pragma unroll
+            for (int i = 0; i < MU; ++i) key[i] = (unsigned)i;
+            if constexpr (kFastSel) {
+    #pragma unroll
+                for (int f = 0; f < F; ++f) s_sel[f * BLOCK + tid] = make_float2((float)dx[f], (float)dy[f]);
+            }
+            auto select_top = [&]() {};
 #else
             bool inhaling;
             T dir;
@@ -528,7 +611,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) salp_step_kernel(const __grid_con
                 const T db = inh ? (T)(kc::B_FULL - kc::B_REST) : (T)(kc::B_REST - kc::B_FULL);
                 ea = sa + da * prog; eb = sb + db * prog;
             }
-            const T radius = pymax<T>(ea, eb);
+            T radius = pymax<T>(ea, eb);
             if (wv_mode == 1) wv = prog;
             // ---- jet thrust through the steerable nozzle (R:261-314)
             if (thrust) {
@@ -606,10 +689,43 @@ __global__ void __launch_bounds__(BLOCK, MINB) salp_step_kernel(const __grid_con
             // nearest live food (strict <, first index wins: S:350-364).  Its bearing is used by the
             // alignment reward AND, when no food was eaten this step, is the first observation entry.
             bool any_food = false;
-            T near_d = 0, near_x = 0, near_y = 0, near_rel = 0;
+            T near_x = 0, near_y = 0, near_rel = 0;
+            unsigned key[MU];   // kFastSel: sorted keys of the MU nearest live foods
+            T dist_sum = 0;     // kFastSel: sum of live-food distances (slot order)
+            // key = distance in 32-bit fixed point (diag -> 2^32, saturating) with the slot in the low kSlotBits
+            // bits: unsigned order == (distance, slot) order at a resolution of diag / 2^(32 - kSlotBits)
+            // (3.7e-6 px for 12 foods in the 800 x 600 tank, finer than one f32 ulp of the distance itself).
+            // Eaten foods sort last.
+            constexpr unsigned kSlotMask = F <= 2 ? 1u : (F <= 4 ? 3u : (F <= 8 ? 7u : (F <= 16 ? 15u : 31u)));
+            const float key_scale = (float)a.inv_diag * (4294967296.0f * 0.9999f);
+            auto make_key = [&](T d, int f) -> unsigned { return (__float2uint_rz((float)d * key_scale) & ~kSlotMask) | (unsigned)f; };
+            auto insert_key = [&](unsigned c) {
     #pragma unroll
-            for (int f = 0; f < F; ++f)
-                if (((mask >> f) & 1u) && (!any_food || dd[f] < near_d)) { any_food = true; near_d = dd[f]; near_x = dx[f]; near_y = dy[f]; }
+                for (int i = 0; i < MU; ++i) { const unsigned lo = min(key[i], c); c = max(key[i], c); key[i] = lo; }
+            };
+            auto select_top = [&]() {
+                dist_sum = 0;
+    #pragma unroll
+                for (int i = 0; i < MU; ++i) key[i] = 0xffffffffu;
+    #pragma unroll
+                for (int f = 0; f < F; ++f) {
+                    const bool alive = (mask >> f) & 1u;
+                    if (alive) dist_sum += dd[f];
+                    insert_key(alive ? make_key(dd[f], f) : (~kSlotMask | (unsigned)f));
+                    s_sel[f * BLOCK + tid] = make_float2((float)dx[f], (float)dy[f]);
+                }
+            };
+            if constexpr (kFastSel) {
+                select_top();
+                any_food = mask != 0u;
+                const float2 nv = s_sel[(key[0] & kSlotMask) * BLOCK + tid];
+                near_x = nv.x; near_y = nv.y;
+            } else {
+                T near_d = 0;
+    #pragma unroll
+                for (int f = 0; f < F; ++f)
+                    if (((mask >> f) & 1u) && (!any_food || dd[f] < near_d)) { any_food = true; near_d = dd[f]; near_x = dx[f]; near_y = dy[f]; }
+            }
             if (any_food && (a.proximity_w > 0 || a.observed > 0)) near_rel = wrap_pi<T>(atan2_(near_y, near_x) - angle);
             if (a.proximity_w > 0 && any_food) reward += (T)a.proximity_w * cos_(near_rel);
             reward += (T)a.time_penalty;
@@ -627,6 +743,11 @@ __global__ void __launch_bounds__(BLOCK, MINB) salp_step_kernel(const __grid_con
                             fx[f] = r.x; fy[f] = r.y;
                             dx[f] = r.x - px; dy[f] = r.y - py;
                             dd[f] = sqrt_(dx[f] * dx[f] + dy[f] * dy[f]);
+                            if constexpr (kFastSel) {  // the new food joins the selection made before it existed
+                                dist_sum += dd[f];
+                                insert_key(make_key(dd[f], f));
+                                s_sel[f * BLOCK + tid] = make_float2((float)dx[f], (float)dy[f]);
+                            }
                         }
                 }
             }
@@ -640,6 +761,11 @@ __global__ void __launch_bounds__(BLOCK, MINB) salp_step_kernel(const __grid_con
             ep_ret += reward;
             ++ep_len;
 
+            // The observation is assembled once per substep -- and a second time, in warps where an episode
+            // ended under auto-reset, from the freshly reset state (the row the caller sees is the new
+            // episode's first observation; the terminal one goes to final_obs).  One copy of the code, two trips.
+    #pragma unroll 1
+            for (int pass = 0;; ++pass) {
             // ---- observation (R:377-388 + S:366-428), assembled in registers, written as 128-bit rows
             float4 v0, v1;
             float o8, o9;
@@ -654,12 +780,11 @@ __global__ void __launch_bounds__(BLOCK, MINB) salp_step_kernel(const __grid_con
             const int n_live = __popc(mask);
             // The MU nearest live foods in order (stable: equal distances keep slot order, S:382) and the
             // mean distance (S:419).
-            constexpr int MU = (MT < F) ? MT : F;  // entries that can ever be real
             T top_d[MU], top_x[MU], top_y[MU];
-            T dist_sum = 0;
+            T obs_sum = 0;
             if constexpr (F == 1) {
                 top_d[0] = dd[0]; top_x[0] = dx[0]; top_y[0] = dy[0];
-                dist_sum = dd[0];
+                obs_sum = dd[0];
             } else if constexpr (is_f64<T>::value) {
                 // validation build: full sorting network on (distance, slot) so that the mean is summed
                 // in sorted order exactly like sum() over the sorted list
@@ -685,7 +810,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) salp_step_kernel(const __grid_con
     #undef SALP_CE
     #pragma unroll
                 for (int f = 0; f < F; ++f)
-                    if (f < n_live) dist_sum = dist_sum + dd[f];
+                    if (f < n_live) obs_sum = obs_sum + dd[f];
     #pragma unroll
                 for (int i = 0; i < MU; ++i) {
                     T sx = 0, sy = 0;
@@ -695,35 +820,15 @@ __global__ void __launch_bounds__(BLOCK, MINB) salp_step_kernel(const __grid_con
                     top_d[i] = dd[i]; top_x[i] = sx; top_y[i] = sy;
                 }
             } else {
-                // throughput build: only the MU nearest are needed -> insertion of every food into a
-                // sorted MU-list of (distance, slot).  Strict < keeps equal distances in slot order
-                // (foods arrive in slot order), i.e. the stable order of list.sort(); the mean is summed
-                // in slot order (differs from the sorted-order sum by rounding only).
-                T kd[MU];
-                int ki[MU];
-    #pragma unroll
-                for (int i = 0; i < MU; ++i) { kd[i] = (T)CUDART_INF_F; ki[i] = F; }
-    #pragma unroll
-                for (int f = 0; f < F; ++f) {
-                    const bool alive = (mask >> f) & 1u;
-                    if (alive) dist_sum += dd[f];
-                    T cd = alive ? dd[f] : (T)CUDART_INF_F;
-                    int ci = alive ? f : F;
-    #pragma unroll
-                    for (int i = 0; i < MU; ++i) {
-                        const bool lt = cd < kd[i];
-                        const T lo_d = lt ? cd : kd[i], hi_d = lt ? kd[i] : cd;
-                        const int lo_i = lt ? ci : ki[i], hi_i = lt ? ki[i] : ci;
-                        kd[i] = lo_d; ki[i] = lo_i; cd = hi_d; ci = hi_i;
-                    }
-                }
+                // throughput build: the MU nearest were selected on packed keys (select_top); fetch their offsets
+                // by slot from the shared-memory scratch.  The mean is summed in slot order (differs from the
+                // sorted-order sum by rounding only).
+                obs_sum = dist_sum;
     #pragma unroll
                 for (int i = 0; i < MU; ++i) {
-                    T sx = 0, sy = 0;
-    #pragma unroll
-                    for (int f = 0; f < F; ++f)
-                        if (ki[i] == f) { sx = dx[f]; sy = dy[f]; }
-                    top_d[i] = kd[i]; top_x[i] = sx; top_y[i] = sy;
+                    const float2 v = s_sel[(key[i] & kSlotMask) * BLOCK + tid];
+                    top_x[i] = v.x; top_y[i] = v.y;
+                    top_d[i] = sqrt_(v.x * v.x + v.y * v.y);
                 }
             }
             // i-th nearest live food -> [dx/W, dy/H, d/diag, wrap(atan2(dy,dx) - angle)/pi]; S:412 padding [0,0,1,0]
@@ -746,7 +851,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) salp_step_kernel(const __grid_con
             float cnt, avg = 1.f;
             cnt = (float)pymin<T>((T)n_live / (T)10.0, (T)1.0);
             if (n_live > 0) {
-                const T mean = dist_sum / (T)n_live;
+                const T mean = obs_sum / (T)n_live;
                 if constexpr (is_f64<T>::value) avg = (float)(mean / diag);
                 else avg = mean * invDiag;
             }
@@ -774,6 +879,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) salp_step_kernel(const __grid_con
                 }
             }
 
+            if (kCoopReset && pass) break;
             // ---- per-step outputs
             const bool done = terminated || truncated;
             if (valid) {
@@ -785,35 +891,37 @@ __global__ void __launch_bounds__(BLOCK, MINB) salp_step_kernel(const __grid_con
             }
             // ---- episode statistics: warp-shuffle reduction, only in warps where an episode ended
             const unsigned done_mask = __ballot_sync(0xffffffffu, done);
-            if (done_mask != 0u) {
-                if (a.stats) {
-                    const double r = warp_sum(done ? (double)ep_ret : 0.0);
-                    const double l = warp_sum(done ? (double)ep_len : 0.0);
-                    const double fc = warp_sum(done ? (double)food_collected : 0.0);
-                    const unsigned coll_mask = __ballot_sync(0xffffffffu, done && collision);
-                    const unsigned trunc_mask = __ballot_sync(0xffffffffu, done && truncated);
-                    const unsigned bad_mask = __ballot_sync(0xffffffffu, done && !(isfinite((double)px) && isfinite((double)py)));
-                    if (lane == 0) {
-                        atomicAdd(a.stats + 0, (double)__popc(done_mask));
-                        atomicAdd(a.stats + 1, r);
-                        atomicAdd(a.stats + 2, l);
-                        atomicAdd(a.stats + 3, fc);
-                        if (coll_mask) atomicAdd(a.stats + 4, (double)__popc(coll_mask));
-                        if (trunc_mask) atomicAdd(a.stats + 5, (double)__popc(trunc_mask));
-                        if (bad_mask) atomicAdd(a.stats + 6, (double)__popc(bad_mask));
-                    }
+            if (done_mask == 0u) break;
+            if (a.stats) {
+                const double r = warp_sum(done ? (double)ep_ret : 0.0);
+                const double l = warp_sum(done ? (double)ep_len : 0.0);
+                const double fc = warp_sum(done ? (double)food_collected : 0.0);
+                const unsigned coll_mask = __ballot_sync(0xffffffffu, done && collision);
+                const unsigned trunc_mask = __ballot_sync(0xffffffffu, done && truncated);
+                const unsigned bad_mask = __ballot_sync(0xffffffffu, done && !(isfinite((double)px) && isfinite((double)py)));
+                if (lane == 0) {
+                    atomicAdd(a.stats + 0, (double)__popc(done_mask));
+                    atomicAdd(a.stats + 1, r);
+                    atomicAdd(a.stats + 2, l);
+                    atomicAdd(a.stats + 3, fc);
+                    if (coll_mask) atomicAdd(a.stats + 4, (double)__popc(coll_mask));
+                    if (trunc_mask) atomicAdd(a.stats + 5, (double)__popc(trunc_mask));
+                    if (bad_mask) atomicAdd(a.stats + 6, (double)__popc(bad_mask));
                 }
-                if (done && a.final_info)
-                    reinterpret_cast<Vec4<T> *>(a.final_info)[(size_t)k * N + e] =
-                        Vec4<T>{ep_ret, (T)ep_len, (T)food_collected, (T)steps_since_food};
-                if (done && a.autoreset) {
-                    if (a.final_obs) {  // terminal observation (gymnasium "final_observation")
-                        float4 *dst = reinterpret_cast<float4 *>(a.final_obs + ((size_t)k * N + e) * OBS);
-                        for (int j = 0; j < OBS / 4; ++j) dst[j] = *reinterpret_cast<const float4 *>(row + 4 * j);
-                    }
+            }
+            if (done && a.final_info)
+                reinterpret_cast<Vec4<T> *>(a.final_info)[(size_t)k * N + e] =
+                    Vec4<T>{ep_ret, (T)ep_len, (T)food_collected, (T)steps_since_food};
+            if (!a.autoreset) break;
+            if (done && a.final_obs) {  // terminal observation (gymnasium "final_observation")
+                float4 *dst = reinterpret_cast<float4 *>(a.final_obs + ((size_t)k * N + e) * OBS);
+                for (int j = 0; j < OBS / 4; ++j) dst[j] = *reinterpret_cast<const float4 *>(row + 4 * j);
+            }
+            if constexpr (!kCoopReset) {
+                // few foods: the in-thread slow path is cheap enough and keeps the hot path free of the loop
+                if (done) {
                     const ResetResult rr = reset_slow<T>(a, e, cur_food, row);
                     cur_food = rr.cur; mask = rr.mask; n_food = rr.n_food;
-                    // R:95-117 deterministic robot reset, S:139-141 counters
                     px = W / 2; py = H / 2; vx = 0; vy = 0; angle = 0; omega = 0; nozzle = 0; wv = 0;
                     phase = kPhaseRest; timer = 0; skind = kShapeReset; stimer = 0;
                     steps_since_food = 0; food_collected = 0; ep_ret = 0; ep_len = 0;
@@ -825,7 +933,41 @@ __global__ void __launch_bounds__(BLOCK, MINB) salp_step_kernel(const __grid_con
                         }
                     }
                 }
+                break;
+            } else {
+            // ---- auto-reset (S:133-155): the whole warp lays out the food of each finished env in turn
+            for (unsigned m = done_mask; m != 0u; m &= m - 1u) {
+                const int src = __ffs((int)m) - 1;
+                const unsigned e_src = __shfl_sync(0xffffffffu, e, src);
+                const LayoutResult<T> L = layout_warp<T>(a, e_src, __shfl_sync(0xffffffffu, cur_food, src), lane);
+                if (lane < L.n_food) reinterpret_cast<Vec2<T> *>(a.food)[(size_t)lane * N + e_src] = Vec2<T>{L.x, L.y};
+    #pragma unroll
+                for (int f = 0; f < F; ++f) {  // food f's position lives in lane f: hand it to the env's own lane
+                    const T tx = __shfl_sync(0xffffffffu, L.x, f), ty = __shfl_sync(0xffffffffu, L.y, f);
+                    if (lane == src && f < L.n_food) { fx[f] = tx; fy[f] = ty; }
+                }
+                if (lane == src) {
+                    cur_food = L.cur; n_food = L.n_food;
+                    mask = L.n_food >= 32 ? 0xffffffffu : ((1u << L.n_food) - 1u);
+                }
             }
+            if (done) {
+                // R:95-117 deterministic robot reset, S:139-141 counters
+                px = W / 2; py = H / 2; vx = 0; vy = 0; angle = 0; omega = 0; nozzle = 0; wv = 0;
+                phase = kPhaseRest; timer = 0; skind = kShapeReset; stimer = 0;
+                steps_since_food = 0; food_collected = 0; ep_ret = 0; ep_len = 0;
+                radius = (T)kc::BASE_R;
+                hit = true;  // the bearing computed for the reward belongs to the finished episode
+            }
+            // distances for the second trip, for every lane (the validation build sorts dd[] in place)
+    #pragma unroll
+            for (int f = 0; f < F; ++f) {
+                dx[f] = fx[f] - px; dy[f] = fy[f] - py;
+                dd[f] = sqrt_(dx[f] * dx[f] + dy[f] * dy[f]);
+            }
+            if constexpr (kFastSel) select_top();
+            }
+            }  // pass
             // ---- publish the observation tile
 #ifndef SALP_LAB_NOOBS
             if constexpr (STORE == kStoreTmaBlock) {
