@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define SALP_ABI_VERSION 1
+#define SALP_ABI_VERSION 2
 
 enum { SALP_OK = 0, SALP_EINVAL = -1, SALP_ECUDA = -2, SALP_EUNBOUND = -3, SALP_EUNSUPPORTED = -4 };
 
@@ -89,7 +89,14 @@ typedef struct SalpLayout {
  *   body      real [2][N][4]   rec0 = (pos.x, pos.y, vel.x, vel.y)          R:61-62
  *                              rec1 = (angle, angular_vel, nozzle, water)    R:63-67,77
  *   ctrl      i32  [2][N][4]   rec0 = (fsm, steps_since_food, food_collected, food_mask)
- *                              rec1 = (food_cursor, jitter_cursor, episode_len, n_food)
+ *                              rec1 = (food_cursor, jitter_cursor, episode_len | n_food << 26,
+ *                                      jitter_cache)
+ *             episode_len saturates at 2^26-1.  jitter_cache is the library-maintained copy of
+ *             jit_words[row][jitter_cursor] (first word of the next np.random draw): the f32 step
+ *             kernel reads it with the rest of the state instead of chasing cursor -> table (a
+ *             dependent DRAM round trip) and refills it right after a draw.  salp_reset sets it for
+ *             the lanes it resets; call salp_refresh_rng after binding new tables or after
+ *             overwriting the cursors in `ctrl` from outside.
  *             fsm bits: [0:2) breathing phase 0 rest/1 inhaling/2 exhaling (R:71)
  *                       [2:10) breathing_timer (R:72)   [10:18) current_exhale_duration (R:223)
  *                       [18:20) body-shape source 0 reset(30,30)/1 rest/2 inhale/3 exhale
@@ -164,6 +171,12 @@ int salp_bind(SalpHandle *h, const SalpBuffers *buffers);
  * consuming its global streams across episodes); pass rewind_rng != 0 to restart them.
  */
 int salp_reset(SalpHandle *h, const uint8_t *mask, int rewind_rng, void *cuda_stream);
+
+/*
+ * Re-read ctrl.jitter_cache of every env from jit_words at the env's current jitter cursor
+ * (see SalpBuffers).  Asynchronous on `cuda_stream`.
+ */
+int salp_refresh_rng(SalpHandle *h, void *cuda_stream);
 
 /*
  * Replaces K consecutive SalpSnakeEnv.step calls (S:157-202 over R:119-156) per env in ONE

@@ -34,7 +34,7 @@ def _unpack_state(env):
                 omega=body[1, :, 1], nozzle=body[1, :, 2], wv=body[1, :, 3], a=a.cpu().numpy(), b=b.cpu().numpy(),
                 phase=ctrl[0, :, 0] & 3, timer=(ctrl[0, :, 0] >> 2) & 0xFF, steps_since_food=ctrl[0, :, 1],
                 food_collected=ctrl[0, :, 2], mask=ctrl[0, :, 3].astype(np.uint32), cur_food=ctrl[1, :, 0],
-                cur_jit=ctrl[1, :, 1], n_food=ctrl[1, :, 3])
+                cur_jit=ctrl[1, :, 1], n_food=(ctrl[1, :, 2] >> 26) & 0x3F)
 
 
 @pytest.mark.parametrize("case", golden_cases())
@@ -220,8 +220,9 @@ def test_fp32_per_step_error_from_synced_states(oracle_lib, salp_lib):
         ctrl[0, :, 3] = np.where(mask >= 2 ** 31, mask - 2 ** 32, mask)
         ctrl[1, :, 0] = e["cur_food"]
         ctrl[1, :, 1] = e["cur_jit"]
-        ctrl[1, :, 3] = e["n_food"]
+        ctrl[1, :, 2] = (ctrl[1, :, 2] & 0x3FFFFFF) | (e["n_food"].astype(np.int64) << 26).astype(np.int32)
         env.ctrl.copy_(torch.from_numpy(ctrl))
+        env.refresh_rng()  # cursors were overwritten from outside
         env.food.copy_(torch.from_numpy(e["food"][:, :F].transpose(1, 0, 2).astype(np.float32)))
         obs_ref, rew_ref, flags_ref = orc.step(acts[t].astype(np.float64))
         obs, rew, term, trunc, info = env.step(torch.from_numpy(acts[t]).cuda())

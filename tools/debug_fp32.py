@@ -23,8 +23,8 @@ for t in range(T):
     ctrl[0, :, 1] = e["steps_since_food"]; ctrl[0, :, 2] = e["food_collected"]
     mask = (e["alive"][:, :F].astype(np.int64) << np.arange(F)).sum(1)
     ctrl[0, :, 3] = np.where(mask >= 2**31, mask - 2**32, mask)
-    ctrl[1, :, 0] = e["cur_food"]; ctrl[1, :, 1] = e["cur_jit"]; ctrl[1, :, 3] = e["n_food"]
-    env.ctrl.copy_(torch.from_numpy(ctrl))
+    ctrl[1, :, 0] = e["cur_food"]; ctrl[1, :, 1] = e["cur_jit"]; ctrl[1, :, 2] = (ctrl[1, :, 2] & 0x3FFFFFF) | (e["n_food"].astype(np.int64) << 26).astype(np.int32)
+    env.ctrl.copy_(torch.from_numpy(ctrl)); env.refresh_rng()
     env.food.copy_(torch.from_numpy(e["food"][:, :F].transpose(1, 0, 2).astype(np.float32)))
     obs_ref, rew_ref, flags_ref = orc.step(acts[t].astype(np.float64))
     obs, rew, term, trunc, info = env.step(torch.from_numpy(acts[t]).cuda())

@@ -11,7 +11,7 @@ import os
 _PKG = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_PKG, "libsalp_b200.so")
 
-SALP_ABI_VERSION = 1
+SALP_ABI_VERSION = 2
 SALP_OK, SALP_EINVAL, SALP_ECUDA, SALP_EUNBOUND, SALP_EUNSUPPORTED = 0, -1, -2, -3, -4
 SALP_F32, SALP_F64 = 0, 1
 SALP_AUTORESET = 1
@@ -20,7 +20,7 @@ EV_TERMINATED, EV_TRUNCATED, EV_COLLISION, EV_FOOD = 1, 2, 4, 8
 # every symbol include/salp_b200.h declares (tests/test_capi_symbols.py parses the header too)
 EXPORTED_SYMBOLS = (
     "salp_abi_version", "salp_last_error", "salp_query_layout", "salp_create", "salp_destroy", "salp_bind",
-    "salp_reset", "salp_step", "salp_step_host", "salp_fill_rng_words", "salp_launch_count",
+    "salp_reset", "salp_refresh_rng", "salp_step", "salp_step_host", "salp_fill_rng_words", "salp_launch_count",
 )
 
 
@@ -81,6 +81,7 @@ def load():
     L.salp_destroy.argtypes = [C.c_void_p]
     L.salp_bind.argtypes = [C.c_void_p, C.POINTER(SalpBuffers)]
     L.salp_reset.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+    L.salp_refresh_rng.argtypes = [C.c_void_p, C.c_void_p]
     L.salp_step.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
     L.salp_step_host.argtypes = [C.c_void_p] + [C.c_void_p] * 6
     L.salp_fill_rng_words.argtypes = [C.c_void_p, C.c_int64, C.c_int64, C.c_uint64, C.c_int64, C.c_int, C.c_int]

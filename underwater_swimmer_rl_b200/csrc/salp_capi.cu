@@ -222,6 +222,16 @@ int salp_reset(SalpHandle *h, const uint8_t *mask, int rewind_rng, void *stream)
     return SALP_OK;
 }
 
+int salp_refresh_rng(SalpHandle *h, void *stream) {
+    if (!h) return fail(SALP_EINVAL, "null handle");
+    if (!h->bound) return fail(SALP_EUNBOUND, "salp_bind has not been called");
+    SALP_CUDA(cudaSetDevice(h->device));
+    cudaError_t e = salp::launch_refresh_rng(h->base, (cudaStream_t)stream);
+    if (e != cudaSuccess) return cuda_fail(e, "salp_refresh_rng kernel launch");
+    ++h->launches;
+    return SALP_OK;
+}
+
 int salp_step(SalpHandle *h, int K, const void *actions, void *stream) {
     if (!h) return fail(SALP_EINVAL, "null handle");
     if (!h->bound) return fail(SALP_EUNBOUND, "salp_bind has not been called");

@@ -13,6 +13,7 @@ constexpr int kMaxObserved = 8;
 
 // fsm word layout (see include/salp_b200.h)
 constexpr int kPhaseRest = 0, kPhaseInhale = 1, kPhaseExhale = 2;
+constexpr int kEpLenMask = (1 << 26) - 1;  // ctrl rec1.z = episode_len (26 bits, saturating) | n_food << 26
 constexpr int kShapeReset = 0, kShapeRest = 1, kShapeInhale = 2, kShapeExhale = 3;
 
 // Passed by value as a __grid_constant__ kernel parameter (lives in the constant bank).
@@ -45,5 +46,6 @@ cudaError_t launch_step_f32(const KernelArgs &a, int food_slots, cudaStream_t s)
 cudaError_t launch_step_f64(const KernelArgs &a, int food_slots, cudaStream_t s);
 cudaError_t launch_reset_f32(const KernelArgs &a, int food_slots, cudaStream_t s);
 cudaError_t launch_reset_f64(const KernelArgs &a, int food_slots, cudaStream_t s);
+cudaError_t launch_refresh_rng(const KernelArgs &a, cudaStream_t s);  // defined in the f32 translation unit
 
 }  // namespace salp

@@ -56,4 +56,12 @@ cudaError_t SALP_LAUNCH_RESET(const KernelArgs &a, int /*food_slots*/, cudaStrea
     return cudaGetLastError();
 }
 
+#if !SALP_BUILD_F64
+cudaError_t launch_refresh_rng(const KernelArgs &a, cudaStream_t s) {
+    if (a.count <= 0) return cudaSuccess;
+    salp_refresh_rng_kernel<<<(unsigned)((a.count + 255) / 256), 256, 0, s>>>(a);
+    return cudaGetLastError();
+}
+#endif
+
 }  // namespace salp

@@ -371,6 +371,18 @@ __device__ __forceinline__ uint2 ld_evict_last_u2(const uint32_t *p) {
     return v;
 }
 
+__device__ __forceinline__ uint32_t ld_evict_last_u1(const uint32_t *p) {
+    uint32_t v;
+#ifdef SALP_LAB_NO_EVICT_LAST
+    v = *p;
+#else
+    uint64_t pol;
+    asm("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+    asm volatile("ld.global.L2::cache_hint.u32 %0, [%1], %2;" : "=r"(v) : "l"(p), "l"(pol));
+#endif
+    return v;
+}
+
 __device__ __forceinline__ double warp_sum(double v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -529,7 +541,8 @@ __global__ void __launch_bounds__(BLOCK, MINB) salp_step_kernel(const __grid_con
         int steps_since_food = c0.y, food_collected = c0.z;
         unsigned mask = (unsigned)c0.w;
         unsigned cur_food = (unsigned)c1.x, cur_jit = (unsigned)c1.y;
-        int ep_len = c1.z, n_food = c1.w;
+        int ep_len = c1.z & kEpLenMask, n_food = (int)((unsigned)c1.z >> 26);
+        unsigned jcache = (unsigned)c1.w;  // first word of the jitter pair at cur_jit (see salp_b200.h)
 
         const unsigned trow = (a.rows == N) ? e : e % a.rows;
         const uint32_t *jit_row = a.jit_words + (size_t)trow * a.jit_len;
@@ -559,9 +572,17 @@ __global__ void __launch_bounds__(BLOCK, MINB) salp_step_kernel(const __grid_con
             //      Known before anything else is computed, so the jitter word load is issued first.
             const int t1 = timer + 1;
             const bool thrust = (phase == kPhaseExhale) && (t1 <= exd) && (10 * t1 >= exd) && (2 * t1 <= exd);
-            uint2 jw = make_uint2(0u, 0u);
+            // f32 build: the np.random word this step draws is already here (ctrl rec1.w, loaded with the state)
+            // and the word for the FOLLOWING draw is fetched now, needed only at write-back -- the
+            // cursor -> table DRAM round trip is off the critical path.  (23 bits of the draw are plenty for a
+            // +-0.025 rad jitter in f32.)  The validation build needs both words of the pair bit-exactly and
+            // keeps the dependent load; it is not a throughput configuration.
+            uint2 jw = make_uint2(jcache, 0u);
 #ifndef SALP_LAB_NOJIT
-            if (thrust) jw = ld_evict_last_u2(jit_row + (cur_jit & a.jit_len_mask));
+            if (thrust) {
+                if constexpr (is_f64<T>::value) jw = ld_evict_last_u2(jit_row + (cur_jit & a.jit_len_mask));
+                else jcache = ld_evict_last_u1(jit_row + ((cur_jit + 2u) & a.jit_len_mask));
+            }
 #endif
             // ---- action (R:121-135)
             T act0 = 0, act1 = 0;
@@ -664,7 +685,9 @@ __global__ void __launch_bounds__(BLOCK, MINB) salp_step_kernel(const __grid_con
                 vx += (c1_ * sm) * (T)0.008;
                 vy += (s1 * sm) * (T)0.008;
                 cur_jit += 2;
-                const T u = (T)res53(jw.x, jw.y);  // np.random.random(), R:311
+                T u;  // np.random.random(), R:311
+                if constexpr (is_f64<T>::value) u = res53(jw.x, jw.y);
+                else u = (float)(jw.x >> 5) * (1.0f / 134217728.0f);
                 const T dn = (u - (T)0.5) * (T)0.05;
                 const T nf = Tm * (T)0.04;
                 T s2, c2;
@@ -1030,7 +1053,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) salp_step_kernel(const __grid_con
             g_body[(size_t)N + e] = Vec4<T>{angle, omega, nozzle, wv};
             const int fsm = phase | (timer << 2) | (exd << 10) | (skind << 18) | (stimer << 20);
             a.ctrl[e] = make_int4(fsm, steps_since_food, food_collected, (int)mask);
-            a.ctrl[(size_t)N + e] = make_int4((int)cur_food, (int)cur_jit, ep_len, n_food);
+            a.ctrl[(size_t)N + e] = make_int4((int)cur_food, (int)cur_jit, (ep_len < kEpLenMask ? ep_len : kEpLenMask) | (n_food << 26), (int)jcache);
             g_epret[e] = ep_ret;
         }
 
@@ -1059,8 +1082,20 @@ __global__ void __launch_bounds__(256) salp_reset_kernel(const __grid_constant__
     g_body[N + e] = Vec4<T>{0, 0, 0, 0};
     const int fsm = kPhaseRest | (kShapeReset << 18);
     a.ctrl[e] = make_int4(fsm, 0, 0, (int)rr.mask);
-    a.ctrl[N + e] = make_int4((int)rr.cur, (int)cur_jit, 0, rr.n_food);
+    const unsigned trow = (unsigned)e % a.rows;
+    const uint32_t jcache = a.jit_words[(size_t)trow * a.jit_len + (cur_jit & a.jit_len_mask)];
+    a.ctrl[N + e] = make_int4((int)rr.cur, (int)cur_jit, rr.n_food << 26, (int)jcache);
     reinterpret_cast<T *>(a.ep_return)[e] = 0;
+}
+
+// ctrl rec1.w = first jitter word at every env's jitter cursor (salp_refresh_rng)
+static __global__ void __launch_bounds__(256) salp_refresh_rng_kernel(const __grid_constant__ KernelArgs a) {
+    const long long e = a.first + (long long)blockIdx.x * 256 + threadIdx.x;
+    if (e >= a.first + a.count) return;
+    int4 c1 = a.ctrl[a.N + e];
+    const unsigned trow = (unsigned)e % a.rows;
+    c1.w = (int)a.jit_words[(size_t)trow * a.jit_len + ((unsigned)c1.y & a.jit_len_mask)];
+    a.ctrl[a.N + e] = c1;
 }
 
 }  // namespace salp

@@ -171,6 +171,12 @@ class SalpVectorEnv(VectorEnv):
         b.table_rows, b.food_len, b.jit_len = self.table_rows, self.food_table_len, self.jitter_table_len
         b.max_substeps = self.max_substeps
         _capi.check(self._L.salp_bind(self._handle, C.byref(b)))
+        self.refresh_rng()
+
+    def refresh_rng(self) -> None:
+        """Re-read the cached jitter word (ctrl rec1.w) after the tables or the cursors in ``ctrl`` changed."""
+        with torch.cuda.device(self.device):
+            _capi.check(self._L.salp_refresh_rng(self._handle, self._stream()))
 
     def _stream(self) -> C.c_void_p:
         return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
@@ -338,11 +344,11 @@ class SalpVectorEnv(VectorEnv):
     @property
     def current_exhale_duration(self): return (self.ctrl[0, :, 0] >> 10) & 0xFF
     @property
-    def num_food_items_per_env(self): return self.ctrl[1, :, 3]
+    def num_food_items_per_env(self): return (self.ctrl[1, :, 2] >> 26) & 0x3F
     @property
     def rng_cursors(self): return self.ctrl[1, :, 0:2]
     @property
-    def episode_length(self): return self.ctrl[1, :, 2]
+    def episode_length(self): return self.ctrl[1, :, 2] & 0x3FFFFFF
     @property
     def score(self): return self.ctrl[0, :, 2].to(torch.float64) * float(self.params.food_reward)
 
@@ -393,7 +399,8 @@ class SalpVectorEnv(VectorEnv):
             alive = torch.as_tensor(alive, device=self.device).to(torch.int64)
             bits = (alive << torch.arange(nf, device=self.device)).sum(1)
             self.ctrl[0, :, 3] = torch.where(bits >= 2 ** 31, bits - 2 ** 32, bits).to(torch.int32)
-            self.ctrl[1, :, 3] = nf
+            w = (self.ctrl[1, :, 2].to(torch.int64) & 0x3FFFFFF) | (int(nf) << 26)
+            self.ctrl[1, :, 2] = torch.where(w >= 2 ** 31, w - 2 ** 32, w).to(torch.int32)
             return
         target = getattr(self, name)
         target.copy_(torch.as_tensor(values, device=self.device).to(target.dtype).expand_as(target))
@@ -413,6 +420,7 @@ class SalpVectorEnv(VectorEnv):
             self.seed_base = int(sd["seed_base"])
             self._load_tables(self.seed_base)
             self._bind()
+        self.refresh_rng()
         self._needs_reset = False
 
 
