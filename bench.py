@@ -54,6 +54,24 @@ def algorithmic_bytes_per_env_step(n_food: int, real_bytes: int, k_fused: int = 
     return A + O + R + D + 2.0 * S / k_fused
 
 
+def min_traffic_bytes_per_env_step(n_food: int, real_bytes: int, k_fused: int = 1, act_dim: int = 1, obs_dim: int = 24) -> float:
+    """Tighter count than SURVEY 8(d): food records are read every launch but only rewritten on a respawn
+    (~1/1000 steps), so the state write-back is S minus the 2F food reals; events (1 B) are written too."""
+    A, O, R, D = real_bytes * act_dim, 4 * obs_dim, real_bytes, 3
+    S = 8 * real_bytes + 4 + 8 + 8 + (real_bytes + 4) + 2 * n_food * real_bytes + 4
+    return A + O + R + D + (2.0 * S - 2 * n_food * real_bytes) / k_fused
+
+
+def ncu_traffic_bytes(workload: str, envs: int, k_fused: int):
+    """DRAM bytes per launch of the step kernel from the committed ncu --set full capture of this
+    workload (profiles/r01_ncu_traffic.json); None when no capture matches the configuration."""
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "r01_ncu_traffic.json")))[workload]
+        return float(t["dram_bytes_per_launch"]) if (t["envs_per_launch"] == envs and k_fused == 1) else None
+    except Exception:
+        return None
+
+
 def measured_peak_gbs():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -291,6 +309,7 @@ def main():
         peak, peak_src = measured_peak_gbs()
         nf = wl["params"]["num_food_items"]
         bpe = algorithmic_bytes_per_env_step(nf, rb, K, env.act_dim, env.obs_dim)
+        bmin = min_traffic_bytes_per_env_step(nf, rb, K, env.act_dim, env.obs_dim)
         kernel_ms = ms_max / args.steps  # the timed region is nothing but back-to-back launches of this kernel
         achieved = bpe * N * K / (kernel_ms * 1e-3) / 1e9
         line = {
@@ -303,8 +322,12 @@ def main():
                              + (" (inputs larger than L2, no flush needed)" if bpe * N > 126e6 else " (L2-resident working set)"),
                        "parallelism": f"env-slab x{world} (no data-path collective; NCCL all-reduce of episode stats only)"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "kernel": "salp_step_kernel", "kernel_ms": kernel_ms,
-                         "algorithmic_bytes_per_env_step": bpe, "peak_source": peak_src},
+                         "traffic": ncu_traffic_bytes(args.workload, N, K), "kernel": "salp_step_kernel", "kernel_ms": kernel_ms,
+                         "algorithmic_bytes_per_env_step": bpe, "algorithmic_bytes_per_launch": bpe * N * K,
+                         "min_traffic_bytes_per_env_step": bmin, "achieved_min_traffic": bmin * N * K / (kernel_ms * 1e-3) / 1e9,
+                         "frac_min_traffic": bmin * N * K / (kernel_ms * 1e-3) / 1e9 / peak,
+                         "traffic_source": "profiles/r01_ncu_traffic.json (dram__bytes_read.sum + dram__bytes_write.sum per launch)",
+                         "peak_source": peak_src},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "steps": args.e2e_steps, "api": "SalpVectorEnv.step_host -> salp_step_host (pinned host buffers)"},
             "gpu_launches": launches, "clocks": clocks,

@@ -77,8 +77,8 @@ int main(int argc, char **argv) {
         P(kStoreTmaBlock, 64, 16), P(kStoreTmaBlock, 128, 8), P(kStoreTmaBlock, 256, 4), P(kStoreTmaBlock, 64, 12), P(kStoreTmaBlock, 32, 32),
         P(kStoreDirect, 64, 16), P(kStoreDirect, 128, 8), P(kStoreDirect, 64, 12),
 #else
-        V(kStoreWarp, 128, 5), V(kStoreDirect, 64, 10), V(kStoreDirect, 128, 5), V(kStoreTmaBlock, 64, 10),
-        P(kStoreDirect, 64, 10), P(kStoreDirect, 128, 5), P(kStoreDirect, 64, 8), P(kStoreWarp, 64, 10), P(kStoreTmaBlock, 64, 10), P(kStoreDirect, 128, 4),
+        V(kStoreDirect, 64, 14), V(kStoreDirect, 64, 12), V(kStoreDirect, 64, 10), V(kStoreWarp, 64, 14), V(kStoreWarp, 64, 12), V(kStoreTmaBlock, 64, 14), V(kStoreTmaBlock, 64, 12),
+        V(kStoreDirect, 128, 7), V(kStoreDirect, 128, 6), V(kStoreWarp, 128, 7), V(kStoreDirect, 32, 28), V(kStoreTmaBlock, 32, 28),
 #endif
     };
     if (argc > 4) {  // keep only variants whose name contains argv[4]

@@ -452,6 +452,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) salp_step_kernel(const __grid_con
     // (distance bits | slot) with min/max, and their offsets fetched from a shared-memory scratch by slot
     constexpr bool kFastSel = (!is_f64<T>::value) && (F > 1);
     constexpr int MU = (MT < F) ? MT : F;  // observation entries that can ever be real
+    constexpr unsigned kSlotMask = F <= 2 ? 1u : (F <= 4 ? 3u : (F <= 8 ? 7u : (F <= 16 ? 15u : 31u)));  // slot bits of a selection key
     __shared__ float2 s_sel[kFastSel ? F * BLOCK : 1];  // [slot][thread] (dx, dy) of this substep
 
     Vec4<T> *g_body = reinterpret_cast<Vec4<T> *>(a.body);
@@ -516,10 +517,12 @@ __global__ void __launch_bounds__(BLOCK, MINB) salp_step_kernel(const __grid_con
                 b0 = reinterpret_cast<const Vec4<T> *>(sb + kOffB0)[tid];
                 b1 = reinterpret_cast<const Vec4<T> *>(sb + kOffB1)[tid];
                 ep_ret = reinterpret_cast<const T *>(sb + kOffEp)[tid];
+                if constexpr (!kFastSel) {
     #pragma unroll
-                for (int f = 0; f < F; ++f) {
-                    const Vec2<T> v = reinterpret_cast<const Vec2<T> *>(sb + kOffFood)[f * BLOCK + tid];
-                    fx[f] = v.x; fy[f] = v.y;
+                    for (int f = 0; f < F; ++f) {
+                        const Vec2<T> v = reinterpret_cast<const Vec2<T> *>(sb + kOffFood)[f * BLOCK + tid];
+                        fx[f] = v.x; fy[f] = v.y;
+                    }
                 }
             }
         } else if (valid) {
@@ -528,10 +531,12 @@ __global__ void __launch_bounds__(BLOCK, MINB) salp_step_kernel(const __grid_con
             b0 = g_body[e];
             b1 = g_body[(size_t)N + e];
             ep_ret = g_epret[e];
+            if constexpr (!kFastSel) {
     #pragma unroll
-            for (int f = 0; f < F; ++f) {
-                const Vec2<T> v = g_food[(size_t)f * N + e];
-                fx[f] = v.x; fy[f] = v.y;
+                for (int f = 0; f < F; ++f) {
+                    const Vec2<T> v = g_food[(size_t)f * N + e];
+                    fx[f] = v.x; fy[f] = v.y;
+                }
             }
         }
         T px = b0.x, py = b0.y, vx = b0.z, vy = b0.w;
@@ -584,6 +589,15 @@ __global__ void __launch_bounds__(BLOCK, MINB) salp_step_kernel(const __grid_con
                 else jcache = ld_evict_last_u1(jit_row + ((cur_jit + 2u) & a.jit_len_mask));
             }
 #endif
+            // ---- kFastSel: the food records are read here, every substep (HBM at k = 0, L1/L2 afterwards;
+            //      they only ever change through the slow paths, which write HBM), so that no food array
+            //      has to stay in registers across the observation assembly.  Issued before the integrator
+            //      so the loads are in flight while it runs.
+            Vec2<T> fv[kFastSel ? F : 1];
+            if constexpr (kFastSel) {
+    #pragma unroll
+                for (int f = 0; f < F; ++f) fv[f] = valid ? g_food[(size_t)f * N + e] : Vec2<T>{0, 0};
+            }
             // ---- action (R:121-135)
             T act0 = 0, act1 = 0;
             if (PF && k == 0) {
@@ -613,7 +627,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) salp_step_kernel(const __grid_con
     #pragma unroll
                 for (int f = 0; f < F; ++f) s_sel[f * BLOCK + tid] = make_float2((float)dx[f], (float)dy[f]);
             }
-            auto select_top = [&]() {};
+            auto reselect = [&]() {};
 #else
             bool inhaling;
             T dir;
@@ -716,14 +730,65 @@ __global__ void __launch_bounds__(BLOCK, MINB) salp_step_kernel(const __grid_con
                 else if (py > H - margin) { py = H - margin; vy = -abs_(vy) * (T)0.4; omega *= (T)0.7; }
             }
             // ---- food distances (shared by hit test S:204-217, reward S:350-364 and obs S:375-379)
-            T dx[F], dy[F], dd[F];
-    #pragma unroll
-            for (int f = 0; f < F; ++f) {
-                dx[f] = fx[f] - px; dy[f] = fy[f] - py;
-                dd[f] = sqrt_(dx[f] * dx[f] + dy[f] * dy[f]);
-            }
+            T dx[kFastSel ? 1 : F], dy[kFastSel ? 1 : F], dd[kFastSel ? 1 : F];
             bool hit = false;
-            {
+            bool any_food = false;
+            T near_x = 0, near_y = 0, near_rel = 0;
+            unsigned key[MU];   // kFastSel: sorted keys of the MU nearest live foods
+            T dist_sum = 0;     // kFastSel: sum of live-food distances (slot order)
+            // key = distance in 32-bit fixed point (diag -> 2^32, saturating) with the slot in the low bits:
+            // unsigned order == (distance, slot) order at a resolution of diag / 2^(32 - slot bits)
+            // (3.7e-6 px for 12 foods in the 800 x 600 tank, finer than one f32 ulp of the distance itself).
+            // Eaten foods sort last.
+            const float key_scale = (float)a.inv_diag * (4294967296.0f * 0.9999f);
+            auto make_key = [&](T d, int f) -> unsigned { return (__float2uint_rz((float)d * key_scale) & ~kSlotMask) | (unsigned)f; };
+            auto insert_key = [&](unsigned c) {
+    #pragma unroll
+                for (int i = 0; i < MU; ++i) { const unsigned lo = min(key[i], c); c = max(key[i], c); key[i] = lo; }
+            };
+            // rare paths (a food was eaten / the env was reset): redo the selection from the (dx, dy) scratch
+            auto reselect = [&]() {
+                dist_sum = 0;
+    #pragma unroll
+                for (int i = 0; i < MU; ++i) key[i] = 0xffffffffu;
+    #pragma unroll 1
+                for (int f = 0; f < F; ++f) {
+                    const float2 v = s_sel[f * BLOCK + tid];
+                    const T d = sqrt_((T)v.x * (T)v.x + (T)v.y * (T)v.y);
+                    const bool alive = (mask >> f) & 1u;
+                    if (alive) dist_sum += d;
+                    insert_key(alive ? make_key(d, f) : (~kSlotMask | (unsigned)f));
+                }
+            };
+            if constexpr (kFastSel) {
+                // one pass per food: offset, distance, hit bit, key insertion, scratch store -- nothing but the
+                // MU keys, the hit bits and the distance sum survives it
+                const T reach = radius + (T)kc::FOOD_R;
+                unsigned hitbits = 0u;
+    #pragma unroll
+                for (int i = 0; i < MU; ++i) key[i] = 0xffffffffu;
+    #pragma unroll
+                for (int f = 0; f < F; ++f) {
+                    const T ox = fv[f].x - px, oy = fv[f].y - py;
+                    const T d = sqrt_(ox * ox + oy * oy);
+                    s_sel[f * BLOCK + tid] = make_float2((float)ox, (float)oy);
+                    const bool alive = (mask >> f) & 1u;
+                    if (d < reach) hitbits |= 1u << f;
+                    if (alive) dist_sum += d;
+                    insert_key(alive ? make_key(d, f) : (~kSlotMask | (unsigned)f));
+                }
+                hitbits &= mask;  // S:204-217: the first live food within reach is eaten
+                if (hitbits != 0u) {
+                    hit = true;
+                    mask &= ~(hitbits & (0u - hitbits));
+                    reselect();
+                }
+            } else {
+    #pragma unroll
+                for (int f = 0; f < F; ++f) {
+                    dx[f] = fx[f] - px; dy[f] = fy[f] - py;
+                    dd[f] = sqrt_(dx[f] * dx[f] + dy[f] * dy[f]);
+                }
                 const T reach = radius + (T)kc::FOOD_R;
     #pragma unroll
                 for (int f = 0; f < F; ++f)
@@ -741,35 +806,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) salp_step_kernel(const __grid_con
             if (collision) reward += (T)a.collision_penalty;
             // nearest live food (strict <, first index wins: S:350-364).  Its bearing is used by the
             // alignment reward AND, when no food was eaten this step, is the first observation entry.
-            bool any_food = false;
-            T near_x = 0, near_y = 0, near_rel = 0;
-            unsigned key[MU];   // kFastSel: sorted keys of the MU nearest live foods
-            T dist_sum = 0;     // kFastSel: sum of live-food distances (slot order)
-            // key = distance in 32-bit fixed point (diag -> 2^32, saturating) with the slot in the low kSlotBits
-            // bits: unsigned order == (distance, slot) order at a resolution of diag / 2^(32 - kSlotBits)
-            // (3.7e-6 px for 12 foods in the 800 x 600 tank, finer than one f32 ulp of the distance itself).
-            // Eaten foods sort last.
-            constexpr unsigned kSlotMask = F <= 2 ? 1u : (F <= 4 ? 3u : (F <= 8 ? 7u : (F <= 16 ? 15u : 31u)));
-            const float key_scale = (float)a.inv_diag * (4294967296.0f * 0.9999f);
-            auto make_key = [&](T d, int f) -> unsigned { return (__float2uint_rz((float)d * key_scale) & ~kSlotMask) | (unsigned)f; };
-            auto insert_key = [&](unsigned c) {
-    #pragma unroll
-                for (int i = 0; i < MU; ++i) { const unsigned lo = min(key[i], c); c = max(key[i], c); key[i] = lo; }
-            };
-            auto select_top = [&]() {
-                dist_sum = 0;
-    #pragma unroll
-                for (int i = 0; i < MU; ++i) key[i] = 0xffffffffu;
-    #pragma unroll
-                for (int f = 0; f < F; ++f) {
-                    const bool alive = (mask >> f) & 1u;
-                    if (alive) dist_sum += dd[f];
-                    insert_key(alive ? make_key(dd[f], f) : (~kSlotMask | (unsigned)f));
-                    s_sel[f * BLOCK + tid] = make_float2((float)dx[f], (float)dy[f]);
-                }
-            };
             if constexpr (kFastSel) {
-                select_top();
                 any_food = mask != 0u;
                 const float2 nv = s_sel[(key[0] & kSlotMask) * BLOCK + tid];
                 near_x = nv.x; near_y = nv.y;
@@ -790,18 +827,23 @@ __global__ void __launch_bounds__(BLOCK, MINB) salp_step_kernel(const __grid_con
                 if (a.respawn) {
                     const RespawnResult<T> r = respawn_slow<T>(a, e, px, py, mask, n_food, cur_food);
                     mask = r.mask; cur_food = r.cur;
-    #pragma unroll
-                    for (int f = 0; f < F; ++f)
-                        if (f == r.slot) {
-                            fx[f] = r.x; fy[f] = r.y;
-                            dx[f] = r.x - px; dy[f] = r.y - py;
-                            dd[f] = sqrt_(dx[f] * dx[f] + dy[f] * dy[f]);
-                            if constexpr (kFastSel) {  // the new food joins the selection made before it existed
-                                dist_sum += dd[f];
-                                insert_key(make_key(dd[f], f));
-                                s_sel[f * BLOCK + tid] = make_float2((float)dx[f], (float)dy[f]);
-                            }
+                    if constexpr (kFastSel) {  // the new food joins the selection made before it existed
+                        if (r.slot >= 0) {
+                            const T ox = r.x - px, oy = r.y - py;
+                            const T d = sqrt_(ox * ox + oy * oy);
+                            s_sel[r.slot * BLOCK + tid] = make_float2((float)ox, (float)oy);
+                            dist_sum += d;
+                            insert_key(make_key(d, r.slot));
                         }
+                    } else {
+    #pragma unroll
+                        for (int f = 0; f < F; ++f)
+                            if (f == r.slot) {
+                                fx[f] = r.x; fy[f] = r.y;
+                                dx[f] = r.x - px; dy[f] = r.y - py;
+                                dd[f] = sqrt_(dx[f] * dx[f] + dy[f] * dy[f]);
+                            }
+                    }
                 }
             }
             // ---- termination (S:182-189): collision > timeout > all collected
@@ -978,11 +1020,13 @@ __global__ void __launch_bounds__(BLOCK, MINB) salp_step_kernel(const __grid_con
                     px = W / 2; py = H / 2; vx = 0; vy = 0; angle = 0; omega = 0; nozzle = 0; wv = 0;
                     phase = kPhaseRest; timer = 0; skind = kShapeReset; stimer = 0;
                     steps_since_food = 0; food_collected = 0; ep_ret = 0; ep_len = 0;
+                    if constexpr (!kFastSel) {
     #pragma unroll
-                    for (int f = 0; f < F; ++f) {
-                        if (f < n_food) {
-                            const Vec2<T> v = g_food[(size_t)f * N + e];
-                            fx[f] = v.x; fy[f] = v.y;
+                        for (int f = 0; f < F; ++f) {
+                            if (f < n_food) {
+                                const Vec2<T> v = g_food[(size_t)f * N + e];
+                                fx[f] = v.x; fy[f] = v.y;
+                            }
                         }
                     }
                 }
@@ -994,10 +1038,12 @@ __global__ void __launch_bounds__(BLOCK, MINB) salp_step_kernel(const __grid_con
                 const unsigned e_src = __shfl_sync(0xffffffffu, e, src);
                 const LayoutResult<T> L = layout_warp<T>(a, e_src, __shfl_sync(0xffffffffu, cur_food, src), lane);
                 if (lane < L.n_food) reinterpret_cast<Vec2<T> *>(a.food)[(size_t)lane * N + e_src] = Vec2<T>{L.x, L.y};
+                if constexpr (!kFastSel) {
     #pragma unroll
-                for (int f = 0; f < F; ++f) {  // food f's position lives in lane f: hand it to the env's own lane
-                    const T tx = __shfl_sync(0xffffffffu, L.x, f), ty = __shfl_sync(0xffffffffu, L.y, f);
-                    if (lane == src && f < L.n_food) { fx[f] = tx; fy[f] = ty; }
+                    for (int f = 0; f < F; ++f) {  // food f's position lives in lane f: hand it to the env's own lane
+                        const T tx = __shfl_sync(0xffffffffu, L.x, f), ty = __shfl_sync(0xffffffffu, L.y, f);
+                        if (lane == src && f < L.n_food) { fx[f] = tx; fy[f] = ty; }
+                    }
                 }
                 if (lane == src) {
                     cur_food = L.cur; n_food = L.n_food;
@@ -1012,13 +1058,26 @@ __global__ void __launch_bounds__(BLOCK, MINB) salp_step_kernel(const __grid_con
                 radius = (T)kc::BASE_R;
                 hit = true;  // the bearing computed for the reward belongs to the finished episode
             }
-            // distances for the second trip, for every lane (the validation build sorts dd[] in place)
+            if constexpr (kFastSel) {
+                // second trip: offsets of the (new) foods from the (new) position, re-read from HBM where the
+                // other lanes of this warp have just written them, then the selection again
+                __syncwarp();
+                if (done) {
+    #pragma unroll 1
+                    for (int f = 0; f < F; ++f) {
+                        const Vec2<T> v = g_food[(size_t)f * N + e];
+                        s_sel[f * BLOCK + tid] = make_float2((float)(v.x - px), (float)(v.y - py));
+                    }
+                    reselect();
+                }
+            } else {
+                // distances for the second trip, for every lane (the validation build sorts dd[] in place)
     #pragma unroll
-            for (int f = 0; f < F; ++f) {
-                dx[f] = fx[f] - px; dy[f] = fy[f] - py;
-                dd[f] = sqrt_(dx[f] * dx[f] + dy[f] * dy[f]);
+                for (int f = 0; f < F; ++f) {
+                    dx[f] = fx[f] - px; dy[f] = fy[f] - py;
+                    dd[f] = sqrt_(dx[f] * dx[f] + dy[f] * dy[f]);
+                }
             }
-            if constexpr (kFastSel) select_top();
             }
             }  // pass
             // ---- publish the observation tile
