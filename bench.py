@@ -11,6 +11,7 @@ interact, so ranks share nothing on the data path):
     single_food_1m   configs/single_food.yaml, 1,048,576 envs / GPU, fp32          [default]
     long_horizon_64k configs/single_food_long_horizon.yaml, 65,536 envs / GPU, fp32 (configs[2])
     defaults_1m      configs/defaults.yaml (12 food), 1,048,576 envs / GPU, fp32   (configs[3])
+    sac_rollout_256k configs/sac_gail.yaml, 262,144 envs / GPU, actor MLP + env step + replay append (configs[4])
     parity_4k        configs/single_food.yaml, 4,096 envs, fp64 validation build   (configs[1])
 Prints ONE JSON line (rank 0).  See DESIGN.md section "Measurement" for every field.
 """
@@ -41,6 +42,9 @@ WORKLOADS = {
     "long_horizon_64k": dict(yaml="configs/single_food_long_horizon.yaml", params=LONG_HORIZON, envs=1 << 16, dtype="float32"),
     "defaults_1m": dict(yaml="configs/defaults.yaml", params=DEFAULTS, envs=1 << 20, dtype="float32"),
     "parity_4k": dict(yaml="configs/single_food.yaml", params=SINGLE_FOOD, envs=1 << 12, dtype="float64"),
+    # configs[4]: SAC rollout collection -- [24->256->256->2] tanh-Gaussian actor (torch, bf16) -> env kernel ->
+    # replay-append kernel, replayed from a CUDA graph; a "step" is one env step of that loop for every env
+    "sac_rollout_256k": dict(yaml="configs/sac_gail.yaml", params=DEFAULTS, envs=1 << 18, dtype="float32", rollout=True),
 }
 METRIC = "salp_env_steps_per_sec"
 UNIT = "env-steps/s"
@@ -212,6 +216,8 @@ def main():
                          "(steady state: resets, respawns and divergent breathing phases inside the timed region)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
+    args.steps += args.steps % 2  # the rollout workload replays two env steps per graph launch
+    args.warmup += args.warmup % 2
     wl = dict(WORKLOADS[args.workload])
     if args.envs_per_gpu:
         wl["envs"] = args.envs_per_gpu
@@ -234,17 +240,33 @@ def main():
         dist.init_process_group("nccl", device_id=dev)
 
     N, K = wl["envs"], args.substeps
+    rollout = bool(wl.get("rollout"))
+    if rollout:
+        K = 1
     real = torch.float64 if wl["dtype"] == "float64" else torch.float32
     env = SalpVectorEnv(N, device=dev, dtype=wl["dtype"], seed=10_000, env_id0=rank * N, food_table_len=128,
-                        jitter_table_len=512, max_substeps=K, autoreset=True, **wl["params"])
+                        jitter_table_len=512, max_substeps=2 if rollout else K, autoreset=True, **wl["params"])
     env.reset()
     # synthetic actions, resident in HBM before the timed region: a pool of 32 [K, N, 1] tensors
     gen = torch.Generator(device=dev)
     gen.manual_seed(1234 + rank)
     pool = [torch.rand(K, N, env.act_dim, device=dev, dtype=real, generator=gen) * 2 - 1 for _ in range(32)]
 
+    launches_per_step = 1
+    if rollout:
+        from underwater_swimmer_rl_b200.rollout import DeviceReplayBuffer, RolloutCollector, TanhGaussianActor
+        torch.manual_seed(1234 + rank)
+        actor = TanhGaussianActor(env.obs_dim, env.act_dim, (256, 256)).to(dev).to(torch.bfloat16)
+        ring = DeviceReplayBuffer(4 * N, env.obs_dim, env.act_dim, dev)
+        col = RolloutCollector(env, actor, ring)
+        replay2 = col.capture()  # one graph launch = two env steps of (actor -> env kernel -> replay append)
+        launches_per_step = 3    # ours, per env step: salp_step_kernel, replay_append_kernel, replay_advance_kernel
+
     def one_step(i):
-        if K == 1:
+        if rollout:
+            if i % 2 == 0:
+                replay2()
+        elif K == 1:
             env.step(pool[i % 32][0])
         else:
             env.step_many(pool[i % 32], K)
@@ -272,12 +294,24 @@ def main():
         dist.barrier()
     torch.cuda.synchronize()
     clocks = sampler.stop() if rank == 0 else None
-    launches = env.launch_count - launches0
+    launches = (env.launch_count - launches0) if not rollout else launches_per_step * args.steps
     t = torch.tensor([ms], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_max = float(t.item())
     value = world * N * K * args.steps / (ms_max * 1e-3)
+
+    env_only_ms = None
+    if rollout:  # the env kernel alone, for the roofline of THE kernel inside the rollout step
+        for i in range(10):
+            env.step(pool[i % 32][0])
+        torch.cuda.synchronize()
+        ev0.record()
+        for i in range(200):
+            env.step(pool[i % 32][0])
+        ev1.record()
+        torch.cuda.synchronize()
+        env_only_ms = ev0.elapsed_time(ev1) / 200
 
     # ---- e2e: the reference-facing call with HOST buffers (H2D actions, step, D2H results) ----
     a_h = (torch.rand(N, env.act_dim, dtype=real) * 2 - 1).pin_memory()
@@ -311,13 +345,15 @@ def main():
         bpe = algorithmic_bytes_per_env_step(nf, rb, K, env.act_dim, env.obs_dim)
         bmin = min_traffic_bytes_per_env_step(nf, rb, K, env.act_dim, env.obs_dim)
         kernel_ms = ms_max / args.steps  # the timed region is nothing but back-to-back launches of this kernel
+        if rollout:
+            kernel_ms = env_only_ms  # env kernel timed alone; the step also holds the actor GEMMs and the append
         achieved = bpe * N * K / (kernel_ms * 1e-3) / 1e9
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f64" if real == torch.float64 else "f32", "data": "synthetic",
             "config": {"workload": args.workload, "reference_yaml": wl["yaml"], "envs_per_gpu": N, "global_envs": world * N,
-                       "substeps_per_launch": K, "prime_steps": args.prime_steps, "obs_dim": env.obs_dim, "act_dim": env.act_dim, "autoreset": True,
+                       "substeps_per_launch": K, "rollout": ("actor MLP [24-256-256-2] bf16 (torch) -> salp_step_kernel -> salp_replay_append, CUDA graph of 2 steps; env kernel share of the step = %.2f" % (env_only_ms / (ms_max / args.steps))) if rollout else None, "prime_steps": args.prime_steps, "obs_dim": env.obs_dim, "act_dim": env.act_dim, "autoreset": True,
                        "l2": f"per-step footprint {bpe * N / 1e6:.0f} MB vs 126 MB L2"
                              + (" (inputs larger than L2, no flush needed)" if bpe * N > 126e6 else " (L2-resident working set)"),
                        "parallelism": f"env-slab x{world} (no data-path collective; NCCL all-reduce of episode stats only)"},

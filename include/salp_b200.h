@@ -188,6 +188,13 @@ int salp_refresh_rng(SalpHandle *h, void *cuda_stream);
 int salp_step(SalpHandle *h, int K, const void *actions, void *cuda_stream);
 
 /*
+ * One env step whose outputs go to row `slot` (0 <= slot < buffers.max_substeps) of the [K][N]...
+ * output buffers instead of row 0, so that a caller can keep the previous step's observation
+ * alive (ping-pong) -- e.g. to store (obs, action, reward, next_obs) transitions without a copy.
+ */
+int salp_step_slot(SalpHandle *h, int slot, const void *actions, void *cuda_stream);
+
+/*
  * Host-buffer convenience path (what a caller holding numpy arrays uses): copies
  * actions host->device (into the caller-owned DEVICE staging buffer `actions_staging`,
  * real [N][act_dim]), runs one step (K=1), copies obs/reward/terminated/truncated
@@ -206,6 +213,40 @@ int salp_step_host(SalpHandle *h, void *actions_staging, const void *actions_hos
  */
 int salp_fill_rng_words(uint32_t *dst, int64_t rows, int64_t len, uint64_t seed0, int64_t first_row,
                         int kind, int num_threads);
+
+/*
+ * Rollout -> replay, on the device.  Replaces the per-step
+ *     replay_buffer.add(obs, action, reward, next_obs, done or truncated)
+ * of the reference's episode loops (src/salp/training/continuous_trainer.py:296-303,
+ * trainer.py:203-216) for all N envs of one step: appends N transitions to a caller-owned f32
+ * ring buffer at rows (*head + e) mod capacity and advances *head (and *size, saturating).
+ * next_obs of a lane whose episode ended is taken from `final_obs` (the terminal observation,
+ * as the reference -- which never auto-resets -- would store); pass NULL without auto-reset.
+ * With reward_aux != NULL the stored reward is w_env * reward + w_aux * reward_aux (the GAIL
+ * mixing of src/salp/config/base_config.py:77-78).  `head`/`size` are DEVICE int64 scalars so the
+ * call is CUDA-graph capturable.  Independent of any SalpHandle; asynchronous on `cuda_stream`.
+ */
+typedef struct SalpReplayAppend {
+    const float *obs_prev;      /* [n][obs_dim]  observation the actions were computed from */
+    const void *actions;        /* [n][act_dim]  real (dtype)                               */
+    const void *reward;         /* [n]           real (dtype)                               */
+    const float *reward_aux;    /* [n] f32 or NULL                                          */
+    const uint8_t *terminated;  /* [n]                                                      */
+    const uint8_t *truncated;   /* [n]                                                      */
+    const float *obs_next;      /* [n][obs_dim]  obs returned by the step                   */
+    const float *final_obs;     /* [n][obs_dim]  or NULL                                    */
+    float *rb_obs, *rb_act, *rb_rew, *rb_next; /* ring: [C][obs_dim], [C][act_dim], [C], [C][obs_dim] */
+    uint8_t *rb_done;           /* ring: [C]                                                */
+    int64_t *head;              /* device scalar                                            */
+    int64_t *size;              /* device scalar or NULL                                    */
+    int64_t n, capacity;        /* 0 < n <= capacity                                        */
+    int32_t obs_dim, act_dim;   /* obs_dim % 4 == 0                                         */
+    int32_t dtype;              /* SALP_F32 / SALP_F64: type of actions and reward          */
+    float w_env, w_aux;
+    int32_t reserved_;
+} SalpReplayAppend;
+
+int salp_replay_append(const SalpReplayAppend *p, void *cuda_stream);
 
 /* Number of kernels this library has launched on behalf of `h` (bench "gpu_launches"). */
 int64_t salp_launch_count(const SalpHandle *h);

@@ -1,0 +1,103 @@
+"""GPU: rollout -> replay path (rollout.py over salp_step_slot + salp_replay_append), SURVEY 8(f) N2/N3.
+The ring contents are checked against the same transitions assembled with plain torch indexing."""
+import numpy as np
+import pytest
+import torch
+
+from helpers import CONFIGS
+
+pytestmark = pytest.mark.gpu
+
+
+def _mk(n, cap, disc=False, dtype="float32", seed=3):
+    from underwater_swimmer_rl_b200 import SalpVectorEnv
+    from underwater_swimmer_rl_b200.rollout import DeviceReplayBuffer, GailDiscriminator, RolloutCollector, TanhGaussianActor
+    torch.manual_seed(seed)
+    env = SalpVectorEnv(n, device="cuda:0", dtype=dtype, max_substeps=2, seed=555, **CONFIGS["sac_gail"])
+    actor = TanhGaussianActor(env.obs_dim, env.act_dim).cuda()
+    buf = DeviceReplayBuffer(cap, env.obs_dim, env.act_dim, "cuda:0")
+    d = GailDiscriminator(env.obs_dim, env.act_dim).cuda() if disc else None
+    return env, actor, buf, RolloutCollector(env, actor, buf, discriminator=d, deterministic=True)
+
+
+@pytest.mark.parametrize("dtype", ["float32", "float64"])
+def test_ring_holds_the_transitions_the_reference_loop_would_store(salp_lib, dtype):
+    n, cap, T = 1000, 300 * 1000 + 500, 900  # capacity is not a multiple of n: rows wrap inside a step
+    env, actor, buf, col = _mk(n, cap, dtype=dtype)
+    col.reset()
+    # force early episode ends so that final_obs rows are exercised inside the window kept by the ring
+    pos = torch.stack([torch.linspace(450.0, 705.0, n), torch.full((n,), 300.0)], 1)
+    env.set_attr("robot_pos", pos.cuda())
+    exp = {k: [] for k in ("obs", "act", "rew", "next", "done")}
+    for t in range(T):
+        cur = col.cur
+        obs_prev = env.obs[cur].clone()
+        col.collect(1)
+        nxt = col.cur
+        done = env.terminated[nxt] | env.truncated[nxt]
+        exp["obs"].append(obs_prev)
+        exp["act"].append(col.act.float().clone())
+        exp["rew"].append(env.reward[nxt].float().clone())
+        exp["next"].append(torch.where(done[:, None], env.final_obs[nxt], env.obs[nxt]).clone())
+        exp["done"].append(done.clone())
+    assert len(buf) == cap and int(buf.head.item()) == (n * T) % cap
+    flat = {k: torch.cat(v) for k, v in exp.items()}
+    rows = torch.arange(n * T - cap, n * T, device="cuda")  # the last `cap` transitions survive, at row (i mod cap)
+    assert int(flat["done"][rows].sum()) > n // 4  # episodes ended inside the window the ring keeps
+    ring = rows % cap
+    assert torch.equal(buf.obs[ring], flat["obs"][rows])
+    assert torch.equal(buf.next_obs[ring], flat["next"][rows])
+    assert torch.equal(buf.act[ring], flat["act"][rows])
+    assert torch.equal(buf.rew[ring], flat["rew"][rows])
+    assert torch.equal(buf.done[ring], flat["done"][rows])
+    # next_obs of a non-final transition is the obs of the same env's next transition (n rows later)
+    r0 = rows[:-n][~flat["done"][rows[:-n]]]
+    assert torch.equal(flat["next"][r0], flat["obs"][r0 + n])
+    batch = buf.sample(256)
+    assert batch["observations"].shape == (256, env.obs_dim) and batch["dones"].dtype == torch.bool
+
+
+def test_gail_reward_mixing(salp_lib):
+    n = 512
+    env, actor, buf, col = _mk(n, 4 * n, disc=True)
+    col.reset()
+    obs_prev = env.obs[0].clone()
+    col.collect(1)
+    r_env = env.reward[col.cur].float()
+    r_gail = col.disc.predict_reward(obs_prev, col.act).reshape(-1)
+    assert torch.allclose(buf.rew[:n], 0.3 * r_env + 0.7 * r_gail, rtol=1e-5, atol=1e-6)
+    assert (r_gail > 0).all()  # -log(1 - D) with D in (0, 1)
+
+
+def test_graph_replay_equals_eager_rollout(salp_lib):
+    n, steps = 2048, 40
+    outs = []
+    for use_graph in (False, True):
+        env, actor, buf, col = _mk(n, n * 8, seed=11)
+        col.reset()
+        if use_graph:
+            replay = col.capture()       # runs 2 warm-up steps eagerly
+            for _ in range((steps - 2) // 2):
+                replay()
+        else:
+            col.collect(steps)
+        torch.cuda.synchronize()
+        assert col.steps == steps
+        outs.append((env.body.clone(), env.ctrl.clone(), buf.obs.clone(), buf.rew.clone(), buf.head.clone()))
+    for x, y in zip(*outs):
+        assert torch.equal(x, y)
+
+
+def test_expert_buffer_and_bad_arguments(salp_lib):
+    from underwater_swimmer_rl_b200 import _capi
+    from underwater_swimmer_rl_b200.rollout import DeviceExpertBuffer
+    z = np.load(__import__("os").path.join(__import__("os").path.dirname(__file__), "golden", "human_demos.npz"))
+    keys = sorted(k for k in z.files if k.endswith("_actions"))
+    eps = [{"observations": np.zeros((len(z[k]), 24), np.float32), "actions": z[k]} for k in keys]
+    eb = DeviceExpertBuffer(eps, "cuda:0")
+    b = eb.sample(128)
+    assert b["observations"].shape == (128, 24) and b["actions"].shape == (128, 1)
+    assert eb.num_transitions == sum(len(z[k]) for k in keys)
+    import ctypes as C
+    p = _capi.SalpReplayAppend()
+    assert salp_lib.salp_replay_append(C.byref(p), None) == _capi.SALP_EINVAL

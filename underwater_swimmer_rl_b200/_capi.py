@@ -20,7 +20,7 @@ EV_TERMINATED, EV_TRUNCATED, EV_COLLISION, EV_FOOD = 1, 2, 4, 8
 # every symbol include/salp_b200.h declares (tests/test_capi_symbols.py parses the header too)
 EXPORTED_SYMBOLS = (
     "salp_abi_version", "salp_last_error", "salp_query_layout", "salp_create", "salp_destroy", "salp_bind",
-    "salp_reset", "salp_refresh_rng", "salp_step", "salp_step_host", "salp_fill_rng_words", "salp_launch_count",
+    "salp_reset", "salp_refresh_rng", "salp_step", "salp_step_slot", "salp_step_host", "salp_fill_rng_words", "salp_launch_count", "salp_replay_append",
 )
 
 
@@ -53,6 +53,14 @@ class SalpBuffers(C.Structure):
     ]
 
 
+class SalpReplayAppend(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n in (
+        "obs_prev", "actions", "reward", "reward_aux", "terminated", "truncated", "obs_next", "final_obs",
+        "rb_obs", "rb_act", "rb_rew", "rb_next", "rb_done", "head", "size")] + [
+        ("n", C.c_int64), ("capacity", C.c_int64), ("obs_dim", C.c_int32), ("act_dim", C.c_int32),
+        ("dtype", C.c_int32), ("w_env", C.c_float), ("w_aux", C.c_float), ("reserved_", C.c_int32)]
+
+
 class SalpError(RuntimeError):
     def __init__(self, code: int, msg: str):
         super().__init__(f"libsalp_b200 error {code}: {msg}")
@@ -83,9 +91,11 @@ def load():
     L.salp_reset.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
     L.salp_refresh_rng.argtypes = [C.c_void_p, C.c_void_p]
     L.salp_step.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
+    L.salp_step_slot.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
     L.salp_step_host.argtypes = [C.c_void_p] + [C.c_void_p] * 6
     L.salp_fill_rng_words.argtypes = [C.c_void_p, C.c_int64, C.c_int64, C.c_uint64, C.c_int64, C.c_int, C.c_int]
     L.salp_launch_count.argtypes = [C.c_void_p]
+    L.salp_replay_append.argtypes = [C.POINTER(SalpReplayAppend), C.c_void_p]
     L.salp_launch_count.restype = C.c_int64
     if L.salp_abi_version() != SALP_ABI_VERSION:
         raise ImportError("libsalp_b200.so ABI version mismatch; rebuild it")

@@ -52,6 +52,10 @@ bool is_pow2(int64_t v) { return v > 0 && (v & (v - 1)) == 0; }
 
 }  // namespace
 
+namespace salp {
+int set_error(int code, const char *msg) { return fail(code, "%s", msg); }  // for the other translation units
+}  // namespace salp
+
 struct SalpHandle {
     SalpParams params;
     SalpLayout layout;
@@ -243,6 +247,26 @@ int salp_step(SalpHandle *h, int K, const void *actions, void *stream) {
     salp::KernelArgs a = h->base;
     a.K = K;
     a.actions = actions;
+    return launch_step(h, a, (cudaStream_t)stream);
+}
+
+int salp_step_slot(SalpHandle *h, int slot, const void *actions, void *stream) {
+    if (!h) return fail(SALP_EINVAL, "null handle");
+    if (!h->bound) return fail(SALP_EUNBOUND, "salp_bind has not been called");
+    if (!actions) return fail(SALP_EINVAL, "actions pointer is null");
+    if (slot < 0 || slot >= h->buf.max_substeps) return fail(SALP_EINVAL, "slot=%d outside 0..max_substeps-1=%d", slot, h->buf.max_substeps - 1);
+    SALP_CUDA(cudaSetDevice(h->device));
+    salp::KernelArgs a = h->base;
+    const size_t n = (size_t)h->num_envs * (size_t)slot, rb = (size_t)h->layout.real_bytes, od = (size_t)h->layout.obs_dim;
+    a.K = 1;
+    a.actions = actions;
+    a.obs += n * od;
+    a.reward = (char *)a.reward + n * rb;
+    a.terminated += n;
+    a.truncated += n;
+    if (a.events) a.events += n;
+    if (a.final_obs) a.final_obs += n * od;
+    if (a.final_info) a.final_info = (char *)a.final_info + n * 4 * rb;
     return launch_step(h, a, (cudaStream_t)stream);
 }
 

@@ -220,7 +220,7 @@ class SalpVectorEnv(VectorEnv):
             buf.copy_(torch.as_tensor(np.asarray(actions)).reshape(shape), non_blocking=True)
         return buf
 
-    def step(self, actions):
+    def step(self, actions, slot: int = 0):
         """One env step for all N envs.  ``actions``: a contiguous [N, act_dim] tensor of this
         build's dtype on this device is consumed in place (zero copy: its pointer is passed to
         the kernel); anything else (numpy, other dtype/device) is staged through a copy.
@@ -229,8 +229,11 @@ class SalpVectorEnv(VectorEnv):
             raise RuntimeError("call reset() before step()")
         a = self._stage_actions(actions, 1)
         with torch.cuda.device(self.device):
-            _capi.check(self._L.salp_step(self._handle, 1, a.data_ptr(), self._stream()))
-        return self.obs[0], self.reward[0], self.terminated[0], self.truncated[0], StepInfos(self, 0)
+            if slot == 0:
+                _capi.check(self._L.salp_step(self._handle, 1, a.data_ptr(), self._stream()))
+            else:  # outputs go to row `slot` of the [max_substeps, N, ...] buffers (ping-pong, see rollout.py)
+                _capi.check(self._L.salp_step_slot(self._handle, int(slot), a.data_ptr(), self._stream()))
+        return self.obs[slot], self.reward[slot], self.terminated[slot], self.truncated[slot], StepInfos(self, slot)
 
     def step_many(self, actions, k_steps: Optional[int] = None):
         """K fused env steps in ONE launch (open-loop actions [K, N, act_dim]): state stays in
