@@ -208,6 +208,7 @@ def main():
     ap.add_argument("--workload", default="single_food_1m", choices=sorted(WORKLOADS))
     ap.add_argument("--envs-per-gpu", type=int, default=0)
     ap.add_argument("--substeps", type=int, default=1, help="K env steps fused per launch (open-loop actions)")
+    ap.add_argument("--torch-actor", action="store_true", help="sac_rollout: torch bf16 MLP instead of the fused tcgen05 actor kernel")
     ap.add_argument("--e2e-steps", type=int, default=20)
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -256,11 +257,14 @@ def main():
     if rollout:
         from underwater_swimmer_rl_b200.rollout import DeviceReplayBuffer, RolloutCollector, TanhGaussianActor
         torch.manual_seed(1234 + rank)
-        actor = TanhGaussianActor(env.obs_dim, env.act_dim, (256, 256)).to(dev).to(torch.bfloat16)
+        from underwater_swimmer_rl_b200.rollout import FusedActor
+        actor = TanhGaussianActor(env.obs_dim, env.act_dim, (256, 256)).to(dev)
+        actor = actor.to(torch.bfloat16) if args.torch_actor else FusedActor(actor)
         ring = DeviceReplayBuffer(4 * N, env.obs_dim, env.act_dim, dev)
         col = RolloutCollector(env, actor, ring)
         replay2 = col.capture()  # one graph launch = two env steps of (actor -> env kernel -> replay append)
-        launches_per_step = 3    # ours, per env step: salp_step_kernel, replay_append_kernel, replay_advance_kernel
+        # ours, per env step: [salp_actor_kernel,] salp_step_kernel, replay_append_kernel, replay_advance_kernel
+        launches_per_step = 3 if args.torch_actor else 4
 
     def one_step(i):
         if rollout:
@@ -303,12 +307,13 @@ def main():
 
     env_only_ms = None
     if rollout:  # the env kernel alone, for the roofline of THE kernel inside the rollout step
+        env_replay = env.capture_graph(pool[0][0])  # graph replay: the Python launch path is slower than this kernel
         for i in range(10):
-            env.step(pool[i % 32][0])
+            env_replay()
         torch.cuda.synchronize()
         ev0.record()
         for i in range(200):
-            env.step(pool[i % 32][0])
+            env_replay()
         ev1.record()
         torch.cuda.synchronize()
         env_only_ms = ev0.elapsed_time(ev1) / 200
@@ -353,7 +358,7 @@ def main():
             "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f64" if real == torch.float64 else "f32", "data": "synthetic",
             "config": {"workload": args.workload, "reference_yaml": wl["yaml"], "envs_per_gpu": N, "global_envs": world * N,
-                       "substeps_per_launch": K, "rollout": ("actor MLP [24-256-256-2] bf16 (torch) -> salp_step_kernel -> salp_replay_append, CUDA graph of 2 steps; env kernel share of the step = %.2f" % (env_only_ms / (ms_max / args.steps))) if rollout else None, "prime_steps": args.prime_steps, "obs_dim": env.obs_dim, "act_dim": env.act_dim, "autoreset": True,
+                       "substeps_per_launch": K, "rollout": ("actor MLP [24-256-256-2] bf16 (" + ("torch" if args.torch_actor else "salp_actor_kernel, tcgen05") + ") -> salp_step_kernel -> salp_replay_append, CUDA graph of 2 steps; env kernel share of the step = %.2f" % (env_only_ms / (ms_max / args.steps))) if rollout else None, "prime_steps": args.prime_steps, "obs_dim": env.obs_dim, "act_dim": env.act_dim, "autoreset": True,
                        "l2": f"per-step footprint {bpe * N / 1e6:.0f} MB vs 126 MB L2"
                              + (" (inputs larger than L2, no flush needed)" if bpe * N > 126e6 else " (L2-resident working set)"),
                        "parallelism": f"env-slab x{world} (no data-path collective; NCCL all-reduce of episode stats only)"},

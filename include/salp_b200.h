@@ -248,6 +248,33 @@ typedef struct SalpReplayAppend {
 
 int salp_replay_append(const SalpReplayAppend *p, void *cuda_stream);
 
+/*
+ * The rollout loop's policy step, fused: actions = tanh(mean + exp(clamp(log_std,-20,2)) * noise) with
+ * (mean, log_std) = MLP(obs), for the reference's SAC actor shape obs -> 256 -> 256 -> 2*act with ReLU
+ * (record_model.py:27-53; `agent.select_action(obs)` at src/salp/training/continuous_trainer.py:293).
+ * One sm_100a kernel: bf16 tcgen05 MMAs with the accumulator in TMEM, weights resident in shared
+ * memory, f32 epilogues; `obs` is read in place, `actions` written in the env build's real type.
+ *   w1_packed / w2_packed: bf16 weights [256][K] (K = obs_dim zero-padded to 32, resp. 256) re-laid as
+ *   [K/8][256][8] (rollout.pack_weight) -- the tcgen05 K-major operand layout.  w3: f32 [2*act][256].
+ *   noise: f32 [n][act] standard normal draws, or NULL for the deterministic action tanh(mean).
+ * Restrictions: hidden == 256, obs_dim % 4 == 0 and <= 32, act_dim in {1, 2}; otherwise SALP_EUNSUPPORTED.
+ */
+typedef struct SalpActorForward {
+    const float *obs;        /* [n][obs_dim] */
+    const void *w1_packed;   /* bf16 [4][256][8]  */
+    const float *b1;         /* [256] */
+    const void *w2_packed;   /* bf16 [32][256][8] */
+    const float *b2;         /* [256] */
+    const float *w3;         /* [2*act_dim][256] */
+    const float *b3;         /* [2*act_dim] */
+    const float *noise;      /* [n][act_dim] or NULL */
+    void *actions;           /* [n][act_dim] real (dtype) */
+    int64_t n;
+    int32_t obs_dim, act_dim, hidden, dtype;
+} SalpActorForward;
+
+int salp_actor_forward(const SalpActorForward *p, void *cuda_stream);
+
 /* Number of kernels this library has launched on behalf of `h` (bench "gpu_launches"). */
 int64_t salp_launch_count(const SalpHandle *h);
 

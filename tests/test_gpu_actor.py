@@ -1,0 +1,65 @@
+"""GPU: the fused tcgen05 actor kernel (csrc/salp_actor.cu) against the torch module it replaces
+(rollout.TanhGaussianActor == record_model.py:27-53), evaluated in fp32 from the same bf16-rounded weights."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _ref(actor, obs, noise):
+    """fp32 evaluation with the roundings the kernel makes: bf16 weights, bf16 inputs to both hidden GEMMs."""
+    bf = lambda t: t.to(torch.bfloat16).float()  # noqa: E731
+    l1, l2, l3 = actor.layers
+    h = torch.relu(bf(obs) @ bf(l1.weight).T + l1.bias.float())
+    h = torch.relu(bf(h) @ bf(l2.weight).T + l2.bias.float())
+    out = h @ bf(l3.weight).T + l3.bias.float()
+    mean, log_std = out.chunk(2, dim=-1)
+    if noise is None:
+        return torch.tanh(mean)
+    return torch.tanh(mean + torch.exp(torch.clamp(log_std, -20, 2)) * noise)
+
+
+@pytest.mark.parametrize("n,obs_dim,act_dim", [(128, 24, 1), (1000, 24, 1), (70001, 24, 1), (4096, 24, 2), (513, 32, 2), (300, 16, 1)])
+def test_fused_actor_matches_torch(salp_lib, n, obs_dim, act_dim):
+    from underwater_swimmer_rl_b200.rollout import FusedActor, TanhGaussianActor
+    torch.manual_seed(n + obs_dim)
+    actor = TanhGaussianActor(obs_dim, act_dim).cuda()
+    with torch.no_grad():
+        for l in actor.layers:  # larger weights than the default init so that errors would show
+            l.weight.mul_(2.0)
+            l.bias.uniform_(-0.5, 0.5)
+    fused = FusedActor(actor)
+    obs = (torch.rand(n, obs_dim, device="cuda") * 2 - 1)
+    noise = torch.randn(n, act_dim, device="cuda")
+    for nz, out_dtype in ((None, torch.float32), (noise, torch.float32), (noise, torch.float64)):
+        out = torch.full((n, act_dim), 7.0, device="cuda", dtype=out_dtype)
+        fused(obs, out, deterministic=nz is None, noise=nz)
+        torch.cuda.synchronize()
+        with torch.no_grad():
+            ref = _ref(actor, obs, nz)
+        err = (out.float() - ref).abs().max().item()
+        assert err <= 5e-3, (err, nz is None, out_dtype)
+        assert out.abs().max().item() <= 1.0
+
+
+def test_fused_actor_in_the_rollout_loop(salp_lib):
+    """Collector with the fused actor == collector with the torch actor up to the actor's bf16 rounding:
+    same env trajectories for a while (deterministic policy), and the graph replay path works."""
+    from helpers import CONFIGS
+    from underwater_swimmer_rl_b200 import SalpVectorEnv
+    from underwater_swimmer_rl_b200.rollout import DeviceReplayBuffer, FusedActor, RolloutCollector, TanhGaussianActor
+    n = 4096
+    torch.manual_seed(5)
+    actor = TanhGaussianActor(24, 1).cuda()
+    env = SalpVectorEnv(n, device="cuda:0", max_substeps=2, seed=77, **CONFIGS["sac_gail"])
+    buf = DeviceReplayBuffer(8 * n, 24, 1, "cuda:0")
+    col = RolloutCollector(env, FusedActor(actor), buf, deterministic=True)
+    col.reset()
+    replay = col.capture()
+    for _ in range(10):
+        replay()
+    torch.cuda.synchronize()
+    assert col.steps == 22 and len(buf) == 8 * n
+    with torch.no_grad():
+        a_ref = _ref(actor, buf.obs[:n], None)
+    assert (buf.act[:n] - a_ref).abs().max().item() <= 5e-3

@@ -20,7 +20,7 @@ EV_TERMINATED, EV_TRUNCATED, EV_COLLISION, EV_FOOD = 1, 2, 4, 8
 # every symbol include/salp_b200.h declares (tests/test_capi_symbols.py parses the header too)
 EXPORTED_SYMBOLS = (
     "salp_abi_version", "salp_last_error", "salp_query_layout", "salp_create", "salp_destroy", "salp_bind",
-    "salp_reset", "salp_refresh_rng", "salp_step", "salp_step_slot", "salp_step_host", "salp_fill_rng_words", "salp_launch_count", "salp_replay_append",
+    "salp_reset", "salp_refresh_rng", "salp_step", "salp_step_slot", "salp_step_host", "salp_fill_rng_words", "salp_launch_count", "salp_replay_append", "salp_actor_forward",
 )
 
 
@@ -61,6 +61,11 @@ class SalpReplayAppend(C.Structure):
         ("dtype", C.c_int32), ("w_env", C.c_float), ("w_aux", C.c_float), ("reserved_", C.c_int32)]
 
 
+class SalpActorForward(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n in ("obs", "w1_packed", "b1", "w2_packed", "b2", "w3", "b3", "noise", "actions")] + [
+        ("n", C.c_int64), ("obs_dim", C.c_int32), ("act_dim", C.c_int32), ("hidden", C.c_int32), ("dtype", C.c_int32)]
+
+
 class SalpError(RuntimeError):
     def __init__(self, code: int, msg: str):
         super().__init__(f"libsalp_b200 error {code}: {msg}")
@@ -95,6 +100,7 @@ def load():
     L.salp_step_host.argtypes = [C.c_void_p] + [C.c_void_p] * 6
     L.salp_fill_rng_words.argtypes = [C.c_void_p, C.c_int64, C.c_int64, C.c_uint64, C.c_int64, C.c_int, C.c_int]
     L.salp_launch_count.argtypes = [C.c_void_p]
+    L.salp_actor_forward.argtypes = [C.POINTER(SalpActorForward), C.c_void_p]
     L.salp_replay_append.argtypes = [C.POINTER(SalpReplayAppend), C.c_void_p]
     L.salp_launch_count.restype = C.c_int64
     if L.salp_abi_version() != SALP_ABI_VERSION:

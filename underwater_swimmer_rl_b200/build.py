@@ -2,12 +2,13 @@
 
     python -m underwater_swimmer_rl_b200.build [--force] [--verbose]
 
-Four translation units, compiled in parallel:
+Five translation units, compiled in parallel:
   salp_kernels.cu  -DSALP_BUILD_F64=0               float   kernels (throughput build)
   salp_kernels.cu  -DSALP_BUILD_F64=1 -fmad=false   double  kernels (validation build: no FMA
                                                     contraction, reference operation order)
   salp_capi.cu                                      extern "C" boundary (include/salp_b200.h)
   salp_replay.cu                                    rollout -> replay ring-buffer append kernel
+  salp_actor.cu                                     fused actor MLP (tcgen05 / TMEM) of the rollout loop
 nvcc cross-compiles without a GPU; the built .so is git-ignored but travels with gpurun.
 """
 from __future__ import annotations
@@ -45,12 +46,14 @@ def build(force: bool = False, verbose: bool = False) -> str:
     kern = os.path.join(CSRC, "salp_kernels.cu")
     capi = os.path.join(CSRC, "salp_capi.cu")
     replay = os.path.join(CSRC, "salp_replay.cu")
+    actor = os.path.join(CSRC, "salp_actor.cu")
     vflag = ["-Xptxas", "-v"] if verbose else []
     jobs = [
         (os.path.join(OBJ, "salp_kernels_f32.o"), [NVCC, "-c", kern, "-DSALP_BUILD_F64=0"] + COMMON + vflag, [kern] + hdrs),
         (os.path.join(OBJ, "salp_kernels_f64.o"), [NVCC, "-c", kern, "-DSALP_BUILD_F64=1", "-fmad=false"] + COMMON + vflag, [kern] + hdrs),
         (os.path.join(OBJ, "salp_capi.o"), [NVCC, "-c", capi] + COMMON, [capi] + hdrs),
         (os.path.join(OBJ, "salp_replay.o"), [NVCC, "-c", replay] + COMMON, [replay] + hdrs),
+        (os.path.join(OBJ, "salp_actor.o"), [NVCC, "-c", actor] + COMMON + vflag, [actor] + hdrs),
     ]
     todo = [(o, c + ["-o", o]) for o, c, d in jobs if force or _stale(o, d)]
 
@@ -62,7 +65,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
         return o, r.stderr
 
     if todo:
-        with ThreadPoolExecutor(max_workers=4) as ex:
+        with ThreadPoolExecutor(max_workers=5) as ex:
             for o, log in ex.map(run, todo):
                 if verbose and log:
                     print(f"---- {os.path.basename(o)}\n{log}")

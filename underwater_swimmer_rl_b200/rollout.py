@@ -53,6 +53,59 @@ class TanhGaussianActor(nn.Module):
         return torch.tanh(mean + std * torch.randn_like(mean))  # Normal(mean, std).rsample()
 
 
+def pack_weight(w: torch.Tensor, k_pad: int) -> torch.Tensor:
+    """torch Linear weight [out, in] -> bf16 [k_pad/8][out][8]: the tcgen05 K-major, no-swizzle operand layout
+    (8x8 core matrices, include/salp_b200.h SalpActorForward); ``in`` is zero-padded to ``k_pad``."""
+    out_f, in_f = w.shape
+    wp = torch.zeros(out_f, k_pad, dtype=torch.bfloat16, device=w.device)
+    wp[:, :in_f] = w.detach().to(torch.bfloat16)
+    return wp.view(out_f, k_pad // 8, 8).permute(1, 0, 2).contiguous()
+
+
+class FusedActor:
+    """The same function as ``TanhGaussianActor.forward`` computed by ONE sm_100a kernel
+    (csrc/salp_actor.cu: bf16 tcgen05 MMAs, accumulator in TMEM, weights resident in shared memory).
+    Built from a ``TanhGaussianActor`` with hidden sizes (256, 256); ``refresh()`` re-packs the weights after
+    a learner update.  ``__call__`` writes the actions straight into ``out`` (the tensor the env kernel reads)."""
+
+    def __init__(self, actor: TanhGaussianActor):
+        self.actor = actor
+        lin = list(actor.layers)
+        if len(lin) != 3 or lin[0].out_features != 256 or lin[1].out_features != 256:
+            raise ValueError("FusedActor needs hidden_sizes == (256, 256)")
+        self.obs_dim, self.act_dim = lin[0].in_features, actor.action_dim
+        if self.obs_dim > 32 or self.obs_dim % 4 or self.act_dim not in (1, 2):
+            raise ValueError("FusedActor supports obs_dim <= 32 (multiple of 4) and act_dim in {1, 2}")
+        self._L = _capi.load()
+        self.refresh()
+
+    def refresh(self) -> None:
+        l1, l2, l3 = self.actor.layers
+        self.w1p, self.w2p = pack_weight(l1.weight, 32), pack_weight(l2.weight, 256)
+        f32 = lambda t: t.detach().float().contiguous()  # noqa: E731
+        # W3 goes through bf16 like the other layers of a bf16 actor would, then is held in f32
+        self.b1, self.b2, self.b3 = f32(l1.bias), f32(l2.bias), f32(l3.bias)
+        self.w3 = f32(l3.weight.detach().to(torch.bfloat16))
+
+    def __call__(self, obs: torch.Tensor, out: torch.Tensor, deterministic: bool = False,
+                 noise: Optional[torch.Tensor] = None) -> torch.Tensor:
+        n = obs.shape[0]
+        assert obs.is_cuda and obs.dtype == torch.float32 and obs.is_contiguous() and obs.shape[1] == self.obs_dim
+        assert out.is_contiguous() and out.numel() == n * self.act_dim and out.dtype in (torch.float32, torch.float64)
+        if not deterministic and noise is None:
+            noise = torch.randn(n, self.act_dim, device=obs.device, dtype=torch.float32)
+        p = _capi.SalpActorForward()
+        p.obs, p.w1_packed, p.b1, p.w2_packed, p.b2 = (obs.data_ptr(), self.w1p.data_ptr(), self.b1.data_ptr(),
+                                                       self.w2p.data_ptr(), self.b2.data_ptr())
+        p.w3, p.b3, p.actions = self.w3.data_ptr(), self.b3.data_ptr(), out.data_ptr()
+        p.noise = None if deterministic else noise.data_ptr()
+        p.n, p.obs_dim, p.act_dim, p.hidden = n, self.obs_dim, self.act_dim, 256
+        p.dtype = _capi.SALP_F64 if out.dtype == torch.float64 else _capi.SALP_F32
+        with torch.cuda.device(obs.device):
+            _capi.check(self._L.salp_actor_forward(C.byref(p), C.c_void_p(torch.cuda.current_stream(obs.device).cuda_stream)))
+        return out
+
+
 class GailDiscriminator(nn.Module):
     """src/salp/agents/discriminator.py:16-85: MLP on cat(obs, action) -> expert probability."""
 
@@ -145,7 +198,7 @@ class RolloutCollector:
     auto-reset on.  With ``discriminator`` the stored reward is ``w_env*r_env + w_gail*r_gail``.
     """
 
-    def __init__(self, env: SalpVectorEnv, actor: nn.Module, buffer: Optional[DeviceReplayBuffer] = None,
+    def __init__(self, env: SalpVectorEnv, actor, buffer: Optional[DeviceReplayBuffer] = None,
                  discriminator: Optional[GailDiscriminator] = None, w_env: float = 0.3, w_gail: float = 0.7,
                  deterministic: bool = False, autocast_dtype: Optional[torch.dtype] = None):
         if env.max_substeps < 2:
@@ -167,8 +220,11 @@ class RolloutCollector:
     def _one_step(self, cur: int) -> int:
         env = self.env
         obs = env.obs[cur]
-        a = self.actor(obs, deterministic=self.deterministic)
-        self.act.copy_(a.reshape(env.num_envs, env.act_dim))  # cast to the build's real type, in place
+        if isinstance(self.actor, FusedActor):
+            self.actor(obs, self.act, deterministic=self.deterministic)  # one kernel, writes the env's action tensor
+        else:
+            a = self.actor(obs, deterministic=self.deterministic)
+            self.act.copy_(a.reshape(env.num_envs, env.act_dim))  # cast to the build's real type, in place
         nxt = 1 - cur
         env.step(self.act, slot=nxt)
         if self.buffer is not None:
