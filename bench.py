@@ -209,6 +209,7 @@ def main():
     ap.add_argument("--envs-per-gpu", type=int, default=0)
     ap.add_argument("--substeps", type=int, default=1, help="K env steps fused per launch (open-loop actions)")
     ap.add_argument("--torch-actor", action="store_true", help="sac_rollout: torch bf16 MLP instead of the fused tcgen05 actor kernel")
+    ap.add_argument("--graph", default="auto", choices=["auto", "on", "off"], help="replay the step from a CUDA graph (auto: slabs <= 262144 envs)")
     ap.add_argument("--e2e-steps", type=int, default=20)
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -266,8 +267,20 @@ def main():
         # ours, per env step: [salp_actor_kernel,] salp_step_kernel, replay_append_kernel, replay_advance_kernel
         launches_per_step = 3 if args.torch_actor else 4
 
+    # small slabs: one step is a few microseconds of device time, less than the Python launch path ->
+    # replay a CUDA graph of 32 steps (one per action tensor of the pool); it is the product API for this regime
+    graphed = (not rollout) and args.graph != "off" and (args.graph == "on" or N <= (1 << 18))
+    if graphed:
+        args.steps = max(32, args.steps // 32 * 32)
+        args.warmup = max(32, args.warmup // 32 * 32)
+        args.prime_steps = (args.prime_steps + 31) // 32 * 32
+        replay32 = env.capture_graph([p if K > 1 else p[0] for p in pool], K)
+
     def one_step(i):
-        if rollout:
+        if graphed:
+            if i % 32 == 0:
+                replay32()
+        elif rollout:
             if i % 2 == 0:
                 replay2()
         elif K == 1:
@@ -298,7 +311,7 @@ def main():
         dist.barrier()
     torch.cuda.synchronize()
     clocks = sampler.stop() if rank == 0 else None
-    launches = (env.launch_count - launches0) if not rollout else launches_per_step * args.steps
+    launches = (env.launch_count - launches0) if not (rollout or graphed) else launches_per_step * args.steps
     t = torch.tensor([ms], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -358,7 +371,7 @@ def main():
             "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f64" if real == torch.float64 else "f32", "data": "synthetic",
             "config": {"workload": args.workload, "reference_yaml": wl["yaml"], "envs_per_gpu": N, "global_envs": world * N,
-                       "substeps_per_launch": K, "rollout": ("actor MLP [24-256-256-2] bf16 (" + ("torch" if args.torch_actor else "salp_actor_kernel, tcgen05") + ") -> salp_step_kernel -> salp_replay_append, CUDA graph of 2 steps; env kernel share of the step = %.2f" % (env_only_ms / (ms_max / args.steps))) if rollout else None, "prime_steps": args.prime_steps, "obs_dim": env.obs_dim, "act_dim": env.act_dim, "autoreset": True,
+                       "substeps_per_launch": K, "cuda_graph": "32 steps per replay" if graphed else ("2 steps per replay" if rollout else None), "rollout": ("actor MLP [24-256-256-2] bf16 (" + ("torch" if args.torch_actor else "salp_actor_kernel, tcgen05") + ") -> salp_step_kernel -> salp_replay_append, CUDA graph of 2 steps; env kernel share of the step = %.2f" % (env_only_ms / (ms_max / args.steps))) if rollout else None, "prime_steps": args.prime_steps, "obs_dim": env.obs_dim, "act_dim": env.act_dim, "autoreset": True,
                        "l2": f"per-step footprint {bpe * N / 1e6:.0f} MB vs 126 MB L2"
                              + (" (inputs larger than L2, no flush needed)" if bpe * N > 126e6 else " (L2-resident working set)"),
                        "parallelism": f"env-slab x{world} (no data-path collective; NCCL all-reduce of episode stats only)"},

@@ -264,22 +264,25 @@ class SalpVectorEnv(VectorEnv):
                                            reward_host.data_ptr(), terminated_host.data_ptr(),
                                            truncated_host.data_ptr()))
 
-    def capture_graph(self, actions: torch.Tensor, k_steps: int = 1):
-        """Capture one step launch (reading ``actions`` in place) into a CUDA graph and return a
-        zero-argument replay function.  For small slabs (<= ~128k envs) a step is a few microseconds
-        of device time, less than the Python/ctypes launch path; replaying the graph removes that
-        overhead.  The caller refills ``actions`` between replays."""
-        a = self._stage_actions(actions, k_steps)
-        if a.data_ptr() != actions.data_ptr():
-            raise ValueError("capture_graph needs a contiguous device tensor of this build's dtype")
+    def capture_graph(self, actions, k_steps: int = 1):
+        """Capture step launches into a CUDA graph and return a zero-argument replay function.
+        ``actions``: one tensor (one launch per replay, read in place) or a list of tensors (one launch per
+        tensor, in order, per replay).  For small slabs (<= ~256k envs) a step is a few microseconds of device
+        time, less than the Python/ctypes launch path; replaying the graph removes that overhead
+        (SURVEY.md section 7 step 6).  The caller refills the action tensors between replays."""
+        acts = list(actions) if isinstance(actions, (list, tuple)) else [actions]
+        staged = [self._stage_actions(a, k_steps) for a in acts]
+        if any(s.data_ptr() != a.data_ptr() for s, a in zip(staged, acts)):
+            raise ValueError("capture_graph needs contiguous device tensors of this build's dtype")
         s = torch.cuda.Stream(self.device)
         s.wait_stream(torch.cuda.current_stream(self.device))
         with torch.cuda.stream(s):  # warm-up launch outside capture (module load, smem attribute)
-            _capi.check(self._L.salp_step(self._handle, k_steps, a.data_ptr(), C.c_void_p(s.cuda_stream)))
+            _capi.check(self._L.salp_step(self._handle, k_steps, staged[0].data_ptr(), C.c_void_p(s.cuda_stream)))
         torch.cuda.current_stream(self.device).wait_stream(s)
         g = torch.cuda.CUDAGraph()
         with torch.cuda.graph(g, stream=s):
-            _capi.check(self._L.salp_step(self._handle, k_steps, a.data_ptr(), self._stream()))
+            for a in staged:
+                _capi.check(self._L.salp_step(self._handle, k_steps, a.data_ptr(), self._stream()))
         return g.replay
 
     def step_async(self, actions):
