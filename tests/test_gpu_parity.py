@@ -290,3 +290,59 @@ def test_slab_sharding_is_rank_invariant(salp_lib):
     idx = torch.tensor([0, 2, 3, 4, 5], device=s.device)  # integer-valued sums are exact in f64
     assert torch.equal(whole.stats[idx], s[idx])
     assert torch.allclose(whole.stats[1], s[1], rtol=1e-12)  # return sum: atomic order differs
+
+
+EDGE_CASES = {
+    # every food-slot instantiation of the kernel (1, 4, 8, 12, 16, 32) and the generic obs-row path (observed != 3)
+    "two_food": dict(num_food_items=2, max_steps_without_food=400),
+    "five_food_default_ctor": dict(max_steps_without_food=300),                                   # SalpSnakeEnv() defaults: 5 foods, eff. bonus 1.0
+    "sixteen_food": dict(num_food_items=16, max_steps_without_food=500),
+    "thirty_two_food": dict(num_food_items=32, max_steps_without_food=500, max_observed_food=8),
+    "thirteen_food_observe_1": dict(num_food_items=13, max_observed_food=1, max_steps_without_food=300),
+    "observe_more_than_food": dict(num_food_items=2, max_observed_food=6, max_steps_without_food=300),
+    "no_food_at_all": dict(num_food_items=0, max_steps_without_food=150),
+    "small_tank": dict(width=400, height=300, num_food_items=3, max_steps_without_food=300, proximity_reward_weight=2.0),
+    "big_tank_manual": dict(width=1600, height=900, num_food_items=8, forced_breathing=False, max_steps_without_food=600),
+    "crowded_no_respawn_random_count": dict(num_food_items=12, respawn_food=False, random_food_count=True,
+                                            max_steps_without_food=500, efficiency_bonus=0.5, proximity_reward_weight=1.0),
+    "timeout_zero": dict(num_food_items=1, max_steps_without_food=0),
+}
+
+
+@pytest.mark.parametrize("name", sorted(EDGE_CASES))
+def test_fp64_edge_cases_vs_oracle(name, oracle_lib, salp_lib):
+    """Parameter corners the reference accepts (SalpSnakeEnv.__init__ keywords, S:29-47): food counts that select
+    every kernel instantiation, more observed slots than foods, zero foods, other tank sizes, manual breathing,
+    no respawn + random food count, immediate timeout.  fp64 build vs the oracle: events bit-exact, obs <= 2e-6."""
+    from underwater_swimmer_rl_b200 import rng_tables
+    params = EDGE_CASES[name]
+    N, T, K = 384, 700, 35
+    act_dim = 1 if params.get("forced_breathing", True) else 2
+    acts = synth_actions(T, N, act_dim, seed=len(name))
+    fw = rng_tables.fill_words(N, 4096, 31_000, 0, 0)
+    jw = rng_tables.fill_words(N, 1024, 31_000, 0, 1)
+    orc, o0, ref = _oracle_rollout(oracle_lib, params, fw, jw, acts)
+    env = _env(N, params, autoreset=True, max_substeps=K)
+    env.set_rng_tables(fw, jw)
+    obs0, _ = env.reset()
+    np.testing.assert_allclose(obs0.cpu().numpy(), o0, atol=OBS_ATOL_F64, rtol=0)
+    a_dev = torch.from_numpy(acts.astype(np.float64)).cuda()
+    worst = 0.0
+    for t0 in range(0, T, K):
+        obs, rew, term, trunc, info = env.step_many(a_dev[t0:t0 + K])
+        ev = info["events"].cpu().numpy()
+        rf = ref["flags"][t0:t0 + K]
+        assert (ev == rf).all(), f"{name}: events differ in steps {t0}..{t0 + K}"
+        done = (rf & 3) != 0
+        o = obs.cpu().numpy()
+        term_obs = np.where(done[..., None], info["final_observation"].cpu().numpy(), o)
+        worst = max(worst, float(np.abs(term_obs - ref["obs"][t0:t0 + K]).max()))
+        if done.any():
+            worst = max(worst, float(np.abs(o[done] - ref["reset_obs"][t0:t0 + K][done]).max()))
+        assert float(np.abs(rew.cpu().numpy() - ref["reward"][t0:t0 + K]).max()) <= 1e-8
+    st, e = _unpack_state(env), orc.envs
+    for k in ("phase", "timer", "steps_since_food", "food_collected", "n_food"):
+        assert (st[k] == e[k]).all(), k
+    assert (st["cur_food"] == e["cur_food"].astype(np.int64)).all() and (st["cur_jit"] == e["cur_jit"].astype(np.int64)).all()
+    assert worst <= OBS_ATOL_F64, worst
+    assert int(((ref["flags"] & 3) != 0).sum()) > 0, "the case must end episodes"

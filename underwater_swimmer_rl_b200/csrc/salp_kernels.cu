@@ -24,7 +24,7 @@ template <int F> struct StepCfg {
     static constexpr int store = (F <= 12) ? kStoreTmaBlock : kStoreDirect;
     static constexpr int block = 64;
     static constexpr int prefetch = 0;
-    static constexpr int regs_f32 = F <= 4 ? 64 : (F <= 8 ? 80 : (F <= 12 ? 80 : (F <= 16 ? 128 : 255)));
+    static constexpr int regs_f32 = F <= 4 ? 64 : (F <= 8 ? 80 : (F <= 12 ? 72 : (F <= 16 ? 128 : 255)));
     static constexpr int regs = SALP_BUILD_F64 ? (2 * regs_f32 > 255 ? 255 : 2 * regs_f32) : regs_f32;
     static constexpr int minb = (65536 / (regs * block)) > 32 ? 32 : (65536 / (regs * block) < 1 ? 1 : 65536 / (regs * block));
 };

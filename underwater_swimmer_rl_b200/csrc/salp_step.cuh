@@ -154,15 +154,21 @@ template <typename T> __device__ __forceinline__ T food_uniform(const KernelArgs
 template <typename T> struct RespawnResult { T x, y; unsigned cur, mask; int slot; };
 struct ResetResult { unsigned cur, mask; int n_food; };
 
-// S:232-276 _respawn_food.  Live foods are read from HBM (food records only ever change here
-// and in reset_slow, so HBM is always current).  Returns the refilled slot and its position.
-template <typename T>
+// S:232-276 _respawn_food.  Live foods are read from HBM (food records only ever change here and in the
+// reset paths, so HBM is always current) -- all of them up front with independent loads, so that a respawn
+// costs about one memory round trip per attempt instead of one per food per attempt: the slowest lane of a
+// launch sets the tail of a one-wave grid.  Returns the refilled slot and its position.
+template <typename T, int F>
 __device__ __noinline__ RespawnResult<T> respawn_slow(const KernelArgs &a, long long e, T px, T py, unsigned mask,
                                                       int n_food, unsigned cur) {
     const unsigned row = (unsigned)e % a.rows;
     Vec2<T> *food = reinterpret_cast<Vec2<T> *>(a.food);
     const T xlo = (T)(kc::TANK_MARGIN + kc::FOOD_R), xhi = (T)a.W - (T)kc::TANK_MARGIN - (T)kc::FOOD_R;
     const T ylo = xlo, yhi = (T)a.H - (T)kc::TANK_MARGIN - (T)kc::FOOD_R;
+    Vec2<T> live[F];
+#pragma unroll
+    for (int j = 0; j < F; ++j)
+        live[j] = (j < n_food && ((mask >> j) & 1u)) ? food[(size_t)j * a.N + e] : Vec2<T>{0, 0};
     int attempts = 0;
     T x = 0, y = 0;
     bool found = false;
@@ -170,13 +176,12 @@ __device__ __noinline__ RespawnResult<T> respawn_slow(const KernelArgs &a, long 
         x = food_uniform<T>(a, row, cur, xlo, xhi);
         y = food_uniform<T>(a, row, cur, ylo, yhi);
         const T rx = x - px, ry = y - py;
-        if (sqrt_(rx * rx + ry * ry) < (T)kc::MIN_FOOD_DIST) { ++attempts; continue; }
-        bool valid = true;
-        for (int j = 0; j < n_food; ++j)
-            if ((mask >> j) & 1u) {
-                const Vec2<T> f = food[(size_t)j * a.N + e];
-                const T dx = x - f.x, dy = y - f.y;
-                if (sqrt_(dx * dx + dy * dy) < (T)kc::MIN_FOOD_DIST) { valid = false; break; }
+        bool valid = !(sqrt_(rx * rx + ry * ry) < (T)kc::MIN_FOOD_DIST);
+#pragma unroll
+        for (int j = 0; j < F; ++j)
+            if (j < n_food && ((mask >> j) & 1u)) {
+                const T dx = x - live[j].x, dy = y - live[j].y;
+                if (sqrt_(dx * dx + dy * dy) < (T)kc::MIN_FOOD_DIST) valid = false;
             }
         if (valid) { found = true; break; }
         ++attempts;
@@ -825,7 +830,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) salp_step_kernel(const __grid_con
                 ++food_collected;
                 steps_since_food = 0;
                 if (a.respawn) {
-                    const RespawnResult<T> r = respawn_slow<T>(a, e, px, py, mask, n_food, cur_food);
+                    const RespawnResult<T> r = respawn_slow<T, F>(a, e, px, py, mask, n_food, cur_food);
                     mask = r.mask; cur_food = r.cur;
                     if constexpr (kFastSel) {  // the new food joins the selection made before it existed
                         if (r.slot >= 0) {
