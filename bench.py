@@ -264,8 +264,8 @@ def main():
         ring = DeviceReplayBuffer(4 * N, env.obs_dim, env.act_dim, dev)
         col = RolloutCollector(env, actor, ring)
         replay2 = col.capture()  # one graph launch = two env steps of (actor -> env kernel -> replay append)
-        # ours, per env step: [salp_actor_kernel,] salp_step_kernel, replay_append_kernel, replay_advance_kernel
-        launches_per_step = 3 if args.torch_actor else 4
+        # ours, per env step: [salp_actor_kernel,] salp_step_kernel, replay_append_kernel
+        launches_per_step = 2 if args.torch_actor else 3
 
     # small slabs: one step is a few microseconds of device time, less than the Python launch path ->
     # replay a CUDA graph of 32 steps (one per action tensor of the pool); it is the product API for this regime

@@ -239,6 +239,8 @@ typedef struct SalpReplayAppend {
     uint8_t *rb_done;           /* ring: [C]                                                */
     int64_t *head;              /* device scalar                                            */
     int64_t *size;              /* device scalar or NULL                                    */
+    uint64_t *ticket;           /* device scalar, 0 between calls, or NULL (then a second, one-thread
+                                   launch advances head/size)                               */
     int64_t n, capacity;        /* 0 < n <= capacity                                        */
     int32_t obs_dim, act_dim;   /* obs_dim % 4 == 0                                         */
     int32_t dtype;              /* SALP_F32 / SALP_F64: type of actions and reward          */
@@ -265,12 +267,20 @@ typedef struct SalpActorForward {
     const float *b1;         /* [256] */
     const void *w2_packed;   /* bf16 [32][256][8] */
     const float *b2;         /* [256] */
-    const float *w3;         /* [2*act_dim][256] */
-    const float *b3;         /* [2*act_dim] */
+    const float *w3;         /* [2*act_dim][256]  (mode 1: [1][256]) */
+    const float *b3;         /* [2*act_dim]       (mode 1: [1]) */
     const float *noise;      /* [n][act_dim] or NULL */
-    void *actions;           /* [n][act_dim] real (dtype) */
+    void *actions;           /* mode 0: [n][act_dim] real (dtype);  mode 1: f32 [n] GAIL reward */
+    const void *extra;       /* [n][extra_dim] real (dtype) appended to obs as input columns, or NULL */
+    uint64_t *rng_state;     /* device u64[4] {seed, draw counter, 0, 0} or NULL: with noise == NULL the kernel
+                                draws the normals itself (Philox4x32-10 keyed by seed, counter (row, draw)) and
+                                advances the draw counter -- graph-replay safe; both NULL = deterministic */
     int64_t n;
     int32_t obs_dim, act_dim, hidden, dtype;
+    int32_t extra_dim;       /* obs_dim + extra_dim <= 32 */
+    int32_t mode;            /* 0: actor (tanh-Gaussian action)
+                                1: GAIL reward -log(1 - sigmoid(MLP(cat(obs, extra))) + 1e-8) for a discriminator
+                                   obs+act -> 256 -> 256 -> 1 (src/salp/agents/discriminator.py:43-85) */
 } SalpActorForward;
 
 int salp_actor_forward(const SalpActorForward *p, void *cuda_stream);

@@ -63,3 +63,62 @@ def test_fused_actor_in_the_rollout_loop(salp_lib):
     with torch.no_grad():
         a_ref = _ref(actor, buf.obs[:n], None)
     assert (buf.act[:n] - a_ref).abs().max().item() <= 5e-3
+
+
+def test_in_kernel_noise_is_standard_normal_and_advances(salp_lib):
+    """Without a noise tensor the kernel draws its own normals (Philox4x32-10 + Box-Muller): with W3 = 0 the action
+    is tanh(b_mean + exp(b_logstd) z), so z is recoverable; it must look N(0,1), differ between calls, and be
+    reproducible from (seed, draw counter)."""
+    from underwater_swimmer_rl_b200.rollout import FusedActor, TanhGaussianActor
+    n = 1 << 18
+    actor = TanhGaussianActor(24, 2).cuda()
+    with torch.no_grad():
+        actor.layers[2].weight.zero_()
+        actor.layers[2].bias.copy_(torch.tensor([0.1, -0.2, -1.0, -1.5]))  # means 0.1/-0.2, log_std -1/-1.5
+    obs = torch.rand(n, 24, device="cuda")
+    draws = []
+    for seed in (7, 7, 8):
+        fused = FusedActor(actor, seed=seed)
+        zs = []
+        for _ in range(2):
+            out = torch.empty(n, 2, device="cuda", dtype=torch.float64)
+            fused(obs, out)
+            z = (torch.atanh(out) - torch.tensor([0.1, -0.2], device="cuda", dtype=torch.float64)) / torch.exp(
+                torch.tensor([-1.0, -1.5], device="cuda", dtype=torch.float64))
+            zs.append(z)
+        assert int(fused.rng_state[1].item()) == 2 and int(fused.rng_state[2].item()) == 0
+        draws.append(zs)
+    z = draws[0][0]
+    assert abs(z.mean().item()) < 0.01 and abs(z.std().item() - 1.0) < 0.01
+    assert abs((z ** 4).mean().item() - 3.0) < 0.1                       # kurtosis of a normal
+    assert abs((z[:, 0] * z[:, 1]).mean().item()) < 0.01                 # the two action dims are independent
+    assert abs((z[1:, 0] * z[:-1, 0]).mean().item()) < 0.01              # neighbouring rows too
+    assert (draws[0][0] - draws[0][1]).abs().mean().item() > 0.5         # consecutive calls differ
+    assert torch.equal(draws[0][0], draws[1][0]) and torch.equal(draws[0][1], draws[1][1])  # same seed -> same draws
+    assert (draws[0][0] - draws[2][0]).abs().mean().item() > 0.5         # other seed differs
+
+
+@pytest.mark.parametrize("n,act_dim,dtype", [(1000, 1, torch.float32), (70001, 2, torch.float64)])
+def test_fused_gail_reward_matches_torch(salp_lib, n, act_dim, dtype):
+    from underwater_swimmer_rl_b200.rollout import FusedGailReward, GailDiscriminator
+    torch.manual_seed(n)
+    disc = GailDiscriminator(24, act_dim).cuda()
+    with torch.no_grad():
+        for l in disc.layers:
+            l.weight.mul_(2.0)
+            l.bias.uniform_(-0.5, 0.5)
+    fused = FusedGailReward(disc, 24, act_dim)
+    obs = torch.rand(n, 24, device="cuda") * 2 - 1
+    act = (torch.rand(n, act_dim, device="cuda") * 2 - 1).to(dtype)
+    out = torch.empty(n, device="cuda")
+    fused(obs, act, out)
+    bf = lambda t: t.to(torch.bfloat16).float()  # noqa: E731
+    with torch.no_grad():
+        l1, l2, l3 = disc.layers
+        x = torch.cat([obs, act.float()], -1)
+        h = torch.relu(bf(x) @ bf(l1.weight).T + l1.bias)
+        h = torch.relu(bf(h) @ bf(l2.weight).T + l2.bias)
+        logit = (h @ bf(l3.weight).T + l3.bias).reshape(-1)
+        ref = -torch.log(1 - torch.sigmoid(logit) + 1e-8)
+    assert (out - ref).abs().max().item() <= 5e-3 * max(1.0, ref.abs().max().item())
+    assert (out > 0).all()

@@ -56,14 +56,16 @@ class SalpBuffers(C.Structure):
 class SalpReplayAppend(C.Structure):
     _fields_ = [(n, C.c_void_p) for n in (
         "obs_prev", "actions", "reward", "reward_aux", "terminated", "truncated", "obs_next", "final_obs",
-        "rb_obs", "rb_act", "rb_rew", "rb_next", "rb_done", "head", "size")] + [
+        "rb_obs", "rb_act", "rb_rew", "rb_next", "rb_done", "head", "size", "ticket")] + [
         ("n", C.c_int64), ("capacity", C.c_int64), ("obs_dim", C.c_int32), ("act_dim", C.c_int32),
         ("dtype", C.c_int32), ("w_env", C.c_float), ("w_aux", C.c_float), ("reserved_", C.c_int32)]
 
 
 class SalpActorForward(C.Structure):
-    _fields_ = [(n, C.c_void_p) for n in ("obs", "w1_packed", "b1", "w2_packed", "b2", "w3", "b3", "noise", "actions")] + [
-        ("n", C.c_int64), ("obs_dim", C.c_int32), ("act_dim", C.c_int32), ("hidden", C.c_int32), ("dtype", C.c_int32)]
+    _fields_ = [(n, C.c_void_p) for n in ("obs", "w1_packed", "b1", "w2_packed", "b2", "w3", "b3", "noise", "actions",
+                                          "extra", "rng_state")] + [
+        ("n", C.c_int64), ("obs_dim", C.c_int32), ("act_dim", C.c_int32), ("hidden", C.c_int32), ("dtype", C.c_int32),
+        ("extra_dim", C.c_int32), ("mode", C.c_int32)]
 
 
 class SalpError(RuntimeError):

@@ -48,9 +48,33 @@ struct ActorArgs {
     const float *b3;       // [2*act]
     const float *noise;    // [n][act] or null (deterministic)
     void *actions;         // [n][act] float or double
+    const void *extra;     // [n][extra_dim] real (dtype): columns appended to obs (GAIL: the action), or null
+    unsigned long long *rng;  // device {seed, draw counter, CTA ticket}: in-kernel Philox noise when noise == null
     long long n;
-    int obs_dim, act_dim, f64;
+    int obs_dim, act_dim, f64, extra_dim, w3_rows, mode;
 };
+
+enum { kModeActor = 0, kModeGailReward = 1 };
+
+// Philox4x32-10 (Salmon et al., SC'11): counter (row, draw), key = seed -> 4 x 32 random bits
+__device__ __forceinline__ uint4 philox4x32(uint4 c, uint2 k) {
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        const uint32_t hi0 = __umulhi(0xD2511F53u, c.x), lo0 = 0xD2511F53u * c.x;
+        const uint32_t hi1 = __umulhi(0xCD9E8D57u, c.z), lo1 = 0xCD9E8D57u * c.z;
+        c = make_uint4(hi1 ^ c.y ^ k.x, lo1, hi0 ^ c.w ^ k.y, lo0);
+        k.x += 0x9E3779B9u; k.y += 0xBB67AE85u;
+    }
+    return c;
+}
+// two independent standard normals from 64 random bits (Box-Muller)
+__device__ __forceinline__ float2 normal_pair(uint32_t a, uint32_t b) {
+    const float u1 = ((float)a + 0.5f) * 2.3283064365386963e-10f, u2 = ((float)b + 0.5f) * 2.3283064365386963e-10f;
+    const float r = sqrtf(-2.f * __logf(u1));
+    float sn, cs;
+    __sincosf(6.283185307179586f * u2, &sn, &cs);
+    return make_float2(r * cs, r * sn);
+}
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -132,11 +156,21 @@ __device__ __forceinline__ ObsChunk load_obs_chunk(const ActorArgs &a, long long
         const float4 *src = reinterpret_cast<const float4 *>(a.obs + row * a.obs_dim);
         if (8 * c < a.obs_dim) v.lo = src[2 * c];
         if (8 * c + 4 < a.obs_dim) v.hi = src[2 * c + 1];
+        if (a.extra && 8 * c + 8 > a.obs_dim && 8 * c < a.obs_dim + a.extra_dim) {  // appended columns fall in this chunk
+            float *f = reinterpret_cast<float *>(&v);
+    #pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const int col = 8 * c + j - a.obs_dim;
+                if (col >= 0 && col < a.extra_dim)
+                    f[j] = a.f64 ? (float)reinterpret_cast<const double *>(a.extra)[row * a.extra_dim + col]
+                                 : reinterpret_cast<const float *>(a.extra)[row * a.extra_dim + col];
+            }
+        }
     }
     return v;
 }
 
-template <int NOUT>  // 2 * act_dim
+template <int NOUT>  // rows of W3 padded to 2 or 4
 __global__ void __launch_bounds__(kThreads, 1) salp_actor_kernel(const __grid_constant__ ActorArgs a) {
     extern __shared__ __align__(1024) unsigned char smem[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -157,8 +191,8 @@ __global__ void __launch_bounds__(kThreads, 1) salp_actor_kernel(const __grid_co
         for (int i = tid; i < (int)(kW2Bytes / 16); i += kThreads) d2[i] = a.w2p[i];
         for (int i = tid; i < (int)(kW1Bytes / 16); i += kThreads) d1[i] = a.w1p[i];
         for (int i = tid; i < kHid; i += kThreads) { s_b1[i] = a.b1[i]; s_b2[i] = a.b2[i]; }
-        for (int i = tid; i < n_out * kHid; i += kThreads) s_w3[i] = a.w3[i];
-        if (tid < n_out) s_b3[tid] = a.b3[tid];
+        for (int i = tid; i < n_out * kHid; i += kThreads) s_w3[i] = i < a.w3_rows * kHid ? a.w3[i] : 0.f;
+        if (tid < n_out) s_b3[tid] = tid < a.w3_rows ? a.b3[tid] : 0.f;
     }
     if (tid == 0) { mbar_init(bar1, 1); mbar_init(bar2, 1); }
     if (warp == 0) {
@@ -191,6 +225,7 @@ __global__ void __launch_bounds__(kThreads, 1) salp_actor_kernel(const __grid_co
     if (tid == 0) issue_gemm1();
     ObsChunk nxt = load_obs_chunk(a, (tile + gridDim.x) * kTileM + lrow, lchunk);
     uint32_t phase1 = 0, phase2 = 0;
+    const unsigned long long rng_seed = a.rng ? a.rng[0] : 0ull, rng_draw = a.rng ? a.rng[1] : 0ull;
 
     for (; tile < n_tiles; tile += gridDim.x) {
         const bool has_next = tile + gridDim.x < n_tiles;
@@ -277,23 +312,41 @@ __global__ void __launch_bounds__(kThreads, 1) salp_actor_kernel(const __grid_co
                 t.x += u.x; t.y += u.y; t.z += u.z; t.w += u.w;
             }
             const float o4[4] = {t.x, t.y, t.z, t.w};
-            for (int d = 0; d < a.act_dim; ++d) {
-                const float mean = o4[d] + s_b3[d];
-                float pre = mean;
-                if (a.noise) {
-                    const float log_std = fminf(fmaxf(o4[a.act_dim + d] + s_b3[a.act_dim + d], -20.f), 2.f);
-                    pre = fmaf(__expf(log_std), a.noise[row * a.act_dim + d], mean);
+            if (a.mode == kModeGailReward) {
+                // D = sigmoid(logit); reward = -log(1 - D + 1e-8)   (src/salp/agents/discriminator.py:59-82)
+                const float d = 1.f / (1.f + __expf(-(o4[0] + s_b3[0])));
+                reinterpret_cast<float *>(a.actions)[row] = -__logf(1.f - d + 1e-8f);
+            } else {
+                float2 z = make_float2(0.f, 0.f);
+                const bool sample = a.noise != nullptr || a.rng != nullptr;
+                if (a.noise) { z.x = a.noise[row * a.act_dim]; if (a.act_dim > 1) z.y = a.noise[row * a.act_dim + 1]; }
+                else if (a.rng) {
+                    const uint4 rnd = philox4x32(make_uint4((uint32_t)row, (uint32_t)(row >> 32), (uint32_t)rng_draw, (uint32_t)(rng_draw >> 32)),
+                                                 make_uint2((uint32_t)rng_seed, (uint32_t)(rng_seed >> 32)));
+                    z = normal_pair(rnd.x, rnd.y);
                 }
-                const float act = tanhf(pre);
-                if (a.f64) reinterpret_cast<double *>(a.actions)[row * a.act_dim + d] = (double)act;
-                else reinterpret_cast<float *>(a.actions)[row * a.act_dim + d] = act;
+                for (int d = 0; d < a.act_dim; ++d) {
+                    const float mean = o4[d] + s_b3[d];
+                    float pre = mean;
+                    if (sample) {
+                        const float log_std = fminf(fmaxf(o4[a.act_dim + d] + s_b3[a.act_dim + d], -20.f), 2.f);
+                        pre = fmaf(__expf(log_std), d == 0 ? z.x : z.y, mean);
+                    }
+                    const float act = tanhf(pre);
+                    if (a.f64) reinterpret_cast<double *>(a.actions)[row * a.act_dim + d] = (double)act;
+                    else reinterpret_cast<float *>(a.actions)[row * a.act_dim + d] = act;
+                }
             }
         }
         __syncthreads();  // epilogue 1 of the next tile overwrites H (and with it these partial sums) right away
     }
-    // ---- teardown: every thread's TMEM reads are done before the columns are released
+    // ---- teardown: every thread's TMEM reads are done before the columns are released; the last CTA to get
+    //      here (every CTA read the draw counter at its start) advances the counter for the next launch
     tc_fence_before();
     __syncthreads();
+    if (tid == 0 && a.rng) {
+        if (atomicAdd(a.rng + 2, 1ull) == (unsigned long long)gridDim.x - 1) { a.rng[2] = 0ull; a.rng[1] = rng_draw + 1; }
+    }
     if (warp == 0) {
         tc_fence_after();
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(kTmemCols) : "memory");
@@ -307,9 +360,12 @@ extern "C" int salp_actor_forward(const SalpActorForward *p, void *cuda_stream) 
     if (!p->obs || !p->w1_packed || !p->w2_packed || !p->b1 || !p->b2 || !p->w3 || !p->b3 || !p->actions)
         return salp::set_error(SALP_EINVAL, "salp_actor_forward: a required pointer is null");
     if (p->hidden != kHid) return salp::set_error(SALP_EUNSUPPORTED, "salp_actor_forward: hidden size must be 256");
-    if (p->obs_dim <= 0 || p->obs_dim > kK1 || (p->obs_dim & 3))
-        return salp::set_error(SALP_EUNSUPPORTED, "salp_actor_forward: obs_dim must be a multiple of 4, <= 32");
-    if (p->act_dim < 1 || 2 * p->act_dim > kMaxOut) return salp::set_error(SALP_EUNSUPPORTED, "salp_actor_forward: act_dim must be 1 or 2");
+    if (p->mode != kModeActor && p->mode != kModeGailReward) return salp::set_error(SALP_EINVAL, "salp_actor_forward: bad mode");
+    const int extra = p->extra ? p->extra_dim : 0;
+    if (p->obs_dim <= 0 || (p->obs_dim & 3) || extra < 0 || p->obs_dim + extra > kK1)
+        return salp::set_error(SALP_EUNSUPPORTED, "salp_actor_forward: obs_dim must be a multiple of 4 and obs_dim + extra_dim <= 32");
+    if (p->mode == kModeActor && (p->act_dim < 1 || 2 * p->act_dim > kMaxOut))
+        return salp::set_error(SALP_EUNSUPPORTED, "salp_actor_forward: act_dim must be 1 or 2");
     if (p->n <= 0) return salp::set_error(SALP_EINVAL, "salp_actor_forward: n must be positive");
     if (p->dtype != SALP_F32 && p->dtype != SALP_F64) return salp::set_error(SALP_EINVAL, "salp_actor_forward: bad dtype");
     if (((uintptr_t)p->obs | (uintptr_t)p->w1_packed | (uintptr_t)p->w2_packed) % 16 != 0)
@@ -317,13 +373,17 @@ extern "C" int salp_actor_forward(const SalpActorForward *p, void *cuda_stream) 
     ActorArgs a;
     a.obs = p->obs; a.w1p = reinterpret_cast<const uint4 *>(p->w1_packed); a.w2p = reinterpret_cast<const uint4 *>(p->w2_packed);
     a.b1 = p->b1; a.b2 = p->b2; a.w3 = p->w3; a.b3 = p->b3; a.noise = p->noise; a.actions = p->actions;
-    a.n = p->n; a.obs_dim = p->obs_dim; a.act_dim = p->act_dim; a.f64 = p->dtype == SALP_F64;
-    auto kern = p->act_dim == 1 ? salp_actor_kernel<2> : salp_actor_kernel<4>;
+    a.extra = p->extra; a.extra_dim = extra; a.rng = reinterpret_cast<unsigned long long *>(p->rng_state);
+    a.n = p->n; a.obs_dim = p->obs_dim; a.act_dim = p->act_dim; a.f64 = p->dtype == SALP_F64; a.mode = p->mode;
+    a.w3_rows = p->mode == kModeGailReward ? 1 : 2 * p->act_dim;
+    if (p->mode == kModeGailReward) { a.noise = nullptr; a.rng = nullptr; }
+    const int which = a.w3_rows <= 2 ? 0 : 1;
+    auto kern = which == 0 ? salp_actor_kernel<2> : salp_actor_kernel<4>;
     static bool attr_set[2] = {false, false};
-    if (!attr_set[p->act_dim - 1]) {
+    if (!attr_set[which]) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
         if (e != cudaSuccess) return salp::set_error(SALP_ECUDA, cudaGetErrorString(e));
-        attr_set[p->act_dim - 1] = true;
+        attr_set[which] = true;
     }
     int dev = 0, sms = 148;
     if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);

@@ -11,7 +11,8 @@
 //
 // Layout of the ring (caller-owned, f32): obs [C][obs_dim], act [C][act_dim], rew [C], next [C][obs_dim],
 // done u8 [C].  Row of env e in this call = (*head + e) mod C; `head` lives on the device so the call can
-// be captured in a CUDA graph; a one-thread kernel advances it afterwards.
+// be captured in a CUDA graph; the last CTA to finish advances it (ticket counter), or, without a ticket
+// buffer, a one-thread kernel does afterwards.
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -31,6 +32,7 @@ struct ReplayArgs {
     uint8_t *rb_done;
     long long *head;         // device scalar: next free row
     long long *size;         // device scalar: rows filled (saturates at capacity), may be null
+    unsigned long long *ticket;  // device scalar (0 between calls): lets the last CTA advance head/size itself
     long long n, capacity;
     int obs_dim, act_dim, f64;
     float w_env, w_aux;
@@ -70,6 +72,16 @@ __global__ void __launch_bounds__(256) replay_append_kernel(const __grid_constan
             a.rb_done[row] = done ? 1 : 0;
         }
     }
+    // every CTA read *head when it started; the last one to finish moves it (no second launch)
+    if (a.ticket) {
+        __syncthreads();
+        if (threadIdx.x == 0 && atomicAdd(a.ticket, 1ull) == (unsigned long long)gridDim.x - 1) {
+            *a.ticket = 0ull;
+            const long long h = head + a.n;
+            *a.head = h >= a.capacity ? h - a.capacity : h;
+            if (a.size) { const long long sz = *a.size + a.n; *a.size = sz > a.capacity ? a.capacity : sz; }
+        }
+    }
 }
 
 __global__ void replay_advance_kernel(long long *head, long long *size, long long n, long long capacity) {
@@ -102,6 +114,7 @@ extern "C" int salp_replay_append(const SalpReplayAppend *p, void *cuda_stream) 
     a.terminated = p->terminated; a.truncated = p->truncated; a.obs_next = p->obs_next; a.final_obs = p->final_obs;
     a.rb_obs = p->rb_obs; a.rb_act = p->rb_act; a.rb_rew = p->rb_rew; a.rb_next = p->rb_next; a.rb_done = p->rb_done;
     a.head = reinterpret_cast<long long *>(p->head); a.size = reinterpret_cast<long long *>(p->size);
+    a.ticket = reinterpret_cast<unsigned long long *>(p->ticket);
     a.n = p->n; a.capacity = p->capacity; a.obs_dim = p->obs_dim; a.act_dim = p->act_dim; a.f64 = p->dtype == SALP_F64;
     a.w_env = p->w_env; a.w_aux = p->w_aux;
     const long long total = a.n * (a.obs_dim >> 2);
@@ -109,7 +122,7 @@ extern "C" int salp_replay_append(const SalpReplayAppend *p, void *cuda_stream) 
     if (blocks > 148LL * 32) blocks = 148LL * 32;  // grid-stride beyond 32 CTAs per SM
     cudaStream_t s = (cudaStream_t)cuda_stream;
     replay_append_kernel<<<(unsigned)blocks, 256, 0, s>>>(a);
-    replay_advance_kernel<<<1, 1, 0, s>>>(a.head, a.size, a.n, a.capacity);
+    if (!a.ticket) replay_advance_kernel<<<1, 1, 0, s>>>(a.head, a.size, a.n, a.capacity);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return salp_set_error_(SALP_ECUDA, cudaGetErrorString(e));
     return SALP_OK;

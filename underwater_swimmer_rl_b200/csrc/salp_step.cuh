@@ -1068,11 +1068,11 @@ __global__ void __launch_bounds__(BLOCK, MINB) salp_step_kernel(const __grid_con
                 // other lanes of this warp have just written them, then the selection again
                 __syncwarp();
                 if (done) {
-    #pragma unroll 1
-                    for (int f = 0; f < F; ++f) {
-                        const Vec2<T> v = g_food[(size_t)f * N + e];
-                        s_sel[f * BLOCK + tid] = make_float2((float)(v.x - px), (float)(v.y - py));
-                    }
+                    Vec2<T> nf[F];  // all loads in flight together: this lane's latency is the tail of a one-wave grid
+    #pragma unroll
+                    for (int f = 0; f < F; ++f) nf[f] = g_food[(size_t)f * N + e];
+    #pragma unroll
+                    for (int f = 0; f < F; ++f) s_sel[f * BLOCK + tid] = make_float2((float)(nf[f].x - px), (float)(nf[f].y - py));
                     reselect();
                 }
             } else {

@@ -68,7 +68,7 @@ class FusedActor:
     Built from a ``TanhGaussianActor`` with hidden sizes (256, 256); ``refresh()`` re-packs the weights after
     a learner update.  ``__call__`` writes the actions straight into ``out`` (the tensor the env kernel reads)."""
 
-    def __init__(self, actor: TanhGaussianActor):
+    def __init__(self, actor: TanhGaussianActor, seed: int = 0):
         self.actor = actor
         lin = list(actor.layers)
         if len(lin) != 3 or lin[0].out_features != 256 or lin[1].out_features != 256:
@@ -77,6 +77,8 @@ class FusedActor:
         if self.obs_dim > 32 or self.obs_dim % 4 or self.act_dim not in (1, 2):
             raise ValueError("FusedActor supports obs_dim <= 32 (multiple of 4) and act_dim in {1, 2}")
         self._L = _capi.load()
+        # {seed, draw counter, ticket, pad}: the kernel draws its own normals (Philox4x32-10) and bumps the counter
+        self.rng_state = torch.tensor([int(seed), 0, 0, 0], dtype=torch.int64, device=lin[0].weight.device)
         self.refresh()
 
     def refresh(self) -> None:
@@ -89,18 +91,61 @@ class FusedActor:
 
     def __call__(self, obs: torch.Tensor, out: torch.Tensor, deterministic: bool = False,
                  noise: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """``noise``: explicit standard-normal draws [n, act]; without it (and not deterministic) the kernel
+        samples in place from its own counter-based generator -- no extra launch, CUDA-graph replay safe."""
         n = obs.shape[0]
         assert obs.is_cuda and obs.dtype == torch.float32 and obs.is_contiguous() and obs.shape[1] == self.obs_dim
         assert out.is_contiguous() and out.numel() == n * self.act_dim and out.dtype in (torch.float32, torch.float64)
-        if not deterministic and noise is None:
-            noise = torch.randn(n, self.act_dim, device=obs.device, dtype=torch.float32)
         p = _capi.SalpActorForward()
         p.obs, p.w1_packed, p.b1, p.w2_packed, p.b2 = (obs.data_ptr(), self.w1p.data_ptr(), self.b1.data_ptr(),
                                                        self.w2p.data_ptr(), self.b2.data_ptr())
         p.w3, p.b3, p.actions = self.w3.data_ptr(), self.b3.data_ptr(), out.data_ptr()
-        p.noise = None if deterministic else noise.data_ptr()
+        p.noise = None if (deterministic or noise is None) else noise.data_ptr()
+        p.rng_state = None if (deterministic or noise is not None) else self.rng_state.data_ptr()
+        p.extra, p.extra_dim, p.mode = None, 0, 0
         p.n, p.obs_dim, p.act_dim, p.hidden = n, self.obs_dim, self.act_dim, 256
         p.dtype = _capi.SALP_F64 if out.dtype == torch.float64 else _capi.SALP_F32
+        with torch.cuda.device(obs.device):
+            _capi.check(self._L.salp_actor_forward(C.byref(p), C.c_void_p(torch.cuda.current_stream(obs.device).cuda_stream)))
+        return out
+
+
+class FusedGailReward:
+    """``GailDiscriminator.predict_reward`` -- -log(1 - sigmoid(MLP(cat(obs, action))) + 1e-8),
+    src/salp/agents/discriminator.py:43-85 -- by the same fused tcgen05 kernel as ``FusedActor`` (mode 1: the
+    action columns are appended to the observation row on the way into shared memory).  Built from a
+    ``GailDiscriminator`` with hidden sizes (256, 256); ``refresh()`` after a discriminator update."""
+
+    def __init__(self, disc: "GailDiscriminator", obs_dim: int, act_dim: int):
+        self.disc, self.obs_dim, self.act_dim = disc, int(obs_dim), int(act_dim)
+        lin = list(disc.layers)
+        if len(lin) != 3 or lin[0].out_features != 256 or lin[1].out_features != 256 or lin[2].out_features != 1:
+            raise ValueError("FusedGailReward needs a discriminator obs+act -> 256 -> 256 -> 1")
+        if lin[0].in_features != obs_dim + act_dim or obs_dim % 4 or obs_dim + act_dim > 32:
+            raise ValueError("FusedGailReward supports obs_dim % 4 == 0 and obs_dim + act_dim <= 32")
+        self._L = _capi.load()
+        self.refresh()
+
+    def refresh(self) -> None:
+        l1, l2, l3 = self.disc.layers
+        self.w1p, self.w2p = pack_weight(l1.weight, 32), pack_weight(l2.weight, 256)
+        f32 = lambda t: t.detach().float().contiguous()  # noqa: E731
+        self.b1, self.b2, self.b3 = f32(l1.bias), f32(l2.bias), f32(l3.bias)
+        self.w3 = f32(l3.weight.detach().to(torch.bfloat16))
+
+    def __call__(self, obs: torch.Tensor, action: torch.Tensor, out: torch.Tensor) -> torch.Tensor:
+        n = obs.shape[0]
+        assert obs.is_cuda and obs.dtype == torch.float32 and obs.is_contiguous() and obs.shape[1] == self.obs_dim
+        assert action.is_contiguous() and action.numel() == n * self.act_dim and action.dtype in (torch.float32, torch.float64)
+        assert out.dtype == torch.float32 and out.is_contiguous() and out.numel() == n
+        p = _capi.SalpActorForward()
+        p.obs, p.w1_packed, p.b1, p.w2_packed, p.b2 = (obs.data_ptr(), self.w1p.data_ptr(), self.b1.data_ptr(),
+                                                       self.w2p.data_ptr(), self.b2.data_ptr())
+        p.w3, p.b3, p.actions = self.w3.data_ptr(), self.b3.data_ptr(), out.data_ptr()
+        p.noise, p.rng_state = None, None
+        p.extra, p.extra_dim, p.mode = action.data_ptr(), self.act_dim, 1
+        p.n, p.obs_dim, p.act_dim, p.hidden = n, self.obs_dim, self.act_dim, 256
+        p.dtype = _capi.SALP_F64 if action.dtype == torch.float64 else _capi.SALP_F32
         with torch.cuda.device(obs.device):
             _capi.check(self._L.salp_actor_forward(C.byref(p), C.c_void_p(torch.cuda.current_stream(obs.device).cuda_stream)))
         return out
@@ -136,6 +181,7 @@ class DeviceReplayBuffer:
         self.act, self.rew = z(capacity, act_dim), z(capacity)
         self.done = z(capacity, dtype=torch.bool)
         self.head, self.size = z(1, dtype=torch.int64), z(1, dtype=torch.int64)
+        self._ticket = z(1, dtype=torch.int64)
         self._L = _capi.load()
 
     def append(self, obs_prev, actions, reward, terminated, truncated, obs_next, final_obs=None,
@@ -146,7 +192,7 @@ class DeviceReplayBuffer:
         for name, t in (("obs_prev", obs_prev), ("actions", actions), ("reward", reward), ("terminated", terminated),
                         ("truncated", truncated), ("obs_next", obs_next), ("rb_obs", self.obs), ("rb_act", self.act),
                         ("rb_rew", self.rew), ("rb_next", self.next_obs), ("rb_done", self.done), ("head", self.head),
-                        ("size", self.size)):
+                        ("size", self.size), ("ticket", self._ticket)):
             assert t.is_cuda and t.is_contiguous(), name
             setattr(p, name, t.data_ptr())
         assert obs_prev.dtype == torch.float32 and obs_next.dtype == torch.float32
@@ -199,7 +245,7 @@ class RolloutCollector:
     """
 
     def __init__(self, env: SalpVectorEnv, actor, buffer: Optional[DeviceReplayBuffer] = None,
-                 discriminator: Optional[GailDiscriminator] = None, w_env: float = 0.3, w_gail: float = 0.7,
+                 discriminator=None, w_env: float = 0.3, w_gail: float = 0.7,
                  deterministic: bool = False, autocast_dtype: Optional[torch.dtype] = None):
         if env.max_substeps < 2:
             raise ValueError("RolloutCollector needs an env with max_substeps >= 2 (ping-pong output rows)")
@@ -210,6 +256,7 @@ class RolloutCollector:
         self.act = torch.zeros(env.num_envs, env.act_dim, dtype=env.real, device=env.device)  # the kernel reads this
         self.steps = 0
         self._graph = None
+        self._aux = torch.zeros(env.num_envs, dtype=torch.float32, device=env.device)  # GAIL reward of the step
 
     def reset(self):
         obs, info = self.env.reset()
@@ -228,7 +275,10 @@ class RolloutCollector:
         nxt = 1 - cur
         env.step(self.act, slot=nxt)
         if self.buffer is not None:
-            aux = self.disc.predict_reward(obs, self.act).reshape(-1).contiguous() if self.disc is not None else None
+            if isinstance(self.disc, FusedGailReward):
+                aux = self.disc(obs, self.act, self._aux)
+            else:
+                aux = self.disc.predict_reward(obs, self.act).reshape(-1).contiguous() if self.disc is not None else None
             self.buffer.append(obs, self.act, env.reward[nxt], env.terminated[nxt], env.truncated[nxt], env.obs[nxt],
                                final_obs=env.final_obs[nxt] if env.autoreset else None, reward_aux=aux,
                                w_env=self.w_env if aux is not None else 1.0, w_aux=self.w_gail if aux is not None else 0.0)
