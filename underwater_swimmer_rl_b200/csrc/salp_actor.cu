@@ -379,11 +379,9 @@ extern "C" int salp_actor_forward(const SalpActorForward *p, void *cuda_stream) 
     if (p->mode == kModeGailReward) { a.noise = nullptr; a.rng = nullptr; }
     const int which = a.w3_rows <= 2 ? 0 : 1;
     auto kern = which == 0 ? salp_actor_kernel<2> : salp_actor_kernel<4>;
-    static bool attr_set[2] = {false, false};
-    if (!attr_set[which]) {
+    {   // per device and cheap: set on every call rather than caching a per-process flag
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
         if (e != cudaSuccess) return salp::set_error(SALP_ECUDA, cudaGetErrorString(e));
-        attr_set[which] = true;
     }
     int dev = 0, sms = 148;
     if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
