@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define SALP_ABI_VERSION 2
+#define SALP_ABI_VERSION 3
 
 enum { SALP_OK = 0, SALP_EINVAL = -1, SALP_ECUDA = -2, SALP_EUNBOUND = -3, SALP_EUNSUPPORTED = -4 };
 
@@ -284,6 +284,73 @@ typedef struct SalpActorForward {
 } SalpActorForward;
 
 int salp_actor_forward(const SalpActorForward *p, void *cuda_stream);
+
+/* =====================================================================================================
+ * Model (B): one env step = one breathing cycle of the 3-D Newton-Euler robot.
+ *
+ * Replaces, for a slab of n environments (reference tree, Python):
+ *   SalpRobotEnv.reset           src/salp/environments/salp_robot_env.py:100-127  (+ generate_target_point :266-328)
+ *   SalpRobotEnv.step            src/salp/environments/salp_robot_env.py:139-201  (+ _rescale_action :129-137,
+ *                                _calculate_reward :203-242, _get_observation :400-420)
+ *   Nozzle.solve_angles / get_nozzle_direction   src/salp/environments/robot.py:55-83, :115-130, :153-178
+ *   Robot.set_control / step_through_cycle / step and everything they call   robot.py:335-777
+ * The calls are stateless: every buffer is caller-owned device memory passed in SalpCycleBuffers.
+ *
+ * Layout (N = n, `real` = float or double by dtype):
+ *   state  real [6][N][4]  rec0 (pos.x, pos.y, pos.z, prev_dist)          rec1 (vel.x, vel.y, vel.z, water volume)
+ *                          rec2 (omega.x, omega.y, omega.z, episode return) rec3 (roll, pitch, yaw, body length)
+ *                          rec4 (prev_I.xx, prev_I.yy, prev_I.zz, body width) rec5 (vel_world.x, .y, .z, 0)
+ *                          velocities are body-frame (robot.py:247-255); vel_world is kept for the reward heading term
+ *   ctrl   i32  [N][4]     (cycle | phase << 16, rng cursor, target.x f32 bits, target.y f32 bits)
+ *   actions real [N][3]    (contraction, coast time, nozzle yaw) in the env's Box [0,1] x [0,1] x [-1,1]
+ *   obs    f32  [N][6]     (pos - target).xy, vel.xy (body), yaw, omega.z        (salp_robot_env.py:413-420)
+ *   reward real [N]; terminated, truncated u8 [N]; n_sub i32 [N] integrator substeps of this cycle (0..1450)
+ *   final_obs f32 [N][6]   terminal observation of lanes that finished (valid where terminated|truncated)
+ *   stats  f64  [8]        += episodes, sum return, sum cycles, targets reached, truncations, non-finite lanes,
+ *                             env steps, integrator substeps
+ *   words  u32  [table_rows][words_len]  np.random MT19937 outputs per env (salp_fill_rng_words kind 1); env e
+ *                          reads row (env_id0 + e) % table_rows; two 53-bit draws per reset (target point)
+ * Finished environments auto-reset inside the step when SALP_CYCLE_AUTORESET is set (the vector-env convention;
+ * the reference env itself never auto-resets): `obs` then holds the first observation of the next episode.
+ */
+#define SALP_CYCLE_AUTORESET 1
+#define SALP_CYCLE_OBS_DIM 6
+#define SALP_CYCLE_ACT_DIM 3
+#define SALP_CYCLE_MAX_SUBSTEPS 4096
+
+typedef struct SalpCycleParams {
+    double dry_mass, init_length, init_width, max_contraction, density; /* Robot.__init__ / set_environment, robot.py:196-222,279 */
+    double nozzle_length1, nozzle_length2, nozzle_length3, nozzle_area, nozzle_mass; /* Nozzle.__init__ robot.py:19-25 */
+    double width, height;     /* SalpRobotEnv.__init__ (pixels; tank_margin 50, 200 px per metre) :32-39,266-277 */
+    int32_t max_cycles;       /* 500 (salp_robot_env.py:187) */
+    int32_t max_substeps;     /* safety cap on the cycle loop for actions outside the Box; 0 = SALP_CYCLE_MAX_SUBSTEPS */
+    int32_t flags;            /* SALP_CYCLE_AUTORESET */
+    int32_t reserved_;
+} SalpCycleParams;
+
+typedef struct SalpCycleBuffers {
+    void *state;          /* real [6][n][4] */
+    void *ctrl;           /* i32  [n][4]    */
+    float *obs;           /* f32  [n][6]    */
+    void *reward;         /* real [n]       */
+    uint8_t *terminated;  /* [n] */
+    uint8_t *truncated;   /* [n] */
+    int32_t *n_sub;       /* [n] or NULL */
+    float *final_obs;     /* [n][6] or NULL */
+    double *stats;        /* [8] or NULL */
+    const uint32_t *words; /* [table_rows][words_len] */
+    int64_t table_rows, words_len;  /* words_len a power of two */
+    int64_t n;
+    int64_t env_id0;      /* global index of env 0 of this slab (RNG row selection; multi-GPU slabs) */
+    int32_t dtype;        /* SALP_F32 | SALP_F64 */
+    int32_t reserved_;
+} SalpCycleBuffers;
+
+/* reset: envs with mask[e] != 0 (mask == NULL: all) draw a new target and return to rest; rewind_rng != 0 puts
+ * their cursor back to 0 first (reset(seed=...) semantics).  Writes `obs`. */
+int salp_cycle_reset(const SalpCycleParams *p, const SalpCycleBuffers *b, const uint8_t *mask, int rewind_rng, void *cuda_stream);
+/* step: one breathing cycle per env for actions real [n][3]. */
+int salp_cycle_step(const SalpCycleParams *p, const SalpCycleBuffers *b, const void *actions, void *cuda_stream);
 
 /* Number of kernels this library has launched on behalf of `h` (bench "gpu_launches"). */
 int64_t salp_launch_count(const SalpHandle *h);

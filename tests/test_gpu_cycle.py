@@ -1,0 +1,176 @@
+"""GPU: the model (B) breathing-cycle kernel (csrc/salp_cycle.cuh, salp_cycle_step) against the CPU oracle
+(oracle/salp_cycle_oracle.c) on the same seeds and action sequences, and against the committed reference
+trajectories (tests/golden/cycle_*.npz, generated from the unmodified Python reference).
+
+Bar (BASELINE.json north_star): discrete state bit-exact in the fp64 validation build, continuous state within
+1e-6 (fp64) / 2e-3 (fp32).  The fp64 floor is the reference's own: its nozzle IK carries ~2e-8 of libm-dependent
+rounding noise (see oracle/salp_cycle_oracle.c)."""
+import glob
+import os
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def _words(seeds, n=256):
+    from underwater_swimmer_rl_b200 import rng_tables
+    assert list(seeds) == list(range(seeds[0], seeds[0] + len(seeds)))
+    return rng_tables.fill_words(len(seeds), n, seeds[0], 0, rng_tables.JITTER_STREAM)
+
+
+def _gpu_rollout(dtype, words, acts, **kw):
+    from underwater_swimmer_rl_b200.cycle_env import SalpCycleVectorEnv
+    T, N, _ = acts.shape
+    env = SalpCycleVectorEnv(N, dtype=dtype, **kw)
+    env.set_rng_table(words)
+    obs0, _ = env.reset()
+    out = dict(obs0=obs0.cpu().numpy().copy(), obs=[], reward=[], terminated=[], truncated=[], n_sub=[], final_obs=[])
+    a = torch.from_numpy(acts).cuda()
+    for t in range(T):
+        o, r, te, tr, info = env.step(a[t])
+        out["obs"].append(o.cpu().numpy().copy()); out["reward"].append(r.cpu().numpy().astype(np.float64))
+        out["terminated"].append(te.cpu().numpy().copy()); out["truncated"].append(tr.cpu().numpy().copy())
+        out["n_sub"].append(info["n_sub"].cpu().numpy().copy()); out["final_obs"].append(info["final_obs"].cpu().numpy().copy())
+    res = {k: (np.stack(v) if isinstance(v, list) else v) for k, v in out.items()}
+    res["env"] = env
+    return res
+
+
+def _oracle_rollout(words, acts, **params):
+    from oracle.salp_cycle_oracle import CycleOracle
+    orc = CycleOracle(acts.shape[1], words, **params)
+    o0 = orc.reset()
+    out = orc.rollout(acts, autoreset=True)
+    out["obs0"] = o0
+    return out
+
+
+def _relerr(a, b):
+    return float((np.abs(a.astype(np.float64) - b) / (1.0 + np.abs(b))).max())
+
+
+FP64_CASES = [
+    # style, T, N, env keywords, which way episodes must end
+    ("uniform", 10, 512, {}, None),
+    ("short", 40, 300, {}, None),
+    ("seek", 16, 256, {}, None),
+    ("tiny", 1005, 96, {}, "truncated"),                                  # 500-cycle truncation, twice
+    ("short", 30, 200, dict(width=102, height=102), "terminated"),        # target within 1 cm: reached
+    ("uniform", 12, 200, dict(width=3000, height=2400), "truncated"),     # targets > 5 m away: out of range
+]
+
+
+@pytest.mark.parametrize("style,T,N,kw,ends", FP64_CASES)
+def test_fp64_vs_oracle(salp_lib, style, T, N, kw, ends):
+    from oracle.validate_cycle_against_reference import make_cycle_actions
+    acts = make_cycle_actions(T, N, style, seed=99)
+    seeds = list(range(31_000, 31_000 + N))
+    words = _words(seeds)
+    ref = _oracle_rollout(words, acts, **kw)
+    got = _gpu_rollout("float64", words, acts, **kw)
+    assert np.array_equal(got["obs0"], ref["obs0"])
+    for k in ("n_sub", "terminated", "truncated"):
+        assert np.array_equal(got[k], ref[k]), k
+    assert _relerr(got["obs"], ref["obs"]) <= 1e-6
+    assert _relerr(got["reward"], ref["reward"]) <= 1e-6
+    done = (ref["terminated"] | ref["truncated"]) != 0
+    if ends:
+        assert ref[ends].any(), f"this case must end episodes by {ends}"
+    if done.any():
+        assert _relerr(got["final_obs"][done], ref["final_obs"][done]) <= 1e-6
+    st = got["env"].episode_stats()
+    assert st["env_steps"] == T * N and st["substeps"] == float(ref["n_sub"].sum())
+    assert st["episodes"] == float(done.sum()) and st["nonfinite"] == 0
+
+
+@pytest.mark.parametrize("style,T,N", [("uniform", 10, 512), ("seek", 16, 256)])
+def test_fp32_vs_oracle(salp_lib, style, T, N):
+    from oracle.validate_cycle_against_reference import make_cycle_actions
+    acts = make_cycle_actions(T, N, style, seed=7).astype(np.float32)
+    seeds = list(range(32_000, 32_000 + N))
+    words = _words(seeds)
+    ref = _oracle_rollout(words, acts.astype(np.float64))
+    got = _gpu_rollout("float32", words, acts)
+    assert np.array_equal(got["obs0"], ref["obs0"])
+    assert np.array_equal(got["n_sub"], ref["n_sub"]), "substep counts must be exact in the fp32 build too"
+    assert np.array_equal(got["terminated"], ref["terminated"]) and np.array_equal(got["truncated"], ref["truncated"])
+    err = _relerr(got["obs"], ref["obs"])
+    print(f"fp32 {style}: max obs err over {T} cycles {err:.2e}")
+    assert err <= 2e-3
+    assert _relerr(got["reward"], ref["reward"]) <= 2e-2   # 100 x (difference of two distances) in float
+
+
+def test_golden_reference_trajectories(salp_lib):
+    """fp64 build against trajectories recorded from the unmodified Python reference."""
+    files = sorted(glob.glob(os.path.join(GOLDEN, "cycle_*.npz")))
+    assert files, "tests/golden/cycle_*.npz missing"
+    from underwater_swimmer_rl_b200.cycle_env import Nozzle, Robot
+    for f in files:
+        g = np.load(f, allow_pickle=False)
+        import json
+        meta = json.loads(str(g["meta"]))
+        pr = meta["params"]
+        robot = Robot(nozzle=Nozzle(pr.get("nozzle_length1", 0.05), pr.get("nozzle_length2", 0.05), pr.get("nozzle_length3", 0.05),
+                                    pr.get("nozzle_area", 0.00016), 1.0))
+        kw = dict(robot=robot, width=pr.get("width", 900), height=pr.get("height", 700))
+        seeds = meta["seeds"]
+        got = _gpu_rollout("float64", _words(seeds), g["actions"], **kw)
+        assert np.array_equal(got["obs0"], g["obs0"]), f
+        for k in ("n_sub", "terminated", "truncated"):
+            assert np.array_equal(got[k], g[k]), (f, k)
+        assert _relerr(got["obs"], g["obs"]) <= 1e-6, f
+        assert _relerr(got["reward"], g["reward"]) <= 1e-6, f
+
+
+def test_masked_reset_and_no_autoreset(salp_lib):
+    from underwater_swimmer_rl_b200.cycle_env import SalpCycleVectorEnv
+    N = 64
+    env = SalpCycleVectorEnv(N, dtype="float64", autoreset=False, seed=500)
+    env.reset()
+    a = torch.tensor([[1.0, 0.0, 0.0]], device="cuda", dtype=torch.float64).repeat(N, 1)
+    for _ in range(3):
+        env.step(a)
+    pos = env.position.clone()
+    assert (env.cycle == 3).all() and pos[:, 0].abs().min() > 1e-3
+    mask = torch.zeros(N, dtype=torch.uint8, device="cuda"); mask[::2] = 1
+    tgt = env.target_point.clone()
+    env.reset(mask=mask)
+    assert (env.cycle[::2] == 0).all() and (env.cycle[1::2] == 3).all()
+    assert torch.equal(env.position[1::2], pos[1::2]) and (env.position[::2] == 0).all()
+    assert torch.equal(env.target_point[1::2], tgt[1::2]) and not torch.equal(env.target_point[::2], tgt[::2])
+
+
+def test_bad_arguments_are_reported(salp_lib):
+    import ctypes as C
+    from underwater_swimmer_rl_b200 import _capi
+    from underwater_swimmer_rl_b200.cycle_env import SalpCycleVectorEnv
+    env = SalpCycleVectorEnv(8)
+    with pytest.raises(ValueError):
+        env.step(torch.zeros(8, 2, device="cuda"))
+    rc = salp_lib.salp_cycle_step(C.byref(env.params), C.byref(env._buffers), None, None)
+    assert rc == _capi.SALP_EINVAL and b"actions" in salp_lib.salp_last_error()
+    p = _capi.SalpCycleParams.from_buffer_copy(env.params); p.nozzle_area = 0.0
+    assert salp_lib.salp_cycle_reset(C.byref(p), C.byref(env._buffers), None, 1, None) == _capi.SALP_EINVAL
+
+
+def test_throughput_print(salp_lib):
+    """Not a benchmark (bench.py --workload robot_cycle_256k is): prints the substep rate of both builds."""
+    from underwater_swimmer_rl_b200.cycle_env import SalpCycleVectorEnv
+    for dtype, N in (("float32", 262144), ("float64", 65536)):
+        env = SalpCycleVectorEnv(N, dtype=dtype, table_rows=4096)
+        env.reset()
+        g = torch.Generator(device="cuda").manual_seed(1)
+        a = torch.rand(N, 3, device="cuda", generator=g, dtype=env.real)
+        a[:, 2] = a[:, 2] * 2 - 1
+        env.step(a); torch.cuda.synchronize()
+        env.episode_stats(reset=True)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); env.step(a); e1.record(); torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1); st = env.episode_stats()
+        print(f"{dtype}: {N} envs, {st['substeps'] / N:.0f} substeps/env, {ms:.2f} ms/step, "
+              f"{st['substeps'] / ms / 1e6:.2f} G substeps/s, {N / ms / 1e3:.2f} M env-steps/s")

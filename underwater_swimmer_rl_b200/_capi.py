@@ -11,7 +11,7 @@ import os
 _PKG = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_PKG, "libsalp_b200.so")
 
-SALP_ABI_VERSION = 2
+SALP_ABI_VERSION = 3
 SALP_OK, SALP_EINVAL, SALP_ECUDA, SALP_EUNBOUND, SALP_EUNSUPPORTED = 0, -1, -2, -3, -4
 SALP_F32, SALP_F64 = 0, 1
 SALP_AUTORESET = 1
@@ -21,7 +21,10 @@ EV_TERMINATED, EV_TRUNCATED, EV_COLLISION, EV_FOOD = 1, 2, 4, 8
 EXPORTED_SYMBOLS = (
     "salp_abi_version", "salp_last_error", "salp_query_layout", "salp_create", "salp_destroy", "salp_bind",
     "salp_reset", "salp_refresh_rng", "salp_step", "salp_step_slot", "salp_step_host", "salp_fill_rng_words", "salp_launch_count", "salp_replay_append", "salp_actor_forward",
+    "salp_cycle_reset", "salp_cycle_step",
 )
+SALP_CYCLE_AUTORESET = 1
+SALP_CYCLE_OBS_DIM, SALP_CYCLE_ACT_DIM, SALP_CYCLE_MAX_SUBSTEPS = 6, 3, 4096
 
 
 class SalpParams(C.Structure):
@@ -68,6 +71,20 @@ class SalpActorForward(C.Structure):
         ("extra_dim", C.c_int32), ("mode", C.c_int32)]
 
 
+class SalpCycleParams(C.Structure):
+    _fields_ = [(n, C.c_double) for n in (
+        "dry_mass", "init_length", "init_width", "max_contraction", "density",
+        "nozzle_length1", "nozzle_length2", "nozzle_length3", "nozzle_area", "nozzle_mass", "width", "height")] + [
+        ("max_cycles", C.c_int32), ("max_substeps", C.c_int32), ("flags", C.c_int32), ("reserved_", C.c_int32)]
+
+
+class SalpCycleBuffers(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n in (
+        "state", "ctrl", "obs", "reward", "terminated", "truncated", "n_sub", "final_obs", "stats", "words")] + [
+        ("table_rows", C.c_int64), ("words_len", C.c_int64), ("n", C.c_int64), ("env_id0", C.c_int64),
+        ("dtype", C.c_int32), ("reserved_", C.c_int32)]
+
+
 class SalpError(RuntimeError):
     def __init__(self, code: int, msg: str):
         super().__init__(f"libsalp_b200 error {code}: {msg}")
@@ -105,6 +122,8 @@ def load():
     L.salp_actor_forward.argtypes = [C.POINTER(SalpActorForward), C.c_void_p]
     L.salp_replay_append.argtypes = [C.POINTER(SalpReplayAppend), C.c_void_p]
     L.salp_launch_count.restype = C.c_int64
+    L.salp_cycle_reset.argtypes = [C.POINTER(SalpCycleParams), C.POINTER(SalpCycleBuffers), C.c_void_p, C.c_int, C.c_void_p]
+    L.salp_cycle_step.argtypes = [C.POINTER(SalpCycleParams), C.POINTER(SalpCycleBuffers), C.c_void_p, C.c_void_p]
     if L.salp_abi_version() != SALP_ABI_VERSION:
         raise ImportError("libsalp_b200.so ABI version mismatch; rebuild it")
     _lib = L

@@ -2,13 +2,15 @@
 
     python -m underwater_swimmer_rl_b200.build [--force] [--verbose]
 
-Five translation units, compiled in parallel:
+Eight translation units, compiled in parallel:
   salp_kernels.cu  -DSALP_BUILD_F64=0               float   kernels (throughput build)
   salp_kernels.cu  -DSALP_BUILD_F64=1 -fmad=false   double  kernels (validation build: no FMA
                                                     contraction, reference operation order)
   salp_capi.cu                                      extern "C" boundary (include/salp_b200.h)
   salp_replay.cu                                    rollout -> replay ring-buffer append kernel
   salp_actor.cu                                     fused actor MLP (tcgen05 / TMEM) of the rollout loop
+  salp_cycle_kernels.cu  (twice, like salp_kernels.cu)  model (B) breathing-cycle kernels, float / double
+  salp_cycle_capi.cu                                extern "C" boundary of the cycle env (salp_cycle_*)
 nvcc cross-compiles without a GPU; the built .so is git-ignored but travels with gpurun.
 """
 from __future__ import annotations
@@ -47,6 +49,8 @@ def build(force: bool = False, verbose: bool = False) -> str:
     capi = os.path.join(CSRC, "salp_capi.cu")
     replay = os.path.join(CSRC, "salp_replay.cu")
     actor = os.path.join(CSRC, "salp_actor.cu")
+    cyck = os.path.join(CSRC, "salp_cycle_kernels.cu")
+    cycc = os.path.join(CSRC, "salp_cycle_capi.cu")
     vflag = ["-Xptxas", "-v"] if verbose else []
     jobs = [
         (os.path.join(OBJ, "salp_kernels_f32.o"), [NVCC, "-c", kern, "-DSALP_BUILD_F64=0"] + COMMON + vflag, [kern] + hdrs),
@@ -54,6 +58,9 @@ def build(force: bool = False, verbose: bool = False) -> str:
         (os.path.join(OBJ, "salp_capi.o"), [NVCC, "-c", capi] + COMMON, [capi] + hdrs),
         (os.path.join(OBJ, "salp_replay.o"), [NVCC, "-c", replay] + COMMON, [replay] + hdrs),
         (os.path.join(OBJ, "salp_actor.o"), [NVCC, "-c", actor] + COMMON + vflag, [actor] + hdrs),
+        (os.path.join(OBJ, "salp_cycle_f32.o"), [NVCC, "-c", cyck, "-DSALP_BUILD_F64=0"] + COMMON + vflag, [cyck] + hdrs),
+        (os.path.join(OBJ, "salp_cycle_f64.o"), [NVCC, "-c", cyck, "-DSALP_BUILD_F64=1", "-fmad=false"] + COMMON + vflag, [cyck] + hdrs),
+        (os.path.join(OBJ, "salp_cycle_capi.o"), [NVCC, "-c", cycc] + COMMON, [cycc] + hdrs),
     ]
     todo = [(o, c + ["-o", o]) for o, c, d in jobs if force or _stale(o, d)]
 
@@ -65,7 +72,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
         return o, r.stderr
 
     if todo:
-        with ThreadPoolExecutor(max_workers=5) as ex:
+        with ThreadPoolExecutor(max_workers=8) as ex:
             for o, log in ex.map(run, todo):
                 if verbose and log:
                     print(f"---- {os.path.basename(o)}\n{log}")

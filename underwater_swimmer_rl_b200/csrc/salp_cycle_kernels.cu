@@ -1,0 +1,33 @@
+// salp_cycle_kernels.cu -- instantiates the model (B) cycle kernels for ONE arithmetic type.
+// Compiled twice by build.py:
+//   -DSALP_BUILD_F64=0                 -> launch_cycle_step_f32 / launch_cycle_reset_f32   (throughput build)
+//   -DSALP_BUILD_F64=1 -fmad=false     -> launch_cycle_step_f64 / launch_cycle_reset_f64   (validation build)
+#include "salp_cycle.cuh"
+
+namespace salp {
+
+#if SALP_BUILD_F64
+using cyc_real_t = double;
+#define SALP_LAUNCH_CYCLE_STEP launch_cycle_step_f64
+#define SALP_LAUNCH_CYCLE_RESET launch_cycle_reset_f64
+#else
+using cyc_real_t = float;
+#define SALP_LAUNCH_CYCLE_STEP launch_cycle_step_f32
+#define SALP_LAUNCH_CYCLE_RESET launch_cycle_reset_f32
+#endif
+
+cudaError_t SALP_LAUNCH_CYCLE_STEP(const CycleArgs &a, cudaStream_t s) {
+    if (a.n <= 0) return cudaSuccess;
+    const unsigned grid = (unsigned)((a.n + kCycleBlock - 1) / kCycleBlock);
+    salp_cycle_step_kernel<cyc_real_t><<<grid, kCycleBlock, 0, s>>>(a);
+    return cudaGetLastError();
+}
+
+cudaError_t SALP_LAUNCH_CYCLE_RESET(const CycleArgs &a, cudaStream_t s) {
+    if (a.n <= 0) return cudaSuccess;
+    const unsigned grid = (unsigned)((a.n + 255) / 256);
+    salp_cycle_reset_kernel<cyc_real_t><<<grid, 256, 0, s>>>(a);
+    return cudaGetLastError();
+}
+
+}  // namespace salp
