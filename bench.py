@@ -45,6 +45,9 @@ WORKLOADS = {
     # configs[4]: SAC rollout collection -- [24->256->256->2] tanh-Gaussian actor (torch, bf16) -> env kernel ->
     # replay-append kernel, replayed from a CUDA graph; a "step" is one env step of that loop for every env
     "sac_rollout_256k": dict(yaml="configs/sac_gail.yaml", params=DEFAULTS, envs=1 << 18, dtype="float32", rollout=True),
+    # model (B), one env step = one breathing cycle (0..1450 integrator substeps, 725 on average
+    # for actions uniform in the env's Box); ALU-bound, reported beside its (tiny) HBM figure
+    "robot_cycle_256k": dict(yaml=None, params={}, envs=1 << 18, dtype="float32", cycle=True),
 }
 METRIC = "salp_env_steps_per_sec"
 UNIT = "env-steps/s"
@@ -159,6 +162,179 @@ def cpu_oracle_throughput(params: dict, budget_s: float, threads: int, n_envs: i
     return done_steps / el, el, f"{n_envs} envs x {T * reps} steps, auto-reset, uniform(-1,1) actions, no output recording"
 
 
+def cycle_actions(torch, n, dev, real, seed):
+    """Uniform actions in the env's Box [0,1] x [0,1] x [-1,1] (salp_robot_env.py:51-55)."""
+    g = torch.Generator(device=dev)
+    g.manual_seed(seed)
+    a = torch.rand(n, 3, device=dev, dtype=real, generator=g)
+    a[:, 2] = a[:, 2] * 2 - 1
+    return a
+
+
+def cpu_cycle_oracle_throughput(budget_s: float, threads: int, n_envs: int):
+    """Time oracle/salp_cycle_oracle.c (OpenMP over envs) on a bounded sample of the robot_cycle workload."""
+    import numpy as np
+
+    from oracle import salp_cycle_oracle
+    from underwater_swimmer_rl_b200 import rng_tables
+    os.environ["OMP_NUM_THREADS"] = str(threads)
+    salp_cycle_oracle.build()
+    words = rng_tables.fill_words(n_envs, 64, 10_000, 0, rng_tables.JITTER_STREAM)
+    orc = salp_cycle_oracle.CycleOracle(n_envs, words)
+    orc.reset()
+    g = np.random.default_rng(1234)
+    mk = lambda: np.stack([g.uniform(0, 1, n_envs), g.uniform(0, 1, n_envs), g.uniform(-1, 1, n_envs)], axis=1)  # noqa: E731
+    orc.step(mk())
+    steps = subs = 0
+    t0 = time.perf_counter()
+    while True:
+        subs += orc.step(mk())["substeps"]
+        steps += n_envs
+        el = time.perf_counter() - t0
+        if el >= budget_s:
+            break
+    return steps / el, subs / el, el, f"{n_envs} envs x {steps // n_envs} cycles, auto-reset, actions uniform in the Box"
+
+
+def run_cycle_reference_arm(args, wl):
+    """--impl reference for robot_cycle: the C restatement of model (B) on all host threads."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    threads = os.cpu_count() or 1
+    n = 256 * threads
+    v, subs, el, sample = cpu_cycle_oracle_throughput(max(5.0, min(60.0, 0.02 * args.steps)), threads, n)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * n / v, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f64", "data": "synthetic",
+        "config": {"workload": args.workload, "envs_per_step": n, "substeps_per_s": subs,
+                   "note": "C restatement of the Python reference's model (B) (oracle/salp_cycle_oracle.c), OpenMP over envs"},
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+def run_cycle_workload(args, wl):
+    """robot_cycle_256k: SalpCycleVectorEnv.step (salp_cycle_step_kernel), one breathing cycle per env and step."""
+    import torch
+    import torch.distributed as dist
+
+    from underwater_swimmer_rl_b200.cycle_env import SalpCycleVectorEnv
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (there is no CPU fallback for the product path)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    N = wl["envs"]
+    real = torch.float64 if wl["dtype"] == "float64" else torch.float32
+    env = SalpCycleVectorEnv(N, device=dev, dtype=wl["dtype"], seed=10_000, env_id0=rank * N, table_rows=min(N, 1 << 16), table_len=64)
+    env.reset()
+    pool = [cycle_actions(torch, N, dev, real, 1234 + 100 * rank + i) for i in range(8)]
+    steps = max(8, min(args.steps, 200))   # one step is milliseconds of device time
+    warmup = max(3, min(args.warmup, 8))
+    for i in range(warmup):
+        env.step(pool[i % 8])
+    sampler = ClockSampler(local)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    env.episode_stats(reset=True)
+    if rank == 0:
+        sampler.start()
+    launches0 = env.launch_count
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for i in range(steps):
+        env.step(pool[(warmup + i) % 8])
+    ev1.record()
+    torch.cuda.synchronize()
+    ms = ev0.elapsed_time(ev1)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    clocks = sampler.stop() if rank == 0 else None
+    launches = env.launch_count - launches0
+    st = env.episode_stats(all_reduce=world > 1)
+    t = torch.tensor([ms], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_max = float(t.item())
+    value = world * N * steps / (ms_max * 1e-3)
+
+    rb = 8 if real == torch.float64 else 4
+    a_h = cycle_actions(torch, N, dev, real, 99).cpu().pin_memory()
+    o_h = torch.empty(N, 6, dtype=torch.float32).pin_memory()
+    r_h = torch.empty(N, dtype=real).pin_memory()
+    te_h = torch.empty(N, dtype=torch.uint8).pin_memory()
+    tr_h = torch.empty(N, dtype=torch.uint8).pin_memory()
+    for _ in range(2):
+        env.step_host(a_h, o_h, r_h, te_h, tr_h)
+    if world > 1:
+        dist.barrier()
+    e2e_steps = max(4, min(args.e2e_steps, 20))
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        env.step_host(a_h, o_h, r_h, te_h, tr_h)
+    torch.cuda.synchronize()
+    t = torch.tensor([time.perf_counter() - t0], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_value = world * N * e2e_steps / float(t.item())
+
+    if rank == 0:
+        peak, peak_src = measured_peak_gbs()
+        # state 6 records + ctrl read and written, actions, obs, reward, two flags, n_sub
+        bpe = 2 * (6 * 4 * rb + 16) + 3 * rb + 24 + rb + 2 + 4
+        kernel_ms = ms_max / steps
+        achieved = bpe * N / (kernel_ms * 1e-3) / 1e9
+        sub_per_s = st["substeps"] / (ms_max * 1e-3)
+        issue = None
+        try:  # warp instructions per substep from the committed ncu capture of this kernel
+            prof = json.load(open(os.path.join(ROOT, "profiles", "r01_ncu_traffic.json"))).get(args.workload)
+            if prof and clocks and clocks.get("sm_mhz"):
+                wi = prof["warp_inst_per_substep"] * sub_per_s / world
+                pk = 148 * 4 * clocks["sm_mhz"] * 1e6
+                issue = {"warp_inst_per_s": wi, "peak": pk, "frac": wi / pk, "warp_inst_per_substep": prof["warp_inst_per_substep"],
+                         "source": "profiles/r01_ncu_traffic.json (smsp__inst_executed.sum / substeps of the captured launch); peak = 148 SMs x 4 schedulers x SM clock"}
+        except (OSError, KeyError, ValueError):
+            issue = None
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": steps, "warmup": warmup,
+            "ms_per_step": ms_max / steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64" if real == torch.float64 else "f32", "data": "synthetic",
+            "config": {"workload": args.workload, "model": "B (robot.py Robot/Nozzle, salp_robot_env.py SalpRobotEnv)",
+                       "envs_per_gpu": N, "global_envs": world * N, "actions": "uniform in Box([0,0,-1],[1,1,1]), 8 resident tensors",
+                       "substeps_per_env_step": st["substeps"] / max(st["env_steps"], 1.0), "integrator_substeps_per_s": sub_per_s,
+                       "l2": "working set 64 MB (L2-resident); the kernel is ALU-bound, cache state is immaterial",
+                       "parallelism": f"env-slab x{world} (no data-path collective; NCCL all-reduce of episode stats only)"},
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                         "kernel": "salp_cycle_step_kernel", "kernel_ms": kernel_ms, "algorithmic_bytes_per_env_step": bpe,
+                         "peak_source": peak_src, "issue": issue,
+                         "note": "~1e5 flops per env step against ~300 B of state: the bound is the FP32/SFU issue rate, see issue"},
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": N * 3 * rb, "d2h_bytes_per_step": N * (24 + rb + 2),
+                    "steps": e2e_steps, "api": "SalpCycleVectorEnv.step_host (pinned host buffers) -> salp_cycle_step"},
+            "gpu_launches": launches, "clocks": clocks,
+            "episode_stats": {k: st[k] for k in ("episodes", "targets_reached", "truncations", "nonfinite", "env_steps", "substeps")},
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            threads = os.cpu_count() or 1
+            v, subs, secs, sample = cpu_cycle_oracle_throughput(args.cpu_seconds, threads, 256 * threads)
+            line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample, "seconds": secs,
+                                    "substeps_per_s": subs, "note": "C restatement of the Python reference (oracle/salp_cycle_oracle.c), "
+                                    "OpenMP; the unmodified Python reference runs ~2.4e3 integrator substeps/s/core in the build container"}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def run_reference_arm(args, wl):
     """--impl reference: the reference's CPU implementation of the path on the host cores.
     The reference is pure Python and cannot travel to the GPU box, so this is its C restatement
@@ -223,6 +399,8 @@ def main():
     wl = dict(WORKLOADS[args.workload])
     if args.envs_per_gpu:
         wl["envs"] = args.envs_per_gpu
+    if wl.get("cycle"):
+        return run_cycle_reference_arm(args, wl) if args.impl == "reference" else run_cycle_workload(args, wl)
     if args.impl == "reference":
         return run_reference_arm(args, wl)
 

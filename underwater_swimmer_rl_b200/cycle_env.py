@@ -181,6 +181,20 @@ class SalpCycleVectorEnv(VectorEnv):
         info = {"n_sub": self.n_sub, "final_obs": self.final_obs}
         return self.obs, self.reward, self.terminated, self.truncated, info
 
+    def step_host(self, actions_h, obs_h, reward_h, terminated_h, truncated_h):
+        """The reference-facing call for callers holding host arrays (what SB3's DummyVecEnv does with one env):
+        pinned host actions -> device, one cycle per env, results -> pinned host buffers; returns when they are
+        filled.  All five arguments are CPU tensors (pin them for full PCIe rate)."""
+        if not hasattr(self, "_a_dev"):
+            self._a_dev = torch.empty((self.num_envs, 3), dtype=self.real, device=self.device)
+        self._a_dev.copy_(actions_h, non_blocking=True)
+        self.step(self._a_dev)
+        obs_h.copy_(self.obs, non_blocking=True)
+        reward_h.copy_(self.reward, non_blocking=True)
+        terminated_h.copy_(self.terminated.view(torch.bool) if terminated_h.dtype == torch.bool else self.terminated, non_blocking=True)
+        truncated_h.copy_(self.truncated.view(torch.bool) if truncated_h.dtype == torch.bool else self.truncated, non_blocking=True)
+        torch.cuda.current_stream(self.device).synchronize()
+
     def close(self, **kwargs):
         self._buffers = None
 
