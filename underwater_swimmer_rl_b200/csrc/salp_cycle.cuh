@@ -53,6 +53,7 @@ struct CycleArgs {
     double dry_mass, L0, W0, density, noz_l12, noz_area, noz_mass;
     double x_min, x_max, y_min, y_max;
     double min_aspect, init_aspect;       // drag-coefficient normalisation (robot.py:638-644), host-computed
+    double inv_aspect_span, inv_noz_area; // float build: 1 / (init_aspect - min_aspect), 1 / nozzle area
     // rest-state geometry, host-computed in the reference's operation order
     double rest_volume, rest_I[3];
 };
@@ -224,7 +225,7 @@ __device__ __forceinline__ void cyc_shape(const CycleArgs &a, double length, dou
     nr = cyc_clip(nr, 0.0, 1.0);
     const double cd = 1.0 - nr * (1.0 - 0.4);
     const double rx = -a.noz_l12 + (-length / 2);        // _get_jet_moment_arm, y = z = 0 (robot.py:567-575)
-    const double nrm = sqrt(rx * rx + 0.0 + 0.0);
+    const double nrm = fabs(rx);                         // np.linalg.norm((rx, 0, 0)) = sqrt(rx^2), exactly |rx|
     const double In = a.noz_mass * (nrm * nrm);
     double I[3];
     I[0] = 0.2 * mass * (hw * hw + hw * hw) + In * 0.0;  // get_inertia_matrix (robot.py:534-551), diagonal
@@ -254,15 +255,65 @@ __device__ __forceinline__ void cyc_shape(const CycleArgs &a, double length, dou
     prev_vol = volume;
 }
 
+// float build: the same quantities with double kept only where nearly equal numbers are subtracted (water volume
+// and inertia between consecutive substeps) -- no double divisions, reciprocals on the SFU.
+template <>
+__device__ __forceinline__ void cyc_shape<float>(const CycleArgs &a, double length, double width, bool jet_phase,
+                                                 double &prev_vol, double prev_I[3], CycleCoef<float> &c) {
+    const double hw = width * 0.5, hl = length * 0.5;
+    const double hw2 = hw * hw, hl2 = hl * hl;
+    const double volume = (4.0 / 3.0 * kCycPi) * hl * hw2;
+    const double mass = a.dry_mass + a.density * volume + a.noz_mass;
+    const double rx = -a.noz_l12 - hl;
+    const double m5 = 0.2 * mass, In = a.noz_mass * (rx * rx);
+    const double I0 = m5 * (hw2 + hw2), I1 = m5 * (hl2 + hw2) + In;   // I_zz == I_yy (robot.py:546-547)
+    const float lf = (float)length, wf = (float)width, hlf = 0.5f * lf, hwf = 0.5f * wf, massf = (float)mass;
+    float nr = (__fdividef(lf, wf) - (float)a.min_aspect) * (float)a.inv_aspect_span;
+    nr = fminf(fmaxf(nr, 0.0f), 1.0f);
+    const float cd = 1.0f - nr * 0.6f;
+    const float dens = (float)a.density;
+    c.mass = massf;
+    c.inv_m = __frcp_rn(massf);
+    c.kd = -0.5f * dens * ((float)kCycPi * hlf * hwf) * cd;
+    const float hl2f = hlf * hlf;
+    c.kt0 = -dens * cd * hwf * (hl2f * hl2f);
+    c.rx = (float)rx;
+    c.cm = 0.0f; c.jet_speed = 0.0f;
+    if (jet_phase) {
+        const float dv = (float)(volume - prev_vol);            // per 0.01 s
+        c.jet_speed = -dv * 100.0f * (float)a.inv_noz_area;
+        c.cm = 0.1f * (dens * dv * 100.0f);
+    }
+    c.dI_rate[0] = (float)(I0 - prev_I[0]) * 100.0f;
+    c.dI_rate[1] = (float)(I1 - prev_I[1]) * 100.0f;
+    c.dI_rate[2] = c.dI_rate[1];
+    prev_I[0] = I0; prev_I[1] = I1; prev_I[2] = I1;
+    c.I[0] = (float)I0; c.I[1] = (float)I1; c.I[2] = c.I[1];
+    c.inv_I[0] = __frcp_rn(c.I[0]); c.inv_I[1] = __frcp_rn(c.I[1]); c.inv_I[2] = c.inv_I[1];
+    prev_vol = volume;
+}
+
 struct CycleStatsAcc {
     double ret = 0.0, cycles = 0.0;
     int episodes = 0, reached = 0, truncs = 0, nonfinite = 0, steps = 0;
     long long substeps = 0;
 };
 
+// sin/cos, sqrt and reciprocal per build.  double: the libm calls the reference makes.  float: SFU
+// approximations (MUFU.SIN/COS after a two-constant reduction to [-pi, pi], MUFU.RSQ, MUFU.RCP; absolute
+// error <= 5e-7, below the resolution the float state carries).
 template <typename T> __device__ __forceinline__ void cyc_sincos(T x, T &s, T &c);
 template <> __device__ __forceinline__ void cyc_sincos<double>(double x, double &s, double &c) { s = sin(x); c = cos(x); }
-template <> __device__ __forceinline__ void cyc_sincos<float>(float x, float &s, float &c) { sincosf(x, &s, &c); }
+template <> __device__ __forceinline__ void cyc_sincos<float>(float x, float &s, float &c) {
+    const float k = rintf(x * 0.15915494f);
+    float r = fmaf(k, -6.2831855f, x);
+    r = fmaf(k, 1.7484555e-7f, r);                 // 2 pi = 6.2831855f - 1.7484555e-7f
+    __sincosf(r, &s, &c);
+}
+__device__ __forceinline__ double cyc_sqrt(double x) { return sqrt(x); }
+__device__ __forceinline__ float cyc_sqrt(float x) { return x > 0.0f ? x * rsqrtf(x) : 0.0f; }
+__device__ __forceinline__ double cyc_rcp(double x) { return 1.0 / x; }
+__device__ __forceinline__ float cyc_rcp(float x) { return __frcp_rn(x); }
 
 // One SalpRobotEnv.step for env e (salp_robot_env.py:139-201): plan the cycle, integrate it, reward,
 // termination, observation, auto-reset.
@@ -308,7 +359,7 @@ __device__ __forceinline__ void cyc_run_env(const CycleArgs &a, long long e, Cyc
         }
         // _newton_equations (:494-505)
         const T cx = w1 * v2 - w2 * v1, cy = w2 * v0 - w0 * v2, cz = w0 * v1 - w1 * v0;
-        const T vnorm = sqrt(v0 * v0 + v1 * v1 + v2 * v2);
+        const T vnorm = cyc_sqrt(v0 * v0 + v1 * v1 + v2 * v2);
         const T kdn = c.kd * vnorm;
         const T fj0 = c.cm * (p.dir[0] * c.jet_speed), fj1 = c.cm * (p.dir[1] * c.jet_speed), fj2 = c.cm * (p.dir[2] * c.jet_speed);
         const T a0 = c.inv_m * (fj0 + (kdn * v0 + c.kd * v0) + c.mass * cx);
@@ -317,7 +368,7 @@ __device__ __forceinline__ void cyc_run_env(const CycleArgs &a, long long e, Cyc
         // _euler_equations (:507-522)
         const T Iw0 = c.I[0] * w0, Iw1 = c.I[1] * w1, Iw2 = c.I[2] * w2;
         const T tc0 = -(w1 * Iw2 - w2 * Iw1), tc1 = -(w2 * Iw0 - w0 * Iw2), tc2 = -(w0 * Iw1 - w1 * Iw0);
-        const T wnorm = sqrt(w0 * w0 + w1 * w1 + w2 * w2);
+        const T wnorm = cyc_sqrt(w0 * w0 + w1 * w1 + w2 * w2);
         const T kt = c.kt0 * wnorm;
         const T tj1 = -(c.rx * fj2), tj2 = c.rx * fj1;   // cross((rx, 0, 0), F_jet)
         const T aa0 = c.inv_I[0] * ((T)0 + kt * w0 + tc0 + (T)0 - c.dI_rate[0] * w0);
@@ -333,7 +384,7 @@ __device__ __forceinline__ void cyc_run_env(const CycleArgs &a, long long e, Cyc
             er1 = 0 * w0 + cphi * w1 + -sphi * w2;
             er2 = 0 * w0 + sphi / cth * w1 + cphi / cth * w2;
         } else {
-            const T icth = (T)1 / cth, tth = sth * icth;
+            const T icth = cyc_rcp(cth), tth = sth * icth;
             er0 = w0 + tth * (sphi * w1 + cphi * w2);
             er1 = cphi * w1 - sphi * w2;
             er2 = icth * (sphi * w1 + cphi * w2);
@@ -425,13 +476,77 @@ __device__ __forceinline__ void cyc_flush_stats(const CycleArgs &a, const CycleS
     }
 }
 
-constexpr int kCycleBlock = 128;
+constexpr int kCycleBlock = 128;   // threads per CTA
+constexpr int kCycleSlice = 1024;  // envs sorted at a time by one CTA
+constexpr int kCycleBuckets = 1;   // coarse contraction-length buckets in front of the substep count in the sort key
 
+// Number of integrator substeps of env e's next cycle and the length of its breathing part, from its action
+// alone (same arithmetic as cyc_plan).
+template <typename T>
+__device__ __forceinline__ void cyc_lengths(const CycleArgs &a, long long e, int &n_total, int &kB) {
+    const T *act = reinterpret_cast<const T *>(a.actions) + 3 * e;
+    const double contraction = (double)act[0] * 0.06, coast = (double)act[1] * 10.0;
+    const double rj = contraction / kContractRate + contraction / kReleaseRate;
+    const double total = rj + coast;
+    const int K = a.max_substeps;
+    const int c = cyc_count_le(a.ct, K, total);
+    const int n = (__ldg(a.ct + c) < total) ? c + 1 : c;
+    n_total = n > K ? K : n;
+    kB = cyc_count_le(a.ct, K, rj);
+}
+
+// Work distribution.  Cycles differ in length by the action (0 .. 1450 substeps), so lanes of a warp that took
+// envs in index order would idle half of the time.  Each CTA owns a contiguous range of envs (all CTAs of the
+// grid are resident: one wave, equal expected work), sorts it in slices of kCycleSlice by substep count
+// (bitonic sort of (count | local index) keys in shared memory), and its warps pull 32-env chunks of the sorted
+// slice, longest first, from a shared counter: the lanes of a warp run cycles of nearly equal length, and a warp
+// that drew short cycles simply draws more of them.
 template <typename T>
 __global__ void __launch_bounds__(kCycleBlock) salp_cycle_step_kernel(const __grid_constant__ CycleArgs a) {
-    const long long e = (long long)blockIdx.x * kCycleBlock + threadIdx.x;
+    __shared__ unsigned s_key[kCycleSlice];
+    __shared__ int s_next, s_valid;
+    const int tid = threadIdx.x, lane = tid & 31;
+    const long long per = (a.n + gridDim.x - 1) / gridDim.x;
+    const long long begin = per * blockIdx.x;
+    const long long end = begin + per < a.n ? begin + per : a.n;
     CycleStatsAcc acc;
-    if (e < a.n) cyc_run_env<T>(a, e, acc);
+    for (long long base = begin; base < end; base += kCycleSlice) {
+        const int cnt = (int)(end - base < kCycleSlice ? end - base : kCycleSlice);
+        if (tid == 0) { s_next = 0; s_valid = cnt; }
+        for (int i = tid; i < kCycleSlice; i += kCycleBlock) {
+            unsigned key = 0xFFFFFFFFu;
+            if (i < cnt) {
+                int n_total, kB;
+                cyc_lengths<T>(a, base + i, n_total, kB);
+                const int bucket = kCycleBuckets > 1 ? min(kCycleBuckets - 1, kB * kCycleBuckets / 451) : 0;
+                key = ((unsigned)bucket << 23) | ((unsigned)n_total << 10) | (unsigned)i;
+            }
+            s_key[i] = key;
+        }
+        __syncthreads();
+        for (int size = 2; size <= kCycleSlice; size <<= 1) {          // bitonic sort, ascending
+            for (int stride = size >> 1; stride > 0; stride >>= 1) {
+                for (int t = tid; t < kCycleSlice / 2; t += kCycleBlock) {
+                    const int lo = 2 * t - (t & (stride - 1)), hi = lo + stride;
+                    const unsigned x = s_key[lo], y = s_key[hi];
+                    const bool up = (lo & size) == 0;
+                    if ((x > y) == up) { s_key[lo] = y; s_key[hi] = x; }
+                }
+                __syncthreads();
+            }
+        }
+        const int n_chunks = (cnt + 31) >> 5;
+        for (;;) {
+            int c = 0;
+            if (lane == 0) c = atomicAdd(&s_next, 1);
+            c = __shfl_sync(0xffffffffu, c, 0);
+            if (c >= n_chunks) break;
+            const int rank = cnt - 1 - (c * 32 + lane);                // longest cycles first
+            if (rank >= 0) cyc_run_env<T>(a, base + (long long)(s_key[rank] & 1023u), acc);
+            __syncwarp();
+        }
+        __syncthreads();                                                 // s_key is rewritten by the next slice
+    }
     cyc_flush_stats(a, acc);
 }
 

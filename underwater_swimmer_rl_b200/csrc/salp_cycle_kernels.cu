@@ -18,8 +18,20 @@ using cyc_real_t = float;
 
 cudaError_t SALP_LAUNCH_CYCLE_STEP(const CycleArgs &a, cudaStream_t s) {
     if (a.n <= 0) return cudaSuccess;
-    const unsigned grid = (unsigned)((a.n + kCycleBlock - 1) / kCycleBlock);
-    salp_cycle_step_kernel<cyc_real_t><<<grid, kCycleBlock, 0, s>>>(a);
+    // one resident wave: (CTAs that fit on an SM) x (SMs), fewer when the slab is small
+    static int resident = 0;
+    if (!resident) {
+        int dev = 0, sms = 0, per_sm = 0;
+        cudaError_t e = cudaGetDevice(&dev);
+        if (e == cudaSuccess) e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, salp_cycle_step_kernel<cyc_real_t>, kCycleBlock, 0);
+        if (e != cudaSuccess) return e;
+        resident = sms * (per_sm > 0 ? per_sm : 1);
+    }
+    long long grid = (a.n + 2 * kCycleBlock - 1) / (2 * kCycleBlock);   // at least two chunks per warp
+    if (grid > resident) grid = resident;
+    if (grid < 1) grid = 1;
+    salp_cycle_step_kernel<cyc_real_t><<<(unsigned)grid, kCycleBlock, 0, s>>>(a);
     return cudaGetLastError();
 }
 
