@@ -53,7 +53,7 @@ struct CycleArgs {
     double dry_mass, L0, W0, density, noz_l12, noz_area, noz_mass;
     double x_min, x_max, y_min, y_max;
     double min_aspect, init_aspect;       // drag-coefficient normalisation (robot.py:638-644), host-computed
-    double inv_aspect_span, inv_noz_area; // float build: 1 / (init_aspect - min_aspect), 1 / nozzle area
+    float f_min_aspect, f_inv_aspect_span, f_density, f_inv_noz_area;  // float build copies
     // rest-state geometry, host-computed in the reference's operation order
     double rest_volume, rest_I[3];
 };
@@ -214,8 +214,9 @@ template <typename T> struct CycleCoef {
 };
 
 template <typename T>
-__device__ __forceinline__ void cyc_shape(const CycleArgs &a, double length, double width, bool jet_phase,
+__device__ __forceinline__ void cyc_shape(const CycleArgs &a, double length, double width, bool jet_phase, const T (&dir)[3],
                                           double &prev_vol, double prev_I[3], CycleCoef<T> &c) {
+    (void)dir;
     const double hw = width / 2, hl = length / 2;
     const double area = kCycPi * hl * hw;
     const double volume = 4.0 / 3.0 * kCycPi * hl * (hw * hw);
@@ -255,10 +256,25 @@ __device__ __forceinline__ void cyc_shape(const CycleArgs &a, double length, dou
     prev_vol = volume;
 }
 
-// float build: the same quantities with double kept only where nearly equal numbers are subtracted (water volume
-// and inertia between consecutive substeps) -- no double divisions, reciprocals on the SFU.
+// float build: every shape-dependent factor is folded into the coefficients the substep multiplies by (forces
+// already divided by the mass, torques by the inertia; I_yy == I_zz, robot.py:546-547, so the gyroscopic
+// term needs I_yy - I_xx only).  double is kept only where nearly equal numbers are subtracted (water volume
+// and inertia of consecutive substeps); no double divisions, reciprocals on the SFU.
+template <> struct CycleCoef<float> {
+    float kda;          // drag: acc_i = kda * (|v| + 1) * v_i
+    float fja[3];       // jet force / mass
+    float kta0, kta1;   // rotational drag: kt0 / I_xx, kt0 / I_yy   (times |omega| * omega_i)
+    float dIa0, dIa1;   // deformation: dI/dt / I
+    float tja1, tja2;   // jet torque / I_yy
+    float g1;           // (I_yy - I_xx) / I_yy
+    float ia;           // 0.1 / I_zz  (asymmetry torque, robot.py:513)
+};
+
+__device__ __forceinline__ float cyc_rcp_approx(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+__device__ __forceinline__ float cyc_rsqrt_approx(float x) { float r; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+
 template <>
-__device__ __forceinline__ void cyc_shape<float>(const CycleArgs &a, double length, double width, bool jet_phase,
+__device__ __forceinline__ void cyc_shape<float>(const CycleArgs &a, double length, double width, bool jet_phase, const float (&dir)[3],
                                                  double &prev_vol, double prev_I[3], CycleCoef<float> &c) {
     const double hw = width * 0.5, hl = length * 0.5;
     const double hw2 = hw * hw, hl2 = hl * hl;
@@ -266,30 +282,31 @@ __device__ __forceinline__ void cyc_shape<float>(const CycleArgs &a, double leng
     const double mass = a.dry_mass + a.density * volume + a.noz_mass;
     const double rx = -a.noz_l12 - hl;
     const double m5 = 0.2 * mass, In = a.noz_mass * (rx * rx);
-    const double I0 = m5 * (hw2 + hw2), I1 = m5 * (hl2 + hw2) + In;   // I_zz == I_yy (robot.py:546-547)
-    const float lf = (float)length, wf = (float)width, hlf = 0.5f * lf, hwf = 0.5f * wf, massf = (float)mass;
-    float nr = (__fdividef(lf, wf) - (float)a.min_aspect) * (float)a.inv_aspect_span;
+    const double I0 = m5 * (hw2 + hw2), I1 = m5 * (hl2 + hw2) + In;
+    const float lf = (float)length, wf = (float)width, hlf = 0.5f * lf, hwf = 0.5f * wf;
+    float nr = (lf * cyc_rcp_approx(wf) - a.f_min_aspect) * a.f_inv_aspect_span;
     nr = fminf(fmaxf(nr, 0.0f), 1.0f);
     const float cd = 1.0f - nr * 0.6f;
-    const float dens = (float)a.density;
-    c.mass = massf;
-    c.inv_m = __frcp_rn(massf);
-    c.kd = -0.5f * dens * ((float)kCycPi * hlf * hwf) * cd;
+    const float inv_m = cyc_rcp_approx((float)mass);
+    const float I0f = (float)I0, I1f = (float)I1;
+    const float inv_I0 = cyc_rcp_approx(I0f), inv_I1 = cyc_rcp_approx(I1f);
+    c.kda = inv_m * (-0.5f * a.f_density * (3.14159265f * hlf * hwf) * cd);
     const float hl2f = hlf * hlf;
-    c.kt0 = -dens * cd * hwf * (hl2f * hl2f);
-    c.rx = (float)rx;
-    c.cm = 0.0f; c.jet_speed = 0.0f;
-    if (jet_phase) {
-        const float dv = (float)(volume - prev_vol);            // per 0.01 s
-        c.jet_speed = -dv * 100.0f * (float)a.inv_noz_area;
-        c.cm = 0.1f * (dens * dv * 100.0f);
-    }
-    c.dI_rate[0] = (float)(I0 - prev_I[0]) * 100.0f;
-    c.dI_rate[1] = (float)(I1 - prev_I[1]) * 100.0f;
-    c.dI_rate[2] = c.dI_rate[1];
+    const float kt0 = -a.f_density * cd * hwf * (hl2f * hl2f);
+    c.kta0 = inv_I0 * kt0; c.kta1 = inv_I1 * kt0;
+    c.fja[0] = 0.0f; c.fja[1] = 0.0f; c.fja[2] = 0.0f; c.tja1 = 0.0f; c.tja2 = 0.0f;
+    c.g1 = inv_I1 * (I1f - I0f);
+    c.ia = 0.1f * inv_I1;
+    c.dIa0 = inv_I0 * ((float)(I0 - prev_I[0]) * 100.0f);
+    c.dIa1 = inv_I1 * ((float)(I1 - prev_I[1]) * 100.0f);
     prev_I[0] = I0; prev_I[1] = I1; prev_I[2] = I1;
-    c.I[0] = (float)I0; c.I[1] = (float)I1; c.I[2] = c.I[1];
-    c.inv_I[0] = __frcp_rn(c.I[0]); c.inv_I[1] = __frcp_rn(c.I[1]); c.inv_I[2] = c.inv_I[1];
+    if (jet_phase) {                                     // robot.py:586-614
+        const float dv = (float)(volume - prev_vol) * 100.0f;            // dV/dt
+        const float f = (0.1f * (a.f_density * dv)) * (-dv * a.f_inv_noz_area);   // C_discharge * mass_rate * jet_speed
+        const float fa = inv_m * f, ta = inv_I1 * ((float)rx * f);
+        c.fja[0] = fa * dir[0]; c.fja[1] = fa * dir[1]; c.fja[2] = fa * dir[2];
+        c.tja1 = -(ta * dir[2]); c.tja2 = ta * dir[1];                   // cross((rx, 0, 0), F_jet) / I
+    }
     prev_vol = volume;
 }
 
@@ -305,15 +322,14 @@ struct CycleStatsAcc {
 template <typename T> __device__ __forceinline__ void cyc_sincos(T x, T &s, T &c);
 template <> __device__ __forceinline__ void cyc_sincos<double>(double x, double &s, double &c) { s = sin(x); c = cos(x); }
 template <> __device__ __forceinline__ void cyc_sincos<float>(float x, float &s, float &c) {
-    const float k = rintf(x * 0.15915494f);
-    float r = fmaf(k, -6.2831855f, x);
-    r = fmaf(k, 1.7484555e-7f, r);                 // 2 pi = 6.2831855f - 1.7484555e-7f
-    __sincosf(r, &s, &c);
+    // MUFU.SIN/COS of x / (2 pi): the phase error of that float product (6e-8 * |x|) is below the spacing of
+    // float angles of that magnitude, so an explicit range reduction would buy nothing
+    __sincosf(x, &s, &c);
 }
 __device__ __forceinline__ double cyc_sqrt(double x) { return sqrt(x); }
-__device__ __forceinline__ float cyc_sqrt(float x) { return x > 0.0f ? x * rsqrtf(x) : 0.0f; }
+__device__ __forceinline__ float cyc_sqrt(float x) { return x * cyc_rsqrt_approx(fmaxf(x, 1e-30f)); }
 __device__ __forceinline__ double cyc_rcp(double x) { return 1.0 / x; }
-__device__ __forceinline__ float cyc_rcp(float x) { return __frcp_rn(x); }
+__device__ __forceinline__ float cyc_rcp(float x) { return cyc_rcp_approx(x); }
 
 // One SalpRobotEnv.step for env e (salp_robot_env.py:139-201): plan the cycle, integrate it, reward,
 // termination, observation, auto-reset.
@@ -355,57 +371,87 @@ __device__ __forceinline__ void cyc_run_env(const CycleArgs &a, long long e, Cyc
                 length = a.L0;
                 width = a.W0;
             }
-            cyc_shape<T>(a, length, width, phase == 1, prev_vol, prev_I, c);
+            cyc_shape<T>(a, length, width, phase == 1, p.dir, prev_vol, prev_I, c);
         }
-        // _newton_equations (:494-505)
-        const T cx = w1 * v2 - w2 * v1, cy = w2 * v0 - w0 * v2, cz = w0 * v1 - w1 * v0;
-        const T vnorm = cyc_sqrt(v0 * v0 + v1 * v1 + v2 * v2);
-        const T kdn = c.kd * vnorm;
-        const T fj0 = c.cm * (p.dir[0] * c.jet_speed), fj1 = c.cm * (p.dir[1] * c.jet_speed), fj2 = c.cm * (p.dir[2] * c.jet_speed);
-        const T a0 = c.inv_m * (fj0 + (kdn * v0 + c.kd * v0) + c.mass * cx);
-        const T a1 = c.inv_m * (fj1 + (kdn * v1 + c.kd * v1) + c.mass * cy);
-        const T a2 = c.inv_m * (fj2 + (kdn * v2 + c.kd * v2) + c.mass * cz);
-        // _euler_equations (:507-522)
-        const T Iw0 = c.I[0] * w0, Iw1 = c.I[1] * w1, Iw2 = c.I[2] * w2;
-        const T tc0 = -(w1 * Iw2 - w2 * Iw1), tc1 = -(w2 * Iw0 - w0 * Iw2), tc2 = -(w0 * Iw1 - w1 * Iw0);
-        const T wnorm = cyc_sqrt(w0 * w0 + w1 * w1 + w2 * w2);
-        const T kt = c.kt0 * wnorm;
-        const T tj1 = -(c.rx * fj2), tj2 = c.rx * fj1;   // cross((rx, 0, 0), F_jet)
-        const T aa0 = c.inv_I[0] * ((T)0 + kt * w0 + tc0 + (T)0 - c.dI_rate[0] * w0);
-        const T aa1 = c.inv_I[1] * (tj1 + kt * w1 + tc1 + (T)0 - c.dI_rate[1] * w1);
-        const T aa2 = c.inv_I[2] * (tj2 + kt * w2 + tc2 + (T)0.1 * vnorm - c.dI_rate[2] * w2);
-        // _update_motion_states (:524-532)
-        v0 += a0 * dt; v1 += a1 * dt; v2 += a2 * dt;
-        w0 += aa0 * dt; w1 += aa1 * dt; w2 += aa2 * dt;
-        T er0, er1, er2;                             // _to_euler_angle_rate (:447-459) on the pre-update angles
         if constexpr (sizeof(T) == 8) {
-            const T tth = tan(e1);
-            er0 = 1 * w0 + sphi * tth * w1 + cphi * tth * w2;
-            er1 = 0 * w0 + cphi * w1 + -sphi * w2;
-            er2 = 0 * w0 + sphi / cth * w1 + cphi / cth * w2;
+            // _newton_equations (:494-505)
+            const T cx = w1 * v2 - w2 * v1, cy = w2 * v0 - w0 * v2, cz = w0 * v1 - w1 * v0;
+            const T vnorm = cyc_sqrt(v0 * v0 + v1 * v1 + v2 * v2);
+            const T kdn = c.kd * vnorm;
+            const T fj0 = c.cm * (p.dir[0] * c.jet_speed), fj1 = c.cm * (p.dir[1] * c.jet_speed), fj2 = c.cm * (p.dir[2] * c.jet_speed);
+            const T a0 = c.inv_m * (fj0 + (kdn * v0 + c.kd * v0) + c.mass * cx);
+            const T a1 = c.inv_m * (fj1 + (kdn * v1 + c.kd * v1) + c.mass * cy);
+            const T a2 = c.inv_m * (fj2 + (kdn * v2 + c.kd * v2) + c.mass * cz);
+            // _euler_equations (:507-522)
+            const T Iw0 = c.I[0] * w0, Iw1 = c.I[1] * w1, Iw2 = c.I[2] * w2;
+            const T tc0 = -(w1 * Iw2 - w2 * Iw1), tc1 = -(w2 * Iw0 - w0 * Iw2), tc2 = -(w0 * Iw1 - w1 * Iw0);
+            const T wnorm = cyc_sqrt(w0 * w0 + w1 * w1 + w2 * w2);
+            const T kt = c.kt0 * wnorm;
+            const T tj1 = -(c.rx * fj2), tj2 = c.rx * fj1;   // cross((rx, 0, 0), F_jet)
+            const T aa0 = c.inv_I[0] * ((T)0 + kt * w0 + tc0 + (T)0 - c.dI_rate[0] * w0);
+            const T aa1 = c.inv_I[1] * (tj1 + kt * w1 + tc1 + (T)0 - c.dI_rate[1] * w1);
+            const T aa2 = c.inv_I[2] * (tj2 + kt * w2 + tc2 + (T)0.1 * vnorm - c.dI_rate[2] * w2);
+            // _update_motion_states (:524-532)
+            v0 += a0 * dt; v1 += a1 * dt; v2 += a2 * dt;
+            w0 += aa0 * dt; w1 += aa1 * dt; w2 += aa2 * dt;
+            T er0, er1, er2;                             // _to_euler_angle_rate (:447-459) on the pre-update angles
+            if constexpr (sizeof(T) == 8) {
+                const T tth = tan(e1);
+                er0 = 1 * w0 + sphi * tth * w1 + cphi * tth * w2;
+                er1 = 0 * w0 + cphi * w1 + -sphi * w2;
+                er2 = 0 * w0 + sphi / cth * w1 + cphi / cth * w2;
+            } else {
+                const T icth = cyc_rcp(cth), tth = sth * icth;
+                er0 = w0 + tth * (sphi * w1 + cphi * w2);
+                er1 = cphi * w1 - sphi * w2;
+                er2 = icth * (sphi * w1 + cphi * w2);
+            }
+            e0 += er0 * dt; e1 += er1 * dt; e2 += er2 * dt;
+            T ss, cs;                                    // _to_world_frame (:461-486) on the updated angles
+            cyc_sincos<T>(e0, sphi, cphi);
+            cyc_sincos<T>(e1, sth, cth);
+            cyc_sincos<T>(e2, ss, cs);
+            const T m00 = cs * cth, m01 = -ss, m02 = cs * sth;
+            const T m10 = ss * cth, m11 = cs, m12 = ss * sth;
+            const T r01 = m01 * cphi + m02 * sphi, r02 = m01 * -sphi + m02 * cphi;
+            const T r11 = m11 * cphi + m12 * sphi, r12 = m11 * -sphi + m12 * cphi;
+            const T r21 = (T)0 * cphi + cth * sphi, r22 = (T)0 * -sphi + cth * cphi;
+            vw0 = m00 * v0 + r01 * v1 + r02 * v2;
+            vw1 = m10 * v0 + r11 * v1 + r12 * v2;
+            vw2 = -sth * v0 + r21 * v1 + r22 * v2;
+            p0 += vw0 * dt; p1 += vw1 * dt; p2 += vw2 * dt;
         } else {
+            // the same equations with the shape-only factors pre-folded (CycleCoef<float>)
+            const T cx = w1 * v2 - w2 * v1, cy = w2 * v0 - w0 * v2, cz = w0 * v1 - w1 * v0;
+            const T vnorm = cyc_sqrt(v0 * v0 + v1 * v1 + v2 * v2);
+            const T kdv = fmaf(c.kda, vnorm, c.kda);
+            const T a0 = fmaf(kdv, v0, c.fja[0]) + cx, a1 = fmaf(kdv, v1, c.fja[1]) + cy, a2 = fmaf(kdv, v2, c.fja[2]) + cz;
+            const T wnorm = cyc_sqrt(w0 * w0 + w1 * w1 + w2 * w2);
+            const T kw0 = fmaf(c.kta0, wnorm, -c.dIa0), kw1 = fmaf(c.kta1, wnorm, -c.dIa1);
+            const T aa0 = kw0 * w0;                                       // I_yy == I_zz: no gyroscopic roll torque
+            const T aa1 = fmaf(c.g1, w0 * w2, fmaf(kw1, w1, c.tja1));
+            const T aa2 = fmaf(c.ia, vnorm, fmaf(-c.g1, w0 * w1, fmaf(kw1, w2, c.tja2)));
+            v0 = fmaf(a0, dt, v0); v1 = fmaf(a1, dt, v1); v2 = fmaf(a2, dt, v2);
+            w0 = fmaf(aa0, dt, w0); w1 = fmaf(aa1, dt, w1); w2 = fmaf(aa2, dt, w2);
             const T icth = cyc_rcp(cth), tth = sth * icth;
-            er0 = w0 + tth * (sphi * w1 + cphi * w2);
-            er1 = cphi * w1 - sphi * w2;
-            er2 = icth * (sphi * w1 + cphi * w2);
+            const T t12 = fmaf(sphi, w1, cphi * w2);
+            e0 = fmaf(fmaf(tth, t12, w0), dt, e0);
+            e1 = fmaf(fmaf(cphi, w1, -sphi * w2), dt, e1);
+            e2 = fmaf(icth * t12, dt, e2);
+            T ss, cs;
+            cyc_sincos<T>(e0, sphi, cphi);
+            cyc_sincos<T>(e1, sth, cth);
+            cyc_sincos<T>(e2, ss, cs);
+            const T m02 = cs * sth, m12 = ss * sth;
+            vw0 = fmaf(cs * cth, v0, fmaf(fmaf(m02, sphi, -ss * cphi), v1, fmaf(m02, cphi, ss * sphi) * v2));
+            vw1 = fmaf(ss * cth, v0, fmaf(fmaf(m12, sphi, cs * cphi), v1, fmaf(m12, cphi, -cs * sphi) * v2));
+            vw2 = fmaf(-sth, v0, cth * fmaf(sphi, v1, cphi * v2));
+            p0 = fmaf(vw0, dt, p0); p1 = fmaf(vw1, dt, p1); p2 = fmaf(vw2, dt, p2);
         }
-        e0 += er0 * dt; e1 += er1 * dt; e2 += er2 * dt;
-        T ss, cs;                                    // _to_world_frame (:461-486) on the updated angles
-        cyc_sincos<T>(e0, sphi, cphi);
-        cyc_sincos<T>(e1, sth, cth);
-        cyc_sincos<T>(e2, ss, cs);
-        const T m00 = cs * cth, m01 = -ss, m02 = cs * sth;
-        const T m10 = ss * cth, m11 = cs, m12 = ss * sth;
-        const T r01 = m01 * cphi + m02 * sphi, r02 = m01 * -sphi + m02 * cphi;
-        const T r11 = m11 * cphi + m12 * sphi, r12 = m11 * -sphi + m12 * cphi;
-        const T r21 = (T)0 * cphi + cth * sphi, r22 = (T)0 * -sphi + cth * cphi;
-        vw0 = m00 * v0 + r01 * v1 + r02 * v2;
-        vw1 = m10 * v0 + r11 * v1 + r12 * v2;
-        vw2 = -sth * v0 + r21 * v1 + r22 * v2;
-        p0 += vw0 * dt; p1 += vw1 * dt; p2 += vw2 * dt;
         if (!steady && phase >= 2) {                 // shape is constant from here on: no deformation torque
             steady = true;
-            c.dI_rate[0] = 0; c.dI_rate[1] = 0; c.dI_rate[2] = 0;
+            if constexpr (sizeof(T) == 8) { c.dI_rate[0] = 0; c.dI_rate[1] = 0; c.dI_rate[2] = 0; }
+            else { c.dIa0 = 0; c.dIa1 = 0; }
         }
     }
     s.vel[0] = v0; s.vel[1] = v1; s.vel[2] = v2; s.w[0] = w0; s.w[1] = w1; s.w[2] = w2;

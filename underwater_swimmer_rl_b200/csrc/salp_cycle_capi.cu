@@ -71,8 +71,8 @@ int fill_args(const SalpCycleParams *p, const SalpCycleBuffers *b, salp::CycleAr
     const double cl = p->init_length - p->max_contraction;
     const double cw = p->init_length - cl + p->init_width;
     a.min_aspect = cl / cw;
-    a.inv_aspect_span = 1.0 / (a.init_aspect - a.min_aspect);
-    a.inv_noz_area = 1.0 / p->nozzle_area;
+    a.f_min_aspect = (float)a.min_aspect; a.f_inv_aspect_span = (float)(1.0 / (a.init_aspect - a.min_aspect));
+    a.f_density = (float)p->density; a.f_inv_noz_area = (float)(1.0 / p->nozzle_area);
     // Robot.reset geometry (robot.py:303-311), reference operation order
     const double kPi = 3.141592653589793;
     const double hw = p->init_width / 2, hl = p->init_length / 2;
