@@ -355,23 +355,31 @@ __device__ __forceinline__ void cyc_run_env(const CycleArgs &a, long long e, Cyc
     cyc_sincos<T>(e0, sphi, cphi);
     cyc_sincos<T>(e1, sth, cth);
 
+    bool rest_shape = false;                         // the coefficients already describe the rest shape
     for (int k = 1; k <= p.n_total; ++k) {          // step_through_cycle (robot.py:435-436), Robot.step (:387-395)
-        phase = k <= p.kA ? 0 : (k <= p.kB ? 1 : (k <= p.kC ? 2 : 3));   // update_state (:360-373)
-        if (!steady) {                              // update_properties (:375-385)
-            if (phase <= 1) {
-                const double ctk = __ldg(a.ct + k);
-                if (phase == 0) {                   // get_current_length / width (:702-730)
-                    length = a.L0 - ctk * kContractRate;
-                    width = a.W0 + ctk * kContractRate;
-                } else {
-                    length = a.L0 - p.contraction + (ctk - p.refill) * kReleaseRate;
-                    width = a.W0 + p.contraction - (ctk - p.refill) * kReleaseRate;
-                }
+        if (!steady) {                              // update_state (:360-373), update_properties (:375-385)
+            phase = k <= p.kA ? 0 : (k <= p.kB ? 1 : (k <= p.kC ? 2 : 3));
+            if (rest_shape) {                       // second substep at rest shape: no deformation torque any more
+                steady = true;
+                if constexpr (sizeof(T) == 8) { c.dI_rate[0] = 0; c.dI_rate[1] = 0; c.dI_rate[2] = 0; }
+                else { c.dIa0 = 0; c.dIa1 = 0; }
             } else {
-                length = a.L0;
-                width = a.W0;
+                if (phase <= 1) {
+                    const double ctk = __ldg(a.ct + k);
+                    if (phase == 0) {               // get_current_length / width (:702-730)
+                        length = a.L0 - ctk * kContractRate;
+                        width = a.W0 + ctk * kContractRate;
+                    } else {
+                        length = a.L0 - p.contraction + (ctk - p.refill) * kReleaseRate;
+                        width = a.W0 + p.contraction - (ctk - p.refill) * kReleaseRate;
+                    }
+                } else {
+                    length = a.L0;
+                    width = a.W0;
+                    rest_shape = true;
+                }
+                cyc_shape<T>(a, length, width, phase == 1, p.dir, prev_vol, prev_I, c);
             }
-            cyc_shape<T>(a, length, width, phase == 1, p.dir, prev_vol, prev_I, c);
         }
         if constexpr (sizeof(T) == 8) {
             // _newton_equations (:494-505)
@@ -448,12 +456,8 @@ __device__ __forceinline__ void cyc_run_env(const CycleArgs &a, long long e, Cyc
             vw2 = fmaf(-sth, v0, cth * fmaf(sphi, v1, cphi * v2));
             p0 = fmaf(vw0, dt, p0); p1 = fmaf(vw1, dt, p1); p2 = fmaf(vw2, dt, p2);
         }
-        if (!steady && phase >= 2) {                 // shape is constant from here on: no deformation torque
-            steady = true;
-            if constexpr (sizeof(T) == 8) { c.dI_rate[0] = 0; c.dI_rate[1] = 0; c.dI_rate[2] = 0; }
-            else { c.dIa0 = 0; c.dIa1 = 0; }
-        }
     }
+    if (p.n_total > 0) phase = p.n_total <= p.kA ? 0 : (p.n_total <= p.kB ? 1 : (p.n_total <= p.kC ? 2 : 3));
     s.vel[0] = v0; s.vel[1] = v1; s.vel[2] = v2; s.w[0] = w0; s.w[1] = w1; s.w[2] = w2;
     s.eu[0] = e0; s.eu[1] = e1; s.eu[2] = e2; s.pos[0] = p0; s.pos[1] = p1; s.pos[2] = p2;
     s.vw[0] = vw0; s.vw[1] = vw1; s.vw[2] = vw2;
@@ -547,8 +551,8 @@ __device__ __forceinline__ void cyc_lengths(const CycleArgs &a, long long e, int
 // (bitonic sort of (count | local index) keys in shared memory), and its warps pull 32-env chunks of the sorted
 // slice, longest first, from a shared counter: the lanes of a warp run cycles of nearly equal length, and a warp
 // that drew short cycles simply draws more of them.
-template <typename T>
-__global__ void __launch_bounds__(kCycleBlock) salp_cycle_step_kernel(const __grid_constant__ CycleArgs a) {
+template <typename T, int MINB>
+__global__ void __launch_bounds__(kCycleBlock, MINB) salp_cycle_step_kernel(const __grid_constant__ CycleArgs a) {
     __shared__ unsigned s_key[kCycleSlice];
     __shared__ int s_next, s_valid;
     const int tid = threadIdx.x, lane = tid & 31;

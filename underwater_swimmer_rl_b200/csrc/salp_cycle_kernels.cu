@@ -2,6 +2,8 @@
 // Compiled twice by build.py:
 //   -DSALP_BUILD_F64=0                 -> launch_cycle_step_f32 / launch_cycle_reset_f32   (throughput build)
 //   -DSALP_BUILD_F64=1 -fmad=false     -> launch_cycle_step_f64 / launch_cycle_reset_f64   (validation build)
+#include <stdlib.h>
+
 #include "salp_cycle.cuh"
 
 namespace salp {
@@ -16,23 +18,40 @@ using cyc_real_t = float;
 #define SALP_LAUNCH_CYCLE_RESET launch_cycle_reset_f32
 #endif
 
-cudaError_t SALP_LAUNCH_CYCLE_STEP(const CycleArgs &a, cudaStream_t s) {
-    if (a.n <= 0) return cudaSuccess;
+template <int MINB>
+static cudaError_t launch_cycle_variant(const CycleArgs &a, cudaStream_t s) {
     // one resident wave: (CTAs that fit on an SM) x (SMs), fewer when the slab is small
     static int resident = 0;
     if (!resident) {
         int dev = 0, sms = 0, per_sm = 0;
         cudaError_t e = cudaGetDevice(&dev);
         if (e == cudaSuccess) e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, salp_cycle_step_kernel<cyc_real_t>, kCycleBlock, 0);
+        if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, salp_cycle_step_kernel<cyc_real_t, MINB>, kCycleBlock, 0);
         if (e != cudaSuccess) return e;
         resident = sms * (per_sm > 0 ? per_sm : 1);
     }
     long long grid = (a.n + 2 * kCycleBlock - 1) / (2 * kCycleBlock);   // at least two chunks per warp
     if (grid > resident) grid = resident;
     if (grid < 1) grid = 1;
-    salp_cycle_step_kernel<cyc_real_t><<<(unsigned)grid, kCycleBlock, 0, s>>>(a);
+    salp_cycle_step_kernel<cyc_real_t, MINB><<<(unsigned)grid, kCycleBlock, 0, s>>>(a);
     return cudaGetLastError();
+}
+
+cudaError_t SALP_LAUNCH_CYCLE_STEP(const CycleArgs &a, cudaStream_t s) {
+    if (a.n <= 0) return cudaSuccess;
+#if SALP_BUILD_F64
+    return launch_cycle_variant<1>(a, s);
+#else
+    static int minb = 0;   // SALP_CYCLE_MINB: tuning knob of tools/ (register budget = 65536 / (128 * MINB))
+    if (!minb) { const char *v = getenv("SALP_CYCLE_MINB"); minb = v ? atoi(v) : 5; }
+    switch (minb) {
+        case 4: return launch_cycle_variant<4>(a, s);
+        case 6: return launch_cycle_variant<6>(a, s);
+        case 7: return launch_cycle_variant<7>(a, s);
+        case 8: return launch_cycle_variant<8>(a, s);
+        default: return launch_cycle_variant<5>(a, s);
+    }
+#endif
 }
 
 cudaError_t SALP_LAUNCH_CYCLE_RESET(const CycleArgs &a, cudaStream_t s) {
