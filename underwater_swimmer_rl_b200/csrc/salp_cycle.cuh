@@ -54,6 +54,7 @@ struct CycleArgs {
     double x_min, x_max, y_min, y_max;
     double min_aspect, init_aspect;       // drag-coefficient normalisation (robot.py:638-644), host-computed
     float f_min_aspect, f_inv_aspect_span, f_density, f_inv_noz_area;  // float build copies
+    float f_L0, f_W0, f_l12, f_noz_mass, f_m_fixed;                    // m_fixed = dry mass + nozzle mass
     // rest-state geometry, host-computed in the reference's operation order
     double rest_volume, rest_I[3];
 };
@@ -273,41 +274,48 @@ template <> struct CycleCoef<float> {
 __device__ __forceinline__ float cyc_rcp_approx(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
 __device__ __forceinline__ float cyc_rsqrt_approx(float x) { float r; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
 
-template <>
-__device__ __forceinline__ void cyc_shape<float>(const CycleArgs &a, double length, double width, bool jet_phase, const float (&dir)[3],
-                                                 double &prev_vol, double prev_I[3], CycleCoef<float> &c) {
-    const double hw = width * 0.5, hl = length * 0.5;
-    const double hw2 = hw * hw, hl2 = hl * hl;
-    const double volume = (4.0 / 3.0 * kCycPi) * hl * hw2;
-    const double mass = a.dry_mass + a.density * volume + a.noz_mass;
-    const double rx = -a.noz_l12 - hl;
-    const double m5 = 0.2 * mass, In = a.noz_mass * (rx * rx);
-    const double I0 = m5 * (hw2 + hw2), I1 = m5 * (hl2 + hw2) + In;
-    const float lf = (float)length, wf = (float)width, hlf = 0.5f * lf, hwf = 0.5f * wf;
-    float nr = (lf * cyc_rcp_approx(wf) - a.f_min_aspect) * a.f_inv_aspect_span;
+// float build.  Shape state is the contraction progress s (length = L0 - s, width = W0 + s).  The rates the
+// dynamics need are differences of the volume / inertia of consecutive substeps; instead of subtracting two
+// nearly equal numbers they are expanded exactly in the step delta = s - s_prev, which keeps everything in
+// float (no double arithmetic, no conversions):
+//   g(s) = L W^2                 V = pi/6 g          g(s) - g(s - delta) = delta (2 L1 W1 - W1^2) + delta^2 (L1 - 2 W1) - delta^3
+//   q(s) = (L^2 + W^2) / 4                           q(s) - q(s - delta) = delta ((W1 + W2) - (L1 + L2)) / 4
+//   rx(s) = -(l1 + l2) - L / 2                       rx^2(s) - rx^2(s - delta) = delta / 2 (rx1 + rx2)
+// with index 1 = previous shape, 2 = current shape.
+__device__ __forceinline__ void cyc_shape_f(const CycleArgs &a, float s2, float delta, bool jet_phase, const float (&dir)[3],
+                                            CycleCoef<float> &c) {
+    const float L2 = a.f_L0 - s2, W2 = a.f_W0 + s2, L1 = L2 + delta, W1 = W2 - delta;
+    const float kv = 0.52359878f * a.f_density;                       // rho pi / 6
+    const float g2 = L2 * W2 * W2;
+    const float dg = delta * (fmaf(2.0f * L1, W1, -W1 * W1) + delta * ((L1 - 2.0f * W1) - delta));
+    const float m2 = fmaf(kv, g2, a.f_m_fixed), dm = kv * dg, m1 = m2 - dm;
+    const float q2 = 0.25f * fmaf(L2, L2, W2 * W2);
+    const float dq = 0.25f * delta * ((W1 + W2) - (L1 + L2));
+    const float rx2 = -a.f_l12 - 0.5f * L2, rx1 = rx2 - 0.5f * delta;
+    const float I1 = fmaf(0.2f * m2, q2, a.f_noz_mass * rx2 * rx2);
+    const float dI1 = fmaf(0.2f, fmaf(dm, q2, m1 * dq), a.f_noz_mass * (0.5f * delta) * (rx1 + rx2));
+    const float I0 = 0.1f * m2 * (W2 * W2);
+    const float dI0 = 0.1f * fmaf(dm, W2 * W2, m1 * delta * (W1 + W2));
+    float nr = (L2 * cyc_rcp_approx(W2) - a.f_min_aspect) * a.f_inv_aspect_span;
     nr = fminf(fmaxf(nr, 0.0f), 1.0f);
-    const float cd = 1.0f - nr * 0.6f;
-    const float inv_m = cyc_rcp_approx((float)mass);
-    const float I0f = (float)I0, I1f = (float)I1;
-    const float inv_I0 = cyc_rcp_approx(I0f), inv_I1 = cyc_rcp_approx(I1f);
-    c.kda = inv_m * (-0.5f * a.f_density * (3.14159265f * hlf * hwf) * cd);
-    const float hl2f = hlf * hlf;
-    const float kt0 = -a.f_density * cd * hwf * (hl2f * hl2f);
+    const float cd = fmaf(nr, -0.6f, 1.0f);
+    const float inv_m = cyc_rcp_approx(m2), inv_I0 = cyc_rcp_approx(I0), inv_I1 = cyc_rcp_approx(I1);
+    const float rcd = a.f_density * cd, hl = 0.5f * L2, hl2 = hl * hl;
+    c.kda = inv_m * (-0.39269908f * rcd * (L2 * W2));                  // -0.5 rho (pi L W / 4) cd / m
+    const float kt0 = -rcd * (0.5f * W2) * (hl2 * hl2);
     c.kta0 = inv_I0 * kt0; c.kta1 = inv_I1 * kt0;
-    c.fja[0] = 0.0f; c.fja[1] = 0.0f; c.fja[2] = 0.0f; c.tja1 = 0.0f; c.tja2 = 0.0f;
-    c.g1 = inv_I1 * (I1f - I0f);
+    c.g1 = inv_I1 * (I1 - I0);
     c.ia = 0.1f * inv_I1;
-    c.dIa0 = inv_I0 * ((float)(I0 - prev_I[0]) * 100.0f);
-    c.dIa1 = inv_I1 * ((float)(I1 - prev_I[1]) * 100.0f);
-    prev_I[0] = I0; prev_I[1] = I1; prev_I[2] = I1;
-    if (jet_phase) {                                     // robot.py:586-614
-        const float dv = (float)(volume - prev_vol) * 100.0f;            // dV/dt
-        const float f = (0.1f * (a.f_density * dv)) * (-dv * a.f_inv_noz_area);   // C_discharge * mass_rate * jet_speed
-        const float fa = inv_m * f, ta = inv_I1 * ((float)rx * f);
-        c.fja[0] = fa * dir[0]; c.fja[1] = fa * dir[1]; c.fja[2] = fa * dir[2];
-        c.tja1 = -(ta * dir[2]); c.tja2 = ta * dir[1];                   // cross((rx, 0, 0), F_jet) / I
+    c.dIa0 = inv_I0 * (dI0 * 100.0f);
+    c.dIa1 = inv_I1 * (dI1 * 100.0f);
+    float f = 0.0f;
+    if (jet_phase) {                                                    // robot.py:586-614
+        const float dv = 0.52359878f * dg * 100.0f;                    // dV/dt
+        f = (0.1f * (a.f_density * dv)) * (-dv * a.f_inv_noz_area);   // C_discharge * mass_rate * jet_speed
     }
-    prev_vol = volume;
+    const float fa = inv_m * f, ta = inv_I1 * (rx2 * f);
+    c.fja[0] = fa * dir[0]; c.fja[1] = fa * dir[1]; c.fja[2] = fa * dir[2];
+    c.tja1 = -(ta * dir[2]); c.tja2 = ta * dir[1];                     // cross((rx, 0, 0), F_jet) / I
 }
 
 struct CycleStatsAcc {
@@ -344,6 +352,7 @@ __device__ __forceinline__ void cyc_run_env(const CycleArgs &a, long long e, Cyc
 
     double prev_vol = (double)s.volume, prev_I[3] = {(double)s.prev_I[0], (double)s.prev_I[1], (double)s.prev_I[2]};
     double length = (double)s.length, width = (double)s.width;
+    double s_prev = a.L0 - length;                   // float build: contraction progress of the previous substep
     int phase = s.phase;
     CycleCoef<T> c;
     bool steady = false;
@@ -364,21 +373,33 @@ __device__ __forceinline__ void cyc_run_env(const CycleArgs &a, long long e, Cyc
                 if constexpr (sizeof(T) == 8) { c.dI_rate[0] = 0; c.dI_rate[1] = 0; c.dI_rate[2] = 0; }
                 else { c.dIa0 = 0; c.dIa1 = 0; }
             } else {
-                if (phase <= 1) {
-                    const double ctk = __ldg(a.ct + k);
-                    if (phase == 0) {               // get_current_length / width (:702-730)
-                        length = a.L0 - ctk * kContractRate;
-                        width = a.W0 + ctk * kContractRate;
+                if constexpr (sizeof(T) == 8) {
+                    if (phase <= 1) {
+                        const double ctk = __ldg(a.ct + k);
+                        if (phase == 0) {           // get_current_length / width (:702-730)
+                            length = a.L0 - ctk * kContractRate;
+                            width = a.W0 + ctk * kContractRate;
+                        } else {
+                            length = a.L0 - p.contraction + (ctk - p.refill) * kReleaseRate;
+                            width = a.W0 + p.contraction - (ctk - p.refill) * kReleaseRate;
+                        }
                     } else {
-                        length = a.L0 - p.contraction + (ctk - p.refill) * kReleaseRate;
-                        width = a.W0 + p.contraction - (ctk - p.refill) * kReleaseRate;
+                        length = a.L0;
+                        width = a.W0;
+                        rest_shape = true;
                     }
+                    cyc_shape<T>(a, length, width, phase == 1, p.dir, prev_vol, prev_I, c);
                 } else {
-                    length = a.L0;
-                    width = a.W0;
-                    rest_shape = true;
+                    double s2 = 0.0;
+                    if (phase <= 1) {
+                        const double ctk = __ldg(a.ct + k);
+                        s2 = phase == 0 ? ctk * kContractRate : p.contraction - (ctk - p.refill) * kReleaseRate;
+                    } else {
+                        rest_shape = true;
+                    }
+                    cyc_shape_f(a, (float)s2, (float)(s2 - s_prev), phase == 1, p.dir, c);
+                    s_prev = s2;
                 }
-                cyc_shape<T>(a, length, width, phase == 1, p.dir, prev_vol, prev_I, c);
             }
         }
         if constexpr (sizeof(T) == 8) {
@@ -462,6 +483,15 @@ __device__ __forceinline__ void cyc_run_env(const CycleArgs &a, long long e, Cyc
     s.eu[0] = e0; s.eu[1] = e1; s.eu[2] = e2; s.pos[0] = p0; s.pos[1] = p1; s.pos[2] = p2;
     s.vw[0] = vw0; s.vw[1] = vw1; s.vw[2] = vw2;
     s.phase = phase;
+    if constexpr (sizeof(T) == 4) {                  // the stored shape state, from the last substep's progress
+        if (p.n_total > 0) {
+            length = a.L0 - s_prev; width = a.W0 + s_prev;
+            const double hw = width * 0.5, hl = length * 0.5, rx = -a.noz_l12 - hl;
+            prev_vol = (4.0 / 3.0 * kCycPi) * hl * (hw * hw);
+            const double m5 = 0.2 * (a.dry_mass + a.density * prev_vol + a.noz_mass), In = a.noz_mass * (rx * rx);
+            prev_I[0] = m5 * (hw * hw + hw * hw); prev_I[1] = m5 * (hl * hl + hw * hw) + In; prev_I[2] = prev_I[1];
+        }
+    }
     s.volume = (T)prev_vol; s.prev_I[0] = (T)prev_I[0]; s.prev_I[1] = (T)prev_I[1]; s.prev_I[2] = (T)prev_I[2];
     s.length = (T)length; s.width = (T)width;
 

@@ -73,6 +73,8 @@ int fill_args(const SalpCycleParams *p, const SalpCycleBuffers *b, salp::CycleAr
     a.min_aspect = cl / cw;
     a.f_min_aspect = (float)a.min_aspect; a.f_inv_aspect_span = (float)(1.0 / (a.init_aspect - a.min_aspect));
     a.f_density = (float)p->density; a.f_inv_noz_area = (float)(1.0 / p->nozzle_area);
+    a.f_L0 = (float)p->init_length; a.f_W0 = (float)p->init_width; a.f_l12 = (float)a.noz_l12;
+    a.f_noz_mass = (float)p->nozzle_mass; a.f_m_fixed = (float)(p->dry_mass + p->nozzle_mass);
     // Robot.reset geometry (robot.py:303-311), reference operation order
     const double kPi = 3.141592653589793;
     const double hw = p->init_width / 2, hl = p->init_length / 2;
