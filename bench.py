@@ -262,7 +262,7 @@ def run_cycle_workload(args, wl):
     torch.cuda.synchronize()
     clocks = sampler.stop() if rank == 0 else None
     launches = env.launch_count - launches0
-    st = env.episode_stats(all_reduce=world > 1)
+    st = env.episode_stats()   # NCCL all-reduce (SUM) of the 8-double stats vector when world > 1
     t = torch.tensor([ms], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)

@@ -24,6 +24,11 @@ def _worker(rank, world, port, total, out_q):
     # per-rank statistics as the kernel would leave them: episodes, sum return, sum length, ...
     stats = torch.tensor([n, -1.5 * n, 10.0 * n, 0.5 * n, n - 1, 1, 0, 100.0 * n], dtype=torch.float64)
     red = all_reduce_stats(stats)
+    # model (B) vector: episodes, sum return, sum cycles, reached, truncations, non-finite, env steps, substeps
+    from underwater_swimmer_rl_b200.sharding import CYCLE_STATS_KEYS
+    cyc = all_reduce_stats(torch.tensor([n, 2.0 * n, 500.0 * n, 1, n - 1, 0, 4.0 * n, 2900.0 * n], dtype=torch.float64),
+                           keys=CYCLE_STATS_KEYS)
+    red["cycle"] = cyc
     out_q.put((rank, start, n, red))
     dist.barrier()
     dist.destroy_process_group()
@@ -47,3 +52,6 @@ def test_two_rank_stats_all_reduce():
     assert red0["episodes"] == total and red0["env_steps"] == 100.0 * total
     assert red0["collisions"] == total - 2 and red0["truncations"] == 2
     assert abs(red0["mean_return"] + 1.5) < 1e-12 and abs(red0["mean_length"] - 10.0) < 1e-12
+    cyc = red0["cycle"]
+    assert cyc["episodes"] == total and cyc["targets_reached"] == 2 and cyc["truncations"] == total - 2
+    assert cyc["mean_cycles"] == 500.0 and cyc["substeps_per_env_step"] == 725.0 and cyc["mean_return"] == 2.0

@@ -49,6 +49,7 @@ struct CycleArgs {
     long long n, env_id0, rows;
     unsigned len_mask;
     int max_cycles, max_substeps, autoreset, rewind_rng;
+    int sort_buckets;  // breathing-length groups in front of the substep count in the sort key (0 = by slice size)
     // robot / nozzle / tank parameters
     double dry_mass, L0, W0, density, noz_l12, noz_area, noz_mass;
     double x_min, x_max, y_min, y_max;
@@ -558,7 +559,6 @@ __device__ __forceinline__ void cyc_flush_stats(const CycleArgs &a, const CycleS
 
 constexpr int kCycleBlock = 128;   // threads per CTA
 constexpr int kCycleSlice = 1024;  // envs sorted at a time by one CTA
-constexpr int kCycleBuckets = 1;   // coarse contraction-length buckets in front of the substep count in the sort key
 
 // Number of integrator substeps of env e's next cycle and the length of its breathing part, from its action
 // alone (same arithmetic as cyc_plan).
@@ -593,12 +593,15 @@ __global__ void __launch_bounds__(kCycleBlock, MINB) salp_cycle_step_kernel(cons
     for (long long base = begin; base < end; base += kCycleSlice) {
         const int cnt = (int)(end - base < kCycleSlice ? end - base : kCycleSlice);
         if (tid == 0) { s_next = 0; s_valid = cnt; }
+        // lanes that still breathe make the whole warp run the shape block: with enough chunks in the slice, group
+        // envs of similar breathing length first (measured: 2 groups at 11 chunks, 3-4 at 32)
+        const int n_buckets = a.sort_buckets > 0 ? a.sort_buckets : max(1, min(4, (((cnt + 31) >> 5) + 3) / 7));
         for (int i = tid; i < kCycleSlice; i += kCycleBlock) {
             unsigned key = 0xFFFFFFFFu;
             if (i < cnt) {
                 int n_total, kB;
                 cyc_lengths<T>(a, base + i, n_total, kB);
-                const int bucket = kCycleBuckets > 1 ? min(kCycleBuckets - 1, kB * kCycleBuckets / 451) : 0;
+                const int bucket = n_buckets > 1 ? min(n_buckets - 1, kB * n_buckets / 451) : 0;
                 key = ((unsigned)bucket << 23) | ((unsigned)n_total << 10) | (unsigned)i;
             }
             s_key[i] = key;

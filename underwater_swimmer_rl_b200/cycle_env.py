@@ -20,8 +20,7 @@ from . import _capi, rng_tables
 from ._gym_compat import Box, VectorEnv, batch_box
 from .vector_env import _torch_dtype
 
-CYCLE_STATS_KEYS = ("episodes", "return_sum", "cycle_sum", "targets_reached", "truncations", "nonfinite",
-                    "env_steps", "substeps")
+from .sharding import CYCLE_STATS_KEYS  # noqa: E402,F401  (re-exported)
 PHASE_NAMES = ("REFILL", "JET", "COAST", "REST")  # Robot.Phase, robot.py:188-192
 
 
@@ -220,14 +219,11 @@ class SalpCycleVectorEnv(VectorEnv):
     @property
     def episode_return(self): return self.state[2, :, 3]
 
-    def episode_stats(self, reset: bool = False, all_reduce: bool = False) -> dict:
-        """Counters accumulated by the kernel since the last reset=True call; with all_reduce they are summed
-        over the ranks of torch.distributed's default group (the path's only collective)."""
-        st = self.stats.clone()
+    def episode_stats(self, reduce_group=None, reset: bool = False) -> dict:
+        """Counters accumulated by the kernel since the last reset=True call.  With an initialised process group the
+        8-double vector is all-reduced (SUM) over ranks -- the path's only collective."""
+        from .sharding import CYCLE_STATS_KEYS as keys, all_reduce_stats
+        out = all_reduce_stats(self.stats, reduce_group, keys)
         if reset:
             self.stats.zero_()
-        if all_reduce:
-            import torch.distributed as dist
-            if dist.is_available() and dist.is_initialized():
-                dist.all_reduce(st)
-        return dict(zip(CYCLE_STATS_KEYS, st.tolist()))
+        return out

@@ -11,6 +11,8 @@ import torch
 import torch.distributed as dist
 
 STATS_KEYS = ("episodes", "return_sum", "length_sum", "food_sum", "collisions", "truncations", "nonfinite", "env_steps")
+# model (B) cycle env (salp_cycle_step, include/salp_b200.h)
+CYCLE_STATS_KEYS = ("episodes", "return_sum", "cycle_sum", "targets_reached", "truncations", "nonfinite", "env_steps", "substeps")
 
 
 def slab_for_rank(total_envs: int, rank: int, world: int) -> Tuple[int, int]:
@@ -24,13 +26,17 @@ def slab_for_rank(total_envs: int, rank: int, world: int) -> Tuple[int, int]:
     return start, n
 
 
-def all_reduce_stats(stats: torch.Tensor, group: Optional[dist.ProcessGroup] = None) -> dict:
+def all_reduce_stats(stats: torch.Tensor, group: Optional[dist.ProcessGroup] = None, keys=STATS_KEYS) -> dict:
     """SUM the per-rank statistics vector over ranks (no-op without an initialised process group)
     and derive the per-episode means."""
     v = stats.detach().clone().to(torch.float64)
     if dist.is_available() and dist.is_initialized():
         dist.all_reduce(v, op=dist.ReduceOp.SUM, group=group)
-    out = dict(zip(STATS_KEYS, v.tolist()))
+    out = dict(zip(keys, v.tolist()))
     ep = max(out["episodes"], 1.0)
-    out.update(mean_return=out["return_sum"] / ep, mean_length=out["length_sum"] / ep, mean_food=out["food_sum"] / ep)
+    out["mean_return"] = out["return_sum"] / ep
+    if "length_sum" in out:
+        out.update(mean_length=out["length_sum"] / ep, mean_food=out["food_sum"] / ep)
+    if "cycle_sum" in out:
+        out.update(mean_cycles=out["cycle_sum"] / ep, substeps_per_env_step=out["substeps"] / max(out["env_steps"], 1.0))
     return out
