@@ -174,3 +174,44 @@ def test_throughput_print(salp_lib):
         ms = e0.elapsed_time(e1); st = env.episode_stats()
         print(f"{dtype}: {N} envs, {st['substeps'] / N:.0f} substeps/env, {ms:.2f} ms/step, "
               f"{st['substeps'] / ms / 1e6:.2f} G substeps/s, {N / ms / 1e3:.2f} M env-steps/s")
+
+
+def test_slab_sharding_is_rank_invariant(salp_lib):
+    """Two slabs (env_id0 = 0 and 96) reproduce one 200-env run: RNG rows are indexed by global env id."""
+    from oracle.validate_cycle_against_reference import make_cycle_actions
+    from underwater_swimmer_rl_b200.cycle_env import SalpCycleVectorEnv
+    N, T, split = 200, 6, 96
+    acts = torch.from_numpy(make_cycle_actions(T, N, "short", seed=3)).cuda()
+    whole = SalpCycleVectorEnv(N, dtype="float64", seed=777, width=3000, height=2400)   # frequent out-of-range resets
+    parts = [SalpCycleVectorEnv(split, dtype="float64", seed=777, env_id0=0, width=3000, height=2400),
+             SalpCycleVectorEnv(N - split, dtype="float64", seed=777, env_id0=split, width=3000, height=2400)]
+    whole.reset()
+    for p in parts:
+        p.reset()
+    n_reset = 0
+    for t in range(T):
+        o, r, te, tr, _ = whole.step(acts[t])
+        o0, r0, te0, tr0, _ = parts[0].step(acts[t, :split])
+        o1, r1, te1, tr1, _ = parts[1].step(acts[t, split:])
+        assert torch.equal(o, torch.cat([o0, o1])) and torch.equal(r, torch.cat([r0, r1]))
+        assert torch.equal(te, torch.cat([te0, te1])) and torch.equal(tr, torch.cat([tr0, tr1]))
+        n_reset += int((te | tr).sum())
+    assert n_reset > 0
+    assert torch.equal(whole.target_point, torch.cat([parts[0].target_point, parts[1].target_point]))
+
+
+def test_reset_seed_replays_the_stream(salp_lib):
+    from underwater_swimmer_rl_b200.cycle_env import SalpCycleVectorEnv
+    env = SalpCycleVectorEnv(32, dtype="float32", seed=1)
+    o1, _ = env.reset(seed=42)
+    t1 = env.target_point.clone()
+    a = torch.rand(32, 3, device="cuda")
+    env.step(a)
+    o2, _ = env.reset(seed=42)
+    assert torch.equal(t1, env.target_point) and torch.equal(o1, o2)
+    env.reset(seed=43)
+    assert not torch.equal(t1, env.target_point)
+    # target points are np.random.uniform draws inside the tank (salp_robot_env.py:274-282): check against numpy
+    rs = np.random.RandomState(43)
+    assert np.allclose(env.target_point[0].cpu().numpy(), [np.float32(rs.uniform(-2.0, 2.0)), np.float32(rs.uniform(-1.5, 1.5))], rtol=0, atol=0)
+    assert env.single_action_space.shape == (3,) and env.single_observation_space.shape == (6,)
