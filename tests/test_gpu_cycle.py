@@ -215,3 +215,25 @@ def test_reset_seed_replays_the_stream(salp_lib):
     rs = np.random.RandomState(43)
     assert np.allclose(env.target_point[0].cpu().numpy(), [np.float32(rs.uniform(-2.0, 2.0)), np.float32(rs.uniform(-1.5, 1.5))], rtol=0, atol=0)
     assert env.single_action_space.shape == (3,) and env.single_observation_space.shape == (6,)
+
+
+def test_sb3_vecenv_protocol_model_b(salp_lib):
+    """train_robot.py:20-25 hands SB3 a 4-env VecEnv of SalpRobotEnv: same protocol over the CUDA env."""
+    from underwater_swimmer_rl_b200.cycle_env import SalpCycleVectorEnv
+    from underwater_swimmer_rl_b200.sb3_adapter import SalpCycleSB3VecEnv
+    N = 4
+    venv = SalpCycleSB3VecEnv(SalpCycleVectorEnv(N, seed=5, width=3000, height=2400))   # far targets: episodes end quickly
+    obs = venv.reset()
+    assert obs.shape == (N, 6) and obs.dtype == np.float32
+    g = np.random.default_rng(0)
+    n_done = 0
+    for t in range(12):
+        a = np.stack([g.uniform(0, 1, N), g.uniform(0, 0.2, N), g.uniform(-1, 1, N)], axis=1).astype(np.float32)
+        obs, rews, dones, infos = venv.step(a)
+        assert rews.dtype == np.float32 and dones.dtype == bool and len(infos) == N
+        for i in np.nonzero(dones)[0]:
+            n_done += 1
+            assert infos[i]["terminal_observation"].shape == (6,) and infos[i]["episode"]["l"] >= 1
+            assert obs[i, 2] == 0.0 and obs[i, 4] == 0.0      # auto-reset: robot at rest in the new episode
+    assert n_done > 0 and len(venv.get_attr("cycle")) == N
+    venv.close()

@@ -1,4 +1,4 @@
-"""Time the model (B) cycle kernel (tools/: tuning aid).  SALP_CYCLE_MINB selects the occupancy variant."""
+"""Time the model (B) cycle kernel (tools/: tuning aid)."""
 import os
 import sys
 
@@ -28,5 +28,5 @@ e1.record()
 torch.cuda.synchronize()
 ms = e0.elapsed_time(e1) / 40
 st = env.episode_stats()
-print(f"MINB={os.environ.get('SALP_CYCLE_MINB', 'default')} N={N}: {ms:.3f} ms/step, {st['substeps'] / 40 / ms / 1e6:.1f} G substeps/s, "
+print(f"N={N}: {ms:.3f} ms/step, {st['substeps'] / 40 / ms / 1e6:.1f} G substeps/s, "
       f"{N / ms / 1e3:.1f} M env-steps/s")

@@ -2,7 +2,6 @@
 #include <cuda_runtime.h>
 #include <math.h>
 #include <stdint.h>
-#include <stdlib.h>
 
 #include <mutex>
 
@@ -61,7 +60,7 @@ int fill_args(const SalpCycleParams *p, const SalpCycleBuffers *b, salp::CycleAr
     a.n = b->n; a.env_id0 = b->env_id0; a.rows = b->table_rows; a.len_mask = (unsigned)(b->words_len - 1);
     a.max_cycles = p->max_cycles; a.max_substeps = p->max_substeps ? p->max_substeps : SALP_CYCLE_MAX_SUBSTEPS;
     a.autoreset = (p->flags & SALP_CYCLE_AUTORESET) ? 1 : 0; a.rewind_rng = 0;
-    { static int b = 0; if (!b) { const char *v = getenv("SALP_CYCLE_BUCKETS"); b = v ? atoi(v) + 1 : 1; if (b < 1 || b > 65) b = 1; } a.sort_buckets = b - 1; }
+    a.sort_buckets = 0;  // sized per slice by the kernel
     a.dry_mass = p->dry_mass; a.L0 = p->init_length; a.W0 = p->init_width; a.density = p->density;
     a.noz_l12 = p->nozzle_length1 + p->nozzle_length2; a.noz_area = p->nozzle_area; a.noz_mass = p->nozzle_mass;
     // generate_target_point("random") bounds (salp_robot_env.py:266-277)

@@ -2,8 +2,6 @@
 // Compiled twice by build.py:
 //   -DSALP_BUILD_F64=0                 -> launch_cycle_step_f32 / launch_cycle_reset_f32   (throughput build)
 //   -DSALP_BUILD_F64=1 -fmad=false     -> launch_cycle_step_f64 / launch_cycle_reset_f64   (validation build)
-#include <stdlib.h>
-
 #include "salp_cycle.cuh"
 
 namespace salp {
@@ -39,19 +37,9 @@ static cudaError_t launch_cycle_variant(const CycleArgs &a, cudaStream_t s) {
 
 cudaError_t SALP_LAUNCH_CYCLE_STEP(const CycleArgs &a, cudaStream_t s) {
     if (a.n <= 0) return cudaSuccess;
-#if SALP_BUILD_F64
-    return launch_cycle_variant<1>(a, s);
-#else
-    static int minb = 0;   // SALP_CYCLE_MINB: tuning knob of tools/ (register budget = 65536 / (128 * MINB))
-    if (!minb) { const char *v = getenv("SALP_CYCLE_MINB"); minb = v ? atoi(v) : 5; }
-    switch (minb) {
-        case 4: return launch_cycle_variant<4>(a, s);
-        case 6: return launch_cycle_variant<6>(a, s);
-        case 7: return launch_cycle_variant<7>(a, s);
-        case 8: return launch_cycle_variant<8>(a, s);
-        default: return launch_cycle_variant<5>(a, s);
-    }
-#endif
+    // register budget 65536 / (128 * MINB): measured on B200 at 262144 envs -- 4: 1.40 ms, 5: 1.39, 6: 1.56 (spills),
+    // 7: 1.51, 8: 1.50 -- (profiles/r01_ncu_robot_cycle.md); the double build takes what it needs
+    return launch_cycle_variant<SALP_BUILD_F64 ? 1 : 5>(a, s);
 }
 
 cudaError_t SALP_LAUNCH_CYCLE_RESET(const CycleArgs &a, cudaStream_t s) {

@@ -109,3 +109,85 @@ try:  # pragma: no cover - stable_baselines3 is absent on this image
     _SB3VecEnv.register(SalpSB3VecEnv)
 except Exception:
     pass
+
+
+class SalpCycleSB3VecEnv:
+    """The same protocol over the model (B) env -- what ``make_vec_env(make_env, n_envs=4, vec_env_cls=SubprocVecEnv)``
+    gives SB3 in the reference's src/salp/environments/train_robot.py:10-25.  Episode returns / lengths (cycles) come
+    from the kernel's per-env accumulators; the info dict of salp_robot_env.py:194-198 (per-substep histories for
+    rendering) is not produced."""
+
+    def __init__(self, venv):
+        if not venv.autoreset:
+            raise ValueError("the SB3 VecEnv protocol needs autoreset=True")
+        self.venv = venv
+        self.num_envs = venv.num_envs
+        self.observation_space = venv.single_observation_space
+        self.action_space = venv.single_action_space
+        self.render_mode = None
+        self._actions = None
+        self._ret = np.zeros(self.num_envs, np.float64)
+        self._len = np.zeros(self.num_envs, np.int64)
+        self.reset_infos: List[dict] = [{} for _ in range(self.num_envs)]
+
+    def reset(self) -> np.ndarray:
+        obs, _ = self.venv.reset()
+        self._ret[:] = 0.0
+        self._len[:] = 0
+        return obs.cpu().numpy().copy()
+
+    def step_async(self, actions: np.ndarray) -> None:
+        self._actions = np.asarray(actions, dtype=np.float32).reshape(self.num_envs, 3)
+
+    def step_wait(self):
+        obs, rew, term, trunc, infos = self.venv.step(self._actions)
+        o = obs.cpu().numpy().copy()
+        r = rew.cpu().numpy().astype(np.float32)
+        te, tr = term.cpu().numpy().astype(bool), trunc.cpu().numpy().astype(bool)
+        dones = te | tr
+        n_sub = infos["n_sub"].cpu().numpy()
+        self._ret += r
+        self._len += 1
+        fo = infos["final_obs"].cpu().numpy() if dones.any() else None
+        out: List[dict] = []
+        for i in range(self.num_envs):
+            d = {"n_sub": int(n_sub[i])}
+            if dones[i]:
+                d["terminal_observation"] = fo[i].copy()
+                d["TimeLimit.truncated"] = bool(tr[i] and not te[i])
+                d["episode"] = {"r": float(self._ret[i]), "l": int(self._len[i])}
+                self._ret[i], self._len[i] = 0.0, 0
+            out.append(d)
+        return o, r, dones, out
+
+    def step(self, actions):
+        self.step_async(actions)
+        return self.step_wait()
+
+    def close(self) -> None:
+        self.venv.close()
+
+    def seed(self, seed: Optional[int] = None) -> Sequence[Optional[int]]:
+        if seed is not None:
+            self.venv.reset(seed=seed)
+        return [None if seed is None else seed + i for i in range(self.num_envs)]
+
+    def get_attr(self, attr_name: str, indices=None) -> List[Any]:
+        v = getattr(self.venv, attr_name)
+        idx = list(range(self.num_envs)) if indices is None else ([indices] if isinstance(indices, int) else list(indices))
+        if hasattr(v, "cpu"):
+            v = v.cpu().numpy()
+            return [v[i] for i in idx]
+        return [v for _ in idx]
+
+    def env_is_wrapped(self, wrapper_class, indices=None) -> List[bool]:
+        return [False] * self.num_envs
+
+    def render(self, mode: Optional[str] = None):
+        return None
+
+
+try:  # pragma: no cover
+    _SB3VecEnv.register(SalpCycleSB3VecEnv)
+except Exception:
+    pass
