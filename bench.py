@@ -49,6 +49,7 @@ WORKLOADS = {
     # for actions uniform in the env's Box); ALU-bound, reported beside its (tiny) HBM figure
     "robot_cycle_256k": dict(yaml=None, params={}, envs=1 << 18, dtype="float32", cycle=True),
 }
+RING_STEPS = 5  # rows of the zero-copy replay ring: (5 - 1) x 262144 envs = 1 048 576 transitions (the reference's buffer_size)
 METRIC = "salp_env_steps_per_sec"
 UNIT = "env-steps/s"
 
@@ -385,6 +386,8 @@ def main():
     ap.add_argument("--envs-per-gpu", type=int, default=0)
     ap.add_argument("--substeps", type=int, default=1, help="K env steps fused per launch (open-loop actions)")
     ap.add_argument("--torch-actor", action="store_true", help="sac_rollout: torch bf16 MLP instead of the fused tcgen05 actor kernel")
+    ap.add_argument("--append-kernel", action="store_true", help="sac_rollout: transition-major DeviceReplayBuffer filled by salp_replay_append "
+                    "instead of the zero-copy StepRingReplay (the env's own output rows are the replay storage)")
     ap.add_argument("--graph", default="auto", choices=["auto", "on", "off"], help="replay the step from a CUDA graph (auto: slabs <= 262144 envs)")
     ap.add_argument("--e2e-steps", type=int, default=20)
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
@@ -394,8 +397,9 @@ def main():
                          "(steady state: resets, respawns and divergent breathing phases inside the timed region)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
-    args.steps += args.steps % 2  # the rollout workload replays two env steps per graph launch
-    args.warmup += args.warmup % 2
+    spr = 2 if (args.append_kernel or args.workload != "sac_rollout_256k") else RING_STEPS  # env steps per rollout graph replay
+    args.steps = (args.steps + spr - 1) // spr * spr
+    args.warmup = (args.warmup + spr - 1) // spr * spr
     wl = dict(WORKLOADS[args.workload])
     if args.envs_per_gpu:
         wl["envs"] = args.envs_per_gpu
@@ -425,7 +429,8 @@ def main():
         K = 1
     real = torch.float64 if wl["dtype"] == "float64" else torch.float32
     env = SalpVectorEnv(N, device=dev, dtype=wl["dtype"], seed=10_000, env_id0=rank * N, food_table_len=128,
-                        jitter_table_len=512, max_substeps=2 if rollout else K, autoreset=True, **wl["params"])
+                        jitter_table_len=512, max_substeps=(2 if args.append_kernel else RING_STEPS) if rollout else K,
+                        autoreset=True, **wl["params"])
     env.reset()
     # synthetic actions, resident in HBM before the timed region: a pool of 32 [K, N, 1] tensors
     gen = torch.Generator(device=dev)
@@ -439,11 +444,13 @@ def main():
         from underwater_swimmer_rl_b200.rollout import FusedActor
         actor = TanhGaussianActor(env.obs_dim, env.act_dim, (256, 256)).to(dev)
         actor = actor.to(torch.bfloat16) if args.torch_actor else FusedActor(actor)
-        ring = DeviceReplayBuffer(4 * N, env.obs_dim, env.act_dim, dev)
+        from underwater_swimmer_rl_b200.rollout import StepRingReplay
+        ring = DeviceReplayBuffer(4 * N, env.obs_dim, env.act_dim, dev) if args.append_kernel else StepRingReplay(env)
         col = RolloutCollector(env, actor, ring)
-        replay2 = col.capture()  # one graph launch = two env steps of (actor -> env kernel -> replay append)
-        # ours, per env step: [salp_actor_kernel,] salp_step_kernel, replay_append_kernel
-        launches_per_step = 2 if args.torch_actor else 3
+        replay2 = col.capture()  # one graph launch = spr env steps of (actor -> env kernel [-> replay append])
+        assert col.steps_per_replay == spr
+        # ours, per env step: [salp_actor_kernel,] salp_step_kernel [, replay_append_kernel]
+        launches_per_step = (0 if args.torch_actor else 1) + 1 + (1 if args.append_kernel else 0)
 
     # small slabs: one step is a few microseconds of device time, less than the Python launch path ->
     # replay a CUDA graph of 32 steps (one per action tensor of the pool); it is the product API for this regime
@@ -459,7 +466,7 @@ def main():
             if i % 32 == 0:
                 replay32()
         elif rollout:
-            if i % 2 == 0:
+            if i % spr == 0:
                 replay2()
         elif K == 1:
             env.step(pool[i % 32][0])
@@ -549,7 +556,7 @@ def main():
             "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f64" if real == torch.float64 else "f32", "data": "synthetic",
             "config": {"workload": args.workload, "reference_yaml": wl["yaml"], "envs_per_gpu": N, "global_envs": world * N,
-                       "substeps_per_launch": K, "cuda_graph": "32 steps per replay" if graphed else ("2 steps per replay" if rollout else None), "rollout": ("actor MLP [24-256-256-2] bf16 (" + ("torch" if args.torch_actor else "salp_actor_kernel, tcgen05") + ") -> salp_step_kernel -> salp_replay_append, CUDA graph of 2 steps; env kernel share of the step = %.2f" % (env_only_ms / (ms_max / args.steps))) if rollout else None, "prime_steps": args.prime_steps, "obs_dim": env.obs_dim, "act_dim": env.act_dim, "autoreset": True,
+                       "substeps_per_launch": K, "cuda_graph": "32 steps per replay" if graphed else (("%d steps per replay" % spr) if rollout else None), "rollout": ("actor MLP [24-256-256-2] bf16 (" + ("torch" if args.torch_actor else "salp_actor_kernel, tcgen05") + ") -> salp_step_kernel -> " + ("salp_replay_append (transition-major ring)" if args.append_kernel else "zero-copy step ring (the env's [5, N] output rows are the replay storage; no append kernel)") + ", CUDA graph of %d steps" % spr + "; env kernel share of the step = %.2f" % (env_only_ms / (ms_max / args.steps))) if rollout else None, "prime_steps": args.prime_steps, "obs_dim": env.obs_dim, "act_dim": env.act_dim, "autoreset": True,
                        "l2": f"per-step footprint {bpe * N / 1e6:.0f} MB vs 126 MB L2"
                              + (" (inputs larger than L2, no flush needed)" if bpe * N > 126e6 else " (L2-resident working set)"),
                        "parallelism": f"env-slab x{world} (no data-path collective; NCCL all-reduce of episode stats only)"},

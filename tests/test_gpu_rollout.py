@@ -101,3 +101,65 @@ def test_expert_buffer_and_bad_arguments(salp_lib):
     import ctypes as C
     p = _capi.SalpReplayAppend()
     assert salp_lib.salp_replay_append(C.byref(p), None) == _capi.SALP_EINVAL
+
+
+@pytest.mark.parametrize("dtype,fused,disc", [("float32", True, True), ("float64", False, False)])
+def test_step_ring_replay_is_zero_copy_and_exact(salp_lib, dtype, fused, disc):
+    """StepRingReplay: the env's [K, N] output rows are the replay storage.  Every transition still inside the ring
+    must equal the one assembled the way the reference loop stores it (continuous_trainer.py:296-303)."""
+    from underwater_swimmer_rl_b200 import SalpVectorEnv
+    from underwater_swimmer_rl_b200.rollout import (FusedActor, FusedGailReward, GailDiscriminator, RolloutCollector,
+                                                     StepRingReplay, TanhGaussianActor)
+    torch.manual_seed(1)
+    n, K, T = 768, 5, 16
+    # episodes are cut after 7 steps without food so that terminal observations fall inside the ring window
+    env = SalpVectorEnv(n, device="cuda:0", dtype=dtype, max_substeps=K, seed=99,
+                        **dict(CONFIGS["sac_gail"], max_steps_without_food=7))
+    actor = TanhGaussianActor(env.obs_dim, env.act_dim).cuda()
+    d = GailDiscriminator(env.obs_dim, env.act_dim).cuda() if disc else None
+    ring = StepRingReplay(env)
+    col = RolloutCollector(env, FusedActor(actor) if fused else actor,
+                           ring, discriminator=FusedGailReward(d, env.obs_dim, env.act_dim) if disc else None,
+                           w_env=0.3, w_gail=0.7, deterministic=True)
+    col.reset()
+    hist = []
+    for t in range(T):
+        prev = env.obs[col.cur].clone()
+        col.collect(1)
+        r = col.cur
+        assert r == (t + 1) % K
+        done = (env.terminated[r] | env.truncated[r]).bool()
+        rew = env.reward[r].float().clone()
+        if disc:
+            with torch.no_grad():
+                rg = d.predict_reward(prev, ring.act[r].float()).reshape(-1)
+            rew_mixed = 0.3 * rew + 0.7 * rg
+        else:
+            rew_mixed = rew
+        hist.append(dict(obs=prev, act=ring.act[r].float().clone(), rew=rew_mixed,
+                         next=torch.where(done[:, None], env.final_obs[r], env.obs[r]).clone(), done=done.clone()))
+    assert len(ring) == (K - 1) * n and ring.capacity == (K - 1) * n
+    assert any(h["done"].any() for h in hist[-(K - 1):]), "no episode ended inside the ring window"
+    g = torch.Generator(device="cuda").manual_seed(7)
+    # the sampler draws (steps back, env) pairs: replay its draws and compare every field
+    g2 = torch.Generator(device="cuda").manual_seed(7)
+    batch = ring.sample(4096, generator=g)
+    back = torch.randint(0, K - 1, (4096,), device="cuda", generator=g2)
+    e = torch.randint(0, n, (4096,), device="cuda", generator=g2)
+    for b in range(K - 1):
+        m = back == b
+        h = hist[T - 1 - b]
+        assert torch.equal(batch["observations"][m], h["obs"][e[m]])
+        assert torch.equal(batch["next_observations"][m], h["next"][e[m]])
+        assert torch.equal(batch["actions"][m], h["act"][e[m]])
+        assert torch.equal(batch["dones"][m], h["done"][e[m]])
+        assert torch.allclose(batch["rewards"][m], h["rew"][e[m]], rtol=2e-2 if disc else 0, atol=2e-2 if disc else 0)
+    # graph replay of one trip through the ring continues the same rollout
+    replay = col.capture()
+    assert col.steps_per_replay == K
+    before = ring.steps
+    replay(); replay()
+    torch.cuda.synchronize()
+    assert ring.steps == before + 2 * K and len(ring) == (K - 1) * n
+    s = ring.sample(256)
+    assert s["observations"].shape == (256, env.obs_dim) and torch.isfinite(s["rewards"]).all()

@@ -221,6 +221,60 @@ class DeviceReplayBuffer:
                 "next_observations": self.next_obs[idx], "dones": self.done[idx]}
 
 
+class StepRingReplay:
+    """Zero-copy replay storage: the env's own ``[K, N, ...]`` output rows ARE the buffer.
+
+    ``salp_step_slot`` writes step j's observation, reward, flags and terminal observation into row ``j % K`` of the
+    tensors the env already owns, and the actor writes its action into row ``j % K`` of ``self.act`` -- so storing a
+    transition costs no kernel and no extra HBM traffic (the transition-major ``DeviceReplayBuffer`` re-reads and
+    re-writes ~410 B per transition in ``salp_replay_append``).  Transition j is
+        (obs[(j-1) % K], act[j % K], reward[j % K], final_obs[j % K] if done else obs[j % K], done[j % K])
+    and stays intact until row ``(j-1) % K`` is overwritten by step ``j-1+K``: the ring holds the last K-1 steps,
+    i.e. ``(K-1) * N`` transitions (K = 5 at 262 144 envs = 1 048 576, the reference's buffer_size).
+    With a GAIL discriminator the imitation reward of each step is kept in ``self.aux`` and mixed when sampling
+    (``w_env * r_env + w_aux * r_gail``, src/salp/config/base_config.py:77-78)."""
+
+    def __init__(self, env: SalpVectorEnv):
+        if env.max_substeps < 3:
+            raise ValueError("StepRingReplay needs an env with max_substeps >= 3 (rows of the ring)")
+        if not env.autoreset:
+            raise ValueError("StepRingReplay needs autoreset=True (terminal observations come from final_obs)")
+        self.env, self.K, self.N = env, env.max_substeps, env.num_envs
+        self.device = env.device
+        self.act = torch.zeros(self.K, self.N, env.act_dim, dtype=env.real, device=env.device)
+        self.aux = torch.zeros(self.K, self.N, dtype=torch.float32, device=env.device)
+        self.w_env, self.w_aux = 1.0, 0.0
+        self.steps = 0                 # env steps written so far (host counter; the rollout is launched from the host)
+
+    @property
+    def capacity(self) -> int:
+        return (self.K - 1) * self.N
+
+    def __len__(self) -> int:
+        return min(self.steps, self.K - 1) * self.N
+
+    def note_steps(self, n: int) -> None:
+        self.steps += int(n)
+
+    def sample(self, batch_size: int, generator: Optional[torch.Generator] = None) -> Dict[str, torch.Tensor]:
+        """Uniform batch over the stored transitions (continuous_trainer.py:312 ``replay_buffer.sample``)."""
+        have = min(self.steps, self.K - 1)
+        if have == 0:
+            raise ValueError("replay buffer is empty")
+        env = self.env
+        back = torch.randint(0, have, (batch_size,), device=self.device, generator=generator)   # 0 = newest step
+        e = torch.randint(0, self.N, (batch_size,), device=self.device, generator=generator)
+        row = (self.steps - back) % self.K           # row of step j = steps - back (steps are numbered from 1)
+        prev = (row - 1) % self.K
+        done = (env.terminated[row, e] | env.truncated[row, e]).bool()
+        nxt = torch.where(done[:, None], env.final_obs[row, e], env.obs[row, e])
+        rew = env.reward[row, e].float()
+        if self.w_aux != 0.0:
+            rew = self.w_env * rew + self.w_aux * self.aux[row, e]
+        return {"observations": env.obs[prev, e], "actions": self.act[row, e].float(), "rewards": rew,
+                "next_observations": nxt, "dones": done}
+
+
 class DeviceExpertBuffer:
     """Expert transitions on the device.  ``episodes``: dicts with 'observations' [T, obs_dim] and
     'actions' [T, act_dim] (the pickle format of data/expert_demos/README.md:57-73)."""
@@ -257,24 +311,38 @@ class RolloutCollector:
         self.steps = 0
         self._graph = None
         self._aux = torch.zeros(env.num_envs, dtype=torch.float32, device=env.device)  # GAIL reward of the step
+        self.ring = buffer if isinstance(buffer, StepRingReplay) else None
+        self.rows = env.max_substeps if self.ring is not None else 2   # output rows the rollout cycles through
+        if self.ring is not None and discriminator is not None:
+            self.ring.w_env, self.ring.w_aux = float(w_env), float(w_gail)
 
     def reset(self):
         obs, info = self.env.reset()
         self.cur = 0
+        if self.ring is not None:
+            self.ring.steps = 0    # rows are numbered from the reset observation in row 0
         return obs, info
 
     @torch.no_grad()
     def _one_step(self, cur: int) -> int:
         env = self.env
         obs = env.obs[cur]
+        nxt = (cur + 1) % self.rows
+        act = self.ring.act[nxt] if self.ring is not None else self.act   # ring: the action row is the storage
         if isinstance(self.actor, FusedActor):
-            self.actor(obs, self.act, deterministic=self.deterministic)  # one kernel, writes the env's action tensor
+            self.actor(obs, act, deterministic=self.deterministic)  # one kernel, writes the env's action tensor
         else:
             a = self.actor(obs, deterministic=self.deterministic)
-            self.act.copy_(a.reshape(env.num_envs, env.act_dim))  # cast to the build's real type, in place
-        nxt = 1 - cur
-        env.step(self.act, slot=nxt)
-        if self.buffer is not None:
+            act.copy_(a.reshape(env.num_envs, env.act_dim))  # cast to the build's real type, in place
+        env.step(act, slot=nxt)
+        if self.ring is not None:
+            # zero-copy storage: everything of the transition already sits in row `nxt`; only the imitation reward
+            # (when there is a discriminator) is computed, straight into its ring row
+            if isinstance(self.disc, FusedGailReward):
+                self.disc(obs, act, self.ring.aux[nxt])
+            elif self.disc is not None:
+                self.ring.aux[nxt].copy_(self.disc.predict_reward(obs, act).reshape(-1))
+        elif self.buffer is not None:
             if isinstance(self.disc, FusedGailReward):
                 aux = self.disc(obs, self.act, self._aux)
             else:
@@ -289,29 +357,39 @@ class RolloutCollector:
         for _ in range(n_steps):
             self.cur = self._one_step(self.cur)
         self.steps += n_steps
+        if self.ring is not None:
+            self.ring.note_steps(n_steps)
         return self.env.obs[self.cur]
 
     def capture(self) -> Callable[[], None]:
-        """Capture TWO steps (row 0 -> 1 -> 0) into a CUDA graph; each replay advances the rollout by two env
-        steps with a single graph launch.  Must be called with the current observation in row 0."""
-        if self.cur != 0:
+        """Capture one trip through the output rows (2 steps with ping-pong rows, K with a StepRingReplay) into a
+        CUDA graph; each replay advances the rollout by that many env steps with a single graph launch.
+        ``steps_per_replay`` holds the count."""
+        R = self.rows
+        while self.cur != 0:
             self.collect(1)
         dev = self.env.device
         s = torch.cuda.Stream(dev)
         s.wait_stream(torch.cuda.current_stream(dev))
         with torch.cuda.stream(s):  # warm-up outside capture (cuBLAS workspaces, lazy module loads)
-            for _ in range(2):
+            for _ in range(R):
                 self.cur = self._one_step(self.cur)
         torch.cuda.current_stream(dev).wait_stream(s)
-        self.steps += 2
+        self.steps += R
+        if self.ring is not None:
+            self.ring.note_steps(R)
         g = torch.cuda.CUDAGraph()
         with torch.cuda.graph(g, stream=s):
-            c = self._one_step(0)
-            c = self._one_step(c)
+            c = 0
+            for _ in range(R):
+                c = self._one_step(c)
         assert c == 0
         self._graph = g
+        self.steps_per_replay = R
 
         def replay():
             g.replay()
-            self.steps += 2
+            self.steps += R
+            if self.ring is not None:
+                self.ring.note_steps(R)
         return replay
