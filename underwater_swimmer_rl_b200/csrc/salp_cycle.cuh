@@ -557,8 +557,7 @@ __device__ __forceinline__ void cyc_flush_stats(const CycleArgs &a, const CycleS
     }
 }
 
-constexpr int kCycleBlock = 128;   // threads per CTA
-constexpr int kCycleSlice = 1024;  // envs sorted at a time by one CTA
+constexpr int kCycleSlice = 2048;  // envs sorted at a time by one CTA
 
 // Number of integrator substeps of env e's next cycle and the length of its breathing part, from its action
 // alone (same arithmetic as cyc_plan).
@@ -576,13 +575,13 @@ __device__ __forceinline__ void cyc_lengths(const CycleArgs &a, long long e, int
 }
 
 // Work distribution.  Cycles differ in length by the action (0 .. 1450 substeps), so lanes of a warp that took
-// envs in index order would idle half of the time.  Each CTA owns a contiguous range of envs (all CTAs of the
-// grid are resident: one wave, equal expected work), sorts it in slices of kCycleSlice by substep count
+// envs in index order would idle half of the time.  Each CTA owns a contiguous range of envs (one CTA per SM, all
+// resident: one wave, equal expected work), sorts it in slices of kCycleSlice by substep count
 // (bitonic sort of (count | local index) keys in shared memory), and its warps pull 32-env chunks of the sorted
 // slice, longest first, from a shared counter: the lanes of a warp run cycles of nearly equal length, and a warp
 // that drew short cycles simply draws more of them.
-template <typename T, int MINB>
-__global__ void __launch_bounds__(kCycleBlock, MINB) salp_cycle_step_kernel(const __grid_constant__ CycleArgs a) {
+template <typename T, int BLOCK, int MINB>
+__global__ void __launch_bounds__(BLOCK, MINB) salp_cycle_step_kernel(const __grid_constant__ CycleArgs a) {
     __shared__ unsigned s_key[kCycleSlice];
     __shared__ int s_next, s_valid;
     const int tid = threadIdx.x, lane = tid & 31;
@@ -594,22 +593,22 @@ __global__ void __launch_bounds__(kCycleBlock, MINB) salp_cycle_step_kernel(cons
         const int cnt = (int)(end - base < kCycleSlice ? end - base : kCycleSlice);
         if (tid == 0) { s_next = 0; s_valid = cnt; }
         // lanes that still breathe make the whole warp run the shape block: with enough chunks in the slice, group
-        // envs of similar breathing length first (measured: 2 groups at 11 chunks, 3-4 at 32)
-        const int n_buckets = a.sort_buckets > 0 ? a.sort_buckets : max(1, min(4, (((cnt + 31) >> 5) + 3) / 7));
-        for (int i = tid; i < kCycleSlice; i += kCycleBlock) {
+        // envs of similar breathing length first (measured at 55 chunks: 1 group 1.122 ms, 2 1.015, 3 1.006, 4 1.018, 8 1.059)
+        const int n_buckets = a.sort_buckets > 0 ? a.sort_buckets : max(1, min(3, ((cnt + 31) >> 5) / 16));
+        for (int i = tid; i < kCycleSlice; i += BLOCK) {
             unsigned key = 0xFFFFFFFFu;
             if (i < cnt) {
                 int n_total, kB;
                 cyc_lengths<T>(a, base + i, n_total, kB);
                 const int bucket = n_buckets > 1 ? min(n_buckets - 1, kB * n_buckets / 451) : 0;
-                key = ((unsigned)bucket << 23) | ((unsigned)n_total << 10) | (unsigned)i;
+                key = ((unsigned)bucket << 24) | ((unsigned)n_total << 11) | (unsigned)i;
             }
             s_key[i] = key;
         }
         __syncthreads();
         for (int size = 2; size <= kCycleSlice; size <<= 1) {          // bitonic sort, ascending
             for (int stride = size >> 1; stride > 0; stride >>= 1) {
-                for (int t = tid; t < kCycleSlice / 2; t += kCycleBlock) {
+                for (int t = tid; t < kCycleSlice / 2; t += BLOCK) {
                     const int lo = 2 * t - (t & (stride - 1)), hi = lo + stride;
                     const unsigned x = s_key[lo], y = s_key[hi];
                     const bool up = (lo & size) == 0;
@@ -625,7 +624,7 @@ __global__ void __launch_bounds__(kCycleBlock, MINB) salp_cycle_step_kernel(cons
             c = __shfl_sync(0xffffffffu, c, 0);
             if (c >= n_chunks) break;
             const int rank = cnt - 1 - (c * 32 + lane);                // longest cycles first
-            if (rank >= 0) cyc_run_env<T>(a, base + (long long)(s_key[rank] & 1023u), acc);
+            if (rank >= 0) cyc_run_env<T>(a, base + (long long)(s_key[rank] & 2047u), acc);
             __syncwarp();
         }
         __syncthreads();                                                 // s_key is rewritten by the next slice

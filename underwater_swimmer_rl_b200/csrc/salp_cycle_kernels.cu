@@ -16,7 +16,7 @@ using cyc_real_t = float;
 #define SALP_LAUNCH_CYCLE_RESET launch_cycle_reset_f32
 #endif
 
-template <int MINB>
+template <int BLOCK, int MINB>
 static cudaError_t launch_cycle_variant(const CycleArgs &a, cudaStream_t s) {
     // one resident wave: (CTAs that fit on an SM) x (SMs), fewer when the slab is small
     static int resident = 0;
@@ -24,22 +24,24 @@ static cudaError_t launch_cycle_variant(const CycleArgs &a, cudaStream_t s) {
         int dev = 0, sms = 0, per_sm = 0;
         cudaError_t e = cudaGetDevice(&dev);
         if (e == cudaSuccess) e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, salp_cycle_step_kernel<cyc_real_t, MINB>, kCycleBlock, 0);
+        if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, salp_cycle_step_kernel<cyc_real_t, BLOCK, MINB>, BLOCK, 0);
         if (e != cudaSuccess) return e;
         resident = sms * (per_sm > 0 ? per_sm : 1);
     }
-    long long grid = (a.n + 2 * kCycleBlock - 1) / (2 * kCycleBlock);   // at least two chunks per warp
+    long long grid = (a.n + 31) / 32;   // at least one 32-env chunk per CTA
     if (grid > resident) grid = resident;
     if (grid < 1) grid = 1;
-    salp_cycle_step_kernel<cyc_real_t, MINB><<<(unsigned)grid, kCycleBlock, 0, s>>>(a);
+    salp_cycle_step_kernel<cyc_real_t, BLOCK, MINB><<<(unsigned)grid, BLOCK, 0, s>>>(a);
     return cudaGetLastError();
 }
 
 cudaError_t SALP_LAUNCH_CYCLE_STEP(const CycleArgs &a, cudaStream_t s) {
     if (a.n <= 0) return cudaSuccess;
-    // register budget 65536 / (128 * MINB): measured on B200 at 262144 envs -- 4: 1.40 ms, 5: 1.39, 6: 1.56 (spills),
-    // 7: 1.51, 8: 1.50 -- (profiles/r01_ncu_robot_cycle.md); the double build takes what it needs
-    return launch_cycle_variant<SALP_BUILD_F64 ? 1 : 5>(a, s);
+    // One CTA per SM whose 20 warps share one pool of sorted chunks (float build; 89 registers x 640 threads).  Measured on
+    // B200 at 262144 envs: 5 CTAs x 128 threads 1.264 ms; 2 x 320 1.133; 2 x 256 1.142; 1 x 512 1.017; 1 x 576 1.022;
+    // 1 x 640 1.017; 1 x 704 / 736 (80 registers) 1.06 (profiles/r01_ncu_robot_cycle.md).  The double build needs 168
+    // registers: 128-thread CTAs.
+    return launch_cycle_variant<SALP_BUILD_F64 ? 128 : 640, 1>(a, s);
 }
 
 cudaError_t SALP_LAUNCH_CYCLE_RESET(const CycleArgs &a, cudaStream_t s) {
