@@ -80,6 +80,8 @@ int main(int argc, char **argv) {
 #else
         V(kStoreDirect, 64, 14), V(kStoreDirect, 64, 12), V(kStoreDirect, 64, 10), V(kStoreWarp, 64, 14), V(kStoreWarp, 64, 12), V(kStoreTmaBlock, 64, 14), V(kStoreTmaBlock, 64, 12),
         V(kStoreDirect, 128, 7), V(kStoreDirect, 128, 6), V(kStoreWarp, 128, 7), V(kStoreDirect, 32, 28), V(kStoreTmaBlock, 32, 28),
+        V(kStoreTmaBlock, 64, 16), V(kStoreTmaBlock, 32, 32), V(kStoreTmaBlock, 128, 7), V(kStoreTmaBlock, 64, 10), V(kStoreTmaBlock, 64, 8),
+        P(kStoreTmaBlock, 64, 14), P(kStoreTmaBlock, 64, 12), P(kStoreTmaBlock, 128, 7), P(kStoreDirect, 64, 14), P(kStoreTmaBlock, 32, 28),
 #endif
     };
     if (argc > 4) {  // keep only variants whose name contains argv[4]
