@@ -210,15 +210,16 @@ __device__ __forceinline__ void cyc_plan(const CycleArgs &a, double a0, double a
 // Coefficients of the dynamics for one body shape (everything in update_properties, robot.py:375-385, plus
 // the shape-only factors of the force / torque laws :494-522, :534-575, :627-674).  Recomputed every substep
 // while the body contracts or releases, constant through coast / rest.
-template <typename T> struct CycleCoef {
-    T mass, inv_m, kd, kt0, rx, cm, jet_speed;
-    T I[3], inv_I[3], dI_rate[3];
+template <typename T> struct CycleCoef;
+template <> struct CycleCoef<double> {
+    double mass, inv_m, kd, kt0, rx, cm, jet_speed;
+    double I[3], inv_I[3], dI_rate[3];
 };
 
-template <typename T>
-__device__ __forceinline__ void cyc_shape(const CycleArgs &a, double length, double width, bool jet_phase, const T (&dir)[3],
-                                          double &prev_vol, double prev_I[3], CycleCoef<T> &c) {
-    (void)dir;
+// double build: the reference's expressions in the reference's operation order
+__device__ __forceinline__ void cyc_shape(const CycleArgs &a, double length, double width, bool jet_phase,
+                                          double &prev_vol, double prev_I[3], CycleCoef<double> &c) {
+    using T = double;
     const double hw = width / 2, hl = length / 2;
     const double area = kCycPi * hl * hw;
     const double volume = 4.0 / 3.0 * kCycPi * hl * (hw * hw);
@@ -237,9 +238,7 @@ __device__ __forceinline__ void cyc_shape(const CycleArgs &a, double length, dou
     c.mass = (T)mass;
     c.inv_m = (T)(1.0 / mass);                           // np.linalg.inv of the diagonal mass matrix
     c.kd = (T)(-0.5 * a.density * area * cd);
-    double hl4;
-    if constexpr (sizeof(T) == 8) hl4 = pow(hl, 4.0); else hl4 = (hl * hl) * (hl * hl);
-    c.kt0 = (T)(-a.density * cd * hw * hl4);
+    c.kt0 = (T)(-a.density * cd * hw * pow(hl, 4.0));   // (self.length / 2) ** 4
     c.rx = (T)rx;
     c.cm = 0; c.jet_speed = 0;
     if (jet_phase) {                                     // _get_jet_velocity / _get_jet_force (robot.py:586-614)
@@ -389,7 +388,7 @@ __device__ __forceinline__ void cyc_run_env(const CycleArgs &a, long long e, Cyc
                         width = a.W0;
                         rest_shape = true;
                     }
-                    cyc_shape<T>(a, length, width, phase == 1, p.dir, prev_vol, prev_I, c);
+                    cyc_shape(a, length, width, phase == 1, prev_vol, prev_I, c);
                 } else {
                     double s2 = 0.0;
                     if (phase <= 1) {
