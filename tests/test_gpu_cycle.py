@@ -62,7 +62,29 @@ FP64_CASES = [
     ("tiny", 1005, 96, {}, "truncated"),                                  # 500-cycle truncation, twice
     ("short", 30, 200, dict(width=102, height=102), "terminated"),        # target within 1 cm: reached
     ("uniform", 12, 200, dict(width=3000, height=2400), "truncated"),     # targets > 5 m away: out of range
+    ("uniform", 25, 4096, {}, None),                                      # 7e7 integrator substeps
+    ("seek", 20, 300, dict(width=500, height=400, robot=dict(nozzle_area=0.00009, nozzle_length1=0.01, nozzle_length2=0.01,
+                                                             nozzle_length3=0.01)), None),
+    ("uniform", 12, 300, dict(robot=dict(dry_mass=2.5, init_length=0.4, init_width=0.12, max_contraction=0.05, density=1025.0,
+                                         nozzle_mass=0.3, nozzle_area=0.0003)), None),
 ]
+
+
+def _split_kw(kw):
+    """Env keywords of a case -> (oracle parameters, SalpCycleVectorEnv keywords)."""
+    from underwater_swimmer_rl_b200.cycle_env import Nozzle, Robot
+    kw = dict(kw)
+    rp = kw.pop("robot", None)
+    okw, gkw = dict(kw), dict(kw)
+    if rp:
+        okw.update(rp)
+        nz = Nozzle(rp.get("nozzle_length1", 0.05), rp.get("nozzle_length2", 0.05), rp.get("nozzle_length3", 0.05),
+                    rp.get("nozzle_area", 0.00016), rp.get("nozzle_mass", 1.0))
+        rb = Robot(dry_mass=rp.get("dry_mass", 1.0), init_length=rp.get("init_length", 0.3), init_width=rp.get("init_width", 0.15),
+                   max_contraction=rp.get("max_contraction", 0.06), nozzle=nz)
+        rb.set_environment(rp.get("density", 1000.0))
+        gkw["robot"] = rb
+    return okw, gkw
 
 
 @pytest.mark.parametrize("style,T,N,kw,ends", FP64_CASES)
@@ -71,8 +93,9 @@ def test_fp64_vs_oracle(salp_lib, style, T, N, kw, ends):
     acts = make_cycle_actions(T, N, style, seed=99)
     seeds = list(range(31_000, 31_000 + N))
     words = _words(seeds)
-    ref = _oracle_rollout(words, acts, **kw)
-    got = _gpu_rollout("float64", words, acts, **kw)
+    okw, gkw = _split_kw(kw)
+    ref = _oracle_rollout(words, acts, **okw)
+    got = _gpu_rollout("float64", words, acts, **gkw)
     assert np.array_equal(got["obs0"], ref["obs0"])
     for k in ("n_sub", "terminated", "truncated"):
         assert np.array_equal(got[k], ref[k]), k
