@@ -73,6 +73,7 @@ int main(int argc, char **argv) {
     std::vector<Variant> vs = {
 #if LAB_F == 1
         V(kStoreWarp, 64, 16), V(kStoreWarp, 128, 8), V(kStoreTmaBlock, 64, 16), V(kStoreTmaBlock, 32, 32),
+        V(kStoreTmaWarp, 64, 16), V(kStoreTmaWarp, 128, 8), V(kStoreTmaWarp, 256, 4),
         V(kStoreTmaBlock, 64, 18), V(kStoreTmaBlock, 64, 20), V(kStoreTmaBlock, 32, 36), V(kStoreTmaBlock, 32, 40), V(kStoreTmaBlock, 128, 8), V(kStoreTmaBlock, 128, 9),
         P(kStoreWarp, 64, 16), P(kStoreWarp, 128, 8), P(kStoreWarp, 256, 4), P(kStoreWarp, 64, 12), P(kStoreWarp, 128, 6),
         P(kStoreTmaBlock, 64, 16), P(kStoreTmaBlock, 128, 8), P(kStoreTmaBlock, 256, 4), P(kStoreTmaBlock, 64, 12), P(kStoreTmaBlock, 32, 32),
@@ -82,6 +83,7 @@ int main(int argc, char **argv) {
         V(kStoreDirect, 128, 7), V(kStoreDirect, 128, 6), V(kStoreWarp, 128, 7), V(kStoreDirect, 32, 28), V(kStoreTmaBlock, 32, 28),
         V(kStoreTmaBlock, 64, 16), V(kStoreTmaBlock, 32, 32), V(kStoreTmaBlock, 128, 7), V(kStoreTmaBlock, 64, 10), V(kStoreTmaBlock, 64, 8),
         P(kStoreTmaBlock, 64, 14), P(kStoreTmaBlock, 64, 12), P(kStoreTmaBlock, 128, 7), P(kStoreDirect, 64, 14), P(kStoreTmaBlock, 32, 28),
+        V(kStoreTmaWarp, 64, 14), V(kStoreTmaWarp, 64, 12), V(kStoreTmaWarp, 128, 7), V(kStoreTmaWarp, 32, 28),
 #endif
     };
     if (argc > 4) {  // keep only variants whose name contains argv[4]
