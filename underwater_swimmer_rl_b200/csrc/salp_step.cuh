@@ -469,6 +469,11 @@ __global__ void __launch_bounds__(BLOCK, MINB) salp_step_kernel(const __grid_con
     const T diag = (T)a.diag;  // sqrt(W^2 + H^2), S:396, computed on the host in double
     const T invW = (T)a.inv_w, invH = (T)a.inv_h, invDiag = (T)a.inv_diag;  // used by the f32 build only
 
+    // programmatic dependent launch (salp_launch.cuh): let the next kernel of the stream be scheduled as soon as every
+    // CTA of this grid is resident, and do not touch global memory before the previous kernel has completed
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+
     // ---- PF: persistent CTAs; the state records of the CTA's next tile are copied global->shared
     //      with cp.async (each thread fetches exactly the records it will read itself, so no CTA
     //      barrier is needed) while the current tile is being integrated.
