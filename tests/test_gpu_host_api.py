@@ -75,9 +75,9 @@ def test_sb3_vecenv_protocol(salp_lib):
     venv.close()
 
 
-def test_cuda_graph_replay_equals_eager(salp_lib):
+@pytest.mark.parametrize("N,T", [(4096, 64), (200_000, 24)])   # the larger slab launches with programmatic dependent launch
+def test_cuda_graph_replay_equals_eager(salp_lib, N, T):
     from underwater_swimmer_rl_b200 import SalpVectorEnv
-    N, T = 4096, 64
     p = CONFIGS["single_food_long_horizon"]
     acts = torch.from_numpy(synth_actions(T + 1, N, 1, seed=4)).cuda()
     e1, e2 = SalpVectorEnv(N, seed=9, **p), SalpVectorEnv(N, seed=9, **p)

@@ -74,7 +74,7 @@ int main(int argc, char **argv) {
 #if LAB_F == 1
         V(kStoreWarp, 64, 16), V(kStoreWarp, 128, 8), V(kStoreTmaBlock, 64, 16), V(kStoreTmaBlock, 32, 32),
         V(kStoreTmaWarp, 64, 16), V(kStoreTmaWarp, 128, 8), V(kStoreTmaWarp, 256, 4),
-        V(kStoreTmaBlock, 64, 18), V(kStoreTmaBlock, 64, 20), V(kStoreTmaBlock, 32, 36), V(kStoreTmaBlock, 32, 40), V(kStoreTmaBlock, 128, 8), V(kStoreTmaBlock, 128, 9),
+        V(kStoreTmaBlock, 64, 17), V(kStoreTmaBlock, 64, 18), V(kStoreTmaBlock, 64, 20), V(kStoreTmaBlock, 32, 36), V(kStoreTmaBlock, 32, 40), V(kStoreTmaBlock, 128, 8), V(kStoreTmaBlock, 128, 9),
         P(kStoreWarp, 64, 16), P(kStoreWarp, 128, 8), P(kStoreWarp, 256, 4), P(kStoreWarp, 64, 12), P(kStoreWarp, 128, 6),
         P(kStoreTmaBlock, 64, 16), P(kStoreTmaBlock, 128, 8), P(kStoreTmaBlock, 256, 4), P(kStoreTmaBlock, 64, 12), P(kStoreTmaBlock, 32, 32),
         P(kStoreDirect, 64, 16), P(kStoreDirect, 128, 8), P(kStoreDirect, 64, 12),
