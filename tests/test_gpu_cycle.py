@@ -260,3 +260,52 @@ def test_sb3_vecenv_protocol_model_b(salp_lib):
             assert obs[i, 2] == 0.0 and obs[i, 4] == 0.0      # auto-reset: robot at rest in the new episode
     assert n_done > 0 and len(venv.get_attr("cycle")) == N
     venv.close()
+
+
+def test_no_write_outside_the_bound_buffers(salp_lib):
+    """compute-sanitizer is not available on the GPU pool: every buffer handed to salp_cycle_reset / salp_cycle_step sits
+    between two canary bands; after resets and steps of an odd-sized slab the bands must be untouched and the results must
+    equal those of the regular env."""
+    import ctypes as C
+    from underwater_swimmer_rl_b200 import _capi, rng_tables
+    from underwater_swimmer_rl_b200.cycle_env import SalpCycleVectorEnv, default_robot, make_cycle_params
+    N, PAD = 1003, 4096                       # bytes of canary on both sides (multiple of every alignment)
+    dev = torch.device("cuda:0")
+    words = rng_tables.fill_words(N, 64, 900, 0, rng_tables.JITTER_STREAM)
+
+    def guarded(nbytes):
+        total = PAD + ((nbytes + 255) // 256) * 256 + PAD
+        raw = torch.full((total,), 0xA5, dtype=torch.uint8, device=dev)
+        return raw, raw[PAD:PAD + nbytes]
+
+    for dtype, code, rb in ((torch.float32, _capi.SALP_F32, 4), (torch.float64, _capi.SALP_F64, 8)):
+        sizes = dict(state=6 * N * 4 * rb, ctrl=N * 16, obs=N * 24, reward=N * rb, terminated=N, truncated=N, n_sub=N * 4,
+                     final_obs=N * 24, stats=64, actions=N * 3 * rb)
+        bufs = {k: guarded(v) for k, v in sizes.items()}
+        for k in ("state", "ctrl", "stats"):
+            bufs[k][1].zero_()
+        w = torch.from_numpy(words.view(np.int32)).to(dev)
+        b = _capi.SalpCycleBuffers()
+        for k in ("state", "ctrl", "obs", "reward", "terminated", "truncated", "n_sub", "final_obs", "stats"):
+            setattr(b, k, bufs[k][1].data_ptr())
+        b.words, b.table_rows, b.words_len, b.n, b.env_id0, b.dtype = w.data_ptr(), N, 64, N, 0, code
+        p = make_cycle_params(default_robot(), 3000, 2400, True)     # far targets: auto-resets happen inside the steps
+        ref = SalpCycleVectorEnv(N, dtype=dtype, width=3000, height=2400)
+        ref.set_rng_table(words)
+        ref.reset()
+        _capi.check(salp_lib.salp_cycle_reset(C.byref(p), C.byref(b), None, 1, None))
+        g = torch.Generator(device="cuda").manual_seed(3)
+        for t in range(5):
+            a = torch.rand(N, 3, device=dev, dtype=dtype, generator=g)
+            a[:, 2] = a[:, 2] * 2 - 1
+            bufs["actions"][1].copy_(a.contiguous().view(torch.uint8).reshape(-1))
+            _capi.check(salp_lib.salp_cycle_step(C.byref(p), C.byref(b), C.c_void_p(bufs["actions"][1].data_ptr()), None))
+            ref.step(a)
+        torch.cuda.synchronize()
+        for k, (raw, view) in bufs.items():
+            n = view.numel()
+            assert bool((raw[:PAD] == 0xA5).all()) and bool((raw[PAD + n:] == 0xA5).all()), f"{k}: canary overwritten ({dtype})"
+        assert torch.equal(bufs["obs"][1].view(torch.float32).reshape(N, 6), ref.obs)
+        assert torch.equal(bufs["state"][1].view(dtype).reshape(6, N, 4), ref.state)
+        assert torch.equal(bufs["n_sub"][1].view(torch.int32), ref.n_sub)
+        assert int(ref.terminated.sum() + ref.truncated.sum()) >= 0
