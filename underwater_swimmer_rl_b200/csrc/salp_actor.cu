@@ -302,7 +302,8 @@ __global__ void __launch_bounds__(kThreads, 1) salp_actor_kernel(const __grid_co
         }
         // H is idle (GEMM 2 has completed): the four column groups meet there
         *reinterpret_cast<float4 *>(s_part + (cgroup * kTileM + erow) * 4) = make_float4(out[0], out[1], out[2], out[3]);
-        __syncthreads();
+        // only the four warps that share this quarter of the rows exchange partial sums: a 128-thread named barrier
+        asm volatile("bar.sync %0, %1;" ::"r"(1 + quarter), "r"(kThreads / 4) : "memory");
         const long long row = tile * kTileM + erow;
         if (cgroup == 0 && row < a.n) {
             float4 t = *reinterpret_cast<const float4 *>(s_part + erow * 4);
@@ -338,7 +339,9 @@ __global__ void __launch_bounds__(kThreads, 1) salp_actor_kernel(const __grid_co
                 }
             }
         }
-        __syncthreads();  // epilogue 1 of the next tile overwrites H (and with it these partial sums) right away
+        // No barrier here: the partial sums of row r live in H chunks 0-3 of row r, which epilogue 1 of the next tile
+        // rewrites from the very thread that has just read them (column group 0 of that row); every other reuse of H,
+        // acc1 and acc2 is ordered by the CTA-wide barrier after epilogue 1.
     }
     // ---- teardown: every thread's TMEM reads are done before the columns are released; the last CTA to get
     //      here (every CTA read the draw counter at its start) advances the counter for the next launch

@@ -12,17 +12,18 @@
 //     accumulated cycle times (cycle_time += 0.01 from 0.0 is the same double sequence for every env), so the
 //     loop carries no double accumulator and the discrete trajectory is exact in both builds;
 //   * body geometry (length, width, area, water volume, mass, drag coefficient, inertia and their rates) only
-//     changes while the body contracts or releases: that block runs in double (differences of nearly equal
-//     volumes / inertias), is skipped for the coast / rest substeps (the majority), and hands the dynamics a
-//     dozen loop-invariant coefficients;
+//     changes while the body contracts or releases: that block is skipped for the coast / rest substeps (the
+//     majority) and hands the dynamics a dozen coefficients.  The double build evaluates it with the reference's
+//     expressions; the float build folds every shape factor into the coefficients and gets the volume / inertia
+//     rates from exact difference expansions in float (cyc_shape_f), no double arithmetic;
 //   * sin / cos of the Euler angles are carried from the end of one substep to the start of the next (the
 //     reference re-evaluates them on the same values);
-//   * lanes of a warp get cycles of different lengths (the coast time is an action), so a finished lane takes
-//     the next unprocessed env of its CTA's slice instead of idling until the longest cycle of the warp ends
-//     (salp_cycle_step_kernel, `kRefill`).
+//   * lanes of a warp would get cycles of different lengths (the coast time is an action): one CTA per SM sorts
+//     its env range by substep count in shared memory and its 20 warps pull 32-env chunks of nearly equal length,
+//     longest first, from a shared counter (salp_cycle_step_kernel).
 // The double build keeps the reference's operation order (compiled with -fmad=false); the float build uses
 // the closed form of the nozzle inverse kinematics (the reference's arcsin argument is analytically
-// -sign(yaw): its result carries ~2e-8 of rounding noise, far below float resolution).
+// -sign(yaw): its result carries ~2e-8 of rounding noise, far below float resolution) and SFU sin/cos/rsqrt/rcp.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
