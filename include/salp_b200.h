@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define SALP_ABI_VERSION 3
+#define SALP_ABI_VERSION 4
 
 enum { SALP_OK = 0, SALP_EINVAL = -1, SALP_ECUDA = -2, SALP_EUNBOUND = -3, SALP_EUNSUPPORTED = -4 };
 
@@ -259,7 +259,10 @@ int salp_replay_append(const SalpReplayAppend *p, void *cuda_stream);
  *   w1_packed / w2_packed: bf16 weights [256][K] (K = obs_dim zero-padded to 32, resp. 256) re-laid as
  *   [K/8][256][8] (rollout.pack_weight) -- the tcgen05 K-major operand layout.  w3: f32 [2*act][256].
  *   noise: f32 [n][act] standard normal draws, or NULL for the deterministic action tanh(mean).
- * Restrictions: hidden == 256, obs_dim % 4 == 0 and <= 32, act_dim in {1, 2}; otherwise SALP_EUNSUPPORTED.
+ * Restrictions: hidden == 256, obs_dim (+ extra_dim) <= 32, act_dim in 1..4; otherwise SALP_EUNSUPPORTED.
+ * Model (A) is obs 24 / act 1; model (B) is obs 6 / act 3 with the Box [0,1] x [0,1] x [-1,1]
+ * (salp_robot_env.py:51-56), for which SB3's SAC maps the squashed action to the Box
+ * (`unscale_action`: low + 0.5 * (a + 1) * (high - low)) -- act_rescale / act_low / act_high below.
  */
 typedef struct SalpActorForward {
     const float *obs;        /* [n][obs_dim] */
@@ -281,6 +284,9 @@ typedef struct SalpActorForward {
     int32_t mode;            /* 0: actor (tanh-Gaussian action)
                                 1: GAIL reward -log(1 - sigmoid(MLP(cat(obs, extra))) + 1e-8) for a discriminator
                                    obs+act -> 256 -> 256 -> 1 (src/salp/agents/discriminator.py:43-85) */
+    int32_t act_rescale;     /* mode 0: nonzero = write low + 0.5 * (tanh(.) + 1) * (high - low) instead of tanh(.) */
+    int32_t reserved_;
+    float act_low[4], act_high[4];
 } SalpActorForward;
 
 int salp_actor_forward(const SalpActorForward *p, void *cuda_stream);

@@ -31,7 +31,7 @@ def test_struct_sizes_match_header(salp_lib):
     assert C.sizeof(_capi.SalpLayout) == 32
     assert C.sizeof(_capi.SalpBuffers) == 14 * 8 + 3 * 8 + 2 * 4
     assert C.sizeof(_capi.SalpReplayAppend) == 16 * 8 + 2 * 8 + 6 * 4
-    assert C.sizeof(_capi.SalpActorForward) == 11 * 8 + 8 + 6 * 4
+    assert C.sizeof(_capi.SalpActorForward) == 11 * 8 + 8 + 8 * 4 + 8 * 4
     assert C.sizeof(_capi.SalpCycleParams) == 12 * 8 + 4 * 4
     assert C.sizeof(_capi.SalpCycleBuffers) == 10 * 8 + 4 * 8 + 2 * 4
 

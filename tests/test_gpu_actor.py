@@ -15,8 +15,8 @@ def _ref(actor, obs, noise):
     out = h @ bf(l3.weight).T + l3.bias.float()
     mean, log_std = out.chunk(2, dim=-1)
     if noise is None:
-        return torch.tanh(mean)
-    return torch.tanh(mean + torch.exp(torch.clamp(log_std, -20, 2)) * noise)
+        return actor.to_box(torch.tanh(mean))
+    return actor.to_box(torch.tanh(mean + torch.exp(torch.clamp(log_std, -20, 2)) * noise))
 
 
 @pytest.mark.parametrize("n,obs_dim,act_dim", [(128, 24, 1), (1000, 24, 1), (70001, 24, 1), (4096, 24, 2), (513, 32, 2), (300, 16, 1)])
@@ -40,6 +40,73 @@ def test_fused_actor_matches_torch(salp_lib, n, obs_dim, act_dim):
         err = (out.float() - ref).abs().max().item()
         assert err <= 5e-3, (err, nz is None, out_dtype)
         assert out.abs().max().item() <= 1.0
+
+
+@pytest.mark.parametrize("n,obs_dim,act_dim,box", [
+    (4097, 6, 3, ([0.0, 0.0, -1.0], [1.0, 1.0, 1.0])),   # model (B): salp_robot_env.py:51-71
+    (1000, 6, 3, None), (777, 7, 4, ([-2.0, 0.0, 0.5, -1.0], [2.0, 3.0, 1.5, 1.0])), (300, 31, 3, None), (129, 1, 1, None)])
+def test_fused_actor_other_shapes_and_box_rescale(salp_lib, n, obs_dim, act_dim, box):
+    """Rows that are not float4 groups, up to 4 action dims (8 rows of W3), and SB3's [-1, 1] -> Box mapping."""
+    from underwater_swimmer_rl_b200.rollout import FusedActor, TanhGaussianActor
+    torch.manual_seed(n + obs_dim)
+    kw = {} if box is None else {"action_low": box[0], "action_high": box[1]}
+    actor = TanhGaussianActor(obs_dim, act_dim, **kw).cuda()
+    with torch.no_grad():
+        for l in actor.layers:
+            l.weight.mul_(2.0)
+            l.bias.uniform_(-0.5, 0.5)
+    fused = FusedActor(actor)
+    base = torch.rand(n * obs_dim + 1, device="cuda") * 2 - 1
+    noise = torch.randn(n, act_dim, device="cuda")
+    for off in (0, 1):  # off = 1: the observation rows start 4 bytes off a 16-byte boundary
+        obs = base[off:off + n * obs_dim].view(n, obs_dim)
+        for nz, out_dtype in ((None, torch.float32), (noise, torch.float32), (noise, torch.float64)):
+            out = torch.full((n, act_dim), 7.0, device="cuda", dtype=out_dtype)
+            fused(obs, out, deterministic=nz is None, noise=nz)
+            torch.cuda.synchronize()
+            with torch.no_grad():
+                ref = _ref(actor, obs, nz)
+            err = (out.float() - ref).abs().max().item()
+            assert err <= 5e-3 * (1.0 if box is None else 2.0), (err, nz is None, out_dtype, off)
+            if box is not None:
+                lo, hi = (torch.tensor(b, device="cuda") for b in box)
+                assert (out.float() >= lo - 1e-6).all() and (out.float() <= hi + 1e-6).all()
+    # in-kernel noise with 3-4 action dims: every dim gets its own draw
+    if act_dim >= 3:
+        f2 = FusedActor(TanhGaussianActor(obs_dim, act_dim).cuda())
+        with torch.no_grad():
+            f2.actor.layers[2].weight.zero_(); f2.actor.layers[2].bias.zero_()
+        f2.refresh()
+        out = torch.empty(1 << 16, act_dim, device="cuda", dtype=torch.float64)
+        f2(torch.rand(1 << 16, obs_dim, device="cuda"), out)
+        z = torch.atanh(out)
+        assert abs(z.mean().item()) < 0.02 and abs(z.std().item() - 1.0) < 0.02
+        c = torch.corrcoef(z.T)
+        assert (c - torch.eye(act_dim, device="cuda", dtype=torch.float64)).abs().max().item() < 0.02
+
+
+def test_fused_gail_reward_model_b_shape(salp_lib):
+    """Discriminator on cat(obs 6, action 3): the appended columns start inside the first 8-feature chunk."""
+    from underwater_swimmer_rl_b200.rollout import FusedGailReward, GailDiscriminator
+    torch.manual_seed(3)
+    n = 5000
+    disc = GailDiscriminator(6, 3).cuda()
+    with torch.no_grad():
+        for l in disc.layers:
+            l.weight.mul_(2.0)
+            l.bias.uniform_(-0.5, 0.5)
+    fused = FusedGailReward(disc, 6, 3)
+    obs = torch.rand(n, 6, device="cuda") * 2 - 1
+    act = torch.rand(n, 3, device="cuda") * 2 - 1
+    out = torch.empty(n, device="cuda")
+    fused(obs, act, out)
+    bf = lambda t: t.to(torch.bfloat16).float()  # noqa: E731
+    with torch.no_grad():
+        l1, l2, l3 = disc.layers
+        h = torch.relu(bf(torch.cat([obs, act], -1)) @ bf(l1.weight).T + l1.bias)
+        h = torch.relu(bf(h) @ bf(l2.weight).T + l2.bias)
+        ref = -torch.log(1 - torch.sigmoid((h @ bf(l3.weight).T + l3.bias).reshape(-1)) + 1e-8)
+    assert (out - ref).abs().max().item() <= 5e-3 * max(1.0, ref.abs().max().item())
 
 
 def test_fused_actor_in_the_rollout_loop(salp_lib):

@@ -163,3 +163,63 @@ def test_step_ring_replay_is_zero_copy_and_exact(salp_lib, dtype, fused, disc):
     assert ring.steps == before + 2 * K and len(ring) == (K - 1) * n
     s = ring.sample(256)
     assert s["observations"].shape == (256, env.obs_dim) and torch.isfinite(s["rewards"]).all()
+
+
+@pytest.mark.parametrize("dtype,fused", [("float64", True), ("float32", True), ("float32", False)])
+def test_model_b_rollout_with_step_ring(salp_lib, dtype, fused):
+    """Model (B) in the same loop: SAC actor obs 6 -> 256 -> 256 -> 2*3 with SB3's Box rescale (train_robot.py:36-49,
+    salp_robot_env.py:51-56) -> salp_cycle_step into ring row j % K.  A second env stepped by hand with the ring's
+    actions must produce the same rows bit for bit, and the sampler must return exactly those transitions."""
+    from underwater_swimmer_rl_b200.cycle_env import SalpCycleVectorEnv
+    from underwater_swimmer_rl_b200.rollout import FusedActor, RolloutCollector, StepRingReplay, TanhGaussianActor
+    torch.manual_seed(2)
+    n, K, T = 512, 4, 11
+    env = SalpCycleVectorEnv(n, device="cuda:0", dtype=dtype, rows=K, seed=5)
+    shadow = SalpCycleVectorEnv(n, device="cuda:0", dtype=dtype, seed=5)
+    env.params.max_cycles = shadow.params.max_cycles = 5      # episodes end inside the ring window
+    actor = TanhGaussianActor(6, 3, action_low=[0.0, 0.0, -1.0], action_high=[1.0, 1.0, 1.0]).cuda()
+    ring = StepRingReplay(env)
+    col = RolloutCollector(env, FusedActor(actor) if fused else actor, ring, deterministic=True)
+    obs0, _ = col.reset()
+    s_obs, _ = shadow.reset()
+    assert torch.equal(obs0, s_obs)
+    lo, hi = torch.tensor([0.0, 0.0, -1.0], device="cuda"), torch.tensor([1.0, 1.0, 1.0], device="cuda")
+    hist = []
+    for t in range(T):
+        prev = env.obs_rows[col.cur].clone()
+        col.collect(1)
+        r = col.cur
+        assert r == (t + 1) % K
+        a = ring.act[r]
+        assert (a.float() >= lo).all() and (a.float() <= hi).all()
+        o, rew, term, trunc, info = shadow.step(a)
+        assert torch.equal(o, env.obs_rows[r]) and torch.equal(rew, env.reward_rows[r])
+        assert torch.equal(term, env.terminated_rows[r]) and torch.equal(trunc, env.truncated_rows[r])
+        assert torch.equal(info["n_sub"], env.n_sub_rows[r])
+        done = (term | trunc).bool()
+        assert torch.equal(info["final_obs"][done], env.final_obs_rows[r][done])
+        hist.append(dict(obs=prev, act=a.float().clone(), rew=rew.float().clone(), done=done.clone(),
+                         next=torch.where(done[:, None], env.final_obs_rows[r], env.obs_rows[r]).clone()))
+    assert any(h["done"].any() for h in hist[-(K - 1):]), "no episode ended inside the ring window"
+    assert len(ring) == (K - 1) * n
+    g, g2 = torch.Generator(device="cuda").manual_seed(3), torch.Generator(device="cuda").manual_seed(3)
+    batch = ring.sample(2048, generator=g)
+    back = torch.randint(0, K - 1, (2048,), device="cuda", generator=g2)
+    e = torch.randint(0, n, (2048,), device="cuda", generator=g2)
+    for b in range(K - 1):
+        m, h = back == b, hist[T - 1 - b]
+        for key, name in (("observations", "obs"), ("next_observations", "next"), ("actions", "act"),
+                          ("rewards", "rew"), ("dones", "done")):
+            assert torch.equal(batch[key][m], h[name][e[m]]), key
+    # one CUDA graph = one trip through the ring; the shadow env follows it step by step through the ring's actions
+    replay = col.capture()
+    assert col.steps_per_replay == K and col.cur == 0
+    shadow.state.copy_(env.state); shadow.ctrl.copy_(env.ctrl)
+    replay()
+    torch.cuda.synchronize()
+    for r in list(range(1, K)) + [0]:
+        o, rew, term, trunc, _ = shadow.step(ring.act[r])
+        assert torch.equal(o, env.obs_rows[r]) and torch.equal(rew, env.reward_rows[r])
+        assert torch.equal(term, env.terminated_rows[r]) and torch.equal(trunc, env.truncated_rows[r])
+    st = env.episode_stats()
+    assert st["episodes"] > 0

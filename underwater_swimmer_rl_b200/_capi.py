@@ -11,7 +11,7 @@ import os
 _PKG = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_PKG, "libsalp_b200.so")
 
-SALP_ABI_VERSION = 3
+SALP_ABI_VERSION = 4
 SALP_OK, SALP_EINVAL, SALP_ECUDA, SALP_EUNBOUND, SALP_EUNSUPPORTED = 0, -1, -2, -3, -4
 SALP_F32, SALP_F64 = 0, 1
 SALP_AUTORESET = 1
@@ -68,7 +68,8 @@ class SalpActorForward(C.Structure):
     _fields_ = [(n, C.c_void_p) for n in ("obs", "w1_packed", "b1", "w2_packed", "b2", "w3", "b3", "noise", "actions",
                                           "extra", "rng_state")] + [
         ("n", C.c_int64), ("obs_dim", C.c_int32), ("act_dim", C.c_int32), ("hidden", C.c_int32), ("dtype", C.c_int32),
-        ("extra_dim", C.c_int32), ("mode", C.c_int32)]
+        ("extra_dim", C.c_int32), ("mode", C.c_int32), ("act_rescale", C.c_int32), ("reserved_", C.c_int32),
+        ("act_low", C.c_float * 4), ("act_high", C.c_float * 4)]
 
 
 class SalpCycleParams(C.Structure):

@@ -27,11 +27,12 @@ namespace salp { int set_error(int code, const char *msg); }
 
 namespace {
 
-constexpr int kTileM = 128, kHid = 256, kK1 = 32, kMaxOut = 4, kThreads = 512;
+constexpr int kTileM = 128, kHid = 256, kK1 = 32, kMaxOut = 8, kMaxAct = 4, kThreads = 512;
 constexpr uint32_t kW2Bytes = kHid * kHid * 2, kW1Bytes = kHid * kK1 * 2, kA1Bytes = kTileM * kK1 * 2, kHBytes = kTileM * kHid * 2;
 constexpr uint32_t kOffW2 = 0, kOffW1 = kOffW2 + kW2Bytes, kOffA1 = kOffW1 + kW1Bytes, kOffH = kOffA1 + kA1Bytes;
 constexpr uint32_t kOffB1 = kOffH + kHBytes, kOffB2 = kOffB1 + kHid * 4, kOffW3 = kOffB2 + kHid * 4;
-constexpr uint32_t kOffB3 = kOffW3 + kMaxOut * kHid * 4, kOffBar = kOffB3 + 16, kOffTmem = kOffBar + 16;
+constexpr uint32_t kOffB3 = kOffW3 + kMaxOut * kHid * 4, kOffBar = kOffB3 + kMaxOut * 4, kOffTmem = kOffBar + 16;
+static_assert(kOffTmem + 8 <= 227 * 1024, "shared memory of one CTA");
 constexpr uint32_t kSmemBytes = kOffTmem + 8;
 static_assert(kSmemBytes <= 232448, "shared memory budget of one sm_100 CTA");
 constexpr uint32_t kTmemCols = 512;  // two 128 x 256 f32 accumulators
@@ -52,6 +53,8 @@ struct ActorArgs {
     unsigned long long *rng;  // device {seed, draw counter, CTA ticket}: in-kernel Philox noise when noise == null
     long long n;
     int obs_dim, act_dim, f64, extra_dim, w3_rows, mode;
+    int obs_vec4;          // rows of obs are 16-byte aligned float4 groups (obs_dim % 4 == 0)
+    float act_scale[kMaxAct], act_shift[kMaxAct];  // action = tanh(.) * scale + shift (Box rescale; 1, 0 = identity)
 };
 
 enum { kModeActor = 0, kModeGailReward = 1 };
@@ -153,9 +156,16 @@ struct ObsChunk { float4 lo, hi; };
 __device__ __forceinline__ ObsChunk load_obs_chunk(const ActorArgs &a, long long row, int c) {
     ObsChunk v{make_float4(0.f, 0.f, 0.f, 0.f), make_float4(0.f, 0.f, 0.f, 0.f)};
     if (row < a.n) {
-        const float4 *src = reinterpret_cast<const float4 *>(a.obs + row * a.obs_dim);
-        if (8 * c < a.obs_dim) v.lo = src[2 * c];
-        if (8 * c + 4 < a.obs_dim) v.hi = src[2 * c + 1];
+        if (a.obs_vec4) {
+            const float4 *src = reinterpret_cast<const float4 *>(a.obs + row * a.obs_dim);
+            if (8 * c < a.obs_dim) v.lo = src[2 * c];
+            if (8 * c + 4 < a.obs_dim) v.hi = src[2 * c + 1];
+        } else if (8 * c < a.obs_dim) {  // rows that are not float4 groups (model B: 6 features): scalar loads
+            float *f = reinterpret_cast<float *>(&v);
+    #pragma unroll
+            for (int j = 0; j < 8; ++j)
+                if (8 * c + j < a.obs_dim) f[j] = a.obs[row * a.obs_dim + 8 * c + j];
+        }
         if (a.extra && 8 * c + 8 > a.obs_dim && 8 * c < a.obs_dim + a.extra_dim) {  // appended columns fall in this chunk
             float *f = reinterpret_cast<float *>(&v);
     #pragma unroll
@@ -170,7 +180,7 @@ __device__ __forceinline__ ObsChunk load_obs_chunk(const ActorArgs &a, long long
     return v;
 }
 
-template <int NOUT>  // rows of W3 padded to 2 or 4
+template <int NOUT>  // rows of W3 padded to 2, 4 or 8
 __global__ void __launch_bounds__(kThreads, 1) salp_actor_kernel(const __grid_constant__ ActorArgs a) {
     extern __shared__ __align__(1024) unsigned char smem[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -274,9 +284,10 @@ __global__ void __launch_bounds__(kThreads, 1) salp_actor_kernel(const __grid_co
         phase2 ^= 1;
         tc_fence_after();
         // ---- epilogue 2: h2 = relu(acc2 + b2); partial dot products with the 2*act rows of W3 over 64 columns
-        float out[kMaxOut];
+        constexpr int kOutRegs = NOUT < 4 ? 4 : NOUT;
+        float out[kOutRegs];
     #pragma unroll
-        for (int j = 0; j < kMaxOut; ++j) out[j] = 0.f;
+        for (int j = 0; j < kOutRegs; ++j) out[j] = 0.f;
         {
             uint32_t r[2][32];
             const int colg = cgroup * 64;
@@ -302,6 +313,8 @@ __global__ void __launch_bounds__(kThreads, 1) salp_actor_kernel(const __grid_co
         }
         // H is idle (GEMM 2 has completed): the four column groups meet there
         *reinterpret_cast<float4 *>(s_part + (cgroup * kTileM + erow) * 4) = make_float4(out[0], out[1], out[2], out[3]);
+        if constexpr (NOUT > 4)  // outputs 4-7 of (column group g, row r) go to H chunk 4 + g of row r
+            *reinterpret_cast<float4 *>(s_part + ((4 + cgroup) * kTileM + erow) * 4) = make_float4(out[4], out[5], out[6], out[7]);
         // only the four warps that share this quarter of the rows exchange partial sums: a 128-thread named barrier
         asm volatile("bar.sync %0, %1;" ::"r"(1 + quarter), "r"(kThreads / 4) : "memory");
         const long long row = tile * kTileM + erow;
@@ -312,28 +325,50 @@ __global__ void __launch_bounds__(kThreads, 1) salp_actor_kernel(const __grid_co
                 const float4 u = *reinterpret_cast<const float4 *>(s_part + (g * kTileM + erow) * 4);
                 t.x += u.x; t.y += u.y; t.z += u.z; t.w += u.w;
             }
-            const float o4[4] = {t.x, t.y, t.z, t.w};
+            float o8[kOutRegs] = {t.x, t.y, t.z, t.w};
+            if constexpr (NOUT > 4) {
+                float4 t2 = *reinterpret_cast<const float4 *>(s_part + (4 * kTileM + erow) * 4);
+    #pragma unroll
+                for (int g = 1; g < kThreads / kTileM; ++g) {
+                    const float4 u = *reinterpret_cast<const float4 *>(s_part + ((4 + g) * kTileM + erow) * 4);
+                    t2.x += u.x; t2.y += u.y; t2.z += u.z; t2.w += u.w;
+                }
+                o8[4] = t2.x; o8[5] = t2.y; o8[6] = t2.z; o8[7] = t2.w;
+            }
+            auto pick = [&](int idx) {  // o8[idx] without a local-memory array
+                float v = o8[0];
+    #pragma unroll
+                for (int j = 1; j < kOutRegs; ++j) v = idx == j ? o8[j] : v;
+                return v;
+            };
             if (a.mode == kModeGailReward) {
                 // D = sigmoid(logit); reward = -log(1 - D + 1e-8)   (src/salp/agents/discriminator.py:59-82)
-                const float d = 1.f / (1.f + __expf(-(o4[0] + s_b3[0])));
+                const float d = 1.f / (1.f + __expf(-(o8[0] + s_b3[0])));
                 reinterpret_cast<float *>(a.actions)[row] = -__logf(1.f - d + 1e-8f);
             } else {
-                float2 z = make_float2(0.f, 0.f);
+                float z[kMaxAct] = {0.f, 0.f, 0.f, 0.f};
                 const bool sample = a.noise != nullptr || a.rng != nullptr;
-                if (a.noise) { z.x = a.noise[row * a.act_dim]; if (a.act_dim > 1) z.y = a.noise[row * a.act_dim + 1]; }
-                else if (a.rng) {
+                if (a.noise) {
+    #pragma unroll
+                    for (int d = 0; d < kMaxAct; ++d)
+                        if (d < a.act_dim) z[d] = a.noise[row * a.act_dim + d];
+                } else if (a.rng) {
                     const uint4 rnd = philox4x32(make_uint4((uint32_t)row, (uint32_t)(row >> 32), (uint32_t)rng_draw, (uint32_t)(rng_draw >> 32)),
                                                  make_uint2((uint32_t)rng_seed, (uint32_t)(rng_seed >> 32)));
-                    z = normal_pair(rnd.x, rnd.y);
+                    const float2 z01 = normal_pair(rnd.x, rnd.y);
+                    z[0] = z01.x; z[1] = z01.y;
+                    if (a.act_dim > 2) { const float2 z23 = normal_pair(rnd.z, rnd.w); z[2] = z23.x; z[3] = z23.y; }
                 }
-                for (int d = 0; d < a.act_dim; ++d) {
-                    const float mean = o4[d] + s_b3[d];
+    #pragma unroll
+                for (int d = 0; d < kMaxAct; ++d) {
+                    if (d >= a.act_dim || 2 * d >= NOUT) break;
+                    const float mean = o8[d] + s_b3[d];
                     float pre = mean;
                     if (sample) {
-                        const float log_std = fminf(fmaxf(o4[a.act_dim + d] + s_b3[a.act_dim + d], -20.f), 2.f);
-                        pre = fmaf(__expf(log_std), d == 0 ? z.x : z.y, mean);
+                        const float log_std = fminf(fmaxf(pick(a.act_dim + d) + s_b3[a.act_dim + d], -20.f), 2.f);
+                        pre = fmaf(__expf(log_std), z[d], mean);
                     }
-                    const float act = tanhf(pre);
+                    const float act = fmaf(tanhf(pre), a.act_scale[d], a.act_shift[d]);
                     if (a.f64) reinterpret_cast<double *>(a.actions)[row * a.act_dim + d] = (double)act;
                     else reinterpret_cast<float *>(a.actions)[row * a.act_dim + d] = act;
                 }
@@ -365,23 +400,28 @@ extern "C" int salp_actor_forward(const SalpActorForward *p, void *cuda_stream) 
     if (p->hidden != kHid) return salp::set_error(SALP_EUNSUPPORTED, "salp_actor_forward: hidden size must be 256");
     if (p->mode != kModeActor && p->mode != kModeGailReward) return salp::set_error(SALP_EINVAL, "salp_actor_forward: bad mode");
     const int extra = p->extra ? p->extra_dim : 0;
-    if (p->obs_dim <= 0 || (p->obs_dim & 3) || extra < 0 || p->obs_dim + extra > kK1)
-        return salp::set_error(SALP_EUNSUPPORTED, "salp_actor_forward: obs_dim must be a multiple of 4 and obs_dim + extra_dim <= 32");
-    if (p->mode == kModeActor && (p->act_dim < 1 || 2 * p->act_dim > kMaxOut))
-        return salp::set_error(SALP_EUNSUPPORTED, "salp_actor_forward: act_dim must be 1 or 2");
+    if (p->obs_dim <= 0 || extra < 0 || p->obs_dim + extra > kK1)
+        return salp::set_error(SALP_EUNSUPPORTED, "salp_actor_forward: obs_dim + extra_dim must be in 1..32");
+    if (p->mode == kModeActor && (p->act_dim < 1 || p->act_dim > kMaxAct))
+        return salp::set_error(SALP_EUNSUPPORTED, "salp_actor_forward: act_dim must be in 1..4");
     if (p->n <= 0) return salp::set_error(SALP_EINVAL, "salp_actor_forward: n must be positive");
     if (p->dtype != SALP_F32 && p->dtype != SALP_F64) return salp::set_error(SALP_EINVAL, "salp_actor_forward: bad dtype");
-    if (((uintptr_t)p->obs | (uintptr_t)p->w1_packed | (uintptr_t)p->w2_packed) % 16 != 0)
-        return salp::set_error(SALP_EINVAL, "salp_actor_forward: obs and packed weights must be 16-byte aligned");
+    if (((uintptr_t)p->w1_packed | (uintptr_t)p->w2_packed) % 16 != 0 || (uintptr_t)p->obs % 4 != 0)
+        return salp::set_error(SALP_EINVAL, "salp_actor_forward: packed weights must be 16-byte aligned, obs 4-byte aligned");
     ActorArgs a;
     a.obs = p->obs; a.w1p = reinterpret_cast<const uint4 *>(p->w1_packed); a.w2p = reinterpret_cast<const uint4 *>(p->w2_packed);
     a.b1 = p->b1; a.b2 = p->b2; a.w3 = p->w3; a.b3 = p->b3; a.noise = p->noise; a.actions = p->actions;
     a.extra = p->extra; a.extra_dim = extra; a.rng = reinterpret_cast<unsigned long long *>(p->rng_state);
     a.n = p->n; a.obs_dim = p->obs_dim; a.act_dim = p->act_dim; a.f64 = p->dtype == SALP_F64; a.mode = p->mode;
     a.w3_rows = p->mode == kModeGailReward ? 1 : 2 * p->act_dim;
+    a.obs_vec4 = (p->obs_dim % 4 == 0) && ((uintptr_t)p->obs % 16 == 0);
+    for (int d = 0; d < kMaxAct; ++d) {  // SB3's unscale_action: [-1, 1] -> [low, high] of the env's Box
+        const bool on = p->act_rescale && d < p->act_dim;
+        a.act_scale[d] = on ? 0.5f * (p->act_high[d] - p->act_low[d]) : 1.f;
+        a.act_shift[d] = on ? 0.5f * (p->act_high[d] + p->act_low[d]) : 0.f;
+    }
     if (p->mode == kModeGailReward) { a.noise = nullptr; a.rng = nullptr; }
-    const int which = a.w3_rows <= 2 ? 0 : 1;
-    auto kern = which == 0 ? salp_actor_kernel<2> : salp_actor_kernel<4>;
+    auto kern = a.w3_rows <= 2 ? salp_actor_kernel<2> : a.w3_rows <= 4 ? salp_actor_kernel<4> : salp_actor_kernel<8>;
     {   // per device and cheap: set on every call rather than caching a per-process flag
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
         if (e != cudaSuccess) return salp::set_error(SALP_ECUDA, cudaGetErrorString(e));

@@ -83,7 +83,7 @@ class SalpCycleVectorEnv(VectorEnv):
     def __init__(self, num_envs: int, device: Any = "cuda:0", dtype: Any = "float32", seed: int = 10_000,
                  env_id0: int = 0, table_rows: Optional[int] = None, table_len: int = 256, autoreset: bool = True,
                  max_substeps: int = 0, render_mode: Optional[str] = None, width: int = 900, height: int = 700,
-                 robot: Optional[Robot] = None):
+                 robot: Optional[Robot] = None, rows: int = 1):
         if render_mode is not None:
             raise ValueError("render_mode must be None: there is no graphics stack on the GPU box (SURVEY.md F11)")
         if not torch.cuda.is_available():
@@ -108,17 +108,25 @@ class SalpCycleVectorEnv(VectorEnv):
         self.action_space = batch_box(self.single_action_space, self.num_envs)
         self.table_rows = int(table_rows) if table_rows else self.num_envs
         self.table_len = int(table_len)
+        if rows < 1:
+            raise ValueError("rows must be >= 1")
+        self.rows = int(rows)
 
-        N, dev = self.num_envs, self.device
+        N, R, dev = self.num_envs, self.rows, self.device
         with torch.cuda.device(dev):
             self.state = torch.zeros((6, N, 4), dtype=self.real, device=dev)
             self.ctrl = torch.zeros((N, 4), dtype=torch.int32, device=dev)
-            self.obs = torch.zeros((N, 6), dtype=torch.float32, device=dev)
-            self.reward = torch.zeros((N,), dtype=self.real, device=dev)
-            self.terminated = torch.zeros((N,), dtype=torch.uint8, device=dev)
-            self.truncated = torch.zeros((N,), dtype=torch.uint8, device=dev)
-            self.n_sub = torch.zeros((N,), dtype=torch.int32, device=dev)
-            self.final_obs = torch.zeros((N, 6), dtype=torch.float32, device=dev)
+            # outputs: `rows` rows each; step(actions, slot=r) writes row r (rollout.StepRingReplay keeps the last
+            # rows - 1 steps in place).  obs / reward / ... are row 0, the only row of the default rows = 1.
+            self.obs_rows = torch.zeros((R, N, 6), dtype=torch.float32, device=dev)
+            self.reward_rows = torch.zeros((R, N), dtype=self.real, device=dev)
+            self.terminated_rows = torch.zeros((R, N), dtype=torch.uint8, device=dev)
+            self.truncated_rows = torch.zeros((R, N), dtype=torch.uint8, device=dev)
+            self.n_sub_rows = torch.zeros((R, N), dtype=torch.int32, device=dev)
+            self.final_obs_rows = torch.zeros((R, N, 6), dtype=torch.float32, device=dev)
+            self.obs, self.reward = self.obs_rows[0], self.reward_rows[0]
+            self.terminated, self.truncated = self.terminated_rows[0], self.truncated_rows[0]
+            self.n_sub, self.final_obs = self.n_sub_rows[0], self.final_obs_rows[0]
             self.stats = torch.zeros((8,), dtype=torch.float64, device=dev)
             self.words = None
         self._buffers = None
@@ -134,15 +142,26 @@ class SalpCycleVectorEnv(VectorEnv):
             raise ValueError("words must be [rows, power-of-two length]")
         self.table_rows, self.table_len = int(w.shape[0]), int(w.shape[1])
         self.words = torch.from_numpy(w.view(np.int32)).to(self.device)
+        self._slot_buffers = [self._make_buffers(r) for r in range(self.rows)]
+        self._buffers = self._slot_buffers[0]
+
+    def _make_buffers(self, r: int) -> _capi.SalpCycleBuffers:
+        """The caller-owned buffer set with the outputs of output row ``r`` (the ABI is stateless: a row is just
+        another set of pointers)."""
         b = _capi.SalpCycleBuffers()
-        b.state, b.ctrl, b.obs, b.reward = self.state.data_ptr(), self.ctrl.data_ptr(), self.obs.data_ptr(), self.reward.data_ptr()
-        b.terminated, b.truncated = self.terminated.data_ptr(), self.truncated.data_ptr()
-        b.n_sub, b.final_obs, b.stats, b.words = self.n_sub.data_ptr(), self.final_obs.data_ptr(), self.stats.data_ptr(), self.words.data_ptr()
+        b.state, b.ctrl, b.stats, b.words = self.state.data_ptr(), self.ctrl.data_ptr(), self.stats.data_ptr(), self.words.data_ptr()
+        b.obs, b.reward = self.obs_rows[r].data_ptr(), self.reward_rows[r].data_ptr()
+        b.terminated, b.truncated = self.terminated_rows[r].data_ptr(), self.truncated_rows[r].data_ptr()
+        b.n_sub, b.final_obs = self.n_sub_rows[r].data_ptr(), self.final_obs_rows[r].data_ptr()
         b.table_rows, b.words_len, b.n = self.table_rows, self.table_len, self.num_envs
         # rows are indexed (env_id0 + e) % table_rows inside the kernel; the table passed here starts at this slab's row 0
         b.env_id0 = 0
         b.dtype = self._dtype_code
-        self._buffers = b
+        return b
+
+    @property
+    def output_rows(self) -> int:
+        return self.rows
 
     def _stream(self):
         return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
@@ -165,8 +184,11 @@ class SalpCycleVectorEnv(VectorEnv):
         self.launch_count += 1
         return self.obs, {}
 
-    def step(self, actions):
-        """One breathing cycle per env.  actions [N, 3] (torch on the device, or numpy)."""
+    def step(self, actions, slot: int = 0):
+        """One breathing cycle per env.  actions [N, 3] (torch on the device, or numpy); the outputs go to output
+        row ``slot`` (0 unless the env was built with ``rows`` > 1)."""
+        if not 0 <= slot < self.rows:
+            raise ValueError(f"slot={slot} outside 0..rows-1={self.rows - 1}")
         a = actions
         if not torch.is_tensor(a):
             a = torch.as_tensor(np.asarray(a), device=self.device)
@@ -174,11 +196,11 @@ class SalpCycleVectorEnv(VectorEnv):
         if a.shape != (self.num_envs, 3):
             raise ValueError(f"actions must have shape ({self.num_envs}, 3), got {tuple(a.shape)}")
         with torch.cuda.device(self.device):
-            _capi.check(self._L.salp_cycle_step(C.byref(self.params), C.byref(self._buffers), C.c_void_p(a.data_ptr()),
-                                                self._stream()))
+            _capi.check(self._L.salp_cycle_step(C.byref(self.params), C.byref(self._slot_buffers[slot]),
+                                                C.c_void_p(a.data_ptr()), self._stream()))
         self.launch_count += 1
-        info = {"n_sub": self.n_sub, "final_obs": self.final_obs}
-        return self.obs, self.reward, self.terminated, self.truncated, info
+        info = {"n_sub": self.n_sub_rows[slot], "final_obs": self.final_obs_rows[slot]}
+        return (self.obs_rows[slot], self.reward_rows[slot], self.terminated_rows[slot], self.truncated_rows[slot], info)
 
     def step_host(self, actions_h, obs_h, reward_h, terminated_h, truncated_h):
         """The reference-facing call for callers holding host arrays (what SB3's DummyVecEnv does with one env):

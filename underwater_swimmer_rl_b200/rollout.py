@@ -33,10 +33,24 @@ from .vector_env import SalpVectorEnv
 
 
 class TanhGaussianActor(nn.Module):
-    """record_model.py:27-53 (CustomActor): hidden ReLU layers, last layer -> (mean, log_std)."""
+    """record_model.py:27-53 (CustomActor): hidden ReLU layers, last layer -> (mean, log_std).
 
-    def __init__(self, obs_dim: int, action_dim: int, hidden_sizes: Sequence[int] = (256, 256)):
+    ``action_low`` / ``action_high``: bounds of the env's action Box.  When given, the squashed action is mapped
+    from [-1, 1] to the Box the way SB3's SAC does before stepping the env (``unscale_action``:
+    low + 0.5 * (a + 1) * (high - low)) -- model (B)'s Box is [0, 1] x [0, 1] x [-1, 1] (salp_robot_env.py:51-56)."""
+
+    def __init__(self, obs_dim: int, action_dim: int, hidden_sizes: Sequence[int] = (256, 256),
+                 action_low: Optional[Sequence[float]] = None, action_high: Optional[Sequence[float]] = None):
         super().__init__()
+        if (action_low is None) != (action_high is None):
+            raise ValueError("give both action_low and action_high, or neither")
+        self.rescale = action_low is not None
+        if self.rescale:
+            lo, hi = torch.as_tensor(action_low, dtype=torch.float32), torch.as_tensor(action_high, dtype=torch.float32)
+            if lo.shape != (action_dim,) or hi.shape != (action_dim,):
+                raise ValueError("action_low / action_high must have action_dim entries")
+            self.register_buffer("action_low", lo)
+            self.register_buffer("action_high", hi)
         sizes = [obs_dim, *hidden_sizes]
         self.layers = nn.ModuleList([nn.Linear(a, b) for a, b in zip(sizes[:-1], sizes[1:])]
                                     + [nn.Linear(sizes[-1], 2 * action_dim)])
@@ -48,9 +62,14 @@ class TanhGaussianActor(nn.Module):
             x = torch.relu(layer(x))
         mean, log_std = self.layers[-1](x).float().chunk(2, dim=-1)
         if deterministic:
-            return torch.tanh(mean)
+            return self.to_box(torch.tanh(mean))
         std = torch.exp(torch.clamp(log_std, -20, 2))
-        return torch.tanh(mean + std * torch.randn_like(mean))  # Normal(mean, std).rsample()
+        return self.to_box(torch.tanh(mean + std * torch.randn_like(mean)))  # Normal(mean, std).rsample()
+
+    def to_box(self, squashed: torch.Tensor) -> torch.Tensor:
+        if not self.rescale:
+            return squashed
+        return squashed * (0.5 * (self.action_high - self.action_low)) + 0.5 * (self.action_high + self.action_low)
 
 
 def pack_weight(w: torch.Tensor, k_pad: int) -> torch.Tensor:
@@ -74,8 +93,8 @@ class FusedActor:
         if len(lin) != 3 or lin[0].out_features != 256 or lin[1].out_features != 256:
             raise ValueError("FusedActor needs hidden_sizes == (256, 256)")
         self.obs_dim, self.act_dim = lin[0].in_features, actor.action_dim
-        if self.obs_dim > 32 or self.obs_dim % 4 or self.act_dim not in (1, 2):
-            raise ValueError("FusedActor supports obs_dim <= 32 (multiple of 4) and act_dim in {1, 2}")
+        if self.obs_dim > 32 or not 1 <= self.act_dim <= 4:
+            raise ValueError("FusedActor supports obs_dim <= 32 and act_dim in 1..4")
         self._L = _capi.load()
         # {seed, draw counter, ticket, pad}: the kernel draws its own normals (Philox4x32-10) and bumps the counter
         self.rng_state = torch.tensor([int(seed), 0, 0, 0], dtype=torch.int64, device=lin[0].weight.device)
@@ -88,6 +107,8 @@ class FusedActor:
         # W3 goes through bf16 like the other layers of a bf16 actor would, then is held in f32
         self.b1, self.b2, self.b3 = f32(l1.bias), f32(l2.bias), f32(l3.bias)
         self.w3 = f32(l3.weight.detach().to(torch.bfloat16))
+        if self.actor.rescale:  # host copies: the bounds travel by value in SalpActorForward
+            self._low, self._high = self.actor.action_low.tolist(), self.actor.action_high.tolist()
 
     def __call__(self, obs: torch.Tensor, out: torch.Tensor, deterministic: bool = False,
                  noise: Optional[torch.Tensor] = None) -> torch.Tensor:
@@ -103,6 +124,10 @@ class FusedActor:
         p.noise = None if (deterministic or noise is None) else noise.data_ptr()
         p.rng_state = None if (deterministic or noise is not None) else self.rng_state.data_ptr()
         p.extra, p.extra_dim, p.mode = None, 0, 0
+        p.act_rescale = 1 if self.actor.rescale else 0
+        if self.actor.rescale:
+            for d in range(self.act_dim):
+                p.act_low[d], p.act_high[d] = self._low[d], self._high[d]
         p.n, p.obs_dim, p.act_dim, p.hidden = n, self.obs_dim, self.act_dim, 256
         p.dtype = _capi.SALP_F64 if out.dtype == torch.float64 else _capi.SALP_F32
         with torch.cuda.device(obs.device):
@@ -121,8 +146,8 @@ class FusedGailReward:
         lin = list(disc.layers)
         if len(lin) != 3 or lin[0].out_features != 256 or lin[1].out_features != 256 or lin[2].out_features != 1:
             raise ValueError("FusedGailReward needs a discriminator obs+act -> 256 -> 256 -> 1")
-        if lin[0].in_features != obs_dim + act_dim or obs_dim % 4 or obs_dim + act_dim > 32:
-            raise ValueError("FusedGailReward supports obs_dim % 4 == 0 and obs_dim + act_dim <= 32")
+        if lin[0].in_features != obs_dim + act_dim or obs_dim + act_dim > 32:
+            raise ValueError("FusedGailReward supports obs_dim + act_dim <= 32")
         self._L = _capi.load()
         self.refresh()
 
@@ -221,6 +246,17 @@ class DeviceReplayBuffer:
                 "next_observations": self.next_obs[idx], "dones": self.done[idx]}
 
 
+class _OutputRows:
+    """The [K, N, ...] output tensors of either env: ``SalpVectorEnv`` (model A) holds them under the plain names,
+    ``SalpCycleVectorEnv`` (model B, built with ``rows=K``) under ``*_rows``."""
+
+    def __init__(self, env):
+        cyc = hasattr(env, "obs_rows")
+        self.K = env.output_rows
+        for name in ("obs", "reward", "terminated", "truncated", "final_obs"):
+            setattr(self, name, getattr(env, name + "_rows") if cyc else getattr(env, name))
+
+
 class StepRingReplay:
     """Zero-copy replay storage: the env's own ``[K, N, ...]`` output rows ARE the buffer.
 
@@ -234,12 +270,14 @@ class StepRingReplay:
     With a GAIL discriminator the imitation reward of each step is kept in ``self.aux`` and mixed when sampling
     (``w_env * r_env + w_aux * r_gail``, src/salp/config/base_config.py:77-78)."""
 
-    def __init__(self, env: SalpVectorEnv):
-        if env.max_substeps < 3:
-            raise ValueError("StepRingReplay needs an env with max_substeps >= 3 (rows of the ring)")
+    def __init__(self, env):
+        if env.output_rows < 3:
+            raise ValueError("StepRingReplay needs an env with >= 3 output rows (max_substeps of SalpVectorEnv, "
+                             "rows of SalpCycleVectorEnv)")
         if not env.autoreset:
             raise ValueError("StepRingReplay needs autoreset=True (terminal observations come from final_obs)")
-        self.env, self.K, self.N = env, env.max_substeps, env.num_envs
+        self.env, self.K, self.N = env, env.output_rows, env.num_envs
+        self.out = _OutputRows(env)
         self.device = env.device
         self.act = torch.zeros(self.K, self.N, env.act_dim, dtype=env.real, device=env.device)
         self.aux = torch.zeros(self.K, self.N, dtype=torch.float32, device=env.device)
@@ -261,7 +299,7 @@ class StepRingReplay:
         have = min(self.steps, self.K - 1)
         if have == 0:
             raise ValueError("replay buffer is empty")
-        env = self.env
+        env = self.out
         back = torch.randint(0, have, (batch_size,), device=self.device, generator=generator)   # 0 = newest step
         e = torch.randint(0, self.N, (batch_size,), device=self.device, generator=generator)
         row = (self.steps - back) % self.K           # row of step j = steps - back (steps are numbered from 1)
@@ -294,16 +332,18 @@ class DeviceExpertBuffer:
 class RolloutCollector:
     """Steps ``env`` with ``actor`` in the loop and appends every transition to ``buffer``.
 
-    ``env`` must have been built with ``max_substeps >= 2`` (two output rows, used alternately) and
-    auto-reset on.  With ``discriminator`` the stored reward is ``w_env*r_env + w_gail*r_gail``.
+    ``env``: a ``SalpVectorEnv`` built with ``max_substeps >= 2`` or a ``SalpCycleVectorEnv`` built with
+    ``rows >= 2`` (two output rows, used alternately; all rows with a ``StepRingReplay``) and auto-reset on.
+    With ``discriminator`` the stored reward is ``w_env*r_env + w_gail*r_gail``.
     """
 
-    def __init__(self, env: SalpVectorEnv, actor, buffer: Optional[DeviceReplayBuffer] = None,
+    def __init__(self, env, actor, buffer: Optional[DeviceReplayBuffer] = None,
                  discriminator=None, w_env: float = 0.3, w_gail: float = 0.7,
                  deterministic: bool = False, autocast_dtype: Optional[torch.dtype] = None):
-        if env.max_substeps < 2:
-            raise ValueError("RolloutCollector needs an env with max_substeps >= 2 (ping-pong output rows)")
+        if env.output_rows < 2:
+            raise ValueError("RolloutCollector needs an env with >= 2 output rows (ping-pong)")
         self.env, self.actor, self.buffer, self.disc = env, actor, buffer, discriminator
+        self.out = _OutputRows(env)
         self.w_env, self.w_gail, self.deterministic = w_env, w_gail, deterministic
         self.autocast_dtype = autocast_dtype
         self.cur = 0          # output row holding the current observation
@@ -312,7 +352,7 @@ class RolloutCollector:
         self._graph = None
         self._aux = torch.zeros(env.num_envs, dtype=torch.float32, device=env.device)  # GAIL reward of the step
         self.ring = buffer if isinstance(buffer, StepRingReplay) else None
-        self.rows = env.max_substeps if self.ring is not None else 2   # output rows the rollout cycles through
+        self.rows = env.output_rows if self.ring is not None else 2   # output rows the rollout cycles through
         if self.ring is not None and discriminator is not None:
             self.ring.w_env, self.ring.w_aux = float(w_env), float(w_gail)
 
@@ -325,8 +365,8 @@ class RolloutCollector:
 
     @torch.no_grad()
     def _one_step(self, cur: int) -> int:
-        env = self.env
-        obs = env.obs[cur]
+        env, out = self.env, self.out
+        obs = out.obs[cur]
         nxt = (cur + 1) % self.rows
         act = self.ring.act[nxt] if self.ring is not None else self.act   # ring: the action row is the storage
         if isinstance(self.actor, FusedActor):
@@ -347,8 +387,8 @@ class RolloutCollector:
                 aux = self.disc(obs, self.act, self._aux)
             else:
                 aux = self.disc.predict_reward(obs, self.act).reshape(-1).contiguous() if self.disc is not None else None
-            self.buffer.append(obs, self.act, env.reward[nxt], env.terminated[nxt], env.truncated[nxt], env.obs[nxt],
-                               final_obs=env.final_obs[nxt] if env.autoreset else None, reward_aux=aux,
+            self.buffer.append(obs, self.act, out.reward[nxt], out.terminated[nxt], out.truncated[nxt], out.obs[nxt],
+                               final_obs=out.final_obs[nxt] if env.autoreset else None, reward_aux=aux,
                                w_env=self.w_env if aux is not None else 1.0, w_aux=self.w_gail if aux is not None else 0.0)
         return nxt
 
@@ -359,7 +399,7 @@ class RolloutCollector:
         self.steps += n_steps
         if self.ring is not None:
             self.ring.note_steps(n_steps)
-        return self.env.obs[self.cur]
+        return self.out.obs[self.cur]
 
     def capture(self) -> Callable[[], None]:
         """Capture one trip through the output rows (2 steps with ping-pong rows, K with a StepRingReplay) into a

@@ -186,6 +186,11 @@ class SalpVectorEnv(VectorEnv):
         return int(self._L.salp_launch_count(self._handle))
 
     # ------------------------------------------------------------------ gymnasium API
+    @property
+    def output_rows(self) -> int:
+        """Rows of the [max_substeps, N, ...] output tensors (``step(..., slot=r)`` writes row r)."""
+        return self.max_substeps
+
     def reset(self, *, seed: Optional[int] = None, options: Optional[dict] = None, mask: Optional[torch.Tensor] = None):
         """Reset all envs (or those where ``mask`` is set).  ``seed`` re-seeds the RNG word tables
         (rows seed+env_id0+r) and rewinds the cursors; without it the streams continue, exactly as
