@@ -3,6 +3,9 @@ replay append, env kernel (graph replay).  CUDA events, 200 launches each."""
 import sys, os
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
+from underwater_swimmer_rl_b200 import _capi
+if os.environ.get("SALP_LAB_LIB"):  # time another build of the library (tools/_lab/*.so)
+    _capi.LIB_PATH = os.path.abspath(os.environ["SALP_LAB_LIB"])
 from underwater_swimmer_rl_b200 import SalpVectorEnv
 from underwater_swimmer_rl_b200.rollout import DeviceReplayBuffer, FusedActor, TanhGaussianActor
 

@@ -52,12 +52,13 @@ def build(force: bool = False, verbose: bool = False) -> str:
     cyck = os.path.join(CSRC, "salp_cycle_kernels.cu")
     cycc = os.path.join(CSRC, "salp_cycle_capi.cu")
     vflag = ["-Xptxas", "-v"] if verbose else []
+    actor_defs = os.environ.get("SALP_ACTOR_DEFS", "").split()  # developer builds, e.g. SALP_ACTOR_DEFS=-DSALP_ACTOR_TRACE
     jobs = [
         (os.path.join(OBJ, "salp_kernels_f32.o"), [NVCC, "-c", kern, "-DSALP_BUILD_F64=0"] + COMMON + vflag, [kern] + hdrs),
         (os.path.join(OBJ, "salp_kernels_f64.o"), [NVCC, "-c", kern, "-DSALP_BUILD_F64=1", "-fmad=false"] + COMMON + vflag, [kern] + hdrs),
         (os.path.join(OBJ, "salp_capi.o"), [NVCC, "-c", capi] + COMMON, [capi] + hdrs),
         (os.path.join(OBJ, "salp_replay.o"), [NVCC, "-c", replay] + COMMON, [replay] + hdrs),
-        (os.path.join(OBJ, "salp_actor.o"), [NVCC, "-c", actor] + COMMON + vflag, [actor] + hdrs),
+        (os.path.join(OBJ, "salp_actor.o"), [NVCC, "-c", actor] + COMMON + vflag + actor_defs, [actor] + hdrs),
         (os.path.join(OBJ, "salp_cycle_f32.o"), [NVCC, "-c", cyck, "-DSALP_BUILD_F64=0"] + COMMON + vflag, [cyck] + hdrs),
         (os.path.join(OBJ, "salp_cycle_f64.o"), [NVCC, "-c", cyck, "-DSALP_BUILD_F64=1", "-fmad=false"] + COMMON + vflag, [cyck] + hdrs),
         (os.path.join(OBJ, "salp_cycle_capi.o"), [NVCC, "-c", cycc] + COMMON, [cycc] + hdrs),

@@ -27,7 +27,13 @@ namespace salp { int set_error(int code, const char *msg); }
 
 namespace {
 
-constexpr int kTileM = 128, kHid = 256, kK1 = 32, kMaxOut = 8, kMaxAct = 4, kThreads = 512;
+constexpr int kTileM = 128, kHid = 256, kK1 = 32, kMaxOut = 8, kMaxAct = 4;
+constexpr int kThreads = 512;  // 16 warps: TMEM lane quarter = warp % 4, column group = warp / 4
+// The MMAs are issued by lane 0 of ONE of the 16 warps.  Its issue of a whole GEMM 2 blocks for about the GEMM's duration
+// (the issue queue is short), so that warp is the slowest of every iteration; it is taken from column group 3 because
+// column group 0 also squashes and stores the actions.  (A 17th warp that only issues was measured slower: 544 threads
+// cap the kernel at 96 registers, and its MMAs paced at ~265 instead of ~155 cycles -- profiles/r01_ncu_actor.md.)
+constexpr int kIssueWarp = 12, kIssueTid = 32 * kIssueWarp;
 constexpr uint32_t kW2Bytes = kHid * kHid * 2, kW1Bytes = kHid * kK1 * 2, kA1Bytes = kTileM * kK1 * 2, kHBytes = kTileM * kHid * 2;
 constexpr uint32_t kOffW2 = 0, kOffW1 = kOffW2 + kW2Bytes, kOffA1 = kOffW1 + kW1Bytes, kOffH = kOffA1 + kA1Bytes;
 constexpr uint32_t kOffB1 = kOffH + kHBytes, kOffB2 = kOffB1 + kHid * 4, kOffW3 = kOffB2 + kHid * 4;
@@ -59,6 +65,19 @@ struct ActorArgs {
 
 enum { kModeActor = 0, kModeGailReward = 1 };
 
+#ifdef SALP_ACTOR_TRACE  // developer build (SALP_ACTOR_TRACE=1 python -m ...build): per-phase clocks of CTA 0, warps 0 and kIssueWarp
+constexpr int kTraceIters = 12, kTracePoints = 8;
+__device__ long long g_trace[2 * kTraceIters * kTracePoints + 8];  // + (clock, globaltimer) at entry / loop start / end
+__device__ __forceinline__ long long gtimer() { long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
+#define TRACE2(k) do { if (blockIdx.x == 0 && threadIdx.x == 0) { g_trace[2 * kTraceIters * kTracePoints + 2 * (k)] = clock64(); \
+    g_trace[2 * kTraceIters * kTracePoints + 2 * (k) + 1] = gtimer(); } } while (0)
+#define TRACE(pt) do { if (blockIdx.x == 0 && lane == 0 && (warp == 0 || warp == kIssueWarp) && it < kTraceIters) \
+    g_trace[((warp != 0) * kTraceIters + it) * kTracePoints + (pt)] = clock64(); } while (0)
+#else
+#define TRACE(pt) do { } while (0)
+#define TRACE2(k) do { } while (0)
+#endif
+
 // Philox4x32-10 (Salmon et al., SC'11): counter (row, draw), key = seed -> 4 x 32 random bits
 __device__ __forceinline__ uint4 philox4x32(uint4 c, uint2 k) {
 #pragma unroll
@@ -88,6 +107,19 @@ __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)_
 __device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t lbo) {
     return (uint64_t)((saddr & 0x3FFFFu) >> 4) | ((uint64_t)((lbo >> 4) & 0x3FFFu) << 16) | ((uint64_t)(128u >> 4) << 32) |
            ((uint64_t)1 << 46);
+}
+
+// The same for the 128-byte swizzled K-major layout GEMM 2 reads (the layout the tensor core fetches at full rate:
+// measured here, the no-swizzle layout above paces a 128 x 256 x 16 MMA at ~300 cycles instead of 128).  An operand
+// of R rows is cut into K blocks of 64 elements; a block is R rows of 128 bytes and the 16-byte chunk c of row r sits
+// at chunk position c ^ (r % 8).  sbo = 1024 (8 rows), layout type 2 (bits 61-63); the K = 16 steps inside a block
+// advance the start address by 32 bytes.
+__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t saddr) {
+    return (uint64_t)((saddr & 0x3FFFFu) >> 4) | ((uint64_t)1 << 16) | ((uint64_t)(1024u >> 4) << 32) | ((uint64_t)1 << 46) |
+           ((uint64_t)2 << 61);
+}
+__device__ __forceinline__ uint32_t sw128_offset(int rows, int row, int kchunk) {  // byte offset of 16-byte chunk kchunk of a row
+    return (uint32_t)((kchunk >> 3) * rows * 128 + row * 128 + (((kchunk & 7) ^ (row & 7)) << 4));
 }
 
 __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t accumulate) {
@@ -144,11 +176,41 @@ __device__ __forceinline__ void tmem_ld32_nowait(uint32_t taddr, uint32_t (&r)[3
         : "memory");
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+// four consecutive columns of this thread's TMEM lane
+__device__ __forceinline__ void tmem_st4(uint32_t taddr, float a, float b, float c, float d) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x4.b32 [%0], {%1, %2, %3, %4};" ::"r"(taddr), "r"(__float_as_uint(a)),
+                 "r"(__float_as_uint(b)), "r"(__float_as_uint(c)), "r"(__float_as_uint(d))
+                 : "memory");
+}
+__device__ __forceinline__ void tmem_ld4_nowait(uint32_t taddr, float &a, float &b, float &c, float &d) {
+    uint32_t x, y, z, w;
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(x), "=r"(y), "=r"(z), "=r"(w) : "r"(taddr) : "memory");
+    a = __uint_as_float(x); b = __uint_as_float(y); c = __uint_as_float(z); d = __uint_as_float(w);
+}
+// meeting point on named barrier ID where only the waiting warps block: the others arrive and go on
+template <int ID>
+__device__ __forceinline__ void cta_meet(bool wait) {
+    if (wait) asm volatile("bar.sync %0, %1;" ::"n"(ID), "n"(kThreads) : "memory");
+    else asm volatile("bar.arrive %0, %1;" ::"n"(ID), "n"(kThreads) : "memory");
+}
+__device__ __forceinline__ void quarter_meet(int quarter, bool wait) {  // the four warps that own the same 32 rows: IDs 1-4
+    if (wait) asm volatile("bar.sync %0, %1;" ::"r"(1 + quarter), "n"(kThreads / 4) : "memory");
+    else asm volatile("bar.arrive %0, %1;" ::"r"(1 + quarter), "n"(kThreads / 4) : "memory");
+}
 
 __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
     const __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
     return *reinterpret_cast<const uint32_t *>(&v);
 }
+
+// bf16x2 of (max(lo, 0), max(hi, 0)): the ReLU rides on the conversion
+__device__ __forceinline__ uint32_t pack_relu_bf16(float lo, float hi) {
+    uint32_t d;
+    asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi), "f"(lo));
+    return d;
+}
+__device__ __forceinline__ float2 u2f2(uint32_t a, uint32_t b) { return make_float2(__uint_as_float(a), __uint_as_float(b)); }
 
 // obs chunk (8 consecutive features) of one row, prefetched into registers one tile ahead
 struct ObsChunk { float4 lo, hi; };
@@ -189,17 +251,29 @@ __global__ void __launch_bounds__(kThreads, 1) salp_actor_kernel(const __grid_co
     const int erow = quarter * 32 + lane;            // row of the tile this thread owns in the epilogues
     const int lrow = tid & (kTileM - 1), lchunk = tid >> 7;  // (row, 8-feature chunk) this thread loads of the obs tile
     constexpr int n_out = NOUT;
+    TRACE2(0);
     float *s_b1 = reinterpret_cast<float *>(smem + kOffB1), *s_b2 = reinterpret_cast<float *>(smem + kOffB2);
     float *s_w3 = reinterpret_cast<float *>(smem + kOffW3), *s_b3 = reinterpret_cast<float *>(smem + kOffB3);
-    float *s_part = reinterpret_cast<float *>(smem + kOffH);  // epilogue-2 partial sums alias H (idle at that point)
     uint32_t *s_tmem = reinterpret_cast<uint32_t *>(smem + kOffTmem);
     const uint32_t bar1 = smem_u32(smem + kOffBar), bar2 = bar1 + 8;
 
     // ---- one-time: weights -> shared memory (already in operand layout), barriers, TMEM columns
     {
-        uint4 *d2 = reinterpret_cast<uint4 *>(smem + kOffW2), *d1 = reinterpret_cast<uint4 *>(smem + kOffW1);
-        for (int i = tid; i < (int)(kW2Bytes / 16); i += kThreads) d2[i] = a.w2p[i];
-        for (int i = tid; i < (int)(kW1Bytes / 16); i += kThreads) d1[i] = a.w1p[i];
+        uint4 *d1 = reinterpret_cast<uint4 *>(smem + kOffW1);
+        // all of a thread's loads are issued before its first store (the loops have 16 and 2 trips): one L2 round trip, not 18
+        static_assert(kW2Bytes / 16 % kThreads == 0 && kW1Bytes / 16 % kThreads == 0, "weight chunks per thread");
+        uint4 w2v[kW2Bytes / 16 / kThreads], w1v[kW1Bytes / 16 / kThreads];
+    #pragma unroll
+        for (int j = 0; j < (int)(kW2Bytes / 16 / kThreads); ++j) w2v[j] = a.w2p[tid + j * kThreads];
+    #pragma unroll
+        for (int j = 0; j < (int)(kW1Bytes / 16 / kThreads); ++j) w1v[j] = a.w1p[tid + j * kThreads];
+    #pragma unroll
+        for (int j = 0; j < (int)(kW2Bytes / 16 / kThreads); ++j) {  // [K/8][256] chunks -> swizzled K blocks
+            const int i = tid + j * kThreads;
+            *reinterpret_cast<uint4 *>(smem + kOffW2 + sw128_offset(kHid, i & (kHid - 1), i >> 8)) = w2v[j];
+        }
+    #pragma unroll
+        for (int j = 0; j < (int)(kW1Bytes / 16 / kThreads); ++j) d1[tid + j * kThreads] = w1v[j];
         for (int i = tid; i < kHid; i += kThreads) { s_b1[i] = a.b1[i]; s_b2[i] = a.b2[i]; }
         for (int i = tid; i < n_out * kHid; i += kThreads) s_w3[i] = i < a.w3_rows * kHid ? a.w3[i] : 0.f;
         if (tid < n_out) s_b3[tid] = tid < a.w3_rows ? a.b3[tid] : 0.f;
@@ -224,32 +298,169 @@ __global__ void __launch_bounds__(kThreads, 1) salp_actor_kernel(const __grid_co
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = *s_tmem;
-    const uint32_t acc2 = tmem, acc1 = tmem + kHid;  // GEMM 2 / GEMM 1 accumulators: 256 f32 columns each
     const uint32_t lane_base = (uint32_t)(quarter * 32) << 16;
-    auto issue_gemm1 = [&]() {  // acc1[128 x 256] = A1[128 x 32] . W1^T
+    // Two TMEM slots of 256 f32 columns.  Tile i lives in slot i & 1: GEMM 1 writes its pre-activations there, epilogue 1
+    // turns them into H, GEMM 2 then overwrites the same columns (the pre-activations are dead by then).
+    auto issue_gemm1 = [&](uint32_t slot) {  // slot[128 x 256] = A1[128 x 32] . W1^T
     #pragma unroll
         for (int kk = 0; kk < kK1 / 16; ++kk)
-            umma_bf16(acc1, umma_desc(sA1 + 2 * kk * kLboA, kLboA), umma_desc(sW1 + 2 * kk * kLboB, kLboB), kk > 0);
+            umma_bf16(slot, umma_desc(sA1 + 2 * kk * kLboA, kLboA), umma_desc(sW1 + 2 * kk * kLboB, kLboB), kk > 0);
         umma_commit(bar1);
     };
-    if (tid == 0) issue_gemm1();
-    ObsChunk nxt = load_obs_chunk(a, (tile + gridDim.x) * kTileM + lrow, lchunk);
     uint32_t phase1 = 0, phase2 = 0;
     const unsigned long long rng_seed = a.rng ? a.rng[0] : 0ull, rng_draw = a.rng ? a.rng[1] : 0ull;
+    constexpr int kOutRegs = NOUT < 4 ? 4 : NOUT;
 
-    for (; tile < n_tiles; tile += gridDim.x) {
-        const bool has_next = tile + gridDim.x < n_tiles;
-        // ---- GEMM 1 of this tile is done: A1 is free again -> next tile's observations go in
+    auto issue_gemm2 = [&](uint32_t slot) {  // slot[128 x 256] = H[128 x 256] . W2^T
+    #pragma unroll
+        for (int kk = 0; kk < kHid / 16; ++kk)
+            umma_bf16(slot, umma_desc_sw128(sH + (kk >> 2) * (kTileM * 128) + (kk & 3) * 32),
+                      umma_desc_sw128(sW2 + (kk >> 2) * (kHid * 128) + (kk & 3) * 32), kk > 0);
+        umma_commit(bar2);
+    };
+    // ---- epilogue 2, first part: h2 = relu(slot + b2); partial dot products with the 2*act rows of W3 over this warp's 64
+    //      columns; the four warps that own the same 32 rows meet in TMEM (each thread parks its partial sums in the first
+    //      columns it has just read -- shared memory has no room left and H is being read by the next tile's GEMM 2);
+    //      column group 0 leaves with the row totals in o8.
+    auto epilogue2_sums = [&](uint32_t slot, float (&o8)[kOutRegs]) {
+        float out[kOutRegs];
+    #pragma unroll
+        for (int j = 0; j < kOutRegs; ++j) out[j] = 0.f;
+        const int colg = cgroup * 64;
+        {
+            uint32_t r[2][32];
+            tmem_ld32_nowait(slot + lane_base + colg, r[0]);
+            tmem_ld32_nowait(slot + lane_base + colg + 32, r[1]);
+            tmem_ld_wait();
+            float2 acc[NOUT];  // packed f32x2 accumulators (even, odd columns), folded at the end
+    #pragma unroll
+            for (int o = 0; o < NOUT; ++o) acc[o] = make_float2(0.f, 0.f);
+    #pragma unroll
+            for (int i = 0; i < 2; ++i) {
+    #pragma unroll
+                for (int c = 0; c < 8; ++c) {
+                    const int col = colg + 32 * i + 4 * c;
+                    const float4 b = *reinterpret_cast<const float4 *>(s_b2 + col);
+                    const uint32_t *q = &r[i][4 * c];
+                    float2 h01 = __fadd2_rn(u2f2(q[0], q[1]), make_float2(b.x, b.y)), h23 = __fadd2_rn(u2f2(q[2], q[3]), make_float2(b.z, b.w));
+                    h01.x = fmaxf(h01.x, 0.f); h01.y = fmaxf(h01.y, 0.f); h23.x = fmaxf(h23.x, 0.f); h23.y = fmaxf(h23.y, 0.f);
+    #pragma unroll
+                    for (int o = 0; o < NOUT; ++o) {
+                        const float4 w = *reinterpret_cast<const float4 *>(s_w3 + o * kHid + col);
+                        acc[o] = __ffma2_rn(h01, make_float2(w.x, w.y), acc[o]);
+                        acc[o] = __ffma2_rn(h23, make_float2(w.z, w.w), acc[o]);
+                    }
+                }
+            }
+    #pragma unroll
+            for (int o = 0; o < NOUT; ++o) out[o] = acc[o].x + acc[o].y;
+        }
+        if (cgroup != 0) {
+            tmem_st4(slot + lane_base + colg, out[0], out[1], out[2], out[3]);
+            if constexpr (NOUT > 4) tmem_st4(slot + lane_base + colg + 4, out[4], out[5], out[6], out[7]);
+            tmem_st_wait();
+        }
+        tc_fence_before();
+        quarter_meet(quarter, cgroup == 0);  // only column group 0 reads the others' sums: the others arrive and go on
+        tc_fence_after();
+    #pragma unroll
+        for (int j = 0; j < kOutRegs; ++j) o8[j] = out[j];
+        if (cgroup == 0) {
+            float u[3][kOutRegs];
+    #pragma unroll
+            for (int g = 1; g < kThreads / kTileM; ++g) {
+                tmem_ld4_nowait(slot + lane_base + 64 * g, u[g - 1][0], u[g - 1][1], u[g - 1][2], u[g - 1][3]);
+                if constexpr (NOUT > 4) tmem_ld4_nowait(slot + lane_base + 64 * g + 4, u[g - 1][4], u[g - 1][5], u[g - 1][6], u[g - 1][7]);
+            }
+            tmem_ld_wait();
+    #pragma unroll
+            for (int g = 0; g < 3; ++g)
+    #pragma unroll
+                for (int j = 0; j < kOutRegs; ++j) o8[j] += u[g][j];
+        }
+    };
+    // ---- epilogue 2, second part (column group 0 only): squash and store the row's actions / reward
+    // the row's standard-normal draws, fetched (or drawn) before epilogue 2 so that their latency hides behind it
+    auto draw_noise = [&](long long row, float (&z)[kMaxAct]) {
+    #pragma unroll
+        for (int d = 0; d < kMaxAct; ++d) z[d] = 0.f;
+        if (a.mode != kModeActor || row >= a.n) return;
+        if (a.noise) {
+    #pragma unroll
+            for (int d = 0; d < kMaxAct; ++d)
+                if (d < a.act_dim) z[d] = a.noise[row * a.act_dim + d];
+        } else if (a.rng) {
+            const uint4 rnd = philox4x32(make_uint4((uint32_t)row, (uint32_t)(row >> 32), (uint32_t)rng_draw, (uint32_t)(rng_draw >> 32)),
+                                         make_uint2((uint32_t)rng_seed, (uint32_t)(rng_seed >> 32)));
+            const float2 z01 = normal_pair(rnd.x, rnd.y);
+            z[0] = z01.x; z[1] = z01.y;
+            if (a.act_dim > 2) { const float2 z23 = normal_pair(rnd.z, rnd.w); z[2] = z23.x; z[3] = z23.y; }
+        }
+    };
+    auto epilogue2_store = [&](long long row, const float (&o8)[kOutRegs], const float (&z)[kMaxAct]) {
+        if (row >= a.n) return;
+        auto pick = [&](int idx) {  // o8[idx] without a local-memory array
+            float v = o8[0];
+    #pragma unroll
+            for (int j = 1; j < kOutRegs; ++j) v = idx == j ? o8[j] : v;
+            return v;
+        };
+        if (a.mode == kModeGailReward) {
+            // D = sigmoid(logit); reward = -log(1 - D + 1e-8)   (src/salp/agents/discriminator.py:59-82)
+            const float d = 1.f / (1.f + __expf(-(o8[0] + s_b3[0])));
+            reinterpret_cast<float *>(a.actions)[row] = -__logf(1.f - d + 1e-8f);
+        } else {
+            const bool sample = a.noise != nullptr || a.rng != nullptr;
+    #pragma unroll
+            for (int d = 0; d < kMaxAct; ++d) {
+                if (d >= a.act_dim || 2 * d >= NOUT) break;
+                const float mean = o8[d] + s_b3[d];
+                float pre = mean;
+                if (sample) {
+                    const float log_std = fminf(fmaxf(pick(a.act_dim + d) + s_b3[a.act_dim + d], -20.f), 2.f);
+                    pre = fmaf(__expf(log_std), z[d], mean);
+                }
+                // tanh(x) = 1 - 2 / (exp(2x) + 1): absolute error ~2e-7, no branches (exp overflow -> 1, underflow -> -1)
+                const float th = 1.f - __fdividef(2.f, __expf(2.f * pre) + 1.f);
+                const float act = fmaf(th, a.act_scale[d], a.act_shift[d]);
+                if (a.f64) reinterpret_cast<double *>(a.actions)[row * a.act_dim + d] = (double)act;
+                else reinterpret_cast<float *>(a.actions)[row * a.act_dim + d] = act;
+            }
+        }
+    };
+
+    // Per iteration the warps run  epilogue 1 (tile i)  ->  epilogue 2 (tile i-1)  while the tensor core runs GEMM 2 (tile i)
+    // behind epilogue 1 and GEMM 1 (tile i+1) behind epilogue 2: epilogue 2, the longer of the two, overlaps GEMM 2 of the
+    // following tile, and one H buffer is enough because epilogue 1 (tile i+1) starts only when GEMM 2 (tile i) has finished
+    // reading it.  The issuing warp does its share of epilogue 2 FIRST (alone, while the others are in epilogue 1), because
+    // after the meeting point its lane 0 sits in the MMA issue for the length of GEMM 2.  The two CTA-wide meeting points are
+    // arrive/sync pairs on named barriers: only the issuing warp waits, the others arrive and go on to their next epilogue.
+    long long prev_tile = -1;
+    uint32_t it = 0;
+    TRACE2(1);
+    if (tid == kIssueTid) issue_gemm1(tmem);
+    ObsChunk nxt = load_obs_chunk(a, (tile + gridDim.x) * kTileM + lrow, lchunk);
+    for (; tile < n_tiles; tile += gridDim.x, ++it) {
+        const bool has_next = tile + gridDim.x < n_tiles, has_prev = prev_tile >= 0;
+        const uint32_t slot = tmem + (it & 1) * kHid, slot_prev = tmem + ((it & 1) ^ 1) * kHid;
+        float o8[kOutRegs], z[kMaxAct];
+        // ---- GEMM 1 of this tile is done (A1 is free: the next tile's observations go in); GEMM 2 of the previous tile
+        //      is done (H is free, its output waits in the other slot)
+        TRACE(0);
         mbar_wait(bar1, phase1);
         phase1 ^= 1;
+        if (has_prev) { mbar_wait(bar2, phase2); phase2 ^= 1; }
         tc_fence_after();
+        TRACE(1);
+        if (has_prev && warp == kIssueWarp) epilogue2_sums(slot_prev, o8);
+        TRACE(2);
         if (has_next) store_obs_chunk(nxt);
-        // ---- epilogue 1: h1 = relu(acc1 + b1) -> bf16 -> H (canonical A layout of GEMM 2); 64 columns per thread
+        // ---- epilogue 1: h1 = relu(slot + b1) -> bf16 -> H (swizzled A layout of GEMM 2); 64 columns per thread
         {
             uint32_t r[2][32];
             const int colg = cgroup * 64;
-            tmem_ld32_nowait(acc1 + lane_base + colg, r[0]);
-            tmem_ld32_nowait(acc1 + lane_base + colg + 32, r[1]);
+            tmem_ld32_nowait(slot + lane_base + colg, r[0]);
+            tmem_ld32_nowait(slot + lane_base + colg + 32, r[1]);
             tmem_ld_wait();
     #pragma unroll
             for (int i = 0; i < 2; ++i) {
@@ -258,126 +469,44 @@ __global__ void __launch_bounds__(kThreads, 1) salp_actor_kernel(const __grid_co
                     const float4 ba = *reinterpret_cast<const float4 *>(s_b1 + colg + 32 * i + 8 * c);
                     const float4 bb = *reinterpret_cast<const float4 *>(s_b1 + colg + 32 * i + 8 * c + 4);
                     const uint32_t *q = &r[i][8 * c];
-                    const float h0 = fmaxf(__uint_as_float(q[0]) + ba.x, 0.f), h1 = fmaxf(__uint_as_float(q[1]) + ba.y, 0.f);
-                    const float h2 = fmaxf(__uint_as_float(q[2]) + ba.z, 0.f), h3 = fmaxf(__uint_as_float(q[3]) + ba.w, 0.f);
-                    const float h4 = fmaxf(__uint_as_float(q[4]) + bb.x, 0.f), h5 = fmaxf(__uint_as_float(q[5]) + bb.y, 0.f);
-                    const float h6 = fmaxf(__uint_as_float(q[6]) + bb.z, 0.f), h7 = fmaxf(__uint_as_float(q[7]) + bb.w, 0.f);
-                    *reinterpret_cast<uint4 *>(smem + kOffH + ((colg + 32 * i) / 8 + c) * kLboA + erow * 16) =
-                        make_uint4(pack_bf16(h0, h1), pack_bf16(h2, h3), pack_bf16(h4, h5), pack_bf16(h6, h7));
+                    // packed f32x2 adds (FADD2) and the ReLU folded into the bf16x2 conversion: one issue slot per element
+                    const float2 x01 = __fadd2_rn(u2f2(q[0], q[1]), make_float2(ba.x, ba.y)), x23 = __fadd2_rn(u2f2(q[2], q[3]), make_float2(ba.z, ba.w));
+                    const float2 x45 = __fadd2_rn(u2f2(q[4], q[5]), make_float2(bb.x, bb.y)), x67 = __fadd2_rn(u2f2(q[6], q[7]), make_float2(bb.z, bb.w));
+                    *reinterpret_cast<uint4 *>(smem + kOffH + sw128_offset(kTileM, erow, (colg + 32 * i) / 8 + c)) =
+                        make_uint4(pack_relu_bf16(x01.x, x01.y), pack_relu_bf16(x23.x, x23.y), pack_relu_bf16(x45.x, x45.y), pack_relu_bf16(x67.x, x67.y));
                 }
             }
         }
         fence_async_smem();
-        tc_fence_before();   // this tile's reads of acc1 and the previous tile's reads of acc2 are complete
-        __syncthreads();
-        // ---- GEMM 2 of this tile, then GEMM 1 of the next one right behind it (it overlaps epilogue 2)
-        if (tid == 0) {
-            tc_fence_after();
-    #pragma unroll
-            for (int kk = 0; kk < kHid / 16; ++kk)
-                umma_bf16(acc2, umma_desc(sH + 2 * kk * kLboA, kLboA), umma_desc(sW2 + 2 * kk * kLboB, kLboB), kk > 0);
-            umma_commit(bar2);
-            if (has_next) issue_gemm1();
-        }
+        tc_fence_before();   // this tile's reads of its slot are complete
+        TRACE(3);
+        cta_meet<5>(warp == kIssueWarp);
+        if (tid == kIssueTid) { tc_fence_after(); issue_gemm2(slot); }  // GEMM 2 of this tile over its own slot
+        __syncwarp();
+        TRACE(4);
         if (has_next) nxt = load_obs_chunk(a, (tile + 2 * (long long)gridDim.x) * kTileM + lrow, lchunk);
-        mbar_wait(bar2, phase2);
-        phase2 ^= 1;
-        tc_fence_after();
-        // ---- epilogue 2: h2 = relu(acc2 + b2); partial dot products with the 2*act rows of W3 over 64 columns
-        constexpr int kOutRegs = NOUT < 4 ? 4 : NOUT;
-        float out[kOutRegs];
-    #pragma unroll
-        for (int j = 0; j < kOutRegs; ++j) out[j] = 0.f;
-        {
-            uint32_t r[2][32];
-            const int colg = cgroup * 64;
-            tmem_ld32_nowait(acc2 + lane_base + colg, r[0]);
-            tmem_ld32_nowait(acc2 + lane_base + colg + 32, r[1]);
-            tmem_ld_wait();
-    #pragma unroll
-            for (int i = 0; i < 2; ++i) {
-    #pragma unroll
-                for (int c = 0; c < 8; ++c) {
-                    const int col = colg + 32 * i + 4 * c;
-                    const float4 b = *reinterpret_cast<const float4 *>(s_b2 + col);
-                    const uint32_t *q = &r[i][4 * c];
-                    const float h0 = fmaxf(__uint_as_float(q[0]) + b.x, 0.f), h1 = fmaxf(__uint_as_float(q[1]) + b.y, 0.f);
-                    const float h2 = fmaxf(__uint_as_float(q[2]) + b.z, 0.f), h3 = fmaxf(__uint_as_float(q[3]) + b.w, 0.f);
-    #pragma unroll
-                    for (int o = 0; o < NOUT; ++o) {
-                        const float4 w = *reinterpret_cast<const float4 *>(s_w3 + o * kHid + col);
-                        out[o] = fmaf(h0, w.x, fmaf(h1, w.y, fmaf(h2, w.z, fmaf(h3, w.w, out[o]))));
-                    }
-                }
-            }
-        }
-        // H is idle (GEMM 2 has completed): the four column groups meet there
-        *reinterpret_cast<float4 *>(s_part + (cgroup * kTileM + erow) * 4) = make_float4(out[0], out[1], out[2], out[3]);
-        if constexpr (NOUT > 4)  // outputs 4-7 of (column group g, row r) go to H chunk 4 + g of row r
-            *reinterpret_cast<float4 *>(s_part + ((4 + cgroup) * kTileM + erow) * 4) = make_float4(out[4], out[5], out[6], out[7]);
-        // only the four warps that share this quarter of the rows exchange partial sums: a 128-thread named barrier
-        asm volatile("bar.sync %0, %1;" ::"r"(1 + quarter), "r"(kThreads / 4) : "memory");
-        const long long row = tile * kTileM + erow;
-        if (cgroup == 0 && row < a.n) {
-            float4 t = *reinterpret_cast<const float4 *>(s_part + erow * 4);
-    #pragma unroll
-            for (int g = 1; g < kThreads / kTileM; ++g) {
-                const float4 u = *reinterpret_cast<const float4 *>(s_part + (g * kTileM + erow) * 4);
-                t.x += u.x; t.y += u.y; t.z += u.z; t.w += u.w;
-            }
-            float o8[kOutRegs] = {t.x, t.y, t.z, t.w};
-            if constexpr (NOUT > 4) {
-                float4 t2 = *reinterpret_cast<const float4 *>(s_part + (4 * kTileM + erow) * 4);
-    #pragma unroll
-                for (int g = 1; g < kThreads / kTileM; ++g) {
-                    const float4 u = *reinterpret_cast<const float4 *>(s_part + ((4 + g) * kTileM + erow) * 4);
-                    t2.x += u.x; t2.y += u.y; t2.z += u.z; t2.w += u.w;
-                }
-                o8[4] = t2.x; o8[5] = t2.y; o8[6] = t2.z; o8[7] = t2.w;
-            }
-            auto pick = [&](int idx) {  // o8[idx] without a local-memory array
-                float v = o8[0];
-    #pragma unroll
-                for (int j = 1; j < kOutRegs; ++j) v = idx == j ? o8[j] : v;
-                return v;
-            };
-            if (a.mode == kModeGailReward) {
-                // D = sigmoid(logit); reward = -log(1 - D + 1e-8)   (src/salp/agents/discriminator.py:59-82)
-                const float d = 1.f / (1.f + __expf(-(o8[0] + s_b3[0])));
-                reinterpret_cast<float *>(a.actions)[row] = -__logf(1.f - d + 1e-8f);
-            } else {
-                float z[kMaxAct] = {0.f, 0.f, 0.f, 0.f};
-                const bool sample = a.noise != nullptr || a.rng != nullptr;
-                if (a.noise) {
-    #pragma unroll
-                    for (int d = 0; d < kMaxAct; ++d)
-                        if (d < a.act_dim) z[d] = a.noise[row * a.act_dim + d];
-                } else if (a.rng) {
-                    const uint4 rnd = philox4x32(make_uint4((uint32_t)row, (uint32_t)(row >> 32), (uint32_t)rng_draw, (uint32_t)(rng_draw >> 32)),
-                                                 make_uint2((uint32_t)rng_seed, (uint32_t)(rng_seed >> 32)));
-                    const float2 z01 = normal_pair(rnd.x, rnd.y);
-                    z[0] = z01.x; z[1] = z01.y;
-                    if (a.act_dim > 2) { const float2 z23 = normal_pair(rnd.z, rnd.w); z[2] = z23.x; z[3] = z23.y; }
-                }
-    #pragma unroll
-                for (int d = 0; d < kMaxAct; ++d) {
-                    if (d >= a.act_dim || 2 * d >= NOUT) break;
-                    const float mean = o8[d] + s_b3[d];
-                    float pre = mean;
-                    if (sample) {
-                        const float log_std = fminf(fmaxf(pick(a.act_dim + d) + s_b3[a.act_dim + d], -20.f), 2.f);
-                        pre = fmaf(__expf(log_std), z[d], mean);
-                    }
-                    const float act = fmaf(tanhf(pre), a.act_scale[d], a.act_shift[d]);
-                    if (a.f64) reinterpret_cast<double *>(a.actions)[row * a.act_dim + d] = (double)act;
-                    else reinterpret_cast<float *>(a.actions)[row * a.act_dim + d] = act;
-                }
-            }
-        }
-        // No barrier here: the partial sums of row r live in H chunks 0-3 of row r, which epilogue 1 of the next tile
-        // rewrites from the very thread that has just read them (column group 0 of that row); every other reuse of H,
-        // acc1 and acc2 is ordered by the CTA-wide barrier after epilogue 1.
+        // ---- epilogue 2 of the previous tile (other slot) while GEMM 2 of this one runs
+        if (has_prev && cgroup == 0) draw_noise(prev_tile * kTileM + erow, z);
+        if (has_prev && warp != kIssueWarp) epilogue2_sums(slot_prev, o8);
+        tc_fence_before();   // every read of the other slot is complete
+        TRACE(5);
+        cta_meet<6>(warp == kIssueWarp);
+        if (tid == kIssueTid && has_next) { tc_fence_after(); issue_gemm1(slot_prev); }  // GEMM 1 of the next tile goes there
+        __syncwarp();
+        if (has_prev && cgroup == 0) epilogue2_store(prev_tile * kTileM + erow, o8, z);
+        TRACE(6);
+        prev_tile = tile;
     }
+    // ---- drain: epilogue 2 of this CTA's last tile
+    {
+        mbar_wait(bar2, phase2);
+        tc_fence_after();
+        float o8[kOutRegs], z[kMaxAct];
+        if (cgroup == 0) draw_noise(prev_tile * kTileM + erow, z);
+        epilogue2_sums(tmem + ((it & 1) ^ 1) * kHid, o8);
+        if (cgroup == 0) epilogue2_store(prev_tile * kTileM + erow, o8, z);
+    }
+    TRACE2(2);
     // ---- teardown: every thread's TMEM reads are done before the columns are released; the last CTA to get
     //      here (every CTA read the draw counter at its start) advances the counter for the next launch
     tc_fence_before();
@@ -392,6 +521,12 @@ __global__ void __launch_bounds__(kThreads, 1) salp_actor_kernel(const __grid_co
 }
 
 }  // namespace
+
+#ifdef SALP_ACTOR_TRACE
+extern "C" int salp_actor_trace_read(long long *host_out) {
+    return (int)cudaMemcpyFromSymbol(host_out, g_trace, sizeof(long long) * (2 * kTraceIters * kTracePoints + 8));
+}
+#endif
 
 extern "C" int salp_actor_forward(const SalpActorForward *p, void *cuda_stream) {
     if (!p) return salp::set_error(SALP_EINVAL, "null argument");
