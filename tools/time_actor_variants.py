@@ -2,7 +2,7 @@
 and repeated so that box-to-box and clock drift show up as spread rather than as a difference between variants."""
 import glob, os, subprocess, sys
 root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-libs = sorted(glob.glob(os.path.join(root, "tools", "_lab", "libsalp_*.so")))
+libs = [l for l in sorted(glob.glob(os.path.join(root, "tools", "_lab", "libsalp_*.so"))) if "libsalp_t_" not in l]  # t_ = trace builds
 code = r'''
 import os, sys, torch
 sys.path.insert(0, %r)
