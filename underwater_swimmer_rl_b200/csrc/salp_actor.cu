@@ -557,12 +557,22 @@ extern "C" int salp_actor_forward(const SalpActorForward *p, void *cuda_stream) 
     }
     if (p->mode == kModeGailReward) { a.noise = nullptr; a.rng = nullptr; }
     auto kern = a.w3_rows <= 2 ? salp_actor_kernel<2> : a.w3_rows <= 4 ? salp_actor_kernel<4> : salp_actor_kernel<8>;
-    {   // per device and cheap: set on every call rather than caching a per-process flag
+    // per device, once: the shared-memory opt-in of this instantiation and the SM count (the eager launch path is host-bound
+    // for a kernel this short; racing first calls do the same idempotent work)
+    constexpr int kMaxDev = 64;
+    static bool attr_set[3][kMaxDev];
+    static int sm_count[kMaxDev];
+    int dev = 0, sms = 148;
+    if (cudaGetDevice(&dev) != cudaSuccess) return salp::set_error(SALP_ECUDA, "cudaGetDevice failed");
+    const int ki = a.w3_rows <= 2 ? 0 : a.w3_rows <= 4 ? 1 : 2;
+    const bool cached = dev >= 0 && dev < kMaxDev;
+    if (!cached || !attr_set[ki][dev]) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
         if (e != cudaSuccess) return salp::set_error(SALP_ECUDA, cudaGetErrorString(e));
+        if (cached) attr_set[ki][dev] = true;
     }
-    int dev = 0, sms = 148;
-    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (cached && sm_count[dev] > 0) sms = sm_count[dev];
+    else if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && cached) sm_count[dev] = sms;
     const long long n_tiles = (a.n + kTileM - 1) / kTileM;
     const unsigned grid = (unsigned)(n_tiles < sms ? n_tiles : sms);  // persistent: one CTA per SM
     kern<<<grid, kThreads, kSmemBytes, (cudaStream_t)cuda_stream>>>(a);
