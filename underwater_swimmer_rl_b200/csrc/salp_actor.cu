@@ -33,13 +33,15 @@ constexpr int kThreads = 512;  // 16 warps: TMEM lane quarter = warp % 4, column
 // (the issue queue is short), so that warp is the slowest of every iteration; it is taken from column group 3 because
 // column group 0 also squashes and stores the actions.  (A 17th warp that only issues was measured slower: 544 threads
 // cap the kernel at 96 registers, and its MMAs paced at ~265 instead of ~155 cycles -- profiles/r01_ncu_actor.md.)
-constexpr int kIssueWarp = 12, kIssueTid = 32 * kIssueWarp;
+constexpr int kIssueWarp = 12, kIssueTid = 32 * kIssueWarp, kIssueQuarter = kIssueWarp & 3, kIssueGroup = kIssueWarp >> 2;
+static_assert(kIssueGroup != 0, "the issuing warp must not be one that stores the actions");
 constexpr uint32_t kW2Bytes = kHid * kHid * 2, kW1Bytes = kHid * kK1 * 2, kA1Bytes = kTileM * kK1 * 2, kHBytes = kTileM * kHid * 2;
 constexpr uint32_t kOffW2 = 0, kOffW1 = kOffW2 + kW2Bytes, kOffA1 = kOffW1 + kW1Bytes, kOffH = kOffA1 + kA1Bytes;
 constexpr uint32_t kOffB1 = kOffH + kHBytes, kOffB2 = kOffB1 + kHid * 4, kOffW3 = kOffB2 + kHid * 4;
 constexpr uint32_t kOffB3 = kOffW3 + kMaxOut * kHid * 4, kOffBar = kOffB3 + kMaxOut * 4, kOffTmem = kOffBar + 16;
-static_assert(kOffTmem + 8 <= 227 * 1024, "shared memory of one CTA");
-constexpr uint32_t kSmemBytes = kOffTmem + 8;
+constexpr uint32_t kOffIss = (kOffTmem + 8 + 15) / 16 * 16;  // the issuing warp's output sums: 32 rows x 16 bytes
+static_assert(kOffIss + 32 * 16 <= 227 * 1024, "shared memory of one CTA");
+constexpr uint32_t kSmemBytes = kOffIss + 32 * 16;
 static_assert(kSmemBytes <= 232448, "shared memory budget of one sm_100 CTA");
 constexpr uint32_t kTmemCols = 512;  // two 128 x 256 f32 accumulators
 
@@ -194,9 +196,10 @@ __device__ __forceinline__ void cta_meet(bool wait) {
     if (wait) asm volatile("bar.sync %0, %1;" ::"n"(ID), "n"(kThreads) : "memory");
     else asm volatile("bar.arrive %0, %1;" ::"n"(ID), "n"(kThreads) : "memory");
 }
-__device__ __forceinline__ void quarter_meet(int quarter, bool wait) {  // the four warps that own the same 32 rows: IDs 1-4
-    if (wait) asm volatile("bar.sync %0, %1;" ::"r"(1 + quarter), "n"(kThreads / 4) : "memory");
-    else asm volatile("bar.arrive %0, %1;" ::"r"(1 + quarter), "n"(kThreads / 4) : "memory");
+// the four warps that own the same 32 rows: named barriers base + quarter (base 1: sums written, base 8: sums consumed)
+__device__ __forceinline__ void quarter_meet(int base, int quarter, bool wait) {
+    if (wait) asm volatile("bar.sync %0, %1;" ::"r"(base + quarter), "n"(kThreads / 4) : "memory");
+    else asm volatile("bar.arrive %0, %1;" ::"r"(base + quarter), "n"(kThreads / 4) : "memory");
 }
 
 __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
@@ -322,46 +325,52 @@ __global__ void __launch_bounds__(kThreads, 1) salp_actor_kernel(const __grid_co
     //      columns; the four warps that own the same 32 rows meet in TMEM (each thread parks its partial sums in the first
     //      columns it has just read -- shared memory has no room left and H is being read by the next tile's GEMM 2);
     //      column group 0 leaves with the row totals in o8.
-    auto epilogue2_sums = [&](uint32_t slot, float (&o8)[kOutRegs]) {
-        float out[kOutRegs];
+    // With at most 4 output rows the sums can meet in 16 bytes per (column group, row): they go through the A1 buffer, which
+    // frees the other TMEM slot as soon as every warp has LOADED its part of it -- GEMM 1 of the next tile is then issued
+    // right behind GEMM 2 instead of after epilogue 2 (kEarlyG1).  8 output rows keep the exchange in TMEM.
+    constexpr bool kEarlyG1 = NOUT <= 4;
+    auto epilogue2_math = [&](uint32_t slot, float (&out)[kOutRegs], bool announce) {
     #pragma unroll
         for (int j = 0; j < kOutRegs; ++j) out[j] = 0.f;
         const int colg = cgroup * 64;
-        {
-            uint32_t r[2][32];
-            tmem_ld32_nowait(slot + lane_base + colg, r[0]);
-            tmem_ld32_nowait(slot + lane_base + colg + 32, r[1]);
-            tmem_ld_wait();
-            float2 acc[NOUT];  // packed f32x2 accumulators (even, odd columns), folded at the end
+        uint32_t r[2][32];
+        tmem_ld32_nowait(slot + lane_base + colg, r[0]);
+        tmem_ld32_nowait(slot + lane_base + colg + 32, r[1]);
+        tmem_ld_wait();
+        if (announce) { tc_fence_before(); cta_meet<7>(false); }  // this warp's part of the slot is in registers
+        float2 acc[NOUT];  // packed f32x2 accumulators (even, odd columns), folded at the end
     #pragma unroll
-            for (int o = 0; o < NOUT; ++o) acc[o] = make_float2(0.f, 0.f);
+        for (int o = 0; o < NOUT; ++o) acc[o] = make_float2(0.f, 0.f);
     #pragma unroll
-            for (int i = 0; i < 2; ++i) {
+        for (int i = 0; i < 2; ++i) {
     #pragma unroll
-                for (int c = 0; c < 8; ++c) {
-                    const int col = colg + 32 * i + 4 * c;
-                    const float4 b = *reinterpret_cast<const float4 *>(s_b2 + col);
-                    const uint32_t *q = &r[i][4 * c];
-                    float2 h01 = __fadd2_rn(u2f2(q[0], q[1]), make_float2(b.x, b.y)), h23 = __fadd2_rn(u2f2(q[2], q[3]), make_float2(b.z, b.w));
-                    h01.x = fmaxf(h01.x, 0.f); h01.y = fmaxf(h01.y, 0.f); h23.x = fmaxf(h23.x, 0.f); h23.y = fmaxf(h23.y, 0.f);
+            for (int c = 0; c < 8; ++c) {
+                const int col = colg + 32 * i + 4 * c;
+                const float4 b = *reinterpret_cast<const float4 *>(s_b2 + col);
+                const uint32_t *q = &r[i][4 * c];
+                float2 h01 = __fadd2_rn(u2f2(q[0], q[1]), make_float2(b.x, b.y)), h23 = __fadd2_rn(u2f2(q[2], q[3]), make_float2(b.z, b.w));
+                h01.x = fmaxf(h01.x, 0.f); h01.y = fmaxf(h01.y, 0.f); h23.x = fmaxf(h23.x, 0.f); h23.y = fmaxf(h23.y, 0.f);
     #pragma unroll
-                    for (int o = 0; o < NOUT; ++o) {
-                        const float4 w = *reinterpret_cast<const float4 *>(s_w3 + o * kHid + col);
-                        acc[o] = __ffma2_rn(h01, make_float2(w.x, w.y), acc[o]);
-                        acc[o] = __ffma2_rn(h23, make_float2(w.z, w.w), acc[o]);
-                    }
+                for (int o = 0; o < NOUT; ++o) {
+                    const float4 w = *reinterpret_cast<const float4 *>(s_w3 + o * kHid + col);
+                    acc[o] = __ffma2_rn(h01, make_float2(w.x, w.y), acc[o]);
+                    acc[o] = __ffma2_rn(h23, make_float2(w.z, w.w), acc[o]);
                 }
             }
-    #pragma unroll
-            for (int o = 0; o < NOUT; ++o) out[o] = acc[o].x + acc[o].y;
         }
-        if (cgroup != 0) {
+    #pragma unroll
+        for (int o = 0; o < NOUT; ++o) out[o] = acc[o].x + acc[o].y;
+    };
+    // the four column groups of a row meet: column group 0 leaves with the row totals in o8
+    auto exchange_tmem = [&](uint32_t slot, const float (&out)[kOutRegs], float (&o8)[kOutRegs]) {
+        const int colg = cgroup * 64;
+        if (cgroup != 0) {  // parked in the first columns this thread has just read
             tmem_st4(slot + lane_base + colg, out[0], out[1], out[2], out[3]);
             if constexpr (NOUT > 4) tmem_st4(slot + lane_base + colg + 4, out[4], out[5], out[6], out[7]);
             tmem_st_wait();
         }
         tc_fence_before();
-        quarter_meet(quarter, cgroup == 0);  // only column group 0 reads the others' sums: the others arrive and go on
+        quarter_meet(1, quarter, cgroup == 0);  // only column group 0 reads the others' sums: the others arrive and go on
         tc_fence_after();
     #pragma unroll
         for (int j = 0; j < kOutRegs; ++j) o8[j] = out[j];
@@ -379,7 +388,32 @@ __global__ void __launch_bounds__(kThreads, 1) salp_actor_kernel(const __grid_co
                 for (int j = 0; j < kOutRegs; ++j) o8[j] += u[g][j];
         }
     };
-    // ---- epilogue 2, second part (column group 0 only): squash and store the row's actions / reward
+    // kEarlyG1: through A1 (idle between GEMM 1 of the next tile and the observation store of the one after): the sums of
+    // (column group g, row r) take the 16 bytes of chunk g of row r -- exactly what the same thread stores there next.
+    // `more` = another exchange or observation store follows: column group 0 then reports when it has read the sums.
+    // The issuing warp has a 512-byte buffer of its own: it computes its sums a whole phase earlier than the others and
+    // must not wait for A1 (that is, for GEMM 1 of the next tile) on its way back into the MMA issue.
+    float4 *s_iss = reinterpret_cast<float4 *>(smem + kOffIss);
+    auto issuer_publish = [&](const float (&out)[kOutRegs]) {
+        s_iss[lane] = make_float4(out[0], out[1], out[2], out[3]);
+        __threadfence_block();
+        quarter_meet(1, quarter, false);
+    };
+    auto exchange_smem = [&](const float (&out)[kOutRegs], float (&o8)[kOutRegs], bool more) {
+        float4 *sc = reinterpret_cast<float4 *>(smem + kOffA1);
+        if (cgroup != 0) { sc[cgroup * kTileM + erow] = make_float4(out[0], out[1], out[2], out[3]); __threadfence_block(); }
+        quarter_meet(1, quarter, cgroup == 0);
+    #pragma unroll
+        for (int j = 0; j < kOutRegs; ++j) o8[j] = out[j];
+        if (cgroup == 0) {
+    #pragma unroll
+            for (int g = 1; g < kThreads / kTileM; ++g) {
+                const float4 u = (quarter == kIssueQuarter && g == kIssueGroup) ? s_iss[lane] : sc[g * kTileM + erow];
+                o8[0] += u.x; o8[1] += u.y; o8[2] += u.z; o8[3] += u.w;
+            }
+            if (more) quarter_meet(8, quarter, false);
+        }
+    };
     // the row's standard-normal draws, fetched (or drawn) before epilogue 2 so that their latency hides behind it
     auto draw_noise = [&](long long row, float (&z)[kMaxAct]) {
     #pragma unroll
@@ -437,23 +471,35 @@ __global__ void __launch_bounds__(kThreads, 1) salp_actor_kernel(const __grid_co
     // arrive/sync pairs on named barriers: only the issuing warp waits, the others arrive and go on to their next epilogue.
     long long prev_tile = -1;
     uint32_t it = 0;
+    bool sums_in_a1 = false;  // kEarlyG1: the last exchange's sums may still be unread in A1
     TRACE2(1);
     if (tid == kIssueTid) issue_gemm1(tmem);
     ObsChunk nxt = load_obs_chunk(a, (tile + gridDim.x) * kTileM + lrow, lchunk);
     for (; tile < n_tiles; tile += gridDim.x, ++it) {
         const bool has_next = tile + gridDim.x < n_tiles, has_prev = prev_tile >= 0;
         const uint32_t slot = tmem + (it & 1) * kHid, slot_prev = tmem + ((it & 1) ^ 1) * kHid;
-        float o8[kOutRegs], z[kMaxAct];
-        // ---- GEMM 1 of this tile is done (A1 is free: the next tile's observations go in); GEMM 2 of the previous tile
-        //      is done (H is free, its output waits in the other slot)
+        float out[kOutRegs], o8[kOutRegs], z[kMaxAct];
+        // ---- GEMM 1 of this tile is done (A1 is free: the next tile's observations go in; with kEarlyG1 that was awaited
+        //      at the end of the previous iteration); GEMM 2 of the previous tile is done (H is free, its output waits in
+        //      the other slot)
         TRACE(0);
-        mbar_wait(bar1, phase1);
-        phase1 ^= 1;
+        const bool wait_g1_here = !kEarlyG1 || it == 0 || warp == kIssueWarp;
+        if (wait_g1_here && !(kEarlyG1 && warp == kIssueWarp)) { mbar_wait(bar1, phase1); phase1 ^= 1; }
         if (has_prev) { mbar_wait(bar2, phase2); phase2 ^= 1; }
         tc_fence_after();
         TRACE(1);
-        if (has_prev && warp == kIssueWarp) epilogue2_sums(slot_prev, o8);
+        if (has_prev && warp == kIssueWarp) {
+            epilogue2_math(slot_prev, out, false);
+            if constexpr (!kEarlyG1) exchange_tmem(slot_prev, out, o8);
+        }
+        if (kEarlyG1 && warp == kIssueWarp) {  // GEMM 1 of this tile: its latency went behind the sums above
+            mbar_wait(bar1, phase1); phase1 ^= 1;
+            tc_fence_after();
+        }
         TRACE(2);
+        if (kEarlyG1 && sums_in_a1 && cgroup != 0) quarter_meet(8, quarter, true);  // column group 0 has read the last sums
+        if (kEarlyG1 && has_prev && warp == kIssueWarp) issuer_publish(out);
+        sums_in_a1 = false;
         if (has_next) store_obs_chunk(nxt);
         // ---- epilogue 1: h1 = relu(slot + b1) -> bf16 -> H (swizzled A layout of GEMM 2); 64 columns per thread
         {
@@ -484,16 +530,39 @@ __global__ void __launch_bounds__(kThreads, 1) salp_actor_kernel(const __grid_co
         if (tid == kIssueTid) { tc_fence_after(); issue_gemm2(slot); }  // GEMM 2 of this tile over its own slot
         __syncwarp();
         TRACE(4);
-        if (has_next) nxt = load_obs_chunk(a, (tile + 2 * (long long)gridDim.x) * kTileM + lrow, lchunk);
-        // ---- epilogue 2 of the previous tile (other slot) while GEMM 2 of this one runs
-        if (has_prev && cgroup == 0) draw_noise(prev_tile * kTileM + erow, z);
-        if (has_prev && warp != kIssueWarp) epilogue2_sums(slot_prev, o8);
-        tc_fence_before();   // every read of the other slot is complete
-        TRACE(5);
-        cta_meet<6>(warp == kIssueWarp);
-        if (tid == kIssueTid && has_next) { tc_fence_after(); issue_gemm1(slot_prev); }  // GEMM 1 of the next tile goes there
-        __syncwarp();
-        if (has_prev && cgroup == 0) epilogue2_store(prev_tile * kTileM + erow, o8, z);
+        if constexpr (kEarlyG1) {
+            if (warp == kIssueWarp) {
+                cta_meet<7>(true);  // every warp holds its part of the other slot in registers: GEMM 1 of the next tile goes there
+                if (tid == kIssueTid && has_next) { tc_fence_after(); issue_gemm1(slot_prev); }
+                __syncwarp();
+                if (has_next) nxt = load_obs_chunk(a, (tile + 2 * (long long)gridDim.x) * kTileM + lrow, lchunk);
+            } else {
+                if (has_next) nxt = load_obs_chunk(a, (tile + 2 * (long long)gridDim.x) * kTileM + lrow, lchunk);
+                if (has_prev && cgroup == 0) draw_noise(prev_tile * kTileM + erow, z);
+                // ---- epilogue 2 of the previous tile (other slot) while GEMM 2 of this one runs
+                if (has_prev) epilogue2_math(slot_prev, out, true);
+                else { tc_fence_before(); cta_meet<7>(false); }
+            }
+            TRACE(5);
+            if (warp != kIssueWarp) {
+                if (has_next) { mbar_wait(bar1, phase1); phase1 ^= 1; }  // GEMM 1 of the next tile has read A1: the sums may go in
+                if (has_prev) {
+                    exchange_smem(out, o8, true);
+                    if (cgroup == 0) epilogue2_store(prev_tile * kTileM + erow, o8, z);
+                }
+            }
+            sums_in_a1 = has_prev;
+        } else {
+            if (has_next) nxt = load_obs_chunk(a, (tile + 2 * (long long)gridDim.x) * kTileM + lrow, lchunk);
+            if (has_prev && cgroup == 0) draw_noise(prev_tile * kTileM + erow, z);
+            if (has_prev && warp != kIssueWarp) { epilogue2_math(slot_prev, out, false); exchange_tmem(slot_prev, out, o8); }
+            tc_fence_before();   // every read of the other slot is complete
+            TRACE(5);
+            cta_meet<6>(warp == kIssueWarp);
+            if (tid == kIssueTid && has_next) { tc_fence_after(); issue_gemm1(slot_prev); }  // GEMM 1 of the next tile goes there
+            __syncwarp();
+            if (has_prev && cgroup == 0) epilogue2_store(prev_tile * kTileM + erow, o8, z);
+        }
         TRACE(6);
         prev_tile = tile;
     }
@@ -501,9 +570,15 @@ __global__ void __launch_bounds__(kThreads, 1) salp_actor_kernel(const __grid_co
     {
         mbar_wait(bar2, phase2);
         tc_fence_after();
-        float o8[kOutRegs], z[kMaxAct];
+        float out[kOutRegs], o8[kOutRegs], z[kMaxAct];
+        const uint32_t slot_last = tmem + ((it & 1) ^ 1) * kHid;
         if (cgroup == 0) draw_noise(prev_tile * kTileM + erow, z);
-        epilogue2_sums(tmem + ((it & 1) ^ 1) * kHid, o8);
+        epilogue2_math(slot_last, out, false);
+        if constexpr (kEarlyG1) {
+            if (sums_in_a1 && cgroup != 0) quarter_meet(8, quarter, true);
+            if (warp == kIssueWarp) issuer_publish(out);
+            else exchange_smem(out, o8, false);
+        } else exchange_tmem(slot_last, out, o8);
         if (cgroup == 0) epilogue2_store(prev_tile * kTileM + erow, o8, z);
     }
     TRACE2(2);
