@@ -34,14 +34,17 @@ constexpr int kThreads = 512;  // 16 warps: TMEM lane quarter = warp % 4, column
 // column group 0 also squashes and stores the actions.  (A 17th warp that only issues was measured slower: 544 threads
 // cap the kernel at 96 registers, and its MMAs paced at ~265 instead of ~155 cycles -- profiles/r01_ncu_actor.md.)
 constexpr int kIssueWarp = 12, kIssueTid = 32 * kIssueWarp, kIssueQuarter = kIssueWarp & 3, kIssueGroup = kIssueWarp >> 2;
-static_assert(kIssueGroup != 0, "the issuing warp must not be one that stores the actions");
+// With at most 4 output rows (kEarlyG1 below) a second warp issues the second half of GEMM 2, so that neither thread sits
+// in the issue for the whole GEMM: warp 13, the same column group in the next quarter.
+constexpr int kIssueWarpB = kIssueWarp + 1, kIssueTidB = 32 * kIssueWarpB;
+static_assert(kIssueGroup != 0 && kIssueQuarter == 0, "the issuing warps: not ones that store the actions; quarters 0 and 1");
 constexpr uint32_t kW2Bytes = kHid * kHid * 2, kW1Bytes = kHid * kK1 * 2, kA1Bytes = kTileM * kK1 * 2, kHBytes = kTileM * kHid * 2;
 constexpr uint32_t kOffW2 = 0, kOffW1 = kOffW2 + kW2Bytes, kOffA1 = kOffW1 + kW1Bytes, kOffH = kOffA1 + kA1Bytes;
 constexpr uint32_t kOffB1 = kOffH + kHBytes, kOffB2 = kOffB1 + kHid * 4, kOffW3 = kOffB2 + kHid * 4;
 constexpr uint32_t kOffB3 = kOffW3 + kMaxOut * kHid * 4, kOffBar = kOffB3 + kMaxOut * 4, kOffTmem = kOffBar + 16;
-constexpr uint32_t kOffIss = (kOffTmem + 8 + 15) / 16 * 16;  // the issuing warp's output sums: 32 rows x 16 bytes
-static_assert(kOffIss + 32 * 16 <= 227 * 1024, "shared memory of one CTA");
-constexpr uint32_t kSmemBytes = kOffIss + 32 * 16;
+constexpr uint32_t kOffIss = kOffW3 + 4 * kHid * 4;  // kEarlyG1 (W3 has at most 4 rows): the issuing warps' output sums, 2 x 32 rows x 16 bytes
+static_assert(kOffTmem + 8 <= 227 * 1024, "shared memory of one CTA");
+constexpr uint32_t kSmemBytes = kOffTmem + 8;
 static_assert(kSmemBytes <= 232448, "shared memory budget of one sm_100 CTA");
 constexpr uint32_t kTmemCols = 512;  // two 128 x 256 f32 accumulators
 
@@ -281,7 +284,7 @@ __global__ void __launch_bounds__(kThreads, 1) salp_actor_kernel(const __grid_co
         for (int i = tid; i < n_out * kHid; i += kThreads) s_w3[i] = i < a.w3_rows * kHid ? a.w3[i] : 0.f;
         if (tid < n_out) s_b3[tid] = tid < a.w3_rows ? a.b3[tid] : 0.f;
     }
-    if (tid == 0) { mbar_init(bar1, 1); mbar_init(bar2, 1); }
+    if (tid == 0) { mbar_init(bar1, 1); mbar_init(bar2, NOUT <= 4 ? 2 : 1); }  // kEarlyG1: GEMM 2 is committed in two halves
     if (warp == 0) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(s_tmem)), "r"(kTmemCols) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
@@ -314,11 +317,12 @@ __global__ void __launch_bounds__(kThreads, 1) salp_actor_kernel(const __grid_co
     const unsigned long long rng_seed = a.rng ? a.rng[0] : 0ull, rng_draw = a.rng ? a.rng[1] : 0ull;
     constexpr int kOutRegs = NOUT < 4 ? 4 : NOUT;
 
-    auto issue_gemm2 = [&](uint32_t slot) {  // slot[128 x 256] = H[128 x 256] . W2^T
+    auto issue_gemm2 = [&](uint32_t slot, int k0, int k1) {  // slot[128 x 256] (+)= H[:, 16 k0 .. 16 k1) . W2[:, same]^T
     #pragma unroll
         for (int kk = 0; kk < kHid / 16; ++kk)
-            umma_bf16(slot, umma_desc_sw128(sH + (kk >> 2) * (kTileM * 128) + (kk & 3) * 32),
-                      umma_desc_sw128(sW2 + (kk >> 2) * (kHid * 128) + (kk & 3) * 32), kk > 0);
+            if (kk >= k0 && kk < k1)
+                umma_bf16(slot, umma_desc_sw128(sH + (kk >> 2) * (kTileM * 128) + (kk & 3) * 32),
+                          umma_desc_sw128(sW2 + (kk >> 2) * (kHid * 128) + (kk & 3) * 32), kk > 0);
         umma_commit(bar2);
     };
     // ---- epilogue 2, first part: h2 = relu(slot + b2); partial dot products with the 2*act rows of W3 over this warp's 64
@@ -329,7 +333,14 @@ __global__ void __launch_bounds__(kThreads, 1) salp_actor_kernel(const __grid_co
     // frees the other TMEM slot as soon as every warp has LOADED its part of it -- GEMM 1 of the next tile is then issued
     // right behind GEMM 2 instead of after epilogue 2 (kEarlyG1).  8 output rows keep the exchange in TMEM.
     constexpr bool kEarlyG1 = NOUT <= 4;
-    auto epilogue2_math = [&](uint32_t slot, float (&out)[kOutRegs], bool announce) {
+    // second half of GEMM 2 (kEarlyG1), by lane 0 of warp 13 once warp 12 has issued the first (named barrier 12, 64 threads)
+    auto second_half = [&](uint32_t gemm_slot) {
+        asm volatile("bar.sync 12, 64;" ::: "memory");
+        if (tid == kIssueTidB) { tc_fence_after(); issue_gemm2(gemm_slot, kHid / 32, kHid / 16); }
+        __syncwarp();
+    };
+    // `issue_mid`: warp 13 issues its half of the running GEMM 2 (into gemm_slot) between the two halves of its columns
+    auto epilogue2_math = [&](uint32_t slot, float (&out)[kOutRegs], bool announce, bool issue_mid, uint32_t gemm_slot) {
     #pragma unroll
         for (int j = 0; j < kOutRegs; ++j) out[j] = 0.f;
         const int colg = cgroup * 64;
@@ -343,6 +354,7 @@ __global__ void __launch_bounds__(kThreads, 1) salp_actor_kernel(const __grid_co
         for (int o = 0; o < NOUT; ++o) acc[o] = make_float2(0.f, 0.f);
     #pragma unroll
         for (int i = 0; i < 2; ++i) {
+            if (i == 1 && issue_mid) second_half(gemm_slot);
     #pragma unroll
             for (int c = 0; c < 8; ++c) {
                 const int col = colg + 32 * i + 4 * c;
@@ -395,7 +407,7 @@ __global__ void __launch_bounds__(kThreads, 1) salp_actor_kernel(const __grid_co
     // must not wait for A1 (that is, for GEMM 1 of the next tile) on its way back into the MMA issue.
     float4 *s_iss = reinterpret_cast<float4 *>(smem + kOffIss);
     auto issuer_publish = [&](const float (&out)[kOutRegs]) {
-        s_iss[lane] = make_float4(out[0], out[1], out[2], out[3]);
+        s_iss[quarter * 32 + lane] = make_float4(out[0], out[1], out[2], out[3]);  // quarter 0 (warp 12) or 1 (warp 13)
         __threadfence_block();
         quarter_meet(1, quarter, false);
     };
@@ -408,7 +420,8 @@ __global__ void __launch_bounds__(kThreads, 1) salp_actor_kernel(const __grid_co
         if (cgroup == 0) {
     #pragma unroll
             for (int g = 1; g < kThreads / kTileM; ++g) {
-                const float4 u = (quarter == kIssueQuarter && g == kIssueGroup) ? s_iss[lane] : sc[g * kTileM + erow];
+                const bool from_issuer = g == kIssueGroup && (quarter == kIssueQuarter || quarter == kIssueQuarter + 1);
+                const float4 u = from_issuer ? s_iss[quarter * 32 + lane] : sc[g * kTileM + erow];
                 o8[0] += u.x; o8[1] += u.y; o8[2] += u.z; o8[3] += u.w;
             }
             if (more) quarter_meet(8, quarter, false);
@@ -489,7 +502,7 @@ __global__ void __launch_bounds__(kThreads, 1) salp_actor_kernel(const __grid_co
         tc_fence_after();
         TRACE(1);
         if (has_prev && warp == kIssueWarp) {
-            epilogue2_math(slot_prev, out, false);
+            epilogue2_math(slot_prev, out, false, false, 0u);
             if constexpr (!kEarlyG1) exchange_tmem(slot_prev, out, o8);
         }
         if (kEarlyG1 && warp == kIssueWarp) {  // GEMM 1 of this tile: its latency went behind the sums above
@@ -527,11 +540,13 @@ __global__ void __launch_bounds__(kThreads, 1) salp_actor_kernel(const __grid_co
         tc_fence_before();   // this tile's reads of its slot are complete
         TRACE(3);
         cta_meet<5>(warp == kIssueWarp);
-        if (tid == kIssueTid) { tc_fence_after(); issue_gemm2(slot); }  // GEMM 2 of this tile over its own slot
+        // GEMM 2 of this tile over its own slot: all of it, or (kEarlyG1) its first half -- warp 13 issues the second one
+        if (tid == kIssueTid) { tc_fence_after(); issue_gemm2(slot, 0, kEarlyG1 ? kHid / 32 : kHid / 16); }
         __syncwarp();
         TRACE(4);
         if constexpr (kEarlyG1) {
             if (warp == kIssueWarp) {
+                asm volatile("bar.arrive 12, 64;" ::: "memory");
                 cta_meet<7>(true);  // every warp holds its part of the other slot in registers: GEMM 1 of the next tile goes there
                 if (tid == kIssueTid && has_next) { tc_fence_after(); issue_gemm1(slot_prev); }
                 __syncwarp();
@@ -539,14 +554,20 @@ __global__ void __launch_bounds__(kThreads, 1) salp_actor_kernel(const __grid_co
             } else {
                 if (has_next) nxt = load_obs_chunk(a, (tile + 2 * (long long)gridDim.x) * kTileM + lrow, lchunk);
                 if (has_prev && cgroup == 0) draw_noise(prev_tile * kTileM + erow, z);
-                // ---- epilogue 2 of the previous tile (other slot) while GEMM 2 of this one runs
-                if (has_prev) epilogue2_math(slot_prev, out, true);
-                else { tc_fence_before(); cta_meet<7>(false); }
+                // ---- epilogue 2 of the previous tile (other slot) while GEMM 2 of this one runs; warp 13 issues its half
+                //      of that GEMM between the two halves of its columns (warp 12 is through with the first by then)
+                if (has_prev) {
+                    epilogue2_math(slot_prev, out, true, warp == kIssueWarpB, slot);
+                } else {
+                    tc_fence_before(); cta_meet<7>(false);
+                    if (warp == kIssueWarpB) second_half(slot);
+                }
             }
             TRACE(5);
+            if (warp == kIssueWarpB && has_prev) issuer_publish(out);  // a buffer of its own: no need to wait for A1
             if (warp != kIssueWarp) {
                 if (has_next) { mbar_wait(bar1, phase1); phase1 ^= 1; }  // GEMM 1 of the next tile has read A1: the sums may go in
-                if (has_prev) {
+                if (has_prev && warp != kIssueWarpB) {
                     exchange_smem(out, o8, true);
                     if (cgroup == 0) epilogue2_store(prev_tile * kTileM + erow, o8, z);
                 }
@@ -555,7 +576,7 @@ __global__ void __launch_bounds__(kThreads, 1) salp_actor_kernel(const __grid_co
         } else {
             if (has_next) nxt = load_obs_chunk(a, (tile + 2 * (long long)gridDim.x) * kTileM + lrow, lchunk);
             if (has_prev && cgroup == 0) draw_noise(prev_tile * kTileM + erow, z);
-            if (has_prev && warp != kIssueWarp) { epilogue2_math(slot_prev, out, false); exchange_tmem(slot_prev, out, o8); }
+            if (has_prev && warp != kIssueWarp) { epilogue2_math(slot_prev, out, false, false, 0u); exchange_tmem(slot_prev, out, o8); }
             tc_fence_before();   // every read of the other slot is complete
             TRACE(5);
             cta_meet<6>(warp == kIssueWarp);
@@ -573,10 +594,10 @@ __global__ void __launch_bounds__(kThreads, 1) salp_actor_kernel(const __grid_co
         float out[kOutRegs], o8[kOutRegs], z[kMaxAct];
         const uint32_t slot_last = tmem + ((it & 1) ^ 1) * kHid;
         if (cgroup == 0) draw_noise(prev_tile * kTileM + erow, z);
-        epilogue2_math(slot_last, out, false);
+        epilogue2_math(slot_last, out, false, false, 0u);
         if constexpr (kEarlyG1) {
             if (sums_in_a1 && cgroup != 0) quarter_meet(8, quarter, true);
-            if (warp == kIssueWarp) issuer_publish(out);
+            if (warp == kIssueWarp || warp == kIssueWarpB) issuer_publish(out);
             else exchange_smem(out, o8, false);
         } else exchange_tmem(slot_last, out, o8);
         if (cgroup == 0) epilogue2_store(prev_tile * kTileM + erow, o8, z);
