@@ -340,7 +340,9 @@ __global__ void __launch_bounds__(kThreads, 1) salp_actor_kernel(const __grid_co
         __syncwarp();
     };
     // `issue_mid`: warp 13 issues its half of the running GEMM 2 (into gemm_slot) between the two halves of its columns
-    auto epilogue2_math = [&](uint32_t slot, float (&out)[kOutRegs], bool announce, bool issue_mid, uint32_t gemm_slot) {
+    // `announce`: 0 nothing, 1 report that this warp's part of the slot is in registers (named barrier 7), 2 (warp 12) wait for
+    // all of those reports and issue GEMM 1 of the next tile into the slot (`g1_next`)
+    auto epilogue2_math = [&](uint32_t slot, float (&out)[kOutRegs], int announce, bool issue_mid, uint32_t gemm_slot, bool g1_next) {
     #pragma unroll
         for (int j = 0; j < kOutRegs; ++j) out[j] = 0.f;
         const int colg = cgroup * 64;
@@ -348,7 +350,13 @@ __global__ void __launch_bounds__(kThreads, 1) salp_actor_kernel(const __grid_co
         tmem_ld32_nowait(slot + lane_base + colg, r[0]);
         tmem_ld32_nowait(slot + lane_base + colg + 32, r[1]);
         tmem_ld_wait();
-        if (announce) { tc_fence_before(); cta_meet<7>(false); }  // this warp's part of the slot is in registers
+        if (announce == 1) { tc_fence_before(); cta_meet<7>(false); }
+        if (announce == 2) {
+            tc_fence_before();
+            cta_meet<7>(true);
+            if (tid == kIssueTid && g1_next) { tc_fence_after(); issue_gemm1(slot); }
+            __syncwarp();
+        }
         float2 acc[NOUT];  // packed f32x2 accumulators (even, odd columns), folded at the end
     #pragma unroll
         for (int o = 0; o < NOUT; ++o) acc[o] = make_float2(0.f, 0.f);
@@ -496,22 +504,15 @@ __global__ void __launch_bounds__(kThreads, 1) salp_actor_kernel(const __grid_co
         //      at the end of the previous iteration); GEMM 2 of the previous tile is done (H is free, its output waits in
         //      the other slot)
         TRACE(0);
-        const bool wait_g1_here = !kEarlyG1 || it == 0 || warp == kIssueWarp;
-        if (wait_g1_here && !(kEarlyG1 && warp == kIssueWarp)) { mbar_wait(bar1, phase1); phase1 ^= 1; }
+        if (!kEarlyG1 || it == 0 || warp == kIssueWarp) { mbar_wait(bar1, phase1); phase1 ^= 1; }  // (warp 12 issues it: waits here)
         if (has_prev) { mbar_wait(bar2, phase2); phase2 ^= 1; }
         tc_fence_after();
         TRACE(1);
-        if (has_prev && warp == kIssueWarp) {
-            epilogue2_math(slot_prev, out, false, false, 0u);
-            if constexpr (!kEarlyG1) exchange_tmem(slot_prev, out, o8);
-        }
-        if (kEarlyG1 && warp == kIssueWarp) {  // GEMM 1 of this tile: its latency went behind the sums above
-            mbar_wait(bar1, phase1); phase1 ^= 1;
-            tc_fence_after();
+        if constexpr (!kEarlyG1) {  // the one issuing warp does its epilogue 2 first: it will sit in the issue of all of GEMM 2
+            if (has_prev && warp == kIssueWarp) { epilogue2_math(slot_prev, out, 0, false, 0u, false); exchange_tmem(slot_prev, out, o8); }
         }
         TRACE(2);
         if (kEarlyG1 && sums_in_a1 && cgroup != 0) quarter_meet(8, quarter, true);  // column group 0 has read the last sums
-        if (kEarlyG1 && has_prev && warp == kIssueWarp) issuer_publish(out);
         sums_in_a1 = false;
         if (has_next) store_obs_chunk(nxt);
         // ---- epilogue 1: h1 = relu(slot + b1) -> bf16 -> H (swizzled A layout of GEMM 2); 64 columns per thread
@@ -547,24 +548,29 @@ __global__ void __launch_bounds__(kThreads, 1) salp_actor_kernel(const __grid_co
         if constexpr (kEarlyG1) {
             if (warp == kIssueWarp) {
                 asm volatile("bar.arrive 12, 64;" ::: "memory");
-                cta_meet<7>(true);  // every warp holds its part of the other slot in registers: GEMM 1 of the next tile goes there
-                if (tid == kIssueTid && has_next) { tc_fence_after(); issue_gemm1(slot_prev); }
-                __syncwarp();
                 if (has_next) nxt = load_obs_chunk(a, (tile + 2 * (long long)gridDim.x) * kTileM + lrow, lchunk);
+                // its part of the other slot into registers, then (every warp has done the same) GEMM 1 of the next tile
+                // into that slot, then the arithmetic while the second half of GEMM 2 and that GEMM 1 run
+                if (has_prev) epilogue2_math(slot_prev, out, 2, false, 0u, has_next);
+                else {
+                    cta_meet<7>(true);
+                    if (tid == kIssueTid && has_next) { tc_fence_after(); issue_gemm1(slot_prev); }
+                    __syncwarp();
+                }
             } else {
                 if (has_next) nxt = load_obs_chunk(a, (tile + 2 * (long long)gridDim.x) * kTileM + lrow, lchunk);
                 if (has_prev && cgroup == 0) draw_noise(prev_tile * kTileM + erow, z);
                 // ---- epilogue 2 of the previous tile (other slot) while GEMM 2 of this one runs; warp 13 issues its half
                 //      of that GEMM between the two halves of its columns (warp 12 is through with the first by then)
                 if (has_prev) {
-                    epilogue2_math(slot_prev, out, true, warp == kIssueWarpB, slot);
+                    epilogue2_math(slot_prev, out, 1, warp == kIssueWarpB, slot, false);
                 } else {
                     tc_fence_before(); cta_meet<7>(false);
                     if (warp == kIssueWarpB) second_half(slot);
                 }
             }
             TRACE(5);
-            if (warp == kIssueWarpB && has_prev) issuer_publish(out);  // a buffer of its own: no need to wait for A1
+            if ((warp == kIssueWarp || warp == kIssueWarpB) && has_prev) issuer_publish(out);  // buffers of their own: no wait for A1
             if (warp != kIssueWarp) {
                 if (has_next) { mbar_wait(bar1, phase1); phase1 ^= 1; }  // GEMM 1 of the next tile has read A1: the sums may go in
                 if (has_prev && warp != kIssueWarpB) {
@@ -576,7 +582,7 @@ __global__ void __launch_bounds__(kThreads, 1) salp_actor_kernel(const __grid_co
         } else {
             if (has_next) nxt = load_obs_chunk(a, (tile + 2 * (long long)gridDim.x) * kTileM + lrow, lchunk);
             if (has_prev && cgroup == 0) draw_noise(prev_tile * kTileM + erow, z);
-            if (has_prev && warp != kIssueWarp) { epilogue2_math(slot_prev, out, false, false, 0u); exchange_tmem(slot_prev, out, o8); }
+            if (has_prev && warp != kIssueWarp) { epilogue2_math(slot_prev, out, 0, false, 0u, false); exchange_tmem(slot_prev, out, o8); }
             tc_fence_before();   // every read of the other slot is complete
             TRACE(5);
             cta_meet<6>(warp == kIssueWarp);
@@ -594,7 +600,7 @@ __global__ void __launch_bounds__(kThreads, 1) salp_actor_kernel(const __grid_co
         float out[kOutRegs], o8[kOutRegs], z[kMaxAct];
         const uint32_t slot_last = tmem + ((it & 1) ^ 1) * kHid;
         if (cgroup == 0) draw_noise(prev_tile * kTileM + erow, z);
-        epilogue2_math(slot_last, out, false, false, 0u);
+        epilogue2_math(slot_last, out, 0, false, 0u, false);
         if constexpr (kEarlyG1) {
             if (sums_in_a1 && cgroup != 0) quarter_meet(8, quarter, true);
             if (warp == kIssueWarp || warp == kIssueWarpB) issuer_publish(out);
