@@ -6,17 +6,18 @@
 // the env kernel.  The observation tensor is read in place (f32 rows straight from the env kernel's
 // output), the action tensor is written in the env build's real type -- nothing else touches HBM.
 //
-// Structure (one persistent CTA per SM, 512 threads, tiles of 128 environments, software-pipelined: the next
-// tile's observations are prefetched into registers, its GEMM 1 runs behind this tile's GEMM 2 into a second
-// TMEM accumulator and overlaps this tile's last epilogue):
-//   weights   W1 (K padded 24->32) and W2 live in shared memory for the whole kernel as bf16, pre-packed
-//             on the host into the tcgen05 canonical K-major no-swizzle layout (8x8 core matrices)
-//   GEMM 1    [128 x 32] x [32 x 256]   2 x tcgen05.mma (M128 N256 K16), accumulator in TMEM (256 cols)
-//   epilogue  tcgen05.ld -> +bias, ReLU -> bf16 -> shared memory, canonical A layout for GEMM 2
-//   GEMM 2    [128 x 256] x [256 x 256] 16 x tcgen05.mma into the same TMEM columns
-//   epilogue  tcgen05.ld -> +bias, ReLU -> dot with the 2*act rows of W3 in registers (f32) -> squash
-// In the epilogues warp w reads TMEM lanes 32*(w%4).. (lane == row) and 64 of the 256 columns (w/4); one
-// elected thread issues the MMAs and signals completion through mbarriers (tcgen05.commit).
+// Structure (one persistent CTA per SM, 512 threads, tiles of 128 environments):
+//   weights   W1 (K padded 24->32) and W2 live in shared memory for the whole kernel as bf16: W1 in the tcgen05
+//             K-major no-swizzle layout the host packs (8x8 core matrices), W2 re-laid into 128-byte-swizzled K blocks
+//   TMEM      two slots of 128 x 256 f32; tile i keeps BOTH its GEMM outputs in slot i & 1
+//   GEMM 1    [128 x 32] x [32 x 256]    2 x tcgen05.mma (M128 N256 K16)
+//   epilogue1 tcgen05.ld -> +bias (FADD2), ReLU folded into cvt.bf16x2 -> H in shared memory (swizzled A layout)
+//   GEMM 2    [128 x 256] x [256 x 256]  16 x tcgen05.mma over the same slot, issued in two halves by two warps
+//   epilogue2 tcgen05.ld -> +bias, ReLU -> FFMA2 dot with the 2*act rows of W3 (f32) -> sums of the 4 column groups
+//             meet in the idle A1 buffer (8 output rows: in TMEM) -> squash -> store
+//   pipeline  per iteration: epilogue 1 (tile i) -> epilogue 2 (tile i-1), while the tensor core runs GEMM 2 (tile i)
+//             and GEMM 1 (tile i+1); hand-offs are bar.arrive / bar.sync pairs and tcgen05.commit -> mbarrier
+// In the epilogues warp w reads TMEM lanes 32*(w%4).. (lane == row) and 64 of the 256 columns (w/4).
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
