@@ -19,7 +19,10 @@ def _ref(actor, obs, noise):
     return actor.to_box(torch.tanh(mean + torch.exp(torch.clamp(log_std, -20, 2)) * noise))
 
 
-@pytest.mark.parametrize("n,obs_dim,act_dim", [(128, 24, 1), (1000, 24, 1), (70001, 24, 1), (4096, 24, 2), (513, 32, 2), (300, 16, 1)])
+# sizes chosen for the kernel's software pipeline on 148 SMs: one tile per CTA (<= 18 944 rows), some CTAs with two tiles
+# and some with one (21 504), three to four (70 001), 13-14 with a ragged last tile (262 221); act_dim 2 = 4 output rows
+@pytest.mark.parametrize("n,obs_dim,act_dim", [(128, 24, 1), (1000, 24, 1), (21504, 24, 1), (70001, 24, 1), (262221, 24, 1),
+                                               (4096, 24, 2), (40000, 24, 2), (513, 32, 2), (300, 16, 1)])
 def test_fused_actor_matches_torch(salp_lib, n, obs_dim, act_dim):
     from underwater_swimmer_rl_b200.rollout import FusedActor, TanhGaussianActor
     torch.manual_seed(n + obs_dim)
@@ -44,6 +47,7 @@ def test_fused_actor_matches_torch(salp_lib, n, obs_dim, act_dim):
 
 @pytest.mark.parametrize("n,obs_dim,act_dim,box", [
     (4097, 6, 3, ([0.0, 0.0, -1.0], [1.0, 1.0, 1.0])),   # model (B): salp_robot_env.py:51-71
+    (50001, 6, 3, ([0.0, 0.0, -1.0], [1.0, 1.0, 1.0])),  # ... with two to three tiles per CTA (8 rows of W3: sums meet in TMEM)
     (1000, 6, 3, None), (777, 7, 4, ([-2.0, 0.0, 0.5, -1.0], [2.0, 3.0, 1.5, 1.0])), (300, 31, 3, None), (129, 1, 1, None)])
 def test_fused_actor_other_shapes_and_box_rescale(salp_lib, n, obs_dim, act_dim, box):
     """Rows that are not float4 groups, up to 4 action dims (8 rows of W3), and SB3's [-1, 1] -> Box mapping."""
