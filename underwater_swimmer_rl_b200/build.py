@@ -52,9 +52,10 @@ def build(force: bool = False, verbose: bool = False) -> str:
     cyck = os.path.join(CSRC, "salp_cycle_kernels.cu")
     cycc = os.path.join(CSRC, "salp_cycle_capi.cu")
     vflag = ["-Xptxas", "-v"] if verbose else []
+    step_defs = os.environ.get("SALP_STEP_DEFS", "").split()  # developer builds of the step kernels, e.g. -DSALP_L2_HINTS=2
     actor_defs = os.environ.get("SALP_ACTOR_DEFS", "").split()  # developer builds, e.g. SALP_ACTOR_DEFS=-DSALP_ACTOR_TRACE
     jobs = [
-        (os.path.join(OBJ, "salp_kernels_f32.o"), [NVCC, "-c", kern, "-DSALP_BUILD_F64=0"] + COMMON + vflag, [kern] + hdrs),
+        (os.path.join(OBJ, "salp_kernels_f32.o"), [NVCC, "-c", kern, "-DSALP_BUILD_F64=0"] + COMMON + vflag + step_defs, [kern] + hdrs),
         (os.path.join(OBJ, "salp_kernels_f64.o"), [NVCC, "-c", kern, "-DSALP_BUILD_F64=1", "-fmad=false"] + COMMON + vflag, [kern] + hdrs),
         (os.path.join(OBJ, "salp_capi.o"), [NVCC, "-c", capi] + COMMON, [capi] + hdrs),
         (os.path.join(OBJ, "salp_replay.o"), [NVCC, "-c", replay] + COMMON, [replay] + hdrs),
