@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define SALP_ABI_VERSION 4
+#define SALP_ABI_VERSION 5
 
 enum { SALP_OK = 0, SALP_EINVAL = -1, SALP_ECUDA = -2, SALP_EUNBOUND = -3, SALP_EUNSUPPORTED = -4 };
 
@@ -43,7 +43,13 @@ enum { SALP_F32 = 0, /* throughput build: float state/actions/reward            
 enum { SALP_MAX_FOOD = 32, SALP_MAX_OBSERVED_FOOD = 8 };
 
 /* flags for SalpParams.flags */
-enum { SALP_AUTORESET = 1 /* done lanes are reset inside the step (gymnasium 0.29 vector semantics) */ };
+enum { SALP_AUTORESET = 1,      /* done lanes are reset inside the step (gymnasium 0.29 vector semantics)           */
+       SALP_RNG_PHILOX = 2,     /* the words of both random streams are computed in the kernel (Philox4x32-10 keyed by
+                                   salp_set_rng_seed, counter = (word index / 4, stream, GLOBAL env id)) instead of
+                                   being read from the host-seeded MT19937 tables: unbounded, aperiodic, no memory;
+                                   food_words / jit_words may be NULL.  Same consumption discipline as the tables
+                                   (cursors in `ctrl` count words), no parity with the reference's generators.    */
+       SALP_GENERIC_KERNEL = 4  /* diagnostics: never select the specialised forced-breathing step kernel          */ };
 
 /* event bits written to SalpBuffers.events */
 enum { SALP_EV_TERMINATED = 1, SALP_EV_TRUNCATED = 2, SALP_EV_COLLISION = 4, SALP_EV_FOOD = 8 };
@@ -161,6 +167,20 @@ int salp_create(const SalpParams *params, int64_t num_envs, int64_t env_id0, int
                 SalpHandle **out);
 int salp_destroy(SalpHandle *h);
 
+/* Seed of the in-kernel Philox streams (SALP_RNG_PHILOX); takes effect for launches issued after the call. */
+int salp_set_rng_seed(SalpHandle *h, uint64_t seed);
+
+/*
+ * Forced breathing (S:31,66 `forced_breathing=True`, R:158-167): phase, timer, ellipse axes, water volume and the thrust
+ * window are functions of the position in the 273-step cycle.  The f32 forced-breathing kernel reads them from a table
+ * built on the host in double with the reference's expressions (R:184-259); this call returns that table's sources so a
+ * test can check them bit-for-bit against the fp64 validation kernel, which runs the recurrences:
+ *   index 0 = fresh reset, index i = 1..273 = state after the i-th step of a cycle;  arrays of 274, any may be NULL.
+ *   touch[i] bits: a clamp onto the low / right / bottom wall registers as a wall contact (R:335-352 + S:225-228).
+ */
+int salp_forced_cycle(const SalpParams *params, double *water_volume, double *ellipse_a, double *ellipse_b,
+                      int32_t *fsm, int32_t *touch);
+
 /* Attach caller-owned device buffers (raw pointers, e.g. torch.Tensor.data_ptr()). */
 int salp_bind(SalpHandle *h, const SalpBuffers *buffers);
 
@@ -177,6 +197,24 @@ int salp_reset(SalpHandle *h, const uint8_t *mask, int rewind_rng, void *cuda_st
  * (see SalpBuffers).  Asynchronous on `cuda_stream`.
  */
 int salp_refresh_rng(SalpHandle *h, void *cuda_stream);
+
+/*
+ * Replaces SalpSnakeEnv._get_extended_observation (S:366-428 over R:371-388) as the reference's callers use it:
+ * they overwrite robot_pos / robot_velocity / robot_angle / robot_angular_velocity / food_positions /
+ * steps_since_food and then ask for the observation of that state WITHOUT stepping
+ * (eval/collect_navigation_data.py:76-89, eval/watch_navigation.py:63).  Writes obs[slot][e][:] for every env
+ * from the current contents of body / ctrl / food; changes no state.  Asynchronous on `cuda_stream`.
+ */
+int salp_observe(SalpHandle *h, int slot, void *cuda_stream);
+
+/*
+ * Replaces the run-time assignment `env.base_num_food_items = n` (src/salp/training/continuous_trainer.py:408-411,
+ * adaptive difficulty): episodes that start after this call (salp_reset, or the in-kernel auto-reset of later
+ * steps) are laid out with n foods (or randint(1, n) with random_food_count).  Running episodes keep their
+ * food.  n must not exceed SalpLayout.food_slots of the handle (SALP_EUNSUPPORTED otherwise: the kernel
+ * instantiation and the `food` buffer were sized at salp_create).  Takes effect for launches issued after it.
+ */
+int salp_set_num_food_items(SalpHandle *h, int32_t num_food_items);
 
 /*
  * Replaces K consecutive SalpSnakeEnv.step calls (S:157-202 over R:119-156) per env in ONE

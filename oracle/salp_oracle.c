@@ -382,6 +382,13 @@ void salp_oracle_reset(const OracleParams *p, OracleEnv *envs, int64_t n, int64_
         env_reset(p, &envs[i], t, (env_id0 + i) % t->rows, obs ? obs + i * od : NULL);
 }
 
+/* S:366-428 _get_extended_observation on the CURRENT state of n envs (no step): what the reference's callers
+ * get after poking robot_pos / robot_angle / food_positions (eval/collect_navigation_data.py:76-89). */
+void salp_oracle_observe(const OracleParams *p, const OracleEnv *envs, int64_t n, float *obs /* [n][obs_dim] */) {
+    const int od = salp_oracle_obs_dim(p);
+    for (int64_t i = 0; i < n; ++i) extended_obs(p, &envs[i], obs + i * od);
+}
+
 /* One step for n envs.  actions [n][act_dim] double.  Outputs may be NULL. */
 void salp_oracle_step(const OracleParams *p, OracleEnv *envs, int64_t n, int64_t env_id0,
                       const OracleTables *t, const double *actions, float *obs, double *reward,

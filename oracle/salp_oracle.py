@@ -141,6 +141,12 @@ class Oracle:
                                 C.byref(self.t), _ptr(obs))
         return obs[0]
 
+    def observe(self) -> np.ndarray:
+        """_get_extended_observation() of the current (possibly poked) state, without stepping."""
+        obs = np.zeros((self.n, self.obs_dim), np.float32)
+        lib().salp_oracle_observe(C.byref(self.p), _ptr(self.envs), C.c_int64(self.n), _ptr(obs))
+        return obs
+
     def step(self, actions: np.ndarray):
         a = np.ascontiguousarray(np.asarray(actions, dtype=np.float64).reshape(self.n, self.act_dim))
         obs = np.zeros((self.n, self.obs_dim), np.float32)
@@ -150,13 +156,17 @@ class Oracle:
                                C.byref(self.t), _ptr(a), _ptr(obs), _ptr(rew), _ptr(flags))
         return obs, rew, flags
 
-    def rollout(self, actions: np.ndarray, autoreset: bool = True, record: bool = True):
-        """actions [T, n, act_dim] float32.  Returns dict (obs/reset_obs/reward/flags if record)."""
+    def rollout(self, actions: np.ndarray, autoreset: bool = True, record=True):
+        """actions [T, n, act_dim] float32.  Returns dict (obs/reset_obs/reward/flags if record;
+        record="flags": only the per-step event flags and rewards -- long free-running comparisons)."""
         a = np.ascontiguousarray(actions, dtype=np.float32)
         T = a.shape[0]
         assert a.shape[1] == self.n and a.reshape(T, self.n, -1).shape[2] == self.act_dim
         obs = reset_obs = rew = flags = None
-        if record:
+        if record == "flags":
+            rew = np.zeros((T, self.n), np.float64)
+            flags = np.zeros((T, self.n), np.uint8)
+        elif record:
             obs = np.zeros((T, self.n, self.obs_dim), np.float32)
             reset_obs = np.zeros((T, self.n, self.obs_dim), np.float32)
             rew = np.zeros((T, self.n), np.float64)

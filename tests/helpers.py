@@ -82,3 +82,46 @@ def bits_equal(a: np.ndarray, b: np.ndarray) -> np.ndarray:
         ib = b.view(f"u{a.dtype.itemsize}")
         return (ia == ib) | ((a == 0) & (b == 0))  # +0 == -0
     return a == b
+
+
+def push_oracle_state(env, orc) -> None:
+    """Teacher forcing: overwrite the device state of ``env`` (SalpVectorEnv, any build) with the
+    fp64 state of the oracle batch ``orc`` (tests only; the kernel then advances exactly one step
+    from the same state the oracle advances from)."""
+    import torch
+    e = orc.envs
+    F = env.food_slots
+    np_real = np.float64 if env.real == torch.float64 else np.float32
+    body = np.stack([np.stack([e["px"], e["py"], e["vx"], e["vy"]], 1),
+                     np.stack([e["angle"], e["omega"], e["nozzle"], e["wv"]], 1)])
+    env.body.copy_(torch.from_numpy(body.astype(np_real)))
+    ctrl = env.ctrl.cpu().numpy()
+    ctrl[0, :, 0] = e["phase"] | (e["timer"] << 2) | (e["exhale_dur"] << 10) | (e["shape_kind"] << 18) | (e["shape_timer"] << 20)
+    ctrl[0, :, 1] = e["steps_since_food"]
+    ctrl[0, :, 2] = e["food_collected"]
+    mask = (e["alive"][:, :F].astype(np.int64) << np.arange(F)).sum(1)
+    ctrl[0, :, 3] = np.where(mask >= 2 ** 31, mask - 2 ** 32, mask)
+    ctrl[1, :, 0] = e["cur_food"]
+    ctrl[1, :, 1] = e["cur_jit"]
+    ctrl[1, :, 2] = (ctrl[1, :, 2] & 0x3FFFFFF) | (e["n_food"].astype(np.int64) << 26).astype(np.int32)
+    env.ctrl.copy_(torch.from_numpy(ctrl))
+    env.food.copy_(torch.from_numpy(np.ascontiguousarray(e["food"][:, :F].transpose(1, 0, 2)).astype(np_real)))
+    env.refresh_rng()  # the cursors were overwritten from outside
+
+
+def steering_actions(obs: np.ndarray, t: int, g: np.random.Generator, act_dim: int = 1) -> np.ndarray:
+    """Closed-loop float32 actions computed from the ORACLE's observation so that every kind of event
+    occurs: a third of the lanes steer towards the nearest food (column 13 = relative bearing / pi, the
+    recipe of oracle.validate_against_reference.seeker_actions), a third steer away from it (they end
+    on a wall), the rest hold random steering segments (they time out or drift into a wall)."""
+    n = obs.shape[0]
+    lane = np.arange(n) % 3
+    noise = 0.15 * g.standard_normal(n)
+    seek = np.clip(-0.4 * obs[:, 13] * 3.0 + noise, -1, 1)
+    flee = np.clip(+0.4 * obs[:, 13] * 3.0 + noise, -1, 1)
+    seg = np.random.default_rng(1000 + t // 60).uniform(-1, 1, n)
+    a = np.where(lane == 0, seek, np.where(lane == 1, flee, np.clip(0.7 * seg + 2 * noise, -1, 1))).astype(np.float32)
+    if act_dim == 1:
+        return a[:, None]
+    hold = (np.random.default_rng(2000 + t // 45).uniform(0, 1, n)).astype(np.float32)
+    return np.stack([hold, a], axis=1)

@@ -1,0 +1,225 @@
+"""fp32 throughput build vs the fp64 oracle -- the instantiations bench.py actually times.
+
+VERDICT round 1, "Parity hole on the very kernel BENCH times": `salp_step_kernel<float, 1, ...>` (F = 1, the
+BENCH kernel) and the 12-food kernel are compared here with the oracle THROUGH thrust steps, jitter-cache
+refills, wall bounces, food hits with respawn, timeouts and in-kernel auto-resets, INCLUDING the reward.
+
+Method (teacher forcing): every step the oracle's fp64 state is loaded into the device state, both sides
+advance one step from it, and outputs are compared -- so the numbers are single-step errors of the fp32
+arithmetic (bar 1e-3 per north_star; typical 1e-6), not accumulated chaos.  A discrete flip (an event flag
+that differs because a comparison fell on the other side of an fp32 rounding) is counted, not
+hidden: the bar is a handful per million env-steps.  The free-running test at the end measures how long
+un-synchronised fp32 trajectories keep the oracle's event stream and that episode statistics agree.
+
+Reference lines matched: scripts/utilities/salp_robot.py:261-314 (thrust), :316-352 (bounce);
+src/salp/environments/salp_snake_env.py:204-327 (food hit, wall contact, respawn, reward), :133-155 (reset).
+"""
+import numpy as np
+import pytest
+import torch
+
+from helpers import CONFIGS, push_oracle_state, py_tables, steering_actions
+
+pytestmark = pytest.mark.gpu
+
+OBS_BAR = 1e-3       # north_star: fp32 continuous state within 1e-3 per step
+REWARD_BAR = 1e-3    # relative to max(1, |reward|)
+FOOD_BAR = 1e-3      # pixels, food layouts of an in-kernel reset (f32 uniform vs f64 uniform)
+ANGLE_COLS = (4, 13, 17, 21)  # observation columns that are angles / pi
+
+
+def _env(n, params, **kw):
+    from underwater_swimmer_rl_b200 import SalpVectorEnv
+    return SalpVectorEnv(n, device="cuda:0", dtype="float32", **kw, **params)
+
+
+def _teacher_forced(oracle_lib, cfg, N, T, autoreset, seed0, extra=None, generic_kernel=False):
+    params = dict(CONFIGS[cfg], **(extra or {}))
+    act_dim = 1 if params.get("forced_breathing", True) else 2
+    fw, jw = py_tables(range(seed0, seed0 + N), 2048, 2048)
+    orc = oracle_lib.Oracle(N, fw, jw, **params)
+    obs_ref = orc.reset()
+    env = _env(N, params, autoreset=autoreset, generic_kernel=generic_kernel)
+    env.set_rng_tables(fw, jw)
+    obs0, _ = env.reset()
+    assert float(np.abs(obs0.cpu().numpy() - obs_ref).max()) <= OBS_BAR
+    F = env.food_slots
+    g = np.random.default_rng(seed0)
+    st = dict(obs=0.0, rew=0.0, reset_obs=0.0, food=0.0, flips=0, swaps=0, jets=0, refills=0, bounces=0, hits=0,
+              collisions=0, timeouts=0, resets=0, reset_flips=0, unexplained=0, flip_kinds={})
+    for t in range(T):
+        acts = steering_actions(obs_ref, t, g, act_dim)
+        push_oracle_state(env, orc)
+        e = orc.envs
+        t1 = e["timer"] + 1
+        jet = (e["phase"] == 2) & (t1 <= e["exhale_dur"]) & (10 * t1 >= e["exhale_dur"]) & (2 * t1 <= e["exhale_dur"])
+        cur_jit0 = e["cur_jit"].copy()
+        obs_ref, rew_ref, flags_ref = orc.step(acts.astype(np.float64))
+        obs, rew, term, trunc, info = env.step(torch.from_numpy(acts).cuda())
+        ev = info["events"].cpu().numpy()
+        done_ref = (flags_ref & 3) != 0
+        o = obs.cpu().numpy()
+        if autoreset:  # done lanes: `obs` is the next episode's first observation, the terminal one is in final_observation
+            o_term = np.where(done_ref[:, None], info["final_observation"].cpu().numpy(), o)
+        else:
+            o_term = o
+        same = ev == flags_ref
+        diff = np.abs(o_term - obs_ref)
+        for c in ANGLE_COLS:  # angles / pi live on a circle: -1 and +1 are the same direction
+            diff[:, c] = np.minimum(diff[:, c], 2.0 - diff[:, c])
+        err = diff.max(axis=1)
+        swapped = same & (err > OBS_BAR) & (F > 1)  # two foods tie within fp32 rounding: whole 4-float entries swap
+        ok = same & ~swapped
+        # A flip must be explained by a decision that sits on an fp32 rounding: the food is within 1e-3 px of the pick-up
+        # radius, or the robot within 1e-3 px of the bounce line (a clamp that one side took and the other did not).
+        for i in np.nonzero(~same)[0]:
+            r = max(e["a"][i], e["b"][i])
+            Wd, Hd = params.get("width", 800), params.get("height", 600)
+            wall = min(abs(e["px"][i] - (50 + r)), abs(e["px"][i] - (Wd - 50 - r)), abs(e["py"][i] - (50 + r)), abs(e["py"][i] - (Hd - 50 - r)))
+            kind = "food" if (ev[i] ^ flags_ref[i]) & 8 else ("wall" if (ev[i] ^ flags_ref[i]) & 5 else "timeout")
+            st["flip_kinds"][kind] = st["flip_kinds"].get(kind, 0) + 1
+            if kind == "timeout" or (kind == "wall" and wall > 2e-3):
+                st["unexplained"] += 1
+        st["flips"] += int((~same).sum())
+        st["swaps"] += int(swapped.sum())
+        st["obs"] = max(st["obs"], float(err[ok].max()))
+        r = rew.cpu().numpy().astype(np.float64)
+        st["rew"] = max(st["rew"], float((np.abs(r - rew_ref) / np.maximum(1.0, np.abs(rew_ref)))[ok].max()))
+        assert (term.cpu().numpy() == ((ev & 1) != 0)).all() and (trunc.cpu().numpy() == ((ev & 2) != 0)).all()
+        # which paths of the kernel did this step exercise?
+        st["jets"] += int(jet.sum())
+        st["refills"] += int((e["cur_jit"] != cur_jit0).sum())
+        m = 50.0 + np.maximum(e["a"], e["b"])  # R:335-352: a bounce leaves the robot exactly on the clamp line
+        st["bounces"] += int(((e["px"] == m) | (e["px"] == params.get("width", 800) - m) | (e["py"] == m) | (e["py"] == params.get("height", 600) - m)).sum())
+        st["hits"] += int(((flags_ref & 8) != 0).sum())
+        st["collisions"] += int(((flags_ref & 4) != 0).sum())
+        st["timeouts"] += int(((flags_ref & 2) != 0).sum())
+        # jitter cursor / cache after the step (the f32 kernel prefetches the next draw's word into ctrl rec1.w)
+        ctrl = env.ctrl.cpu().numpy()
+        nd = ok & ~(done_ref & autoreset)
+        assert (ctrl[1, nd, 1] == e["cur_jit"][nd].astype(np.int64)).all(), "jitter cursor"
+        assert (ctrl[1, nd, 0] == e["cur_food"][nd].astype(np.int64)).all(), "food cursor (respawn draws)"
+        assert (ctrl[1, nd, 3].view(np.uint32) == jw[np.nonzero(nd)[0], e["cur_jit"][nd].astype(np.int64) % jw.shape[1]]).all(), "jitter cache"
+        for i in np.nonzero(done_ref)[0]:
+            ro = orc.reset_one(int(i))
+            obs_ref[i] = ro  # the caller-style auto-reset: the next action is computed from the reset observation
+            if not autoreset or not same[i]:
+                continue
+            st["resets"] += 1
+            # S:133-155 in-kernel auto-reset: reset observation, food layout, cursor, food count vs the oracle's reset
+            good = (ctrl[1, i, 0] == int(orc.envs["cur_food"][i])) and (((ctrl[1, i, 2] >> 26) & 0x3F) == int(orc.envs["n_food"][i]))
+            if not good:  # a rejection test (80 px) fell on the other side of an fp32 rounding
+                st["reset_flips"] += 1
+                continue
+            nf = int(orc.envs["n_food"][i])
+            food = env.food[:nf, i].cpu().numpy().astype(np.float64)
+            st["food"] = max(st["food"], float(np.abs(food - orc.envs["food"][i, :nf]).max()))
+            d = np.abs(o[i] - ro)
+            for c in ANGLE_COLS:
+                d[c] = min(d[c], 2.0 - d[c])
+            if F > 1 and d.max() > OBS_BAR:
+                st["swaps"] += 1
+            else:
+                st["reset_obs"] = max(st["reset_obs"], float(d.max()))
+    return st
+
+
+CASES = [
+    # cfg, N, T, autoreset, first seed, extra params, generic kernel
+    ("single_food", 768, 1700, True, 61_000, None, False),                 # BENCH kernel salp_step_fast_kernel<1, 0>, auto-reset on
+    ("single_food", 384, 1700, False, 62_000, None, False),                # same kernel, caller-style reset
+    ("single_food_long_horizon", 768, 2300, True, 63_000, None, False),    # configs[2]: timeouts at 2000, collision penalty -500
+    ("defaults", 512, 1600, True, 64_000, None, False),                    # salp_step_fast_kernel<12, 0>: warp-cooperative reset + second obs pass
+    ("defaults", 384, 1500, False, 65_000, dict(proximity_reward_weight=2.0), False),  # 12 foods with the alignment reward
+    ("single_food", 384, 1500, True, 66_000, dict(forced_breathing=False), False),     # manual breathing: generic kernel <float, 1, ...>
+    ("single_food", 384, 1700, True, 67_000, None, True),                  # the generic f32 kernel on the forced configs (K > 1 launches, odd slabs)
+    ("defaults", 384, 1600, True, 68_000, None, True),
+    ("single_food", 777, 400, True, 69_000, None, False),                  # slab that ends in a partial tile (777 = 24 * 32 + 9)
+]
+
+
+@pytest.mark.parametrize("cfg,N,T,autoreset,seed0,extra,generic", CASES)
+def test_fp32_teacher_forced_through_every_event(cfg, N, T, autoreset, seed0, extra, generic, oracle_lib, salp_lib):
+    st = _teacher_forced(oracle_lib, cfg, N, T, autoreset, seed0, extra, generic)
+    if T < 1000:  # short case: only the numbers
+        assert st["obs"] <= OBS_BAR and st["rew"] <= REWARD_BAR and st["unexplained"] == 0 and st["jets"] > 0, st
+        return
+    print(f"\n[fp32 parity] {cfg} N={N} T={T} autoreset={autoreset} extra={extra}: {st}")
+    # every path was walked
+    assert st["jets"] > N and st["refills"] > N, "thrust steps / jitter-cache refills"
+    assert st["bounces"] > 0 and st["collisions"] > 0, "wall bounces and wall contacts"
+    assert st["hits"] > 0, "food hits (and respawns)"
+    if cfg.startswith("single_food") and not extra:
+        assert st["timeouts"] > 0, "episodes that end by max_steps_without_food"
+    if autoreset:
+        assert st["resets"] > 40, "in-kernel auto-resets compared with the oracle's reset"
+    # and the numbers hold
+    assert st["obs"] <= OBS_BAR and st["rew"] <= REWARD_BAR, st
+    assert st["reset_obs"] <= OBS_BAR and st["food"] <= FOOD_BAR, st
+    # Discrete flips.  Wall contacts are decided in double from the integer shape state on the clamp branch, so
+    # the only flips left are decisions that sit within an fp32 rounding of their threshold: bar 10 per million env-steps,
+    # none unexplained (a flip of the integer timeout, or a wall flip with the robot farther than 2e-3 px from the line).
+    n_steps = N * T
+    assert st["unexplained"] == 0, st
+    assert st["flips"] <= max(3, n_steps // 100_000), f"{st['flips']} event flips in {n_steps} teacher-forced fp32 steps: {st['flip_kinds']}"
+    assert st["swaps"] <= max(3, n_steps // 100_000) and st["reset_flips"] <= 2, st
+
+
+def test_fp32_free_running_long_horizon_65536(oracle_lib, salp_lib):
+    """BASELINE configs[2]: single_food_long_horizon, 65 536 envs, fp32, 5 000 steps, NOT teacher-forced, against
+    the OpenMP oracle on the same seeds and open-loop actions.  fp32 and fp64 trajectories separate (positions are
+    chaotic through the wall bounces), so this measures (a) the fraction of envs whose complete event stream
+    (terminated / truncated / collision / food, every step) is still identical to the oracle's at t = 300 / 1000 /
+    5000, and (b) that the episode statistics of the two populations agree within their sampling error."""
+    from underwater_swimmer_rl_b200 import rng_tables
+    N, T, K = 65_536, 5_000, 50
+    params = CONFIGS["single_food_long_horizon"]
+    fw = rng_tables.fill_words(N, 256, 70_000, 0, rng_tables.FOOD_STREAM)
+    jw = rng_tables.fill_words(N, 2048, 70_000, 0, rng_tables.JITTER_STREAM)
+    orc = oracle_lib.Oracle(N, fw, jw, **params)
+    orc.reset()
+    env = _env(N, params, autoreset=True, max_substeps=K)
+    env.set_rng_tables(fw, jw)
+    env.reset()
+    g = np.random.default_rng(4242)
+    first_diff = np.full(N, T, np.int64)
+    ref_stats = np.zeros(4, np.int64)
+    ref_ret = 0.0
+    CH = 500
+    ep_len_ref, ep_len_gpu = [], []
+    last_ref, last_gpu = np.zeros(N, np.int64), np.zeros(N, np.int64)
+    for t0 in range(0, T, CH):
+        seg = np.repeat(g.uniform(-1, 1, (CH // 50, N, 1)), 50, axis=0)
+        acts = np.clip(0.6 * seg + 0.4 * g.uniform(-1, 1, (CH, N, 1)), -1, 1).astype(np.float32)
+        ref = orc.rollout(acts, autoreset=True, record="flags")
+        ref_stats += ref["stats"][:4]
+        ref_ret += ref["return_sum"]
+        a_dev = torch.from_numpy(acts).cuda()
+        evs = []
+        for k0 in range(0, CH, K):
+            _, _, _, _, info = env.step_many(a_dev[k0:k0 + K])
+            evs.append(info["events"].clone())
+        ev = torch.cat(evs).cpu().numpy()
+        neq = ev != ref["flags"]
+        idx = np.where(neq.any(0), neq.argmax(0) + t0, T)
+        first_diff = np.minimum(first_diff, idx)
+        for flags, last, out in ((ref["flags"], last_ref, ep_len_ref), (ev, last_gpu, ep_len_gpu)):
+            tt, ee = np.nonzero(flags & 3)
+            for t_, e_ in zip(tt + t0, ee):  # episode lengths in order of completion
+                out.append(t_ + 1 - last[e_])
+                last[e_] = t_ + 1
+    same_at = {t: float((first_diff >= t).mean()) for t in (300, 1000, 2000, 5000)}
+    s = env.episode_stats()
+    la, lb = np.array(ep_len_ref, float), np.array(ep_len_gpu, float)
+    se = np.sqrt(la.var() / la.size + lb.var() / lb.size)
+    msg = (f"\n[fp32 free-running, 65536 x 5000] event stream identical to the oracle's up to t: {same_at}; episodes ref/gpu "
+           f"{la.size}/{lb.size}; mean length {la.mean():.2f}/{lb.mean():.2f} (se {se:.2f}); collisions {ref_stats[2]}/{int(s['collisions'])}; "
+           f"truncations {ref_stats[3]}/{int(s['truncations'])}; food {ref_stats[1]}/{int(s['food_sum'])}+open")
+    print(msg)
+    assert s["episodes"] == lb.size and s["nonfinite"] == 0 and s["env_steps"] == N * T
+    # (a) the first jet fires at step ~137; up to t = 300 only fp32 rounding separates the runs
+    assert same_at[300] >= 0.999 and same_at[1000] >= 0.90, msg
+    # (b) same population statistics: means within 5 standard errors (+ 0.1 % slack), event counts within 2 %
+    assert abs(la.mean() - lb.mean()) <= 5 * se + 1e-3 * la.mean(), msg
+    assert abs(la.size - lb.size) <= 0.02 * la.size and abs(ref_stats[2] - s["collisions"]) <= 0.02 * max(ref_stats[2], 1), msg
+    assert abs(ref_stats[3] - s["truncations"]) <= 0.05 * max(ref_stats[3], 20) + 10, msg

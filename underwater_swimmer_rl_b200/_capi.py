@@ -11,16 +11,16 @@ import os
 _PKG = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_PKG, "libsalp_b200.so")
 
-SALP_ABI_VERSION = 4
+SALP_ABI_VERSION = 5
 SALP_OK, SALP_EINVAL, SALP_ECUDA, SALP_EUNBOUND, SALP_EUNSUPPORTED = 0, -1, -2, -3, -4
 SALP_F32, SALP_F64 = 0, 1
-SALP_AUTORESET = 1
+SALP_AUTORESET, SALP_RNG_PHILOX, SALP_GENERIC_KERNEL = 1, 2, 4
 EV_TERMINATED, EV_TRUNCATED, EV_COLLISION, EV_FOOD = 1, 2, 4, 8
 
 # every symbol include/salp_b200.h declares (tests/test_capi_symbols.py parses the header too)
 EXPORTED_SYMBOLS = (
     "salp_abi_version", "salp_last_error", "salp_query_layout", "salp_create", "salp_destroy", "salp_bind",
-    "salp_reset", "salp_refresh_rng", "salp_step", "salp_step_slot", "salp_step_host", "salp_fill_rng_words", "salp_launch_count", "salp_replay_append", "salp_actor_forward",
+    "salp_reset", "salp_refresh_rng", "salp_observe", "salp_set_num_food_items", "salp_set_rng_seed", "salp_forced_cycle", "salp_step", "salp_step_slot", "salp_step_host", "salp_fill_rng_words", "salp_launch_count", "salp_replay_append", "salp_actor_forward",
     "salp_cycle_reset", "salp_cycle_step",
 )
 SALP_CYCLE_AUTORESET = 1
@@ -115,6 +115,10 @@ def load():
     L.salp_bind.argtypes = [C.c_void_p, C.POINTER(SalpBuffers)]
     L.salp_reset.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
     L.salp_refresh_rng.argtypes = [C.c_void_p, C.c_void_p]
+    L.salp_observe.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+    L.salp_set_num_food_items.argtypes = [C.c_void_p, C.c_int32]
+    L.salp_set_rng_seed.argtypes = [C.c_void_p, C.c_uint64]
+    L.salp_forced_cycle.argtypes = [C.POINTER(SalpParams)] + [C.c_void_p] * 5
     L.salp_step.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
     L.salp_step_slot.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
     L.salp_step_host.argtypes = [C.c_void_p] + [C.c_void_p] * 6

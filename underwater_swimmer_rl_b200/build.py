@@ -2,10 +2,11 @@
 
     python -m underwater_swimmer_rl_b200.build [--force] [--verbose]
 
-Eight translation units, compiled in parallel:
+Nine translation units, compiled in parallel:
   salp_kernels.cu  -DSALP_BUILD_F64=0               float   kernels (throughput build)
   salp_kernels.cu  -DSALP_BUILD_F64=1 -fmad=false   double  kernels (validation build: no FMA
                                                     contraction, reference operation order)
+  salp_kernels_fast.cu                              forced-breathing f32 kernel: persistent warps, TMA in/out, cycle table
   salp_capi.cu                                      extern "C" boundary (include/salp_b200.h)
   salp_replay.cu                                    rollout -> replay ring-buffer append kernel
   salp_actor.cu                                     fused actor MLP (tcgen05 / TMEM) of the rollout loop
@@ -46,6 +47,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
     os.makedirs(OBJ, exist_ok=True)
     hdrs = _sources()
     kern = os.path.join(CSRC, "salp_kernels.cu")
+    fast = os.path.join(CSRC, "salp_kernels_fast.cu")
     capi = os.path.join(CSRC, "salp_capi.cu")
     replay = os.path.join(CSRC, "salp_replay.cu")
     actor = os.path.join(CSRC, "salp_actor.cu")
@@ -56,6 +58,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
     actor_defs = os.environ.get("SALP_ACTOR_DEFS", "").split()  # developer builds, e.g. SALP_ACTOR_DEFS=-DSALP_ACTOR_TRACE
     jobs = [
         (os.path.join(OBJ, "salp_kernels_f32.o"), [NVCC, "-c", kern, "-DSALP_BUILD_F64=0"] + COMMON + vflag + step_defs, [kern] + hdrs),
+        (os.path.join(OBJ, "salp_kernels_fast.o"), [NVCC, "-c", fast] + COMMON + vflag + step_defs, [fast] + hdrs),
         (os.path.join(OBJ, "salp_kernels_f64.o"), [NVCC, "-c", kern, "-DSALP_BUILD_F64=1", "-fmad=false"] + COMMON + vflag, [kern] + hdrs),
         (os.path.join(OBJ, "salp_capi.o"), [NVCC, "-c", capi] + COMMON, [capi] + hdrs),
         (os.path.join(OBJ, "salp_replay.o"), [NVCC, "-c", replay] + COMMON, [replay] + hdrs),

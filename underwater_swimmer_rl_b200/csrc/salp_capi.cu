@@ -16,6 +16,7 @@
 
 #include "../../include/salp_b200.h"
 #include "salp_internal.h"
+#include "salp_shape_host.h"
 
 namespace {
 
@@ -56,6 +57,66 @@ namespace salp {
 int set_error(int code, const char *msg) { return fail(code, "%s", msg); }  // for the other translation units
 }  // namespace salp
 
+namespace salp {
+
+// Forced breathing (R:158-167 `(breathing_timer % 330) < 120`): the FSM, the body shape, the water volume and the thrust
+// window are functions of the position in the 273-step cycle.  Run the reference's update (R:184-259) once on
+// the host, in double, for two cycles from the reset state and keep the second one (its fsm words carry the steady-state
+// exhale duration of 150, which is also what R:233's getattr default gives before the first exhale).
+// out[0] = fresh reset; out[i], i = 1..273 = after the i-th step of a cycle.  wv64 / a64 / b64 (optional) receive the
+// doubles the entries were rounded from (salp_forced_cycle: tests check them bit-for-bit against the fp64 kernel).
+void build_forced_cycle(double W, double H, const uint8_t *exhale_lut, CycleEntry *out, double *wv64, double *a64, double *b64) {
+    int phase = kPhaseRest, timer = 0, exd = 0, skind = kShapeReset, stimer = 0;
+    double wv = 0.0;
+    auto emit = [&](int i, double tm) {
+        double ea, eb;
+        shape_axes_f64(skind, stimer, exd, ea, eb);
+        const double r = eb > ea ? eb : ea;
+        CycleEntry &c = out[i];
+        c.radius = (float)r;
+        c.tm = (float)tm;
+        c.wv = (float)wv;
+        const uint32_t fsm = (uint32_t)(phase | (timer << 2) | (exd << 10) | (skind << 18) | (stimer << 20));
+        c.fsm_touch = fsm | (wall_touch_bits_r(r, W, H) << 28);
+        c.margin = (float)(kc::TANK_MARGIN + r);
+        c.reach = (float)(r + kc::FOOD_R);
+        c.obs6 = (float)(r / kc::BASE_R);
+        c.obs7 = (float)((double)phase / 2.0);
+        if (wv64) wv64[i] = wv;
+        if (a64) a64[i] = ea;
+        if (b64) b64[i] = eb;
+    };
+    emit(0, 0.0);
+    for (int pass = 0; pass < 2; ++pass)
+        for (int i = 1; i < kCycleLen; ++i) {
+            const bool inhaling = timer < kc::INHALE_DUR;  // timer <= 151 < 330: the modulo is the identity
+            const int t1 = timer + 1;
+            const bool thrust = (phase == kPhaseExhale) && (t1 <= exd) && (10 * t1 >= exd) && (2 * t1 <= exd);
+            int wv_mode = 0;
+            if (phase == kPhaseRest) {
+                skind = kShapeRest;
+                if (inhaling) { phase = kPhaseInhale; timer = 0; }
+            } else if (phase == kPhaseInhale) {
+                if (inhaling && timer < kc::INHALE_DUR) { ++timer; skind = kShapeInhale; stimer = timer; wv_mode = 1; }
+                else if (wv > 0.05) { exd = exhale_lut[timer]; phase = kPhaseExhale; timer = 0; }
+                else { phase = kPhaseRest; timer = 0; wv_mode = 3; }
+            } else {
+                ++timer;
+                if (timer <= exd) { skind = kShapeExhale; stimer = timer; wv_mode = 2; }
+                else { phase = kPhaseRest; timer = 0; wv_mode = 3; }
+            }
+            const double prog = (skind == kShapeInhale) ? (double)stimer / (double)kc::INHALE_DUR
+                                                        : (skind == kShapeExhale ? (double)stimer / (double)exd : 0.0);
+            if (wv_mode == 1) wv = prog;
+            const double tm = thrust ? 100.0 * wv * 0.4 : 0.0;  // R:268, uses water_volume before this step's decay
+            if (wv_mode == 2) { const double w2 = wv * (1.0 - prog); wv = w2 > 0.0 ? w2 : 0.0; }
+            else if (wv_mode == 3) wv = 0.0;
+            if (pass == 1) emit(i, tm);
+        }
+}
+
+}  // namespace salp
+
 struct SalpHandle {
     SalpParams params;
     SalpLayout layout;
@@ -67,6 +128,7 @@ struct SalpHandle {
     int64_t launches;
     cudaStream_t host_streams[kHostChunks];
     bool host_streams_ready;
+    salp::CycleEntry *cycle_tab;  // device copy of the forced-breathing cycle table (handle-owned parameter data)
 };
 
 extern "C" {
@@ -151,12 +213,49 @@ int salp_create(const SalpParams *p, int64_t num_envs, int64_t env_id0, int devi
         const double wv = (double)std::min(t, 120) / 120.0;
         a.exhale_lut[t] = (uint8_t)(int)(150.0 * std::max(wv, 0.3));
     }
+    a.fW = (float)a.W; a.fH = (float)a.H; a.f_diag = (float)a.diag;
+    a.f_inv_w = (float)a.inv_w; a.f_inv_h = (float)a.inv_h; a.f_inv_diag = (float)a.inv_diag;
+    a.f_food_reward = (float)p->food_reward; a.f_collision_penalty = (float)p->collision_penalty;
+    a.f_time_penalty = (float)p->time_penalty; a.f_efficiency_bonus = (float)p->efficiency_bonus;
+    a.f_proximity_w = (float)p->proximity_reward_weight;
+    a.rng_mode = (p->flags & SALP_RNG_PHILOX) ? 1 : 0;
+    a.rng_seed = 0;
+    a.env_id0 = env_id0;
+    {   // forced-breathing cycle table: parameter data of the handle, like the exhale LUT, but too large for the constant bank
+        salp::CycleEntry tab[salp::kCycleLen];
+        salp::build_forced_cycle(a.W, a.H, a.exhale_lut, tab, nullptr, nullptr, nullptr);
+        cudaError_t ce = cudaSetDevice(device);
+        if (ce == cudaSuccess) ce = cudaMalloc(&h->cycle_tab, sizeof(tab));
+        if (ce == cudaSuccess) ce = cudaMemcpy(h->cycle_tab, tab, sizeof(tab), cudaMemcpyHostToDevice);
+        if (ce != cudaSuccess) { if (h->cycle_tab) cudaFree(h->cycle_tab); delete h; return cuda_fail(ce, "forced-breathing cycle table"); }
+        a.cycle_tab = h->cycle_tab;
+    }
     *out = h;
+    return SALP_OK;
+}
+
+int salp_forced_cycle(const SalpParams *p, double *wv, double *ellipse_a, double *ellipse_b, int32_t *fsm, int32_t *touch) {
+    if (!p) return fail(SALP_EINVAL, "null argument");
+    uint8_t lut[128];
+    for (int t = 0; t < 128; ++t) lut[t] = (uint8_t)(int)(150.0 * std::max((double)std::min(t, 120) / 120.0, 0.3));
+    salp::CycleEntry tab[salp::kCycleLen];
+    salp::build_forced_cycle(p->width, p->height, lut, tab, wv, ellipse_a, ellipse_b);
+    for (int i = 0; i < salp::kCycleLen; ++i) {
+        if (fsm) fsm[i] = (int32_t)(tab[i].fsm_touch & 0x0fffffffu);
+        if (touch) touch[i] = (int32_t)(tab[i].fsm_touch >> 28);
+    }
+    return SALP_OK;
+}
+
+int salp_set_rng_seed(SalpHandle *h, uint64_t seed) {
+    if (!h) return fail(SALP_EINVAL, "null handle");
+    h->base.rng_seed = seed;
     return SALP_OK;
 }
 
 int salp_destroy(SalpHandle *h) {
     if (!h) return SALP_OK;
+    if (h->cycle_tab) { cudaSetDevice(h->device); cudaFree(h->cycle_tab); }
     if (h->host_streams_ready) {
         cudaSetDevice(h->device);
         for (auto &s : h->host_streams) cudaStreamDestroy(s);
@@ -169,11 +268,14 @@ int salp_bind(SalpHandle *h, const SalpBuffers *b) {
     if (!h || !b) return fail(SALP_EINVAL, "null argument");
     if (!b->body || !b->ctrl || !b->ep_return || !b->food || !b->obs || !b->reward || !b->terminated || !b->truncated)
         return fail(SALP_EINVAL, "body/ctrl/ep_return/food/obs/reward/terminated/truncated must be non-null");
-    if (!b->food_words || !b->jit_words) return fail(SALP_EINVAL, "RNG word tables must be non-null");
-    if (b->table_rows <= 0 || b->table_rows > h->num_envs) return fail(SALP_EINVAL, "table_rows must be in 1..num_envs");
-    if (!is_pow2(b->food_len) || !is_pow2(b->jit_len) || b->jit_len < 2 || b->food_len < 2)
-        return fail(SALP_EINVAL, "food_len/jit_len must be powers of two >= 2");
-    if (b->food_len > ((int64_t)1 << 30) || b->jit_len > ((int64_t)1 << 30)) return fail(SALP_EINVAL, "table rows too long");
+    const bool philox = (h->params.flags & SALP_RNG_PHILOX) != 0;
+    if (!philox) {
+        if (!b->food_words || !b->jit_words) return fail(SALP_EINVAL, "RNG word tables must be non-null (or create the handle with SALP_RNG_PHILOX)");
+        if (b->table_rows <= 0 || b->table_rows > h->num_envs) return fail(SALP_EINVAL, "table_rows must be in 1..num_envs");
+        if (!is_pow2(b->food_len) || !is_pow2(b->jit_len) || b->jit_len < 2 || b->food_len < 2)
+            return fail(SALP_EINVAL, "food_len/jit_len must be powers of two >= 2");
+        if (b->food_len > ((int64_t)1 << 30) || b->jit_len > ((int64_t)1 << 30)) return fail(SALP_EINVAL, "table rows too long");
+    }
     if (b->max_substeps < 1) return fail(SALP_EINVAL, "max_substeps must be >= 1");
     const uintptr_t align16[] = {(uintptr_t)b->body, (uintptr_t)b->ctrl, (uintptr_t)b->food, (uintptr_t)b->obs,
                                  (uintptr_t)b->final_obs, (uintptr_t)b->final_info, (uintptr_t)b->jit_words};
@@ -195,18 +297,25 @@ int salp_bind(SalpHandle *h, const SalpBuffers *b) {
     a.stats = b->stats;
     a.food_words = b->food_words;
     a.jit_words = b->jit_words;
-    a.rows = (unsigned)b->table_rows;
-    a.food_len = (unsigned)b->food_len;
-    a.jit_len = (unsigned)b->jit_len;
-    a.food_len_mask = (unsigned)b->food_len - 1;
-    a.jit_len_mask = (unsigned)b->jit_len - 1;
+    a.rows = philox ? 1u : (unsigned)b->table_rows;
+    a.food_len = philox ? 2u : (unsigned)b->food_len;
+    a.jit_len = philox ? 2u : (unsigned)b->jit_len;
+    a.food_len_mask = a.food_len - 1;
+    a.jit_len_mask = a.jit_len - 1;
     h->bound = true;
     return SALP_OK;
 }
 
 static int launch_step(SalpHandle *h, const salp::KernelArgs &a, cudaStream_t s) {
-    cudaError_t e = h->dtype == SALP_F64 ? salp::launch_step_f64(a, h->layout.food_slots, s)
-                                         : salp::launch_step_f32(a, h->layout.food_slots, s);
+    cudaError_t e;
+    bool handled = false;
+    if (h->dtype == SALP_F32 && !(h->params.flags & SALP_GENERIC_KERNEL)) {
+        e = salp::launch_step_fast_f32(a, h->layout.food_slots, s, &handled);  // forced breathing, 1 / 12 foods, 3 observed
+        if (e != cudaSuccess) return cuda_fail(e, "salp_step (forced-cycle kernel) launch");
+    }
+    if (!handled)
+        e = h->dtype == SALP_F64 ? salp::launch_step_f64(a, h->layout.food_slots, s)
+                                 : salp::launch_step_f32(a, h->layout.food_slots, s);
     if (e != cudaSuccess) return cuda_fail(e, "salp_step kernel launch");
     ++h->launches;
     return SALP_OK;
@@ -233,6 +342,30 @@ int salp_refresh_rng(SalpHandle *h, void *stream) {
     cudaError_t e = salp::launch_refresh_rng(h->base, (cudaStream_t)stream);
     if (e != cudaSuccess) return cuda_fail(e, "salp_refresh_rng kernel launch");
     ++h->launches;
+    return SALP_OK;
+}
+
+int salp_observe(SalpHandle *h, int slot, void *stream) {
+    if (!h) return fail(SALP_EINVAL, "null handle");
+    if (!h->bound) return fail(SALP_EUNBOUND, "salp_bind has not been called");
+    if (slot < 0 || slot >= h->buf.max_substeps) return fail(SALP_EINVAL, "slot=%d outside 0..max_substeps-1=%d", slot, h->buf.max_substeps - 1);
+    SALP_CUDA(cudaSetDevice(h->device));
+    salp::KernelArgs a = h->base;
+    a.obs += (size_t)h->num_envs * (size_t)slot * (size_t)h->layout.obs_dim;
+    cudaError_t e = h->dtype == SALP_F64 ? salp::launch_observe_f64(a, (cudaStream_t)stream) : salp::launch_observe_f32(a, (cudaStream_t)stream);
+    if (e != cudaSuccess) return cuda_fail(e, "salp_observe kernel launch");
+    ++h->launches;
+    return SALP_OK;
+}
+
+int salp_set_num_food_items(SalpHandle *h, int32_t num_food_items) {
+    if (!h) return fail(SALP_EINVAL, "null handle");
+    if (num_food_items < 0) num_food_items = 0;  // S:36 max(0, num_food_items)
+    if (num_food_items > h->layout.food_slots)
+        return fail(SALP_EUNSUPPORTED, "num_food_items=%d exceeds the %d food slots this handle was created with; create a new handle",
+                    (int)num_food_items, (int)h->layout.food_slots);
+    h->params.num_food_items = num_food_items;
+    h->base.num_food = num_food_items;
     return SALP_OK;
 }
 

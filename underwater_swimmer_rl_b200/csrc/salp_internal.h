@@ -16,6 +16,22 @@ constexpr int kPhaseRest = 0, kPhaseInhale = 1, kPhaseExhale = 2;
 constexpr int kEpLenMask = (1 << 26) - 1;  // ctrl rec1.z = episode_len (26 bits, saturating) | n_food << 26
 constexpr int kShapeReset = 0, kShapeRest = 1, kShapeInhale = 2, kShapeExhale = 3;
 
+// One entry per position of the forced-breathing cycle: index 0 = fresh reset (R:95-117), 1..273 = state after the
+// 1 rest + 121 inhale + 151 exhale steps of a cycle.  Built on the host in double with the reference's
+// expressions (R:184-259) and rounded once; 32 bytes = two 128-bit loads.
+struct CycleEntry {
+    float radius;        // max(ellipse_a, ellipse_b) after this step's FSM update (R:190-191,207-213,240-246)
+    float tm;            // jet thrust 100 * water_volume * 0.4 of this step (R:268), 0 outside the thrust window
+    float wv;            // water_volume after this step (R:215,253,258)
+    uint32_t fsm_touch;  // bits 0..27: fsm word after this step; bits 28..30: does a clamp onto the low / right / bottom
+                         // wall register as a wall contact -- (50+r)-r <= 50, (W-(50+r))+r >= W-50, same with H -- evaluated
+                         // in DOUBLE exactly as the reference does (R:335-352 + S:225-228)
+    float margin;        // 50 + radius
+    float reach;         // radius + 15 (food pick-up distance, S:209-212)
+    float obs6, obs7;    // radius / 30, phase / 2 (observation columns 6, 7)
+};
+constexpr int kCycleLen = 274;
+
 // Passed by value as a __grid_constant__ kernel parameter (lives in the constant bank).
 struct KernelArgs {
     void *body;        // real [2][N][4]
@@ -39,13 +55,28 @@ struct KernelArgs {
     double W, H, food_reward, collision_penalty, time_penalty, efficiency_bonus, proximity_w;
     double diag, inv_w, inv_h, inv_diag;  // sqrt(W^2+H^2) and reciprocals, computed once on the host
     uint8_t exhale_lut[128];  // int(150 * max(t/120, 0.3)) for inhale timer t (R:223)
+    // ---- f32 throughput build: the same constants rounded once on the host (a per-thread F2F.F32.F64 is an XU-pipe op)
+    float fW, fH, f_inv_w, f_inv_h, f_inv_diag, f_diag;
+    float f_food_reward, f_collision_penalty, f_time_penalty, f_efficiency_bonus, f_proximity_w;
+    // ---- forced breathing: everything the breathing subsystem contributes to a step is a function of the position in
+    //      the 273-step cycle; table of kCycleLen entries in device memory owned by the handle
+    const CycleEntry *cycle_tab;
+    // ---- RNG word source: 0 = host-seeded MT19937 tables (parity with the reference), 1 = Philox4x32-10 computed in the
+    //      kernel, keyed by rng_seed, counter (word index / 4, stream, global env id); see include/salp_b200.h
+    int rng_mode;
+    unsigned long long rng_seed;
+    long long env_id0;          // global id of env 0 of this handle
 };
+
+cudaError_t launch_step_fast_f32(const KernelArgs &a, int food_slots, cudaStream_t s, bool *handled);
 
 // food_slots must be one of 1, 2, 4, 8, 12, 16, 32
 cudaError_t launch_step_f32(const KernelArgs &a, int food_slots, cudaStream_t s);
 cudaError_t launch_step_f64(const KernelArgs &a, int food_slots, cudaStream_t s);
 cudaError_t launch_reset_f32(const KernelArgs &a, int food_slots, cudaStream_t s);
 cudaError_t launch_reset_f64(const KernelArgs &a, int food_slots, cudaStream_t s);
+cudaError_t launch_observe_f32(const KernelArgs &a, cudaStream_t s);
+cudaError_t launch_observe_f64(const KernelArgs &a, cudaStream_t s);
 cudaError_t launch_refresh_rng(const KernelArgs &a, cudaStream_t s);  // defined in the f32 translation unit
 
 }  // namespace salp

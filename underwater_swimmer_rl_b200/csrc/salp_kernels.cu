@@ -10,10 +10,12 @@ namespace salp {
 using real_t = double;
 #define SALP_LAUNCH_STEP launch_step_f64
 #define SALP_LAUNCH_RESET launch_reset_f64
+#define SALP_LAUNCH_OBSERVE launch_observe_f64
 #else
 using real_t = float;
 #define SALP_LAUNCH_STEP launch_step_f32
 #define SALP_LAUNCH_RESET launch_reset_f32
+#define SALP_LAUNCH_OBSERVE launch_observe_f32
 #endif
 
 // Launch configuration per food-slot count, chosen from tools/kernel_lab.cu timings on B200
@@ -53,6 +55,12 @@ cudaError_t SALP_LAUNCH_RESET(const KernelArgs &a, int /*food_slots*/, cudaStrea
     if (a.count <= 0) return cudaSuccess;
     const unsigned grid = (unsigned)((a.count + 255) / 256);
     salp_reset_kernel<real_t><<<grid, 256, 0, s>>>(a);
+    return cudaGetLastError();
+}
+
+cudaError_t SALP_LAUNCH_OBSERVE(const KernelArgs &a, cudaStream_t s) {
+    if (a.count <= 0) return cudaSuccess;
+    salp_observe_kernel<real_t><<<(unsigned)((a.count + 127) / 128), 128, 0, s>>>(a);
     return cudaGetLastError();
 }
 

@@ -22,6 +22,7 @@
 #include <math_constants.h>
 
 #include "salp_internal.h"
+#include "salp_shape_host.h"
 #include "salp_sortnets.cuh"
 
 namespace salp {
@@ -29,21 +30,22 @@ namespace salp {
 template <typename T> struct alignas(4 * sizeof(T)) Vec4 { T x, y, z, w; };
 template <typename T> struct alignas(2 * sizeof(T)) Vec2 { T x, y; };
 
-// Model constants, evaluated in double exactly as the Python expressions are (R:34-53, S:53-54).
-namespace kc {
-constexpr double PI = 3.141592653589793;   // math.pi
-constexpr double TWO_PI = 2 * PI;
-constexpr double MAX_NOZZLE = PI / 3;      // R:47
-constexpr double HALF_PI = PI / 2;         // R:301
-constexpr double TANK_MARGIN = 50.0, BASE_R = 30.0, FOOD_R = 15.0, MIN_FOOD_DIST = 80.0;
-constexpr double A_REST = BASE_R * 1.3, B_REST = BASE_R * 0.8;  // R:190-191
-constexpr double A_FULL = BASE_R * 1.1, B_FULL = BASE_R * 1.1;  // R:209-210
-constexpr double NOZZLE_RATE = 0.05;       // R:48
-constexpr int INHALE_DUR = 120;            // R:51
-}  // namespace kc
 
 template <typename T> struct is_f64 { static constexpr bool value = false; };
 template <> struct is_f64<double> { static constexpr bool value = true; };
+
+// Task constants in the build's real type: the doubles of the parameter block (validation build) or their float
+// roundings made once on the host (throughput build; a per-thread double -> float conversion is an XU-pipe op).
+#define SALP_CONST(name, dfield, ffield)                                                             \
+    template <typename T> __device__ __forceinline__ T name(const KernelArgs &a) {                  \
+        if constexpr (is_f64<T>::value) return a.dfield; else return a.ffield;                     \
+    }
+SALP_CONST(c_W, W, fW) SALP_CONST(c_H, H, fH) SALP_CONST(c_diag, diag, f_diag)
+SALP_CONST(c_inv_w, inv_w, f_inv_w) SALP_CONST(c_inv_h, inv_h, f_inv_h) SALP_CONST(c_inv_diag, inv_diag, f_inv_diag)
+SALP_CONST(c_food_reward, food_reward, f_food_reward) SALP_CONST(c_collision_penalty, collision_penalty, f_collision_penalty)
+SALP_CONST(c_time_penalty, time_penalty, f_time_penalty) SALP_CONST(c_efficiency_bonus, efficiency_bonus, f_efficiency_bonus)
+SALP_CONST(c_proximity_w, proximity_w, f_proximity_w)
+#undef SALP_CONST
 
 #ifdef SALP_LAB_NOMATH  // tools/kernel_lab.cu only: how much of the step is transcendental math?
 __device__ __forceinline__ float sqrt_(float x) { return x * 0.5f; }
@@ -117,6 +119,12 @@ template <typename T> __device__ __forceinline__ T divc(T x, double c) {
     else return x * (float)(1.0 / c);
 }
 
+static __device__ __noinline__ unsigned wall_touch_bits(int skind, int stimer, int exd, double W, double H) {
+    double ea, eb;
+    shape_axes_f64(skind, stimer, exd, ea, eb);
+    return wall_touch_bits_r(eb > ea ? eb : ea, W, H);
+}
+
 // R:329-332, S:311-314, S:403-406:  while x > pi: x -= 2pi;  while x < -pi: x += 2pi.
 // One predicated correction per direction reproduces the loops' first iterations (same operations,
 // same order, bit-identical) and is all that ever runs for values the model itself produces
@@ -137,13 +145,44 @@ template <typename T> __device__ __forceinline__ T wrap_pi(T x) {
 __device__ __forceinline__ double res53(uint32_t w0, uint32_t w1) {
     return ((double)(w0 >> 5) * 67108864.0 + (double)(w1 >> 6)) * (1.0 / 9007199254740992.0);
 }
-__device__ __forceinline__ uint32_t food_word(const KernelArgs &a, unsigned row, unsigned &cur) {
-    const uint32_t w = a.food_words[(size_t)row * a.food_len + (cur & a.food_len_mask)];
+// Philox4x32-10 (Salmon et al., SC'11).  rng_mode 1: word w of stream s (0 = the `random` stream of food
+// positions, 1 = the `np.random` stream of thrust jitter) of the env with GLOBAL id g is
+//     philox4x32_10(counter = (w >> 2, s, g_lo, g_hi), key = (seed_lo, seed_hi))[w & 3]
+// -- unbounded, aperiodic streams that need no memory and do not depend on how envs are sharded over GPUs.
+__device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint2 k) {
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        const uint32_t hi0 = __umulhi(0xD2511F53u, c.x), lo0 = 0xD2511F53u * c.x;
+        const uint32_t hi1 = __umulhi(0xCD9E8D57u, c.z), lo1 = 0xCD9E8D57u * c.z;
+        c = make_uint4(hi1 ^ c.y ^ k.x, lo1, hi0 ^ c.w ^ k.y, lo0);
+        k.x += 0x9E3779B9u; k.y += 0xBB67AE85u;
+    }
+    return c;
+}
+__device__ __forceinline__ uint4 philox_block(const KernelArgs &a, unsigned e, unsigned stream, unsigned w) {
+    const unsigned long long g = (unsigned long long)a.env_id0 + e;
+    return philox4x32_10(make_uint4(w >> 2, stream, (uint32_t)g, (uint32_t)(g >> 32)),
+                         make_uint2((uint32_t)a.rng_seed, (uint32_t)(a.rng_seed >> 32)));
+}
+__device__ __forceinline__ uint32_t pick_word(uint4 r, unsigned w) {
+    const unsigned i = w & 3u;
+    return i == 0 ? r.x : (i == 1 ? r.y : (i == 2 ? r.z : r.w));
+}
+// the pair of words (w, w + 1) of the jitter stream, w even (np.random.random() consumes two words, R:311)
+__device__ __forceinline__ uint2 philox_jitter_pair(const KernelArgs &a, unsigned e, unsigned w) {
+    const uint4 r = philox_block(a, e, 1u, w);
+    return (w & 2u) ? make_uint2(r.z, r.w) : make_uint2(r.x, r.y);
+}
+// `e` is the env's index within the handle: table row e % rows, or the Philox stream of global env env_id0 + e
+__device__ __forceinline__ uint32_t food_word(const KernelArgs &a, unsigned e, unsigned &cur) {
+    uint32_t w;
+    if (a.rng_mode) w = pick_word(philox_block(a, e, 0u, cur), cur);
+    else w = a.food_words[(size_t)(e % a.rows) * a.food_len + (cur & a.food_len_mask)];
     ++cur;
     return w;
 }
 template <typename T> __device__ __forceinline__ T food_uniform(const KernelArgs &a, unsigned row, unsigned &cur, T lo, T hi) {
-    const uint32_t w0 = food_word(a, row, cur), w1 = food_word(a, row, cur);
+    const uint32_t w0 = food_word(a, row, cur), w1 = food_word(a, row, cur);  // `row` = env index, see food_word
     return lo + (hi - lo) * (T)res53(w0, w1);  // random.uniform: a + (b-a)*random()
 }
 
@@ -161,7 +200,7 @@ struct ResetResult { unsigned cur, mask; int n_food; };
 template <typename T, int F>
 __device__ __noinline__ RespawnResult<T> respawn_slow(const KernelArgs &a, long long e, T px, T py, unsigned mask,
                                                       int n_food, unsigned cur) {
-    const unsigned row = (unsigned)e % a.rows;
+    const unsigned row = (unsigned)e;  // env index: food_word picks the table row or the Philox stream
     Vec2<T> *food = reinterpret_cast<Vec2<T> *>(a.food);
     const T xlo = (T)(kc::TANK_MARGIN + kc::FOOD_R), xhi = (T)a.W - (T)kc::TANK_MARGIN - (T)kc::FOOD_R;
     const T ylo = xlo, yhi = (T)a.H - (T)kc::TANK_MARGIN - (T)kc::FOOD_R;
@@ -204,7 +243,7 @@ __device__ __noinline__ RespawnResult<T> respawn_slow(const KernelArgs &a, long 
 // reset observation (S:366-428 with the robot at the tank centre, R:95-117) written to obs_row.
 template <typename T>
 __device__ __noinline__ ResetResult reset_slow(const KernelArgs &a, long long e, unsigned cur, float *obs_row) {
-    const unsigned row = (unsigned)e % a.rows;
+    const unsigned row = (unsigned)e;  // env index: food_word picks the table row or the Philox stream
     Vec2<T> *food = reinterpret_cast<Vec2<T> *>(a.food);
     int n_food = a.num_food;
     if (a.random_food_count) {  // random.randint(1, max(1, base)) == 1 + _randbelow(n)
@@ -295,13 +334,13 @@ template <typename T>
 __device__ __noinline__ LayoutResult<T> layout_warp(const KernelArgs &a, unsigned e, unsigned cur, int lane) {
     constexpr unsigned kFull = 0xffffffffu;
     const unsigned row = (a.rows == (unsigned)a.N) ? e : e % a.rows;
-    const uint32_t *words = a.food_words + (size_t)row * a.food_len;
+    const uint32_t *words = a.rng_mode ? nullptr : a.food_words + (size_t)row * a.food_len;
     int n_food = a.num_food;
     if (a.random_food_count) {  // random.randint(1, max(1, base)) == 1 + _randbelow(n); same words in every lane
         const uint32_t n = (uint32_t)(a.num_food > 1 ? a.num_food : 1);
         const int kbits = 32 - __clz(n);
         uint32_t r;
-        do { r = words[cur & a.food_len_mask] >> (32 - kbits); ++cur; } while (r >= n);
+        do { unsigned c2 = cur; r = food_word(a, e, c2) >> (32 - kbits); ++cur; } while (r >= n);
         n_food = 1 + (int)r;
     }
     const T xlo = (T)(kc::TANK_MARGIN + kc::FOOD_R), xhi = (T)a.W - (T)kc::TANK_MARGIN - (T)kc::FOOD_R;
@@ -317,8 +356,14 @@ __device__ __noinline__ LayoutResult<T> layout_warp(const KernelArgs &a, unsigne
         for (;;) {
             if (ptr == 32) {
                 const unsigned w = base + 4u * (unsigned)lane;
-                const uint32_t w0 = words[w & a.food_len_mask], w1 = words[(w + 1) & a.food_len_mask];
-                const uint32_t w2 = words[(w + 2) & a.food_len_mask], w3 = words[(w + 3) & a.food_len_mask];
+                uint32_t w0, w1, w2, w3;
+                if (a.rng_mode) {  // the cursor need not be a multiple of 4 (randint draws single words)
+                    unsigned c2 = w;
+                    w0 = food_word(a, e, c2); w1 = food_word(a, e, c2); w2 = food_word(a, e, c2); w3 = food_word(a, e, c2);
+                } else {
+                    w0 = words[w & a.food_len_mask]; w1 = words[(w + 1) & a.food_len_mask];
+                    w2 = words[(w + 2) & a.food_len_mask]; w3 = words[(w + 3) & a.food_len_mask];
+                }
                 candx = xlo + (xhi - xlo) * (T)res53(w0, w1);  // random.uniform: a + (b-a)*random()
                 candy = ylo + (yhi - ylo) * (T)res53(w2, w3);
                 const T rx = candx - cx, ry = candy - cy;
@@ -465,9 +510,9 @@ __global__ void __launch_bounds__(BLOCK, MINB) salp_step_kernel(const __grid_con
     const Vec2<T> *g_food = reinterpret_cast<const Vec2<T> *>(a.food);
     T *g_reward = reinterpret_cast<T *>(a.reward);
     const T *g_act = reinterpret_cast<const T *>(a.actions);
-    const T W = (T)a.W, H = (T)a.H;
-    const T diag = (T)a.diag;  // sqrt(W^2 + H^2), S:396, computed on the host in double
-    const T invW = (T)a.inv_w, invH = (T)a.inv_h, invDiag = (T)a.inv_diag;  // used by the f32 build only
+    const T W = c_W<T>(a), H = c_H<T>(a);
+    const T diag = c_diag<T>(a);  // sqrt(W^2 + H^2), S:396, computed on the host in double
+    const T invW = c_inv_w<T>(a), invH = c_inv_h<T>(a), invDiag = c_inv_diag<T>(a);  // used by the f32 build only
 
     // programmatic dependent launch (salp_launch.cuh): let the next kernel of the stream be scheduled as soon as every
     // CTA of this grid is resident, and do not touch global memory before the previous kernel has completed
@@ -560,7 +605,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) salp_step_kernel(const __grid_con
         unsigned jcache = (unsigned)c1.w;  // first word of the jitter pair at cur_jit (see salp_b200.h)
 
         const unsigned trow = (a.rows == N) ? e : e % a.rows;
-        const uint32_t *jit_row = a.jit_words + (size_t)trow * a.jit_len;
+        const uint32_t *jit_row = a.rng_mode ? nullptr : a.jit_words + (size_t)trow * a.jit_len;
 
         for (int k = 0; k < a.K; ++k, ++gk) {
             // ---- where this thread's observation row goes
@@ -595,7 +640,8 @@ __global__ void __launch_bounds__(BLOCK, MINB) salp_step_kernel(const __grid_con
             uint2 jw = make_uint2(jcache, 0u);
 #ifndef SALP_LAB_NOJIT
             if (thrust) {
-                if constexpr (is_f64<T>::value) jw = ld_evict_last_u2(jit_row + (cur_jit & a.jit_len_mask));
+                if (a.rng_mode) jw = philox_jitter_pair(a, e, cur_jit);
+                else if constexpr (is_f64<T>::value) jw = ld_evict_last_u2(jit_row + (cur_jit & a.jit_len_mask));
                 else jcache = ld_evict_last_u1(jit_row + ((cur_jit + 2u) & a.jit_len_mask));
             }
 #endif
@@ -732,12 +778,13 @@ __global__ void __launch_bounds__(BLOCK, MINB) salp_step_kernel(const __grid_con
             vx *= (T)0.98; vy *= (T)0.98; omega *= (T)0.95;
             px += vx; py += vy;
             angle = wrap_pi<T>(angle + omega);
+            unsigned clamped = 0u;  // f32 build: walls the robot was clamped onto this step (1 low x / y, 2 right, 4 bottom)
             {
                 const T margin = (T)kc::TANK_MARGIN + radius;
-                if (px < margin) { px = margin; vx = abs_(vx) * (T)0.4; omega *= (T)0.7; }
-                else if (px > W - margin) { px = W - margin; vx = -abs_(vx) * (T)0.4; omega *= (T)0.7; }
-                if (py < margin) { py = margin; vy = abs_(vy) * (T)0.4; omega *= (T)0.7; }
-                else if (py > H - margin) { py = H - margin; vy = -abs_(vy) * (T)0.4; omega *= (T)0.7; }
+                if (px < margin) { px = margin; vx = abs_(vx) * (T)0.4; omega *= (T)0.7; clamped |= 1u; }
+                else if (px > W - margin) { px = W - margin; vx = -abs_(vx) * (T)0.4; omega *= (T)0.7; clamped |= 2u; }
+                if (py < margin) { py = margin; vy = abs_(vy) * (T)0.4; omega *= (T)0.7; clamped |= 1u; }
+                else if (py > H - margin) { py = H - margin; vy = -abs_(vy) * (T)0.4; omega *= (T)0.7; clamped |= 4u; }
             }
             // ---- food distances (shared by hit test S:204-217, reward S:350-364 and obs S:375-379)
             T dx[kFastSel ? 1 : F], dy[kFastSel ? 1 : F], dd[kFastSel ? 1 : F];
@@ -750,7 +797,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) salp_step_kernel(const __grid_con
             // unsigned order == (distance, slot) order at a resolution of diag / 2^(32 - slot bits)
             // (3.7e-6 px for 12 foods in the 800 x 600 tank, finer than one f32 ulp of the distance itself).
             // Eaten foods sort last.
-            const float key_scale = (float)a.inv_diag * (4294967296.0f * 0.9999f);
+            const float key_scale = a.f_inv_diag * (4294967296.0f * 0.9999f);
             auto make_key = [&](T d, int f) -> unsigned { return (__float2uint_rz((float)d * key_scale) & ~kSlotMask) | (unsigned)f; };
             auto insert_key = [&](unsigned c) {
     #pragma unroll
@@ -805,15 +852,26 @@ __global__ void __launch_bounds__(BLOCK, MINB) salp_step_kernel(const __grid_con
                     if (!hit && ((mask >> f) & 1u) && dd[f] < reach) { hit = true; mask &= ~(1u << f); }
             }
             // ---- wall contact (S:219-230), rounding-critical: same operands/order as the reference
-            const bool collision = (px - radius <= (T)kc::TANK_MARGIN) || (px + radius >= W - (T)kc::TANK_MARGIN) ||
-                                   (py - radius <= (T)kc::TANK_MARGIN) || (py + radius >= H - (T)kc::TANK_MARGIN);
+            bool collision;
+            if constexpr (is_f64<T>::value) {
+                collision = (px - radius <= (T)kc::TANK_MARGIN) || (px + radius >= W - (T)kc::TANK_MARGIN) ||
+                            (py - radius <= (T)kc::TANK_MARGIN) || (py + radius >= H - (T)kc::TANK_MARGIN);
+            } else {
+                // The bounce above puts the robot EXACTLY on the line 50 + r, so whether that touch registers as a contact
+                // is decided by the rounding of (50 + r) - r <= 50 in the reference's doubles (~5 % of the
+                // touches bounce and survive).  A float comparison cannot reproduce that; the radius, however, is a pure
+                // function of the integer shape fields, so on the (rare) clamp branch the reference's expression is
+                // evaluated in double from them.  Away from a clamp the robot is strictly inside and nothing registers.
+                collision = false;
+                if (clamped != 0u) collision = (wall_touch_bits(skind, stimer, exd, a.W, a.H) & clamped) != 0u;
+            }
             // ---- reward (S:278-327)
             T reward = 0;
             if (hit) {
-                reward += (T)a.food_reward;
-                if (a.efficiency_bonus > 0) reward += (T)a.efficiency_bonus * (T)(a.max_steps - steps_since_food);
+                reward += c_food_reward<T>(a);
+                if (c_efficiency_bonus<T>(a) > 0) reward += c_efficiency_bonus<T>(a) * (T)(a.max_steps - steps_since_food);
             }
-            if (collision) reward += (T)a.collision_penalty;
+            if (collision) reward += c_collision_penalty<T>(a);
             // nearest live food (strict <, first index wins: S:350-364).  Its bearing is used by the
             // alignment reward AND, when no food was eaten this step, is the first observation entry.
             if constexpr (kFastSel) {
@@ -826,9 +884,9 @@ __global__ void __launch_bounds__(BLOCK, MINB) salp_step_kernel(const __grid_con
                 for (int f = 0; f < F; ++f)
                     if (((mask >> f) & 1u) && (!any_food || dd[f] < near_d)) { any_food = true; near_d = dd[f]; near_x = dx[f]; near_y = dy[f]; }
             }
-            if (any_food && (a.proximity_w > 0 || a.observed > 0)) near_rel = wrap_pi<T>(atan2_(near_y, near_x) - angle);
-            if (a.proximity_w > 0 && any_food) reward += (T)a.proximity_w * cos_(near_rel);
-            reward += (T)a.time_penalty;
+            if (any_food && (c_proximity_w<T>(a) > 0 || a.observed > 0)) near_rel = wrap_pi<T>(atan2_(near_y, near_x) - angle);
+            if (c_proximity_w<T>(a) > 0 && any_food) reward += c_proximity_w<T>(a) * cos_(near_rel);
+            reward += c_time_penalty<T>(a);
             // ---- counters, respawn (S:171-180)
             ++steps_since_food;
             if (hit) {
@@ -1152,9 +1210,85 @@ __global__ void __launch_bounds__(256) salp_reset_kernel(const __grid_constant__
     const int fsm = kPhaseRest | (kShapeReset << 18);
     a.ctrl[e] = make_int4(fsm, 0, 0, (int)rr.mask);
     const unsigned trow = (unsigned)e % a.rows;
-    const uint32_t jcache = a.jit_words[(size_t)trow * a.jit_len + (cur_jit & a.jit_len_mask)];
+    const uint32_t jcache = a.rng_mode ? 0u : a.jit_words[(size_t)trow * a.jit_len + (cur_jit & a.jit_len_mask)];
     a.ctrl[N + e] = make_int4((int)rr.cur, (int)cur_jit, rr.n_food << 26, (int)jcache);
     reinterpret_cast<T *>(a.ep_return)[e] = 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Observation of the CURRENT state, no step (salp_observe): S:366-428 _get_extended_observation over
+// R:371-388 _get_observation -- what the reference's callers get after poking robot_pos / robot_angle /
+// food_positions (eval/collect_navigation_data.py:76-89, eval/watch_navigation.py:63).  Generic in the
+// food count and in max_observed_food; off the hot path (one thread per env, live foods read from HBM,
+// stable insertion sort exactly like list.sort on (distance, position) tuples with distinct distances).
+// ---------------------------------------------------------------------------------------------
+template <typename T> __device__ __forceinline__ void shape_axes(int fsm, T &ea, T &eb) {
+    const int exd = (fsm >> 10) & 0xff, skind = (fsm >> 18) & 3, stimer = (fsm >> 20) & 0xff;
+    if (skind == kShapeReset) { ea = (T)kc::BASE_R; eb = (T)kc::BASE_R; }            // R:111-113
+    else if (skind == kShapeRest) { ea = (T)kc::A_REST; eb = (T)kc::B_REST; }       // R:190-191
+    else {                                                                          // R:207-213, 240-246
+        const bool inh = (skind == kShapeInhale);
+        const T prog = (T)stimer / (T)(inh ? kc::INHALE_DUR : (exd > 0 ? exd : 1));
+        const T sa = inh ? (T)kc::A_REST : (T)kc::A_FULL, sb = inh ? (T)kc::B_REST : (T)kc::B_FULL;
+        const T da = inh ? (T)(kc::A_FULL - kc::A_REST) : (T)(kc::A_REST - kc::A_FULL);
+        const T db = inh ? (T)(kc::B_FULL - kc::B_REST) : (T)(kc::B_REST - kc::B_FULL);
+        ea = sa + da * prog; eb = sb + db * prog;
+    }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(128) salp_observe_kernel(const __grid_constant__ KernelArgs a) {
+    const long long e = a.first + (long long)blockIdx.x * 128 + threadIdx.x;
+    if (e >= a.first + a.count) return;
+    const long long N = a.N;
+    const Vec4<T> b0 = reinterpret_cast<const Vec4<T> *>(a.body)[e], b1 = reinterpret_cast<const Vec4<T> *>(a.body)[N + e];
+    const int4 c0 = a.ctrl[e], c1 = a.ctrl[N + e];
+    const Vec2<T> *food = reinterpret_cast<const Vec2<T> *>(a.food);
+    const T px = b0.x, py = b0.y, angle = b1.x;
+    const T W = (T)a.W, H = (T)a.H, diag = (T)a.diag;
+    T ea, eb;
+    shape_axes<T>(c0.x, ea, eb);
+    float *o = a.obs + (size_t)e * a.obs_dim;
+    o[0] = (float)(px / W); o[1] = (float)(py / H);
+    o[2] = (float)(b0.z / (T)5.0); o[3] = (float)(b0.w / (T)5.0);
+    o[4] = (float)(angle / (T)kc::PI); o[5] = (float)(b1.y / (T)0.1);
+    o[6] = (float)(pymax<T>(ea, eb) / (T)kc::BASE_R);
+    o[7] = (float)((T)(c0.x & 3) / (T)2.0);
+    o[8] = (float)b1.w;
+    o[9] = (float)(b1.z / (T)kc::MAX_NOZZLE);
+    int n_food = (int)((unsigned)c1.z >> 26);
+    if (n_food > kMaxFood) n_food = kMaxFood;
+    const unsigned mask = (unsigned)c0.w;
+    T dist[kMaxFood];
+    int idx[kMaxFood];
+    int n = 0;
+    for (int j = 0; j < n_food; ++j)
+        if ((mask >> j) & 1u) {
+            const Vec2<T> f = food[(size_t)j * N + e];
+            const T dx = f.x - px, dy = f.y - py;
+            const T d = sqrt_(dx * dx + dy * dy);
+            int k = n - 1;  // stable insertion: equal distances keep slot order
+            while (k >= 0 && dist[k] > d) { dist[k + 1] = dist[k]; idx[k + 1] = idx[k]; --k; }
+            dist[k + 1] = d; idx[k + 1] = j;
+            ++n;
+        }
+    float *fo = o + 10;
+    for (int i = 0; i < a.observed; ++i) {
+        if (i < n) {
+            const Vec2<T> f = food[(size_t)idx[i] * N + e];
+            const T dx = f.x - px, dy = f.y - py;
+            const T rel = wrap_pi<T>(atan2_(dy, dx) - angle);
+            fo[0] = (float)(dx / W); fo[1] = (float)(dy / H);
+            fo[2] = (float)(dist[i] / diag); fo[3] = (float)(rel / (T)kc::PI);
+        } else { fo[0] = 0.f; fo[1] = 0.f; fo[2] = 1.f; fo[3] = 0.f; }
+        fo += 4;
+    }
+    fo[0] = (float)pymin<T>((T)n / (T)10.0, (T)1.0);
+    if (n > 0) {
+        T s = 0;
+        for (int i = 0; i < n; ++i) s = s + dist[i];
+        fo[1] = (float)((s / (T)n) / diag);
+    } else fo[1] = 1.f;
 }
 
 // ctrl rec1.w = first jitter word at every env's jitter cursor (salp_refresh_rng)
@@ -1163,7 +1297,7 @@ static __global__ void __launch_bounds__(256) salp_refresh_rng_kernel(const __gr
     if (e >= a.first + a.count) return;
     int4 c1 = a.ctrl[a.N + e];
     const unsigned trow = (unsigned)e % a.rows;
-    c1.w = (int)a.jit_words[(size_t)trow * a.jit_len + ((unsigned)c1.y & a.jit_len_mask)];
+    c1.w = a.rng_mode ? 0 : (int)a.jit_words[(size_t)trow * a.jit_len + ((unsigned)c1.y & a.jit_len_mask)];
     a.ctrl[a.N + e] = c1;
 }
 

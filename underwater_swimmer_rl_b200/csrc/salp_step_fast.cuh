@@ -1,0 +1,577 @@
+// salp_step_fast.cuh -- the f32 throughput kernel for forced breathing (every BASELINE config): persistent warps,
+// TMA bulk loads / stores through shared memory, breathing subsystem read from the 273-step cycle table.
+//
+// What it replaces (reference tree, Python): the same path as salp_step.cuh --
+//   R = scripts/utilities/salp_robot.py             SalpRobotEnv.step            R:119-156
+//   S = src/salp/environments/salp_snake_env.py     SalpSnakeEnv.step / reset    S:133-202
+// for `forced_breathing=True` (S:31,66; R:158-167), max_observed_food = 3 (S:32) and 1 or 12 food slots, i.e. the four
+// reference YAMLs.  Everything else (manual breathing, other food counts, the fp64 validation build) runs the generic
+// kernel of salp_step.cuh; both are checked against the same oracle.
+//
+// Why a second kernel.  The generic one-thread-per-env kernel loads its state straight into registers: a warp sits on
+// its first dependent instruction for a DRAM round trip, then runs ~760 dependent instructions, and the only thing that
+// hides either is occupancy (ncu round 1: 45 % of stall samples on the state loads, 13 % on the CTA barrier before the TMA
+// store, issue slots 45 % busy).  Here
+//   * every WARP is its own pipeline over 32-env tiles: lane 0 issues cp.async.bulk (TMA) loads of the tile's SoA
+//     records -- each record array of a tile is 512 contiguous bytes -- into a two-stage shared-memory ring, completion
+//     on an mbarrier; the loads of tile i+1 are in flight while tile i is integrated, so HBM latency is off the
+//     critical path at any occupancy;
+//   * results leave the same way: the new state is written over the tile's input slots, the 32 observation rows
+//     (3 KB, contiguous in HBM), rewards and flags into an output buffer, and lane 0 issues bulk stores -- no per-thread
+//     global address arithmetic, no CTA-wide barrier (warps never synchronise with each other);
+//   * forced breathing makes phase, timer, ellipse axes, water volume, thrust window (and whether a wall touch at that
+//     radius registers as a contact in the reference's doubles) functions of the position in the 273-step
+//     cycle: two 128-bit loads from a host-built table (CycleEntry, L1-resident) replace the FSM, the morph, the
+//     divisions and the water-volume recurrence.
+#pragma once
+#include "salp_step.cuh"
+
+namespace salp {
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n"
+        "SALP_MBAR_WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@!p bra SALP_MBAR_WAIT_%=;\n\t}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+// 1-D TMA: global -> this CTA's shared memory, completion counted in bytes on an mbarrier
+__device__ __forceinline__ void bulk_load(void *sdst, const void *gsrc, uint32_t bytes, uint64_t *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(sdst)),
+                 "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_store(void *gdst, const void *ssrc, uint32_t bytes) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(smem_u32(ssrc)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+// One lane of a converged warp.  With elect.sync (instead of `lane == 0`) and operands derived from warp-uniform values
+// the compiler issues the bulk copies from the uniform datapath; with per-thread operands it wraps every copy in a
+// ~12-instruction "waterfall" loop (measured: half of all warp instructions of the first version of this kernel).
+__device__ __forceinline__ bool elect_one_sync() {
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred P;\n\telect.sync _|P, 0xffffffff;\n\tselp.u32 %0, 1, 0, P;\n\t}" : "=r"(pred));
+    return pred != 0;
+}
+
+// Per-warp shared-memory layout (bytes).  A "core" stage holds the 32-env tile's four 128-bit state records in the order
+// of the state arrays, so the new state is written over them and stored from the same place.
+template <int F, int FS> struct FastLayout {
+    static constexpr int kC0 = 0, kC1 = 512, kB0 = 1024, kB1 = 1536, kCore = 2048;
+    static constexpr int kFood = F * 256;                       // [F][32] float2
+    static constexpr int kObs = 32 * 24 * 4;                    // 32 rows of 24 floats
+    static constexpr int kOffCore = 0;                          // 2 stages
+    static constexpr int kOffFood = 2 * kCore;                  // FS stages
+    static constexpr int kOffObs = kOffFood + FS * kFood;
+    static constexpr int kOffBar = kOffObs + kObs;              // core[2], food[FS]: 8 bytes each
+    static constexpr int kWarpBytes = (kOffBar + 8 * (2 + FS) + 127) & ~127;
+};
+
+// Launch shape per food-slot count: warps per CTA, CTAs per SM (registers: 65536 / (32 * warps * minb)).
+template <int F> struct FastCfg;
+template <> struct FastCfg<1> { static constexpr int warps = 8, minb = 3, food_stages = 2; };    // 24 warps/SM, 80 regs
+template <> struct FastCfg<12> { static constexpr int warps = 8, minb = 2, food_stages = 1; };   // 16 warps/SM, 128 regs
+
+template <int F, int RNG>
+__global__ void __launch_bounds__(FastCfg<F>::warps * 32, FastCfg<F>::minb) salp_step_fast_kernel(const __grid_constant__ KernelArgs a) {
+    using Cfg = FastCfg<F>;
+    constexpr int FS = Cfg::food_stages;
+    using L = FastLayout<F, FS>;
+    constexpr int OBS = 24;
+    constexpr int MU = F < 3 ? F : 3;
+    constexpr unsigned kSlotMask = F <= 1 ? 0u : (F <= 2 ? 1u : (F <= 4 ? 3u : (F <= 8 ? 7u : (F <= 16 ? 15u : 31u))));
+    constexpr unsigned kFull = 0xffffffffu;
+    extern __shared__ __align__(128) unsigned char s_raw[];
+    __shared__ __align__(16) CycleEntry s_tab[kCycleLen];  // the forced-breathing cycle, 8.8 KB per CTA
+    const int lane = threadIdx.x & 31;
+    const int warp = __shfl_sync(kFull, (int)(threadIdx.x >> 5), 0);  // warp-uniform for the compiler
+    unsigned char *ws = s_raw + (size_t)warp * L::kWarpBytes;
+    uint64_t *bar_core = reinterpret_cast<uint64_t *>(ws + L::kOffBar);
+    uint64_t *bar_food = bar_core + 2;
+    float *s_obs = reinterpret_cast<float *>(ws + L::kOffObs);
+
+    const unsigned N = (unsigned)a.N;
+    const unsigned first = (unsigned)a.first, end = first + (unsigned)a.count;
+    const unsigned ntiles = ((unsigned)a.count + 31u) / 32u;
+    const unsigned gw = blockIdx.x * Cfg::warps + warp, nw = gridDim.x * Cfg::warps;
+
+    const float4 *g_body = reinterpret_cast<const float4 *>(a.body);
+    const float2 *g_food = reinterpret_cast<const float2 *>(a.food);
+    float *g_epret = reinterpret_cast<float *>(a.ep_return);
+    const float *g_act = reinterpret_cast<const float *>(a.actions);
+    float *g_reward = reinterpret_cast<float *>(a.reward);
+    const float W = a.fW, H = a.fH, invW = a.f_inv_w, invH = a.f_inv_h, invDiag = a.f_inv_diag;
+
+    if (elect_one_sync()) {
+        mbar_init(bar_core + 0, 1);
+        mbar_init(bar_core + 1, 1);
+#pragma unroll
+        for (int i = 0; i < FS; ++i) mbar_init(bar_food + i, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    // the cycle table is parameter data of the handle (never written by a kernel): it may be read before the previous
+    // kernel of the stream has completed
+    for (unsigned i = threadIdx.x; i < kCycleLen * 2u; i += Cfg::warps * 32)
+        reinterpret_cast<uint4 *>(s_tab)[i] = __ldg(reinterpret_cast<const uint4 *>(a.cycle_tab) + i);
+    __syncthreads();
+    // programmatic dependent launch (salp_launch.cuh): the next kernel of the stream may become resident as CTAs of this
+    // one retire; no state is touched before the previous kernel has completed
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+
+    // ---- tile loads.  Full tiles: TMA, one elected lane, every operand warp-uniform.  The last, partial tile of a slab
+    //      whose size is not a multiple of 32: each lane copies its own records (bulk copies need 16-byte multiples).
+    auto rows_of = [&](unsigned tile) -> unsigned { const unsigned e0 = first + tile * 32u; return end - e0 < 32u ? end - e0 : 32u; };
+    auto load_core = [&](unsigned tile, int st) {
+        unsigned char *sc = ws + L::kOffCore + st * L::kCore;
+        const unsigned e0 = first + tile * 32u;
+        if (rows_of(tile) == 32u) {
+            if (elect_one_sync()) {
+                uint64_t *bar = bar_core + st;
+                mbar_expect_tx(bar, L::kCore + ((FS == 2) ? L::kFood : 0));
+                bulk_load(sc + L::kC0, a.ctrl + e0, 512, bar);
+                bulk_load(sc + L::kC1, a.ctrl + (size_t)N + e0, 512, bar);
+                bulk_load(sc + L::kB0, g_body + e0, 512, bar);
+                bulk_load(sc + L::kB1, g_body + (size_t)N + e0, 512, bar);
+                if constexpr (FS == 2) {
+                    unsigned char *sf = ws + L::kOffFood + st * L::kFood;
+#pragma unroll
+                    for (int f = 0; f < F; ++f) bulk_load(sf + f * 256, g_food + (size_t)f * N + e0, 256, bar);
+                }
+            }
+        } else {
+            const unsigned e = e0 + lane;
+            const bool v = e < end;
+            reinterpret_cast<int4 *>(sc + L::kC0)[lane] = v ? a.ctrl[e] : make_int4(0, 0, 0, 0);
+            reinterpret_cast<int4 *>(sc + L::kC1)[lane] = v ? a.ctrl[(size_t)N + e] : make_int4(0, 0, 0, 0);
+            reinterpret_cast<float4 *>(sc + L::kB0)[lane] = v ? g_body[e] : make_float4(0.f, 0.f, 0.f, 0.f);
+            reinterpret_cast<float4 *>(sc + L::kB1)[lane] = v ? g_body[(size_t)N + e] : make_float4(0.f, 0.f, 0.f, 0.f);
+            if constexpr (FS == 2) {
+                float2 *sf = reinterpret_cast<float2 *>(ws + L::kOffFood + st * L::kFood);
+#pragma unroll
+                for (int f = 0; f < F; ++f) sf[f * 32 + lane] = v ? g_food[(size_t)f * N + e] : make_float2(0.f, 0.f);
+            }
+            __syncwarp();
+        }
+    };
+    auto load_food = [&](unsigned tile) {  // FS == 1 only: the single food buffer, its own mbarrier
+        unsigned char *sf = ws + L::kOffFood;
+        const unsigned e0 = first + tile * 32u;
+        if (rows_of(tile) == 32u) {
+            if (elect_one_sync()) {
+                mbar_expect_tx(bar_food, L::kFood);
+#pragma unroll
+                for (int f = 0; f < F; ++f) bulk_load(sf + f * 256, g_food + (size_t)f * N + e0, 256, bar_food);
+            }
+        } else {
+            const unsigned e = e0 + lane;
+#pragma unroll
+            for (int f = 0; f < F; ++f)
+                reinterpret_cast<float2 *>(sf)[f * 32 + lane] = e < end ? g_food[(size_t)f * N + e] : make_float2(0.f, 0.f);
+            __syncwarp();
+        }
+    };
+
+    unsigned ph_core = 0u, ph_food = 0u;  // mbarrier phase parities: bit st of ph_core, bit 0 of ph_food
+    // the two scalars of the state that are not 128-bit records travel in registers, fetched one tile ahead
+    float act_nx = 0.f, ep_nx = 0.f;
+    if (gw < ntiles) {
+        load_core(gw, 0);
+        if constexpr (FS == 1) load_food(gw);
+        const unsigned e = first + gw * 32u + lane;
+        if (e < end) { act_nx = g_act[e]; ep_nx = g_epret[e]; }
+    }
+
+    unsigned it = 0;
+    for (unsigned tile = gw; tile < ntiles; tile += nw, ++it) {
+        const int st = (int)(it & 1u);
+        const unsigned e0 = first + tile * 32u;
+        const unsigned e = e0 + lane;
+        const unsigned rows = rows_of(tile);
+        const bool full = rows == 32u;
+        const bool valid = (unsigned)lane < rows;
+        const unsigned nxt = tile + nw;
+        unsigned char *sc = ws + L::kOffCore + st * L::kCore;
+        float2 *sfood = reinterpret_cast<float2 *>(ws + L::kOffFood + (FS == 2 ? st : 0) * L::kFood);
+
+        float act = act_nx, ep_ret = ep_nx;
+        if (nxt < ntiles) {
+            const unsigned en = first + nxt * 32u + lane;
+            if (en < end) { act_nx = g_act[en]; ep_nx = g_epret[en]; }
+        }
+        if (full) { mbar_wait(bar_core + st, (ph_core >> st) & 1u); ph_core ^= 1u << st; }
+        // ---- state of this lane's env
+        const int4 c0 = reinterpret_cast<const int4 *>(sc + L::kC0)[lane];
+        const int4 c1 = reinterpret_cast<const int4 *>(sc + L::kC1)[lane];
+        const float4 b0 = reinterpret_cast<const float4 *>(sc + L::kB0)[lane];
+        const float4 b1 = reinterpret_cast<const float4 *>(sc + L::kB1)[lane];
+        // ---- the other stage is free once the bulk stores issued from it (previous tile) have read it; refill it so the
+        //      loads have this tile's arithmetic to land
+#ifndef SALP_FAST_PREFETCH_LATE
+        if (elect_one_sync()) bulk_wait_read<0>();
+        __syncwarp();
+        if (nxt < ntiles) load_core(nxt, st ^ 1);
+#endif
+
+        float px = b0.x, py = b0.y, vx = b0.z, vy = b0.w;
+        float angle = b1.x, omega = b1.y, nozzle = b1.z;
+        int fsm = c0.x;
+        int steps_since_food = c0.y, food_collected = c0.z;
+        unsigned mask = (unsigned)c0.w;
+        unsigned cur_food = (unsigned)c1.x, cur_jit = (unsigned)c1.y;
+        int ep_len = c1.z & kEpLenMask, n_food = (int)((unsigned)c1.z >> 26);
+        unsigned jcache = (unsigned)c1.w;
+        float wv_now = b1.w;
+        // position in the breathing cycle: 0 fresh reset, 1..121 inhaling (timer 0..120), 122..272 exhaling
+        // (timer 0..150), 273 the one rest step
+        int q;
+        {
+            const int phase = fsm & 3, timer = (fsm >> 2) & 0xff;
+            q = phase == kPhaseInhale ? 1 + timer : (phase == kPhaseExhale ? 122 + timer : (((fsm >> 18) & 3) == kShapeReset ? 0 : 273));
+        }
+        const uint32_t *jit_row = nullptr;
+        if constexpr (RNG == 0) jit_row = a.jit_words + (size_t)((a.rows == N) ? e : e % a.rows) * a.jit_len;
+
+        for (int k = 0; k < a.K; ++k) {
+            if (k > 0) {  // K fused substeps: later actions come straight from HBM; the observation tile buffer is single
+                act = valid ? g_act[(size_t)k * N + e] : 0.f;
+                if (elect_one_sync()) bulk_wait_read<0>();
+                __syncwarp();
+            }
+            float *row = s_obs + lane * OBS;
+            q = q >= 273 ? 1 : q + 1;
+            const uint4 t0 = reinterpret_cast<const uint4 *>(s_tab + q)[0];
+            const float4 t1 = reinterpret_cast<const float4 *>(s_tab + q)[1];
+            const float radius = __uint_as_float(t0.x), tm = __uint_as_float(t0.y);
+            const bool thrust = tm != 0.f;
+            // ---- thrust jitter draw (R:311): table mode -- the word for THIS draw came with the state (ctrl rec1.w), fetch
+            //      the one for the next draw now, it is needed only at write-back; Philox mode -- computed, no memory
+            uint32_t jword = jcache;
+            if (thrust) {
+                if constexpr (RNG == 0) jcache = ld_evict_last_u1(jit_row + ((cur_jit + 2u) & a.jit_len_mask));
+                else jword = philox_jitter_pair(a, e, cur_jit).x;
+            }
+            // ---- nozzle slew (R:169-182)
+            {
+                const float target = act * (float)kc::MAX_NOZZLE;
+                const float diff = target - nozzle;
+                if (fabsf(diff) > (float)kc::NOZZLE_RATE) nozzle = (diff > 0.f) ? nozzle + (float)kc::NOZZLE_RATE : nozzle - (float)kc::NOZZLE_RATE;
+                else nozzle = target;
+                nozzle = pymax<float>((float)(-kc::MAX_NOZZLE), pymin<float>((float)kc::MAX_NOZZLE, nozzle));
+            }
+            // ---- jet thrust through the steerable nozzle (R:261-314); Tm = 100 * water_volume * 0.4 from the table
+            if (thrust) {
+                const float wvb = tm * 0.025f;  // water volume before this step's decay
+                const float th = angle - nozzle;
+                float s0, cs0;
+                __sincosf(th, &s0, &cs0);
+                vx += (cs0 * tm) * 0.012f;
+                vy += (s0 * tm) * 0.012f;
+                const float primary = -nozzle * tm * 0.0002f;
+                const float perp = tm * __sinf(-nozzle);
+                const float moment = perp * (radius * 0.7f) * 0.00005f;
+                const float shape = -nozzle * tm * wvb * 0.00003f;
+                omega += primary + moment + shape;
+                const float sm = tm * fabsf(nozzle) * 0.3f;
+                vx += (-s0 * sm) * 0.008f;  // cos(x + pi/2) = -sin x
+                vy += (cs0 * sm) * 0.008f;  // sin(x + pi/2) =  cos x
+                cur_jit += 2;
+                const float u = (float)(jword >> 5) * (1.0f / 134217728.0f);
+                const float dn = (u - 0.5f) * 0.05f;
+                const float nf = tm * 0.04f;
+                const float d2 = dn * dn;  // sin/cos(th + dn) by angle addition, |dn| <= 0.025
+                const float sd = dn * (1.0f - d2 * ((1.0f / 6.0f) - d2 * (1.0f / 120.0f)));
+                const float cd = 1.0f - d2 * (0.5f - d2 * (1.0f / 24.0f));
+                vx += (cs0 * cd - s0 * sd) * nf * 0.002f;
+                vy += (s0 * cd + cs0 * sd) * nf * 0.002f;
+            }
+            wv_now = __uint_as_float(t0.z);
+            fsm = (int)(t0.w & 0x0fffffffu);
+            // ---- drag, integrate, wrap, wall bounce (R:316-352)
+            vx *= 0.98f; vy *= 0.98f; omega *= 0.95f;
+            px += vx; py += vy;
+            angle = wrap_pi<float>(angle + omega);
+            unsigned clamped = 0u;
+            {
+                const float margin = t1.x;
+                if (px < margin) { px = margin; vx = fabsf(vx) * 0.4f; omega *= 0.7f; clamped |= 1u; }
+                else if (px > W - margin) { px = W - margin; vx = -fabsf(vx) * 0.4f; omega *= 0.7f; clamped |= 2u; }
+                if (py < margin) { py = margin; vy = fabsf(vy) * 0.4f; omega *= 0.7f; clamped |= 1u; }
+                else if (py > H - margin) { py = H - margin; vy = -fabsf(vy) * 0.4f; omega *= 0.7f; clamped |= 4u; }
+            }
+#ifdef SALP_FAST_PREFETCH_LATE
+            if (k == 0) {
+                if (elect_one_sync()) bulk_wait_read<0>();
+                __syncwarp();
+                if (nxt < ntiles) load_core(nxt, st ^ 1);
+            }
+#endif
+            // ---- wall contact (S:219-230): a bounce leaves the robot exactly on the clamp line; whether that registers is
+            //      the rounding of (50 + r) - r <= 50 in the reference's doubles -- a table bit per cycle position
+            const bool collision = (clamped & (t0.w >> 28)) != 0u;
+
+            // ---- food: offsets, distances, first live food within reach is eaten (S:204-217), nearest MU selected
+            bool hit = false;
+            float dx0 = 0.f, dy0 = 0.f, dd0 = 0.f;  // F == 1
+            unsigned key[MU > 0 ? MU : 1];
+            float dist_sum = 0.f;
+            const float key_scale = invDiag * (4294967296.0f * 0.9999f);
+            auto make_key = [&](float d, int f) -> unsigned { return (__float2uint_rz(d * key_scale) & ~kSlotMask) | (unsigned)f; };
+            auto insert_key = [&](unsigned c) {
+#pragma unroll
+                for (int i = 0; i < MU; ++i) { const unsigned lo = min(key[i], c); c = max(key[i], c); key[i] = lo; }
+            };
+            auto reselect = [&]() {  // rare: a food was eaten / the env was reset -- redo the selection from the scratch
+                dist_sum = 0.f;
+#pragma unroll
+                for (int i = 0; i < MU; ++i) key[i] = 0xffffffffu;
+#pragma unroll 1
+                for (int f = 0; f < F; ++f) {
+                    const float2 v = sfood[f * 32 + lane];
+                    const float d = sqrt_(v.x * v.x + v.y * v.y);
+                    const bool alive = (mask >> f) & 1u;
+                    if (alive) dist_sum += d;
+                    insert_key(alive ? make_key(d, f) : (~kSlotMask | (unsigned)f));
+                }
+            };
+            const float reach = t1.y;
+            if constexpr (F == 1) {
+                const float2 fv = sfood[lane];
+                dx0 = fv.x - px; dy0 = fv.y - py;
+                dd0 = sqrt_(dx0 * dx0 + dy0 * dy0);
+                if ((mask & 1u) && dd0 < reach) { hit = true; mask &= ~1u; }
+            } else {
+                if (FS == 1 && k == 0 && full) { mbar_wait(bar_food, ph_food & 1u); ph_food ^= 1u; }
+                unsigned hitbits = 0u;
+#pragma unroll
+                for (int i = 0; i < MU; ++i) key[i] = 0xffffffffu;
+#pragma unroll
+                for (int f = 0; f < F; ++f) {
+                    const float2 fv = sfood[f * 32 + lane];
+                    const float ox = fv.x - px, oy = fv.y - py;  // the buffer holds positions on entry, offsets afterwards
+                    const float d = sqrt_(ox * ox + oy * oy);
+                    sfood[f * 32 + lane] = make_float2(ox, oy);
+                    const bool alive = (mask >> f) & 1u;
+                    if (d < reach) hitbits |= 1u << f;
+                    if (alive) dist_sum += d;
+                    insert_key(alive ? make_key(d, f) : (~kSlotMask | (unsigned)f));
+                }
+                hitbits &= mask;
+                if (hitbits != 0u) { hit = true; mask &= ~(hitbits & (0u - hitbits)); reselect(); }
+            }
+            // ---- reward (S:278-327)
+            float reward = 0.f;
+            if (hit) {
+                reward += a.f_food_reward;
+                if (a.f_efficiency_bonus > 0.f) reward += a.f_efficiency_bonus * (float)(a.max_steps - steps_since_food);
+            }
+            if (collision) reward += a.f_collision_penalty;
+            bool any_food = mask != 0u;
+            float near_x, near_y, near_rel = 0.f;
+            if constexpr (F == 1) { near_x = dx0; near_y = dy0; }
+            else { const float2 nv = sfood[(key[0] & kSlotMask) * 32 + lane]; near_x = nv.x; near_y = nv.y; }
+            if (any_food) near_rel = wrap_pi<float>(atan2_(near_y, near_x) - angle);
+            if (a.f_proximity_w > 0.f && any_food) reward += a.f_proximity_w * __cosf(near_rel);
+            reward += a.f_time_penalty;
+            // ---- counters, respawn (S:171-180)
+            ++steps_since_food;
+            if (hit) {
+                ++food_collected;
+                steps_since_food = 0;
+                if (a.respawn) {
+                    const RespawnResult<float> r = respawn_slow<float, F>(a, e, px, py, mask, n_food, cur_food);
+                    mask = r.mask; cur_food = r.cur;
+                    if (r.slot >= 0) {
+                        const float ox = r.x - px, oy = r.y - py;
+                        const float d = sqrt_(ox * ox + oy * oy);
+                        if constexpr (F == 1) { dx0 = ox; dy0 = oy; dd0 = d; sfood[lane] = make_float2(r.x, r.y); }
+                        else { sfood[r.slot * 32 + lane] = make_float2(ox, oy); dist_sum += d; insert_key(make_key(d, r.slot)); }
+                    }
+                }
+            }
+            // ---- termination (S:182-189): collision > timeout > all collected
+            bool terminated = false, truncated = false;
+            if (collision) terminated = true;
+            else if (steps_since_food > a.max_steps) truncated = true;
+            else if (!a.respawn && mask == 0u) terminated = true;
+            if (!valid) { terminated = false; truncated = false; }
+            ep_ret += reward;
+            ++ep_len;
+            // ---- per-step scalars: one coalesced store each (a warp's 32 rewards are 128 contiguous bytes, its flags 32)
+            const bool done = terminated || truncated;
+            if (valid) {
+                const size_t oi = (size_t)k * N + e;
+                g_reward[oi] = reward;
+                a.terminated[oi] = terminated ? 1 : 0;
+                a.truncated[oi] = truncated ? 1 : 0;
+                if (a.events) a.events[oi] = (uint8_t)((terminated ? 1 : 0) | (truncated ? 2 : 0) | (collision ? 4 : 0) | (hit ? 8 : 0));
+            }
+
+            float obs6 = t1.z, obs7 = t1.w;
+#pragma unroll 1
+            for (int pass = 0;; ++pass) {
+                // ---- observation (R:377-388 + S:366-428) assembled in registers, written as 128-bit pieces of the row
+                const int n_live = __popc(mask);
+                auto food_entry = [&](int i) -> float4 {
+                    float4 qv = make_float4(0.f, 0.f, 1.f, 0.f);  // S:412 padding
+                    if (i < MU && i < n_live) {
+                        float sx, sy, sd;
+                        if constexpr (F == 1) { sx = dx0; sy = dy0; sd = dd0; }
+                        else {
+                            const float2 v = sfood[(key[i < MU ? i : 0] & kSlotMask) * 32 + lane];
+                            sx = v.x; sy = v.y; sd = sqrt_(v.x * v.x + v.y * v.y);
+                        }
+                        float rel;
+                        if (i == 0) rel = hit ? wrap_pi<float>(atan2_(sy, sx) - angle) : near_rel;
+                        else rel = wrap_pi<float>(atan2_(sy, sx) - angle);
+                        qv = make_float4(sx * invW, sy * invH, sd * invDiag, rel * (float)(1.0 / kc::PI));
+                    }
+                    return qv;
+                };
+                const float cnt = fminf((float)n_live * 0.1f, 1.0f);
+                float avg = 1.f;
+                if (n_live > 0) avg = ((F == 1 ? dd0 : dist_sum) / (float)n_live) * invDiag;
+                const float4 e0v = food_entry(0), e1v = food_entry(1), e2v = food_entry(2);
+                float4 *r4 = reinterpret_cast<float4 *>(row);
+                r4[0] = make_float4(px * invW, py * invH, vx * 0.2f, vy * 0.2f);
+                r4[1] = make_float4(angle * (float)(1.0 / kc::PI), omega * 10.0f, obs6, obs7);
+                r4[2] = make_float4(wv_now, nozzle * (float)(1.0 / kc::MAX_NOZZLE), e0v.x, e0v.y);
+                r4[3] = make_float4(e0v.z, e0v.w, e1v.x, e1v.y);
+                r4[4] = make_float4(e1v.z, e1v.w, e2v.x, e2v.y);
+                r4[5] = make_float4(e2v.z, e2v.w, cnt, avg);
+                if (pass) break;
+                // ---- episode statistics: warp-shuffle reduction, only in warps where an episode ended
+                const unsigned done_mask = __ballot_sync(kFull, done);
+                if (done_mask == 0u) break;
+                if (a.stats) {
+                    const double r = warp_sum(done ? (double)ep_ret : 0.0);
+                    const double l = warp_sum(done ? (double)ep_len : 0.0);
+                    const double fc = warp_sum(done ? (double)food_collected : 0.0);
+                    const unsigned coll_mask = __ballot_sync(kFull, done && collision);
+                    const unsigned trunc_mask = __ballot_sync(kFull, done && truncated);
+                    const unsigned bad_mask = __ballot_sync(kFull, done && !(isfinite(px) && isfinite(py)));
+                    if (lane == 0) {
+                        atomicAdd(a.stats + 0, (double)__popc(done_mask));
+                        atomicAdd(a.stats + 1, r);
+                        atomicAdd(a.stats + 2, l);
+                        atomicAdd(a.stats + 3, fc);
+                        if (coll_mask) atomicAdd(a.stats + 4, (double)__popc(coll_mask));
+                        if (trunc_mask) atomicAdd(a.stats + 5, (double)__popc(trunc_mask));
+                        if (bad_mask) atomicAdd(a.stats + 6, (double)__popc(bad_mask));
+                    }
+                }
+                if (done && a.final_info)
+                    reinterpret_cast<float4 *>(a.final_info)[(size_t)k * N + e] =
+                        make_float4(ep_ret, (float)ep_len, (float)food_collected, (float)steps_since_food);
+                if (!a.autoreset) break;
+                if (done && a.final_obs) {  // terminal observation (gymnasium "final_observation")
+                    float4 *dst = reinterpret_cast<float4 *>(a.final_obs + ((size_t)k * N + e) * OBS);
+#pragma unroll
+                    for (int j = 0; j < OBS / 4; ++j) dst[j] = r4[j];
+                }
+                if constexpr (F < 8) {
+                    if (done) {  // few foods: the in-thread reset is cheap and writes the reset observation itself
+                        const ResetResult rr = reset_slow<float>(a, e, cur_food, row);
+                        cur_food = rr.cur; mask = rr.mask; n_food = rr.n_food;
+                        px = W * 0.5f; py = H * 0.5f; vx = 0.f; vy = 0.f; angle = 0.f; omega = 0.f; nozzle = 0.f; wv_now = 0.f;
+                        fsm = kPhaseRest | (kShapeReset << 18); q = 0;
+                        steps_since_food = 0; food_collected = 0; ep_ret = 0.f; ep_len = 0;
+                        if (a.K > 1) sfood[lane] = g_food[e];  // the next substep reads the food position from the tile buffer
+                    }
+                    break;
+                } else {
+                    // ---- auto-reset (S:133-155): the whole warp lays out the food of each finished env in turn
+                    for (unsigned m = done_mask; m != 0u; m &= m - 1u) {
+                        const int src = __ffs((int)m) - 1;
+                        const unsigned e_src = __shfl_sync(kFull, e, src);
+                        const LayoutResult<float> Lr = layout_warp<float>(a, e_src, __shfl_sync(kFull, cur_food, src), lane);
+                        if (lane < Lr.n_food) reinterpret_cast<float2 *>(a.food)[(size_t)lane * N + e_src] = make_float2(Lr.x, Lr.y);
+                        if (lane == src) {
+                            cur_food = Lr.cur; n_food = Lr.n_food;
+                            mask = Lr.n_food >= 32 ? 0xffffffffu : ((1u << Lr.n_food) - 1u);
+                        }
+                    }
+                    __syncwarp();
+                    if (done) {
+                        px = W * 0.5f; py = H * 0.5f; vx = 0.f; vy = 0.f; angle = 0.f; omega = 0.f; nozzle = 0.f; wv_now = 0.f;
+                        fsm = kPhaseRest | (kShapeReset << 18); q = 0;
+                        steps_since_food = 0; food_collected = 0; ep_ret = 0.f; ep_len = 0;
+                        obs6 = 1.0f; obs7 = 0.f;
+                        hit = true;  // the bearing computed for the reward belongs to the finished episode
+#pragma unroll 1
+                        for (int f = 0; f < F; ++f) {  // offsets of the new foods from the new position (HBM: other lanes wrote them)
+                            const float2 nf = g_food[(size_t)f * N + e];
+                            sfood[f * 32 + lane] = make_float2(nf.x - px, nf.y - py);
+                        }
+                        reselect();
+                    }
+                }
+            }  // pass
+            if constexpr (F > 1) {
+                // K > 1: the next substep expects positions in the buffer again; re-read them from HBM (L1/L2 hits;
+                // foods change only through the slow paths, which write HBM)
+                if (k + 1 < a.K) {
+#pragma unroll
+                    for (int f = 0; f < F; ++f) sfood[f * 32 + lane] = valid ? g_food[(size_t)f * N + e] : make_float2(0.f, 0.f);
+                }
+            }
+            // ---- publish this substep's observation tile (3 KB, contiguous in HBM)
+            if (full) {
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                __syncwarp();
+                if (elect_one_sync()) {
+                    bulk_store(a.obs + ((size_t)k * N + e0) * OBS, s_obs, L::kObs);
+                    if (k + 1 < a.K) bulk_commit();
+                }
+            } else if (valid) {
+                float4 *dst = reinterpret_cast<float4 *>(a.obs + ((size_t)k * N + e) * OBS);
+                const float4 *src = reinterpret_cast<const float4 *>(row);
+#pragma unroll
+                for (int j = 0; j < OBS / 4; ++j) dst[j] = src[j];
+            }
+        }  // substeps
+
+        // ---- the food buffer is free (FS == 1): fetch the next tile's foods
+        if constexpr (FS == 1) {
+            __syncwarp();
+            if (nxt < ntiles) load_food(nxt);
+        }
+        // ---- new state over the tile's input slots, stored from there (food records are only written by the slow paths)
+        {
+            const int4 n0 = make_int4(fsm, steps_since_food, food_collected, (int)mask);
+            const int4 n1 = make_int4((int)cur_food, (int)cur_jit, (ep_len < kEpLenMask ? ep_len : kEpLenMask) | (n_food << 26), (int)jcache);
+            if (valid) g_epret[e] = ep_ret;
+            if (full) {
+                reinterpret_cast<int4 *>(sc + L::kC0)[lane] = n0;
+                reinterpret_cast<int4 *>(sc + L::kC1)[lane] = n1;
+                reinterpret_cast<float4 *>(sc + L::kB0)[lane] = make_float4(px, py, vx, vy);
+                reinterpret_cast<float4 *>(sc + L::kB1)[lane] = make_float4(angle, omega, nozzle, wv_now);
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                __syncwarp();
+                if (elect_one_sync()) {
+                    bulk_store(a.ctrl + e0, sc + L::kC0, 512);
+                    bulk_store(a.ctrl + (size_t)N + e0, sc + L::kC1, 512);
+                    bulk_store(reinterpret_cast<float4 *>(a.body) + e0, sc + L::kB0, 512);
+                    bulk_store(reinterpret_cast<float4 *>(a.body) + (size_t)N + e0, sc + L::kB1, 512);
+                    bulk_commit();
+                }
+            } else if (valid) {
+                a.ctrl[e] = n0;
+                a.ctrl[(size_t)N + e] = n1;
+                reinterpret_cast<float4 *>(a.body)[e] = make_float4(px, py, vx, vy);
+                reinterpret_cast<float4 *>(a.body)[(size_t)N + e] = make_float4(angle, omega, nozzle, wv_now);
+            }
+        }
+    }  // tiles
+    if (blockIdx.x == 0 && threadIdx.x == 0 && a.stats) atomicAdd(a.stats + 7, (double)a.count * (double)a.K);
+    if (elect_one_sync()) bulk_wait_read<0>();  // shared memory must stay allocated until the last bulk store has read it
+}
+
+}  // namespace salp

@@ -38,7 +38,7 @@ class SalpSnakeEnv(Env):
         self.observation_space = self._v.single_observation_space
         for k in ("food_reward", "collision_penalty", "time_penalty", "efficiency_bonus", "forced_breathing",
                   "max_observed_food", "random_food_count", "respawn_food", "proximity_reward_weight",
-                  "max_steps_without_food", "base_num_food_items"):
+                  "max_steps_without_food"):
             setattr(self, k, getattr(self._v, k))
         self.reset()  # the reference constructor resets (salp_robot.py:93)
 
@@ -58,7 +58,14 @@ class SalpSnakeEnv(Env):
         return o, float(rew[0].item()), bool(term[0].item()), bool(trunc[0].item()), info
 
     def _get_extended_observation(self):
-        raise NotImplementedError("observations are produced by step()/reset(); poke state with the setters, then step")
+        """salp_snake_env.py:366-428: the observation of the current (possibly poked) state, no step
+        (eval/collect_navigation_data.py:89, eval/watch_navigation.py:63) -- the salp_observe kernel."""
+        return self._v.observe()[0].cpu().numpy().copy()
+
+    @property
+    def base_num_food_items(self): return self._v.base_num_food_items
+    @base_num_food_items.setter
+    def base_num_food_items(self, n): self._v.base_num_food_items = n  # continuous_trainer.py:408-411
 
     def _get_info(self) -> dict:
         a, b = self._v.ellipse_axes()

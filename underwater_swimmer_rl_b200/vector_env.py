@@ -19,7 +19,7 @@ import numpy as np
 import torch
 
 from . import _capi, rng_tables
-from ._gym_compat import Box, VectorEnv, batch_box
+from ._gym_compat import HAVE_GYMNASIUM, Box, VectorEnv, batch_box
 
 # SalpSnakeEnv.__init__ defaults (salp_snake_env.py:29-33)
 ENV_DEFAULTS = dict(
@@ -83,6 +83,9 @@ class SalpVectorEnv(VectorEnv):
       table_rows                 rows of the RNG word tables (default num_envs; fewer rows are
                                  shared round-robin -- throughput runs only)
       food_table_len, jitter_table_len   words per row (powers of two; cursors wrap)
+      rng                        "table": the two random streams are read from host-seeded MT19937 word tables (parity with
+                                 the reference's `random` / `np.random`); "philox": computed in the kernel (Philox4x32-10
+                                 keyed by seed, global env id and word index) -- unbounded streams, no memory, no parity
       max_substeps               K: env steps fused per kernel launch (``step_many``)
       autoreset                  Gymnasium vector auto-reset inside the kernel (default True)
     """
@@ -92,7 +95,7 @@ class SalpVectorEnv(VectorEnv):
     def __init__(self, num_envs: int, device: Any = "cuda:0", dtype: Any = "float32", seed: int = 10_000,
                  env_id0: int = 0, table_rows: Optional[int] = None, food_table_len: int = 256,
                  jitter_table_len: int = 1024, max_substeps: int = 1, autoreset: bool = True,
-                 render_mode: Optional[str] = None, **env_kwargs):
+                 render_mode: Optional[str] = None, rng: str = "table", generic_kernel: bool = False, **env_kwargs):
         if render_mode is not None:
             raise ValueError("render_mode must be None: there is no graphics stack on the GPU box (SURVEY.md F11)")
         if not torch.cuda.is_available():
@@ -109,7 +112,14 @@ class SalpVectorEnv(VectorEnv):
         self.max_substeps = int(max_substeps)
         self.autoreset = bool(autoreset)
         self.render_mode = None
+        if rng not in ("table", "philox"):
+            raise ValueError("rng must be 'table' (host-seeded MT19937 word tables shared with the reference) or 'philox'")
+        self.rng = rng
         self.params = make_params(self.autoreset, **env_kwargs)
+        if rng == "philox":
+            self.params.flags |= _capi.SALP_RNG_PHILOX
+        if generic_kernel:  # diagnostics / tests: never select the specialised forced-breathing kernel
+            self.params.flags |= _capi.SALP_GENERIC_KERNEL
         self.layout = _capi.SalpLayout()
         _capi.check(self._L.salp_query_layout(C.byref(self.params), self._dtype_code, C.byref(self.layout)))
         self.obs_dim, self.act_dim, self.food_slots = self.layout.obs_dim, self.layout.act_dim, self.layout.food_slots
@@ -118,8 +128,14 @@ class SalpVectorEnv(VectorEnv):
         # reference-visible attributes
         for k in ENV_DEFAULTS:
             setattr(self, k, env_kwargs.get(k, ENV_DEFAULTS[k]))
-        self.base_num_food_items = self.params.num_food_items
-        self.single_observation_space, self.single_action_space = single_spaces(self.params, self.layout)
+        self._base_num_food_items = self.params.num_food_items
+        obs_space, act_space = single_spaces(self.params, self.layout)
+        if HAVE_GYMNASIUM:  # gymnasium 0.29.1: VectorEnv.__init__(num_envs, observation_space, action_space) batches the spaces
+            try:
+                VectorEnv.__init__(self, self.num_envs, obs_space, act_space)
+            except TypeError:  # gymnasium >= 1.0: VectorEnv has no constructor arguments
+                VectorEnv.__init__(self)
+        self.single_observation_space, self.single_action_space = obs_space, act_space
         self.observation_space = batch_box(self.single_observation_space, self.num_envs)
         self.action_space = batch_box(self.single_action_space, self.num_envs)
 
@@ -147,6 +163,10 @@ class SalpVectorEnv(VectorEnv):
 
     # ------------------------------------------------------------------ plumbing
     def _load_tables(self, seed: int) -> None:
+        if self.rng == "philox":  # both streams are computed in the kernel: no tables, no memory
+            _capi.check(self._L.salp_set_rng_seed(self._handle, int(seed)))
+            self.food_words = self.jit_words = torch.zeros(8, dtype=torch.int32, device=self.device)
+            return
         rows, first = self.table_rows, self.env_id0
         fw = rng_tables.fill_words(rows, self.food_table_len, seed, first, rng_tables.FOOD_STREAM)
         jw = rng_tables.fill_words(rows, self.jitter_table_len, seed, first, rng_tables.JITTER_STREAM)
@@ -239,6 +259,24 @@ class SalpVectorEnv(VectorEnv):
             else:  # outputs go to row `slot` of the [max_substeps, N, ...] buffers (ping-pong, see rollout.py)
                 _capi.check(self._L.salp_step_slot(self._handle, int(slot), a.data_ptr(), self._stream()))
         return self.obs[slot], self.reward[slot], self.terminated[slot], self.truncated[slot], StepInfos(self, slot)
+
+    def observe(self, slot: int = 0) -> torch.Tensor:
+        """Observation of the CURRENT state without stepping: the reference's ``_get_extended_observation()``
+        (salp_snake_env.py:366-428) as its callers use it after poking robot_pos / robot_angle / food_positions
+        (eval/collect_navigation_data.py:76-89).  Writes and returns ``obs[slot]``."""
+        with torch.cuda.device(self.device):
+            _capi.check(self._L.salp_observe(self._handle, int(slot), self._stream()))
+        return self.obs[slot]
+
+    @property
+    def base_num_food_items(self) -> int:
+        return self._base_num_food_items
+
+    @base_num_food_items.setter
+    def base_num_food_items(self, n: int) -> None:
+        """``env.base_num_food_items = n`` (continuous_trainer.py:408-411): episodes that start after this use n foods."""
+        _capi.check(self._L.salp_set_num_food_items(self._handle, int(n)))
+        self._base_num_food_items = max(0, int(n))
 
     def step_many(self, actions, k_steps: Optional[int] = None):
         """K fused env steps in ONE launch (open-loop actions [K, N, act_dim]): state stays in
@@ -413,7 +451,12 @@ class SalpVectorEnv(VectorEnv):
             w = (self.ctrl[1, :, 2].to(torch.int64) & 0x3FFFFFF) | (int(nf) << 26)
             self.ctrl[1, :, 2] = torch.where(w >= 2 ** 31, w - 2 ** 32, w).to(torch.int32)
             return
+        if name == "base_num_food_items":
+            self.base_num_food_items = int(values)
+            return
         target = getattr(self, name)
+        if not isinstance(target, torch.Tensor):
+            raise AttributeError(f"{name!r} is not per-env state; pass it to the constructor")
         target.copy_(torch.as_tensor(values, device=self.device).to(target.dtype).expand_as(target))
 
     def call(self, name: str, *args, **kwargs):
