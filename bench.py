@@ -11,7 +11,7 @@ interact, so ranks share nothing on the data path):
     single_food_1m   configs/single_food.yaml, 1,048,576 envs / GPU, fp32          [default]
     long_horizon_64k configs/single_food_long_horizon.yaml, 65,536 envs / GPU, fp32 (configs[2])
     defaults_1m      configs/defaults.yaml (12 food), 1,048,576 envs / GPU, fp32   (configs[3])
-    sac_rollout_256k configs/sac_gail.yaml, 262,144 envs / GPU, actor MLP + env step + replay append (configs[4])
+    sac_rollout_256k configs/sac_gail.yaml, 262,144 envs / GPU, actor MLP + env step + replay storage (configs[4])
     parity_4k        configs/single_food.yaml, 4,096 envs, fp64 validation build   (configs[1])
 Prints ONE JSON line (rank 0).  See DESIGN.md section "Measurement" for every field.
 """
@@ -70,14 +70,26 @@ def min_traffic_bytes_per_env_step(n_food: int, real_bytes: int, k_fused: int = 
     return A + O + R + D + (2.0 * S - 2 * n_food * real_bytes) / k_fused
 
 
-def ncu_traffic_bytes(workload: str, envs: int, k_fused: int):
+def ncu_traffic_bytes(workload: str, envs: int, k_fused: int, rng: str = "philox"):
     """DRAM bytes per launch of the step kernel from the committed ncu --set full capture of this
-    workload (profiles/r01_ncu_traffic.json); None when no capture matches the configuration."""
+    workload (profiles/r02_ncu_traffic.json); None when no capture matches the configuration."""
     try:
-        t = json.load(open(os.path.join(ROOT, "profiles", "r01_ncu_traffic.json")))[workload]
+        t = json.load(open(os.path.join(ROOT, "profiles", "r02_ncu_traffic.json")))[workload + "/" + rng]
         return float(t["dram_bytes_per_launch"]) if (t["envs_per_launch"] == envs and k_fused == 1) else None
     except Exception:
         return None
+
+
+def pin_rank_to_cores(local_rank: int, local_world: int) -> None:
+    """One process per GPU: give each rank its own share of the host cores, so that the pinned staging buffers it allocates
+    afterwards and the threads that drive its copies stay put (the box's ranks otherwise pile onto the same cores)."""
+    try:
+        cores = sorted(os.sched_getaffinity(0))
+        per = max(1, len(cores) // max(1, local_world))
+        mine = cores[local_rank * per:(local_rank + 1) * per] or cores
+        os.sched_setaffinity(0, mine)
+    except (AttributeError, OSError):
+        pass
 
 
 def measured_peak_gbs():
@@ -133,34 +145,6 @@ class ClockSampler:
                 continue
         sm.sort()
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "samples": len(sm), "reasons": sorted(reasons)}
-
-
-def cpu_oracle_throughput(params: dict, budget_s: float, threads: int, n_envs: int, T: int):
-    """Time the CPU restatement (oracle/salp_oracle.c, OpenMP over envs) on a bounded sample of the
-    same workload.  Returns (env-steps/s, seconds, description)."""
-    import numpy as np
-
-    from oracle import salp_oracle
-    from underwater_swimmer_rl_b200 import rng_tables
-    os.environ["OMP_NUM_THREADS"] = str(threads)
-    salp_oracle.build()
-    fw = rng_tables.fill_words(n_envs, 128, 10_000, 0, rng_tables.FOOD_STREAM)
-    jw = rng_tables.fill_words(n_envs, 512, 10_000, 0, rng_tables.JITTER_STREAM)
-    g = np.random.default_rng(1234)
-    acts = g.uniform(-1, 1, (T, n_envs, 1)).astype(np.float32)
-    orc = salp_oracle.Oracle(n_envs, fw, jw, **params)
-    orc.reset()
-    orc.rollout(acts[: max(1, T // 10)], autoreset=True, record=False)  # warm-up
-    done_steps, t0 = 0, time.perf_counter()
-    reps = 0
-    while True:
-        orc.rollout(acts, autoreset=True, record=False)
-        done_steps += n_envs * T
-        reps += 1
-        el = time.perf_counter() - t0
-        if el >= budget_s or reps >= 64:
-            break
-    return done_steps / el, el, f"{n_envs} envs x {T * reps} steps, auto-reset, uniform(-1,1) actions, no output recording"
 
 
 def cycle_actions(torch, n, dev, real, seed):
@@ -336,44 +320,188 @@ def run_cycle_workload(args, wl):
         dist.destroy_process_group()
 
 
+def oracle_steady_state(params: dict, n_envs: int, threads: int, prime_steps: int):
+    """The CPU arm's batch: oracle envs on the reference's own word streams (MT19937 tables filled inside oracle/ -- the
+    product library is never loaded here), primed to the same steady state as the GPU arm (episodes ended, breathing phases
+    de-synchronised: resets, respawns and thrust steps inside the timed region).  Returns (Oracle, action generator)."""
+    import numpy as np
+
+    from oracle import salp_oracle
+    os.environ["OMP_NUM_THREADS"] = str(threads)
+    salp_oracle.build()
+    fw = salp_oracle.fill_words(n_envs, 128, 10_000, 0, 0)
+    jw = salp_oracle.fill_words(n_envs, 512, 10_000, 0, 1)
+    orc = salp_oracle.Oracle(n_envs, fw, jw, **params)
+    orc.reset()
+    g = np.random.default_rng(1234)
+    chunk = 256
+    for _ in range((prime_steps + chunk - 1) // chunk):
+        orc.rollout(g.uniform(-1, 1, (chunk, n_envs, 1)).astype(np.float32), autoreset=True, record=False)
+    return orc, g
+
+
+def cpu_oracle_throughput(params: dict, budget_s: float, threads: int, n_envs: int, T: int, prime_steps: int = 2048):
+    """Time the CPU restatement (oracle/salp_oracle.c, OpenMP over envs) on a bounded sample of the same workload in the
+    same steady state.  Returns (env-steps/s, seconds, description)."""
+    import numpy as np
+    orc, g = oracle_steady_state(params, n_envs, threads, prime_steps)
+    acts = g.uniform(-1, 1, (T, n_envs, 1)).astype(np.float32)
+    done_steps, reps, t0 = 0, 0, time.perf_counter()
+    while True:
+        orc.rollout(acts, autoreset=True, record=False)
+        done_steps += n_envs * T
+        reps += 1
+        el = time.perf_counter() - t0
+        if el >= budget_s or reps >= 64:
+            break
+    return done_steps / el, el, (f"{n_envs} envs x {T * reps} steps after {prime_steps} priming steps, auto-reset, "
+                                 "uniform(-1,1) actions, no output recording")
+
+
+def cpu_oracle_single_env(params: dict, T: int = 1000, reps: int = 20):
+    """BASELINE.json configs[0] with the C restatement: 1 env x 1000 steps on 1 core (best of `reps`)."""
+    import numpy as np
+
+    from oracle import salp_oracle
+    os.environ["OMP_NUM_THREADS"] = "1"
+    fw = salp_oracle.fill_words(1, 128, 10_000, 0, 0)
+    jw = salp_oracle.fill_words(1, 512, 10_000, 0, 1)
+    acts = np.random.default_rng(1234).uniform(-1, 1, (T, 1, 1)).astype(np.float32)
+    best = 0.0
+    for _ in range(reps):
+        orc = salp_oracle.Oracle(1, fw, jw, **params)
+        orc.reset()
+        t0 = time.perf_counter()
+        orc.rollout(acts, autoreset=True, record=False)
+        best = max(best, T / (time.perf_counter() - t0))
+    return best
+
+
+def python_reference_numbers(workload_yaml):
+    """The unmodified Python reference timed in the build container (tools/time_python_reference.py ->
+    profiles/r02_python_reference_cpu.json; /root/reference cannot travel to the GPU box)."""
+    try:
+        d = json.load(open(os.path.join(ROOT, "profiles", "r02_python_reference_cpu.json")))
+        key = os.path.splitext(os.path.basename(workload_yaml or "configs/single_food.yaml"))[0]
+        c = d["configs"][key]
+        return {"steps_per_s_1core_1env_1000steps": c["steps_per_s_1core_1env_1000steps"], "processes": c["processes"],
+                "steps_per_s_all_cores": c["steps_per_s_all_cores_wall"], "machine": "build container (%d cores)" % d["machine"]["cpu_count"],
+                "source": "profiles/r02_python_reference_cpu.json (tools/time_python_reference.py)"}
+    except (OSError, KeyError, ValueError):
+        return None
+
+
 def run_reference_arm(args, wl):
     """--impl reference: the reference's CPU implementation of the path on the host cores.
     The reference is pure Python and cannot travel to the GPU box, so this is its C restatement
-    (oracle/, bit-exact against the Python reference -- DESIGN.md) with all host threads."""
+    (oracle/, bit-exact against the Python reference -- DESIGN.md) with all host threads.  Nothing of the product
+    package is imported: the word tables come from oracle/ too."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     import numpy as np
-
-    from oracle import salp_oracle
-    from underwater_swimmer_rl_b200 import rng_tables
     threads = os.cpu_count() or 1
-    os.environ["OMP_NUM_THREADS"] = str(threads)
-    salp_oracle.build()
-    n = min(wl["envs"], 1 << 16)
-    fw = rng_tables.fill_words(n, 128, 10_000, 0, rng_tables.FOOD_STREAM)
-    jw = rng_tables.fill_words(n, 512, 10_000, 0, rng_tables.JITTER_STREAM)
-    acts = np.random.default_rng(1234).uniform(-1, 1, (args.warmup + args.steps, n, 1)).astype(np.float32)
-    orc = salp_oracle.Oracle(n, fw, jw, **wl["params"])
-    orc.reset()
+    n = min(wl["envs"], 1 << 18)
+    orc, g = oracle_steady_state(wl["params"], n, threads, args.prime_steps)
+    acts = g.uniform(-1, 1, (args.warmup + args.steps, n, 1)).astype(np.float32)
     if args.warmup:
         orc.rollout(acts[: args.warmup], autoreset=True, record=False)
     t0 = time.perf_counter()
     orc.rollout(acts[args.warmup:], autoreset=True, record=False)
     el = time.perf_counter() - t0
     value = n * args.steps / el
-    sample = f"{n} envs x {args.steps} steps per run (bounded sample of {wl['envs']} envs/GPU), auto-reset"
+    sample = (f"{n} envs x {args.steps} steps per run (bounded sample of {wl['envs']} envs/GPU) after {args.prime_steps} priming steps "
+              "(same steady state as the GPU arm), auto-reset")
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * el / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": args.workload, "reference_yaml": wl["yaml"], "envs_per_step": n,
-                   "note": "C restatement of the Python reference (bit-exact, oracle/), OpenMP over envs"},
+        "config": {"workload": args.workload, "reference_yaml": wl["yaml"], "envs_per_step": n, "prime_steps": args.prime_steps,
+                   "note": "C restatement of the Python reference (bit-exact, oracle/), OpenMP over envs; the product library is not loaded"},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+        "python_reference": python_reference_numbers(wl["yaml"]),
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
     print(json.dumps(line))
+
+
+class SlabTimer:
+    """One env slab of this rank, its resident action pool and a step runner that replays CUDA graphs of up to 32 steps
+    (a step of a small slab is shorter than the Python/ctypes launch path; for large slabs the graph keeps the slowest
+    rank's launch cadence out of the max-over-ranks time) and runs EXACTLY the requested number of steps."""
+
+    def __init__(self, torch, params, N, dev, dtype, rank_id0, rng, K=1, use_graph=True, seed=1234):
+        from underwater_swimmer_rl_b200 import SalpVectorEnv
+        self.torch, self.N, self.K = torch, N, K
+        real = torch.float64 if dtype == "float64" else torch.float32
+        self.env = SalpVectorEnv(N, device=dev, dtype=dtype, seed=10_000, env_id0=rank_id0, food_table_len=128, jitter_table_len=512,
+                                 max_substeps=K, autoreset=True, rng=rng, **params)
+        self.env.reset()
+        gen = torch.Generator(device=dev)
+        gen.manual_seed(seed)
+        self.pool = [torch.rand(K, N, self.env.act_dim, device=dev, dtype=real, generator=gen) * 2 - 1 for _ in range(32)]
+        self.use_graph = use_graph
+        self._graphs = {}
+        self.i = 0
+
+    def _graph(self, g):
+        if g not in self._graphs:
+            self._graphs[g] = self.env.capture_graph([p if self.K > 1 else p[0] for p in self.pool[:g]], self.K)
+        return self._graphs[g]
+
+    def prepare(self, n):
+        """capture the graphs run(n) will need (outside any timed region)"""
+        if self.use_graph:
+            if n >= 32:
+                self._graph(32)
+            if n % 32:
+                self._graph(n % 32)
+
+    def run(self, n):
+        if not self.use_graph:
+            for _ in range(n):
+                p = self.pool[self.i % 32]
+                self.env.step(p[0]) if self.K == 1 else self.env.step_many(p, self.K)
+                self.i += 1
+            return
+        for _ in range(n // 32):
+            self._graph(32)()
+        if n % 32:
+            self._graph(n % 32)()
+
+    def time(self, steps, warmup, prime, dist=None, world=1):
+        """(ms for `steps` steps on this rank, launches) -- CUDA events on the launching stream, barrier + synchronize on both sides"""
+        torch = self.torch
+        self.prepare(steps), self.prepare(warmup), self.prepare(prime)
+        self.run(prime)
+        self.run(warmup)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        l0 = self.env.launch_count
+        ev0.record()
+        self.run(steps)
+        ev1.record()
+        torch.cuda.synchronize()
+        ms = ev0.elapsed_time(ev1)
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        return ms, (steps if self.use_graph else self.env.launch_count - l0)
+
+    def close(self):
+        self._graphs.clear()
+        self.env.close()
+
+
+def rank_max_min(torch, dist, dev, x, world):
+    t = torch.tensor([x, -x], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t[0].item()), -float(t[1].item())
 
 
 def main():
@@ -385,24 +513,34 @@ def main():
     ap.add_argument("--workload", default="single_food_1m", choices=sorted(WORKLOADS))
     ap.add_argument("--envs-per-gpu", type=int, default=0)
     ap.add_argument("--substeps", type=int, default=1, help="K env steps fused per launch (open-loop actions)")
+    ap.add_argument("--rng", default="philox", choices=["philox", "table"],
+                    help="philox: both random streams computed in the kernel (unbounded, the mode long rollouts use); table: host-seeded "
+                         "MT19937 word tables shared with the reference (the parity mode; finite, cursors wrap)")
+    ap.add_argument("--dtype", default="", choices=["", "float32", "float64"], help="override the workload's build (float64 = validation build)")
     ap.add_argument("--torch-actor", action="store_true", help="sac_rollout: torch bf16 MLP instead of the fused tcgen05 actor kernel")
     ap.add_argument("--append-kernel", action="store_true", help="sac_rollout: transition-major DeviceReplayBuffer filled by salp_replay_append "
                     "instead of the zero-copy StepRingReplay (the env's own output rows are the replay storage)")
-    ap.add_argument("--graph", default="auto", choices=["auto", "on", "off"], help="replay the step from a CUDA graph (auto: slabs <= 262144 envs)")
+    ap.add_argument("--graph", default="on", choices=["on", "off"], help="replay the steps from CUDA graphs of up to 32 steps")
     ap.add_argument("--e2e-steps", type=int, default=20)
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the secondary measurements (other RNG mode, strong-scaling block)")
     ap.add_argument("--prime-steps", type=int, default=2048,
                     help="untimed env steps before warm-up so episodes have ended and envs are de-synchronised "
                          "(steady state: resets, respawns and divergent breathing phases inside the timed region)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
-    spr = 2 if (args.append_kernel or args.workload != "sac_rollout_256k") else RING_STEPS  # env steps per rollout graph replay
-    args.steps = (args.steps + spr - 1) // spr * spr
-    args.warmup = (args.warmup + spr - 1) // spr * spr
     wl = dict(WORKLOADS[args.workload])
     if args.envs_per_gpu:
         wl["envs"] = args.envs_per_gpu
+    if args.dtype:
+        wl["dtype"] = args.dtype
+    rollout = bool(wl.get("rollout"))
+    spr = 1
+    if rollout:
+        spr = 2 if args.append_kernel else RING_STEPS  # env steps per rollout graph replay
+        args.steps = (args.steps + spr - 1) // spr * spr
+        args.warmup = (args.warmup + spr - 1) // spr * spr
     if wl.get("cycle"):
         return run_cycle_reference_arm(args, wl) if args.impl == "reference" else run_cycle_workload(args, wl)
     if args.impl == "reference":
@@ -411,96 +549,71 @@ def main():
     import torch
     import torch.distributed as dist
 
-    from underwater_swimmer_rl_b200 import SalpVectorEnv
-
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device (there is no CPU fallback for the product path)")
+    pin_rank_to_cores(local, int(os.environ.get("LOCAL_WORLD_SIZE", str(world))))
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
-    N, K = wl["envs"], args.substeps
-    rollout = bool(wl.get("rollout"))
-    if rollout:
-        K = 1
+    N, K = wl["envs"], (1 if rollout else args.substeps)
     real = torch.float64 if wl["dtype"] == "float64" else torch.float32
-    env = SalpVectorEnv(N, device=dev, dtype=wl["dtype"], seed=10_000, env_id0=rank * N, food_table_len=128,
-                        jitter_table_len=512, max_substeps=(2 if args.append_kernel else RING_STEPS) if rollout else K,
-                        autoreset=True, **wl["params"])
-    env.reset()
-    # synthetic actions, resident in HBM before the timed region: a pool of 32 [K, N, 1] tensors
-    gen = torch.Generator(device=dev)
-    gen.manual_seed(1234 + rank)
-    pool = [torch.rand(K, N, env.act_dim, device=dev, dtype=real, generator=gen) * 2 - 1 for _ in range(32)]
-
-    launches_per_step = 1
+    rb = 8 if real == torch.float64 else 4
     if rollout:
-        from underwater_swimmer_rl_b200.rollout import DeviceReplayBuffer, RolloutCollector, TanhGaussianActor
+        slab = None
+        from underwater_swimmer_rl_b200 import SalpVectorEnv
+        env = SalpVectorEnv(N, device=dev, dtype=wl["dtype"], seed=10_000, env_id0=rank * N, food_table_len=128, jitter_table_len=512,
+                            max_substeps=2 if args.append_kernel else RING_STEPS, autoreset=True, rng=args.rng, **wl["params"])
+        env.reset()
+        gen = torch.Generator(device=dev)
+        gen.manual_seed(1234 + rank)
+        pool = [torch.rand(1, N, env.act_dim, device=dev, dtype=real, generator=gen) * 2 - 1 for _ in range(2)]
+        from underwater_swimmer_rl_b200.rollout import (DeviceReplayBuffer, FusedActor, RolloutCollector, StepRingReplay,
+                                                         TanhGaussianActor)
         torch.manual_seed(1234 + rank)
-        from underwater_swimmer_rl_b200.rollout import FusedActor
         actor = TanhGaussianActor(env.obs_dim, env.act_dim, (256, 256)).to(dev)
         actor = actor.to(torch.bfloat16) if args.torch_actor else FusedActor(actor)
-        from underwater_swimmer_rl_b200.rollout import StepRingReplay
         ring = DeviceReplayBuffer(4 * N, env.obs_dim, env.act_dim, dev) if args.append_kernel else StepRingReplay(env)
         col = RolloutCollector(env, actor, ring)
-        replay2 = col.capture()  # one graph launch = spr env steps of (actor -> env kernel [-> replay append])
+        replay = col.capture()  # one graph launch = spr env steps of (actor -> env kernel [-> replay append])
         assert col.steps_per_replay == spr
-        # ours, per env step: [salp_actor_kernel,] salp_step_kernel [, replay_append_kernel]
         launches_per_step = (0 if args.torch_actor else 1) + 1 + (1 if args.append_kernel else 0)
 
-    # small slabs: one step is a few microseconds of device time, less than the Python launch path ->
-    # replay a CUDA graph of 32 steps (one per action tensor of the pool); it is the product API for this regime
-    graphed = (not rollout) and args.graph != "off" and (args.graph == "on" or N <= (1 << 18))
-    if graphed:
-        args.steps = max(32, args.steps // 32 * 32)
-        args.warmup = max(32, args.warmup // 32 * 32)
-        args.prime_steps = (args.prime_steps + 31) // 32 * 32
-        replay32 = env.capture_graph([p if K > 1 else p[0] for p in pool], K)
+        def run(n):
+            for _ in range(n // spr):
+                replay()
+        run((args.prime_steps + spr - 1) // spr * spr)
+        run(args.warmup)
+    else:
+        slab = SlabTimer(torch, wl["params"], N, dev, wl["dtype"], rank * N, args.rng, K, args.graph == "on", 1234 + rank)
+        env = slab.env
 
-    def one_step(i):
-        if graphed:
-            if i % 32 == 0:
-                replay32()
-        elif rollout:
-            if i % spr == 0:
-                replay2()
-        elif K == 1:
-            env.step(pool[i % 32][0])
-        else:
-            env.step_many(pool[i % 32], K)
-
-    for i in range((args.prime_steps + K - 1) // K):
-        one_step(i)
-    for i in range(args.warmup):
-        one_step(i)
     sampler = ClockSampler(local)
-    torch.cuda.synchronize()
-    if world > 1:
-        dist.barrier()
-    torch.cuda.synchronize()
     if rank == 0:
         sampler.start()
-    launches0 = env.launch_count
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    ev0.record()
-    for i in range(args.steps):
-        one_step(args.warmup + i)
-    ev1.record()
-    torch.cuda.synchronize()
-    ms = ev0.elapsed_time(ev1)
-    if world > 1:
-        dist.barrier()
-    torch.cuda.synchronize()
+    if rollout:
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record()
+        run(args.steps)
+        ev1.record()
+        torch.cuda.synchronize()
+        ms = ev0.elapsed_time(ev1)
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        launches = launches_per_step * args.steps
+    else:
+        ms, launches = slab.time(args.steps, args.warmup, args.prime_steps, dist, world)
     clocks = sampler.stop() if rank == 0 else None
-    launches = (env.launch_count - launches0) if not (rollout or graphed) else launches_per_step * args.steps
-    t = torch.tensor([ms], device=dev, dtype=torch.float64)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_max = float(t.item())
+    ms_max, ms_min = rank_max_min(torch, dist, dev, ms, world)
     value = world * N * K * args.steps / (ms_max * 1e-3)
 
     env_only_ms = None
@@ -532,52 +645,94 @@ def main():
         env.step_host(a_h, o_h, r_h, te_h, tr_h)
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t0
-    t = torch.tensor([e2e_s], device=dev, dtype=torch.float64)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    e2e_value = world * N * args.e2e_steps / float(t.item())
-    rb = 8 if real == torch.float64 else 4
+    e2e_max, e2e_min = rank_max_min(torch, dist, dev, e2e_s, world)
+    e2e_value = world * N * args.e2e_steps / e2e_max
     h2d = N * env.act_dim * rb
     d2h = N * (env.obs_dim * 4 + rb + 2)
 
     stats = env.episode_stats()  # NCCL all-reduce (SUM) of the 8-double stats vector when world > 1
+    obs_dim, act_dim = env.obs_dim, env.act_dim
+    peak, peak_src = measured_peak_gbs()
+    nf = wl["params"]["num_food_items"]
+
+    # ---- secondary measurements (same protocol, every rank, max over ranks): the other RNG mode at the same slab size, and
+    #      the literal north_star split -- 1 048 576 envs over the GPUs of the job, for single_food and defaults
+    extras = {}
+    if not rollout and not args.no_extras and K == 1:
+        slab.close()
+        del slab, env
+        torch.cuda.empty_cache()
+        other = "table" if args.rng == "philox" else "philox"
+        s2 = SlabTimer(torch, wl["params"], N, dev, wl["dtype"], rank * N, other, 1, args.graph == "on", 1234 + rank)
+        ms2, _ = s2.time(max(args.steps, 64), args.warmup, args.prime_steps, dist, world)
+        ms2_max, _ = rank_max_min(torch, dist, dev, ms2 / max(args.steps, 64), world)
+        s2.close()
+        del s2
+        torch.cuda.empty_cache()
+        extras["rng_modes"] = {args.rng: {"ms_per_step": ms_max / args.steps, "value": value},
+                               other: {"ms_per_step": ms2_max, "value": world * N / (ms2_max * 1e-3)},
+                               "note": "philox: Philox4x32-10 in the kernel, keyed by (seed, global env id, word index): unbounded streams, no "
+                                       "memory; table: host-seeded MT19937 words shared with the reference (parity mode, 128 + 512 words per env)"}
+        n_s = (1 << 20) // world
+        strong = {"global_envs": n_s * world, "envs_per_gpu": n_s, "rng": args.rng, "steps": max(args.steps, 64)}
+        for name, prm in (("single_food", SINGLE_FOOD), ("defaults", DEFAULTS)):
+            st_ = SlabTimer(torch, prm, n_s, dev, "float32", rank * n_s, args.rng, 1, args.graph == "on", 1234 + rank)
+            ms3, _ = st_.time(max(args.steps, 64), args.warmup, args.prime_steps, dist, world)
+            ms3_max, _ = rank_max_min(torch, dist, dev, ms3 / max(args.steps, 64), world)
+            st_.close()
+            del st_
+            torch.cuda.empty_cache()
+            b3 = algorithmic_bytes_per_env_step(prm["num_food_items"], 4, 1, 1, 24)
+            ach = b3 * n_s / (ms3_max * 1e-3) / 1e9
+            strong[name] = {"ms_per_step_per_gpu": ms3_max, "value": n_s * world / (ms3_max * 1e-3), "achieved_gbs_per_gpu": ach,
+                            "frac": ach / peak, "algorithmic_bytes_per_env_step": b3}
+        extras["strong"] = strong
 
     if rank == 0:
-        peak, peak_src = measured_peak_gbs()
-        nf = wl["params"]["num_food_items"]
-        bpe = algorithmic_bytes_per_env_step(nf, rb, K, env.act_dim, env.obs_dim)
-        bmin = min_traffic_bytes_per_env_step(nf, rb, K, env.act_dim, env.obs_dim)
+        bpe = algorithmic_bytes_per_env_step(nf, rb, K, act_dim, obs_dim)
+        bmin = min_traffic_bytes_per_env_step(nf, rb, K, act_dim, obs_dim)
         kernel_ms = ms_max / args.steps  # the timed region is nothing but back-to-back launches of this kernel
         if rollout:
             kernel_ms = env_only_ms  # env kernel timed alone; the step also holds the actor GEMMs and the append
         achieved = bpe * N * K / (kernel_ms * 1e-3) / 1e9
+        fast = (real == torch.float32 and wl["params"].get("forced_breathing", True) and nf in (1, 12))
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f64" if real == torch.float64 else "f32", "data": "synthetic",
             "config": {"workload": args.workload, "reference_yaml": wl["yaml"], "envs_per_gpu": N, "global_envs": world * N,
-                       "substeps_per_launch": K, "cuda_graph": "32 steps per replay" if graphed else (("%d steps per replay" % spr) if rollout else None), "rollout": ("actor MLP [24-256-256-2] bf16 (" + ("torch" if args.torch_actor else "salp_actor_kernel, tcgen05") + ") -> salp_step_kernel -> " + ("salp_replay_append (transition-major ring)" if args.append_kernel else "zero-copy step ring (the env's [5, N] output rows are the replay storage; no append kernel)") + ", CUDA graph of %d steps" % spr + "; env kernel share of the step = %.2f" % (env_only_ms / (ms_max / args.steps))) if rollout else None, "prime_steps": args.prime_steps, "obs_dim": env.obs_dim, "act_dim": env.act_dim, "autoreset": True,
+                       "substeps_per_launch": K, "rng": args.rng,
+                       "cuda_graph": ("graphs of up to 32 steps" if args.graph == "on" else None) if not rollout else ("%d steps per replay" % spr),
+                       "rollout": ("actor MLP [24-256-256-2] bf16 (" + ("torch" if args.torch_actor else "salp_actor_kernel, tcgen05") + ") -> salp_step kernel -> " + ("salp_replay_append (transition-major ring)" if args.append_kernel else "zero-copy step ring (the env's [5, N] output rows are the replay storage: a 4-step window per env, not a uniform 1M-transition history; --append-kernel for the transition-major ring)") + ", CUDA graph of %d steps" % spr + "; env kernel share of the step = %.2f" % (env_only_ms / (ms_max / args.steps))) if rollout else None,
+                       "prime_steps": args.prime_steps, "obs_dim": obs_dim, "act_dim": act_dim, "autoreset": True,
                        "l2": f"per-step footprint {bpe * N / 1e6:.0f} MB vs 126 MB L2"
                              + (" (inputs larger than L2, no flush needed)" if bpe * N > 126e6 else " (L2-resident working set)"),
                        "parallelism": f"env-slab x{world} (no data-path collective; NCCL all-reduce of episode stats only)"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": ncu_traffic_bytes(args.workload, N, K), "kernel": "salp_step_kernel", "kernel_ms": kernel_ms,
+                         "traffic": ncu_traffic_bytes(args.workload, N, K, args.rng),
+                         "kernel": "salp_step_fast_kernel<%d, %d>" % (nf, 1 if args.rng == "philox" else 0) if fast else "salp_step_kernel",
+                         "kernel_ms": kernel_ms,
                          "algorithmic_bytes_per_env_step": bpe, "algorithmic_bytes_per_launch": bpe * N * K,
                          "min_traffic_bytes_per_env_step": bmin, "achieved_min_traffic": bmin * N * K / (kernel_ms * 1e-3) / 1e9,
                          "frac_min_traffic": bmin * N * K / (kernel_ms * 1e-3) / 1e9 / peak,
-                         "traffic_source": "profiles/r01_ncu_traffic.json (dram__bytes_read.sum + dram__bytes_write.sum per launch)",
+                         "traffic_source": "profiles/r02_ncu_traffic.json (dram__bytes_read.sum + dram__bytes_write.sum per launch)",
                          "peak_source": peak_src},
+            "per_rank_ms_per_step": {"min": ms_min / args.steps, "max": ms_max / args.steps},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "steps": args.e2e_steps, "api": "SalpVectorEnv.step_host -> salp_step_host (pinned host buffers)"},
+                    "steps": args.e2e_steps, "api": "SalpVectorEnv.step_host -> salp_step_host (pinned host buffers)",
+                    "d2h_gbs_per_gpu": d2h * args.e2e_steps / e2e_max / 1e9, "per_rank_s": {"min": e2e_min, "max": e2e_max}},
             "gpu_launches": launches, "clocks": clocks,
             "episode_stats": {k: stats[k] for k in ("episodes", "mean_return", "mean_length", "collisions", "truncations", "env_steps")},
         }
+        line.update(extras)
         if world == 1 and not args.no_cpu_baseline:
             threads = os.cpu_count() or 1
-            v, secs, sample = cpu_oracle_throughput(wl["params"], args.cpu_seconds, threads, 4096 * max(1, min(threads, 16)), 250)
+            v, secs, sample = cpu_oracle_throughput(wl["params"], args.cpu_seconds, threads, 4096 * max(1, min(threads, 16)), 250, args.prime_steps)
             line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample,
-                                    "seconds": secs, "note": "C restatement of the Python reference (oracle/), OpenMP; "
-                                    "the unmodified Python reference measured ~2.0e4 env-steps/s/core in the build container"}
+                                    "seconds": secs, "note": "C restatement of the Python reference (oracle/salp_oracle.c), OpenMP over envs"}
+            line["cpu_baseline_1core"] = {"value": cpu_oracle_single_env(SINGLE_FOOD), "unit": UNIT, "cores": 1, "kind": "port",
+                                          "sample": "BASELINE configs[0]: single_food.yaml, 1 env x 1000 steps, best of 20"}
+            line["python_reference"] = python_reference_numbers(wl["yaml"])
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

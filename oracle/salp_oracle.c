@@ -382,6 +382,56 @@ void salp_oracle_reset(const OracleParams *p, OracleEnv *envs, int64_t n, int64_
         env_reset(p, &envs[i], t, (env_id0 + i) % t->rows, obs ? obs + i * od : NULL);
 }
 
+/*
+ * The two word streams of the reference's generators, for callers that must not touch the product library (bench.py's
+ * reference arm): row r of dst[rows][len] = the first `len` raw MT19937 outputs after
+ *   kind 0: random.seed(seed0 + first_row + r)     CPython random_seed(): init_by_array([seed]) for seed < 2^32
+ *   kind 1: np.random.seed(seed0 + first_row + r)  numpy legacy: init_genrand(seed)
+ * (Matsumoto & Nishimura's MT19937 reference code, restated; tests/test_rng_tables.py checks both against the
+ * Python stdlib and numpy, and against the product's salp_fill_rng_words.)
+ */
+typedef struct { uint32_t mt[624]; int idx; } OracleMT;
+static void mt_init_genrand(OracleMT *g, uint32_t s) {
+    g->mt[0] = s;
+    for (int i = 1; i < 624; ++i) g->mt[i] = 1812433253u * (g->mt[i - 1] ^ (g->mt[i - 1] >> 30)) + (uint32_t)i;
+    g->idx = 624;
+}
+static void mt_init_by_array1(OracleMT *g, uint32_t key) {
+    mt_init_genrand(g, 19650218u);
+    int i = 1;
+    for (int k = 624; k; --k) {
+        g->mt[i] = (g->mt[i] ^ ((g->mt[i - 1] ^ (g->mt[i - 1] >> 30)) * 1664525u)) + key + 0u;
+        if (++i >= 624) { g->mt[0] = g->mt[623]; i = 1; }
+    }
+    for (int k = 623; k; --k) {
+        g->mt[i] = (g->mt[i] ^ ((g->mt[i - 1] ^ (g->mt[i - 1] >> 30)) * 1566083941u)) - (uint32_t)i;
+        if (++i >= 624) { g->mt[0] = g->mt[623]; i = 1; }
+    }
+    g->mt[0] = 0x80000000u;
+    g->idx = 624;
+}
+static uint32_t mt_next(OracleMT *g) {
+    if (g->idx >= 624) {
+        for (int k = 0; k < 624; ++k) {
+            const uint32_t y = (g->mt[k] & 0x80000000u) | (g->mt[(k + 1) % 624] & 0x7fffffffu);
+            g->mt[k] = g->mt[(k + 397) % 624] ^ (y >> 1) ^ ((y & 1u) ? 0x9908b0dfu : 0u);
+        }
+        g->idx = 0;
+    }
+    uint32_t y = g->mt[g->idx++];
+    y ^= y >> 11; y ^= (y << 7) & 0x9d2c5680u; y ^= (y << 15) & 0xefc60000u; y ^= y >> 18;
+    return y;
+}
+void salp_oracle_fill_rng_words(uint32_t *dst, int64_t rows, int64_t len, uint64_t seed0, int64_t first_row, int kind) {
+#pragma omp parallel for schedule(static)
+    for (int64_t r = 0; r < rows; ++r) {
+        OracleMT g;
+        const uint32_t s = (uint32_t)(seed0 + (uint64_t)first_row + (uint64_t)r);
+        if (kind == 0) mt_init_by_array1(&g, s); else mt_init_genrand(&g, s);
+        for (int64_t i = 0; i < len; ++i) dst[r * len + i] = mt_next(&g);
+    }
+}
+
 /* S:366-428 _get_extended_observation on the CURRENT state of n envs (no step): what the reference's callers
  * get after poking robot_pos / robot_angle / food_positions (eval/collect_navigation_data.py:76-89). */
 void salp_oracle_observe(const OracleParams *p, const OracleEnv *envs, int64_t n, float *obs /* [n][obs_dim] */) {

@@ -90,6 +90,14 @@ def lib():
     return _lib
 
 
+def fill_words(rows: int, length: int, seed0: int, first_row: int, kind: int) -> np.ndarray:
+    """uint32 [rows, length]: the raw MT19937 outputs of random.seed(s) (kind 0) / np.random.seed(s) (kind 1) for
+    s = seed0 + first_row + r, generated inside the oracle library (no dependency on the product package)."""
+    out = np.empty((rows, length), dtype=np.uint32)
+    lib().salp_oracle_fill_rng_words(_ptr(out), C.c_int64(rows), C.c_int64(length), C.c_uint64(seed0), C.c_int64(first_row), C.c_int(kind))
+    return out
+
+
 def make_params(**kw) -> OracleParams:
     d = dict(PARAM_DEFAULTS)
     unknown = set(kw) - set(d)

@@ -13,6 +13,22 @@ def pytest_configure(config):
     config.addinivalue_line("markers", "reference: needs the reference tree at /root/reference (build container)")
 
 
+def pytest_collection_modifyitems(config, items):
+    """`pytest tests` on a machine without a CUDA device (the build container) skips the gpu-marked tests instead of
+    failing in them; the driver selects them explicitly with -m gpu on the B200 box."""
+    try:
+        import torch
+        have_gpu = torch.cuda.is_available()
+    except Exception:
+        have_gpu = False
+    if have_gpu:
+        return
+    skip = pytest.mark.skip(reason="needs a CUDA device (B200 box: pytest -m gpu)")
+    for item in items:
+        if "gpu" in item.keywords:
+            item.add_marker(skip)
+
+
 @pytest.fixture(scope="session")
 def oracle_lib():
     from oracle import salp_oracle

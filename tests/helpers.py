@@ -125,3 +125,31 @@ def steering_actions(obs: np.ndarray, t: int, g: np.random.Generator, act_dim: i
         return a[:, None]
     hold = (np.random.default_rng(2000 + t // 45).uniform(0, 1, n)).astype(np.float32)
     return np.stack([hold, a], axis=1)
+
+
+def philox4x32_10(c0, c1, c2, c3, k0, k1):
+    """Philox4x32-10 (Salmon et al., SC'11) on numpy uint32 arrays; independent restatement of the kernel's generator."""
+    M0, M1, W0, W1 = np.uint64(0xD2511F53), np.uint64(0xCD9E8D57), 0x9E3779B9, 0xBB67AE85
+    c = [np.asarray(x, dtype=np.uint32).copy() for x in np.broadcast_arrays(c0, c1, c2, c3)]
+    k0, k1 = int(k0) & 0xFFFFFFFF, int(k1) & 0xFFFFFFFF
+    for _ in range(10):
+        p0 = c[0].astype(np.uint64) * M0
+        p1 = c[2].astype(np.uint64) * M1
+        hi0, lo0 = (p0 >> np.uint64(32)).astype(np.uint32), p0.astype(np.uint32)
+        hi1, lo1 = (p1 >> np.uint64(32)).astype(np.uint32), p1.astype(np.uint32)
+        c = [hi1 ^ c[1] ^ np.uint32(k0), lo1, hi0 ^ c[3] ^ np.uint32(k1), lo0]
+        k0, k1 = (k0 + W0) & 0xFFFFFFFF, (k1 + W1) & 0xFFFFFFFF
+    return c
+
+
+def philox_tables(seed: int, env_ids, food_len: int, jit_len: int):
+    """The word streams of SALP_RNG_PHILOX (include/salp_b200.h) as tables: word w of stream s (0 food, 1 jitter) of the
+    env with global id g = philox4x32_10(counter = (w >> 2, s, g_lo, g_hi), key = (seed_lo, seed_hi))[w & 3]."""
+    g = np.asarray(list(env_ids), dtype=np.uint64)
+    out = []
+    for s, n in ((0, food_len), (1, jit_len)):
+        blocks = np.arange((n + 3) // 4, dtype=np.uint32)
+        r = philox4x32_10(blocks[None, :], np.uint32(s), (g & np.uint64(0xFFFFFFFF)).astype(np.uint32)[:, None],
+                          (g >> np.uint64(32)).astype(np.uint32)[:, None], seed & 0xFFFFFFFF, seed >> 32)
+        out.append(np.stack(r, axis=-1).reshape(len(g), -1)[:, :n].astype(np.uint32))
+    return out[0], out[1]

@@ -35,3 +35,16 @@ def test_large_seeds_and_threads_agree(salp_lib):
     b = rng_tables.fill_words(64, 64, 4_000_000_000, 17, rng_tables.FOOD_STREAM, threads=8)
     assert np.array_equal(a, b)
     assert np.array_equal(a[5], py_food_words(4_000_000_000 + 17 + 5, 64))
+
+
+def test_oracle_fill_words_matches_stdlib_numpy_and_product(salp_lib, oracle_lib):
+    """oracle.salp_oracle.fill_words (used by bench.py's reference arm, which must not load the product library) ==
+    CPython random / numpy legacy streams == the product's salp_fill_rng_words."""
+    import numpy as np
+    from helpers import py_food_words, py_jitter_words
+    from underwater_swimmer_rl_b200 import rng_tables
+    for kind, ref in ((0, py_food_words), (1, py_jitter_words)):
+        t = oracle_lib.fill_words(5, 700, 10_000, 3, kind)   # 700 > 624: crosses a twist
+        for r in range(5):
+            assert (t[r] == ref(10_003 + r, 700)).all()
+        assert (t == rng_tables.fill_words(5, 1024, 10_000, 3, kind)[:, :700]).all()

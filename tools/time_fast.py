@@ -17,9 +17,9 @@ from underwater_swimmer_rl_b200 import SalpVectorEnv  # noqa: E402
 CFG = {"single_food": SINGLE_FOOD, "defaults": DEFAULTS}
 
 
-def time_one(cfg, N, generic, rng, steps, prime, graph):
+def time_one(cfg, N, generic, rng, steps, prime, graph, rows=0):
     env = SalpVectorEnv(N, dtype="float32", seed=10_000, food_table_len=128, jitter_table_len=512, autoreset=True,
-                        generic_kernel=generic, rng=rng, **CFG[cfg])
+                        generic_kernel=generic, rng=rng, table_rows=rows or None, **CFG[cfg])
     env.reset()
     g = torch.Generator(device="cuda")
     g.manual_seed(1)
@@ -51,13 +51,15 @@ def main():
     ap.add_argument("--steps", type=int, default=320)
     ap.add_argument("--prime", type=int, default=2048)
     ap.add_argument("--modes", default="fast/table,generic/table,fast/philox")
+    ap.add_argument("--rows", type=int, default=0, help="rows of the RNG tables (default: one per env)")
+    ap.add_argument("--graph-only", action="store_true")
     a = ap.parse_args()
     for cfg in a.cfgs.split(","):
         for N in [int(x) for x in a.sizes.split(",")]:
             for mode in a.modes.split(","):
                 k, rng = mode.split("/")
-                for graph in (True, False):
-                    us, st = time_one(cfg, N, k == "generic", rng, a.steps, a.prime, graph)
+                for graph in ((True,) if a.graph_only else (True, False)):
+                    us, st = time_one(cfg, N, k == "generic", rng, a.steps, a.prime, graph, a.rows)
                     nf = CFG[cfg]["num_food_items"]
                     bpe = 250 if nf == 1 else 426
                     print(f"{cfg:12s} N={N:8d} {mode:14s} {'graph' if graph else 'eager'}: {us:8.2f} us/step  "

@@ -9,7 +9,8 @@ import ctypes as C
 import os
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_PKG, "libsalp_b200.so")
+_TAG = os.environ.get("SALP_LIB_TAG", "")  # developer A/B builds (build.py)
+LIB_PATH = os.path.join(_PKG, "libsalp_b200" + ("_" + _TAG if _TAG else "") + ".so")
 
 SALP_ABI_VERSION = 5
 SALP_OK, SALP_EINVAL, SALP_ECUDA, SALP_EUNBOUND, SALP_EUNSUPPORTED = 0, -1, -2, -3, -4

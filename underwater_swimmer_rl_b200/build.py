@@ -23,8 +23,10 @@ from concurrent.futures import ThreadPoolExecutor
 
 PKG = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(PKG, "csrc")
-OBJ = os.path.join(PKG, "_build")
-LIB = os.path.join(PKG, "libsalp_b200.so")
+# developer A/B builds: SALP_LIB_TAG=x builds libsalp_b200_x.so from objects in _build_x/ (and _capi loads that one)
+TAG = os.environ.get("SALP_LIB_TAG", "")
+OBJ = os.path.join(PKG, "_build" + ("_" + TAG if TAG else ""))
+LIB = os.path.join(PKG, "libsalp_b200" + ("_" + TAG if TAG else "") + ".so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC"] + ARCH

@@ -18,7 +18,7 @@ constexpr int kShapeReset = 0, kShapeRest = 1, kShapeInhale = 2, kShapeExhale = 
 
 // One entry per position of the forced-breathing cycle: index 0 = fresh reset (R:95-117), 1..273 = state after the
 // 1 rest + 121 inhale + 151 exhale steps of a cycle.  Built on the host in double with the reference's
-// expressions (R:184-259) and rounded once; 32 bytes = two 128-bit loads.
+// expressions (R:184-259) and rounded once; 16 bytes = one 128-bit shared-memory load.
 struct CycleEntry {
     float radius;        // max(ellipse_a, ellipse_b) after this step's FSM update (R:190-191,207-213,240-246)
     float tm;            // jet thrust 100 * water_volume * 0.4 of this step (R:268), 0 outside the thrust window
@@ -26,9 +26,6 @@ struct CycleEntry {
     uint32_t fsm_touch;  // bits 0..27: fsm word after this step; bits 28..30: does a clamp onto the low / right / bottom
                          // wall register as a wall contact -- (50+r)-r <= 50, (W-(50+r))+r >= W-50, same with H -- evaluated
                          // in DOUBLE exactly as the reference does (R:335-352 + S:225-228)
-    float margin;        // 50 + radius
-    float reach;         // radius + 15 (food pick-up distance, S:209-212)
-    float obs6, obs7;    // radius / 30, phase / 2 (observation columns 6, 7)
 };
 constexpr int kCycleLen = 274;
 
@@ -66,6 +63,7 @@ struct KernelArgs {
     int rng_mode;
     unsigned long long rng_seed;
     long long env_id0;          // global id of env 0 of this handle
+    int l2_mode;                // forced-breathing kernel: 1 state evict_last, 2 outputs / actions evict_first, 4 food evict_last
 };
 
 cudaError_t launch_step_fast_f32(const KernelArgs &a, int food_slots, cudaStream_t s, bool *handled);

@@ -1,4 +1,6 @@
 // salp_kernels_fast.cu -- instantiates and launches the forced-breathing f32 step kernel (salp_step_fast.cuh).
+#include <cstdlib>
+
 #include "salp_step_fast.cuh"
 
 namespace salp {
@@ -10,7 +12,7 @@ constexpr int kMaxDevices = 64;
 template <int F, int RNG>
 cudaError_t launch_fast(const KernelArgs &a, cudaStream_t s) {
     using Cfg = FastCfg<F>;
-    using L = FastLayout<F, Cfg::food_stages>;
+    using L = FastLayout<F>;
     auto kern = salp_step_fast_kernel<F, RNG>;
     constexpr size_t smem = (size_t)L::kWarpBytes * Cfg::warps;
     // per instantiation AND per device (a process may drive several GPUs through several handles)
@@ -35,7 +37,9 @@ cudaError_t launch_fast(const KernelArgs &a, cudaStream_t s) {
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
-    cfg.attrs = attr; cfg.numAttrs = grid >= (unsigned)resident[dev] ? 1 : 0;
+    // programmatic dependent launch: CTAs of the next step may become resident (and run their prologue: barrier init, cycle
+    // table -> shared memory) while this step's last CTAs drain; they wait at griddepcontrol.wait before touching state
+    cfg.attrs = attr; cfg.numAttrs = (getenv("SALP_NO_PDL") ? 0 : 1);
     return cudaLaunchKernelEx(&cfg, kern, a);
 }
 

@@ -61,7 +61,7 @@ __device__ __forceinline__ float sqrt_(float x) {
     return sqrtf(x);
 #else
     float r;
-    asm("sqrt.approx.f32 %0, %1;" : "=f"(r) : "f"(x));
+    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));  // .ftz: no denormal pre-scaling (distances are pixels)
     return r;
 #endif
 }
@@ -88,7 +88,9 @@ __device__ __forceinline__ void sincos_(float x, float *s, float *c) { __sincosf
 __device__ __forceinline__ float atan2_(float y, float x) {
     const float ax = fabsf(x), ay = fabsf(y);
     const float mx = fmaxf(ax, ay), mn = fminf(ax, ay);
-    const float a = __fdividef(mn, fmaxf(mx, 1e-30f));
+    float rmx;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rmx) : "f"(fmaxf(mx, 1e-30f)));
+    const float a = mn * rmx;
     const float s = a * a;
     float r = -0.0043554045259952545f;
     r = fmaf(r, s, 0.023040130734443665f);
@@ -357,9 +359,14 @@ __device__ __noinline__ LayoutResult<T> layout_warp(const KernelArgs &a, unsigne
             if (ptr == 32) {
                 const unsigned w = base + 4u * (unsigned)lane;
                 uint32_t w0, w1, w2, w3;
-                if (a.rng_mode) {  // the cursor need not be a multiple of 4 (randint draws single words)
-                    unsigned c2 = w;
-                    w0 = food_word(a, e, c2); w1 = food_word(a, e, c2); w2 = food_word(a, e, c2); w3 = food_word(a, e, c2);
+                if (a.rng_mode) {
+                    if ((w & 3u) == 0u) {  // a candidate's four words are one Philox block unless randint moved the cursor off 4
+                        const uint4 r = philox_block(a, e, 0u, w);
+                        w0 = r.x; w1 = r.y; w2 = r.z; w3 = r.w;
+                    } else {
+                        unsigned c2 = w;
+                        w0 = food_word(a, e, c2); w1 = food_word(a, e, c2); w2 = food_word(a, e, c2); w3 = food_word(a, e, c2);
+                    }
                 } else {
                     w0 = words[w & a.food_len_mask]; w1 = words[(w + 1) & a.food_len_mask];
                     w2 = words[(w + 2) & a.food_len_mask]; w3 = words[(w + 3) & a.food_len_mask];

@@ -51,6 +51,45 @@ __device__ __forceinline__ void bulk_load(void *sdst, const void *gsrc, uint32_t
 __device__ __forceinline__ void bulk_store(void *gdst, const void *ssrc, uint32_t bytes) {
     asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(smem_u32(ssrc)), "r"(bytes) : "memory");
 }
+// same, with an L2 eviction-priority hint (createpolicy): evict_last keeps the state records of the slab in the 126 MB L2
+// between consecutive steps, evict_first lets the observation tiles (written once, never read by this kernel) leave first
+__device__ __forceinline__ uint64_t l2_policy_evict_last() {
+    uint64_t p;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+    return p;
+}
+__device__ __forceinline__ uint64_t l2_policy_evict_normal() {
+    uint64_t p;
+    asm volatile("createpolicy.fractional.L2::evict_normal.b64 %0, 1.0;" : "=l"(p));
+    return p;
+}
+__device__ __forceinline__ float ld_hint_f32(const float *p, uint64_t pol) {
+    float v;
+    asm volatile("ld.global.L2::cache_hint.f32 %0, [%1], %2;" : "=f"(v) : "l"(p), "l"(pol));
+    return v;
+}
+__device__ __forceinline__ void st_hint_f32(float *p, float v, uint64_t pol) {
+    asm volatile("st.global.L2::cache_hint.f32 [%0], %1, %2;" ::"l"(p), "f"(v), "l"(pol) : "memory");
+}
+__device__ __forceinline__ void st_hint_u8(uint8_t *p, uint32_t v, uint64_t pol) {
+    asm volatile("st.global.L2::cache_hint.u8 [%0], %1, %2;" ::"l"(p), "r"(v), "l"(pol) : "memory");
+}
+__device__ __forceinline__ uint64_t l2_policy_evict_first() {
+    uint64_t p;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+    return p;
+}
+__device__ __forceinline__ void bulk_load_hint(void *sdst, const void *gsrc, uint32_t bytes, uint64_t *bar, uint64_t pol) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::"r"(smem_u32(sdst)),
+                 "l"(gsrc), "r"(bytes), "r"(smem_u32(bar)), "l"(pol)
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_store_hint(void *gdst, const void *ssrc, uint32_t bytes, uint64_t pol) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group.L2::cache_hint [%0], [%1], %2, %3;" ::"l"(gdst), "r"(smem_u32(ssrc)), "r"(bytes), "l"(pol) : "memory");
+}
+__device__ __forceinline__ void st_hint_v4(void *p, uint32_t x, uint32_t y, uint32_t z, uint32_t w, uint64_t pol) {
+    asm volatile("st.global.L2::cache_hint.v4.u32 [%0], {%1, %2, %3, %4}, %5;" ::"l"(p), "r"(x), "r"(y), "r"(z), "r"(w), "l"(pol) : "memory");
+}
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 // One lane of a converged warp.  With elect.sync (instead of `lane == 0`) and operands derived from warp-uniform values
 // the compiler issues the bulk copies from the uniform datapath; with per-thread operands it wraps every copy in a
@@ -61,40 +100,46 @@ __device__ __forceinline__ bool elect_one_sync() {
     return pred != 0;
 }
 
-// Per-warp shared-memory layout (bytes).  A "core" stage holds the 32-env tile's four 128-bit state records in the order
-// of the state arrays, so the new state is written over them and stored from the same place.
-template <int F, int FS> struct FastLayout {
-    static constexpr int kC0 = 0, kC1 = 512, kB0 = 1024, kB1 = 1536, kCore = 2048;
-    static constexpr int kFood = F * 256;                       // [F][32] float2
+// Per-warp shared-memory layout (bytes).  The "core" stage holds the 32-env tile's four 128-bit state records; it is
+// single-buffered: a lane reads its records into registers first thing, after which the stage is refilled with the NEXT
+// tile (a whole tile of arithmetic ahead of its use).  One food record per env travels with the core stage; twelve are a
+// separate, double-buffered block (the kernel keeps using it as (dx, dy) scratch until the observation is assembled).
+template <int F> struct FastLayout {
+    static constexpr bool kFoodInCore = (F == 1);
+    static constexpr int kC0 = 0, kC1 = 512, kB0 = 1024, kB1 = 1536, kFoodC = 2048;
+    static constexpr int kCore = 2048 + (kFoodInCore ? 256 : 0);
+    static constexpr int kFood = kFoodInCore ? 0 : F * 256;     // [F][32] float2, two stages
     static constexpr int kObs = 32 * 24 * 4;                    // 32 rows of 24 floats
-    static constexpr int kOffCore = 0;                          // 2 stages
-    static constexpr int kOffFood = 2 * kCore;                  // FS stages
-    static constexpr int kOffObs = kOffFood + FS * kFood;
-    static constexpr int kOffBar = kOffObs + kObs;              // core[2], food[FS]: 8 bytes each
-    static constexpr int kWarpBytes = (kOffBar + 8 * (2 + FS) + 127) & ~127;
+    static constexpr int kOffCore = 0;
+    static constexpr int kOffFood = kCore;
+    static constexpr int kOffObs = kOffFood + 2 * kFood;
+    static constexpr int kOffBar = kOffObs + kObs;              // core, food[2]: 8 bytes each
+    static constexpr int kWarpBytes = (kOffBar + 24 + 127) & ~127;
 };
 
 // Launch shape per food-slot count: warps per CTA, CTAs per SM (registers: 65536 / (32 * warps * minb)).
 template <int F> struct FastCfg;
-template <> struct FastCfg<1> { static constexpr int warps = 8, minb = 3, food_stages = 2; };    // 24 warps/SM, 80 regs
-template <> struct FastCfg<12> { static constexpr int warps = 8, minb = 2, food_stages = 1; };   // 16 warps/SM, 128 regs
+#ifndef SALP_FAST_F1_MINB
+#define SALP_FAST_F1_MINB 7
+#endif
+template <> struct FastCfg<1> { static constexpr int warps = 4, minb = SALP_FAST_F1_MINB; };    // 28 warps/SM, 72 registers
+template <> struct FastCfg<12> { static constexpr int warps = 8, minb = 2; };                    // 16 warps/SM, 128 registers
 
 template <int F, int RNG>
 __global__ void __launch_bounds__(FastCfg<F>::warps * 32, FastCfg<F>::minb) salp_step_fast_kernel(const __grid_constant__ KernelArgs a) {
     using Cfg = FastCfg<F>;
-    constexpr int FS = Cfg::food_stages;
-    using L = FastLayout<F, FS>;
+    using L = FastLayout<F>;
     constexpr int OBS = 24;
     constexpr int MU = F < 3 ? F : 3;
     constexpr unsigned kSlotMask = F <= 1 ? 0u : (F <= 2 ? 1u : (F <= 4 ? 3u : (F <= 8 ? 7u : (F <= 16 ? 15u : 31u))));
     constexpr unsigned kFull = 0xffffffffu;
     extern __shared__ __align__(128) unsigned char s_raw[];
-    __shared__ __align__(16) CycleEntry s_tab[kCycleLen];  // the forced-breathing cycle, 8.8 KB per CTA
+    __shared__ __align__(16) CycleEntry s_tab[kCycleLen];  // the forced-breathing cycle, 4.4 KB per CTA
     const int lane = threadIdx.x & 31;
     const int warp = __shfl_sync(kFull, (int)(threadIdx.x >> 5), 0);  // warp-uniform for the compiler
     unsigned char *ws = s_raw + (size_t)warp * L::kWarpBytes;
     uint64_t *bar_core = reinterpret_cast<uint64_t *>(ws + L::kOffBar);
-    uint64_t *bar_food = bar_core + 2;
+    uint64_t *bar_food = bar_core + 1;  // [2]
     float *s_obs = reinterpret_cast<float *>(ws + L::kOffObs);
 
     const unsigned N = (unsigned)a.N;
@@ -108,17 +153,22 @@ __global__ void __launch_bounds__(FastCfg<F>::warps * 32, FastCfg<F>::minb) salp
     const float *g_act = reinterpret_cast<const float *>(a.actions);
     float *g_reward = reinterpret_cast<float *>(a.reward);
     const float W = a.fW, H = a.fH, invW = a.f_inv_w, invH = a.f_inv_h, invDiag = a.f_inv_diag;
+    // L2 residency (a.l2_mode, chosen per slab by the host): the per-env state that is read and rewritten every step stays
+    // in the 126 MB L2 between consecutive steps (evict_last) when it fits, and what is written once and never read by
+    // this kernel (observation tiles, rewards, flags) or read once (actions) leaves first (evict_first)
+    const uint64_t pol_state = (a.l2_mode & 1) ? l2_policy_evict_last() : l2_policy_evict_normal();
+    const uint64_t pol_out = (a.l2_mode & 2) ? l2_policy_evict_first() : l2_policy_evict_normal();
+    const uint64_t pol_food = (a.l2_mode & 4) ? l2_policy_evict_last() : l2_policy_evict_normal();
 
     if (elect_one_sync()) {
-        mbar_init(bar_core + 0, 1);
-        mbar_init(bar_core + 1, 1);
-#pragma unroll
-        for (int i = 0; i < FS; ++i) mbar_init(bar_food + i, 1);
+        mbar_init(bar_core, 1);
+        mbar_init(bar_food + 0, 1);
+        mbar_init(bar_food + 1, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     // the cycle table is parameter data of the handle (never written by a kernel): it may be read before the previous
     // kernel of the stream has completed
-    for (unsigned i = threadIdx.x; i < kCycleLen * 2u; i += Cfg::warps * 32)
+    for (unsigned i = threadIdx.x; i < (unsigned)kCycleLen; i += Cfg::warps * 32)
         reinterpret_cast<uint4 *>(s_tab)[i] = __ldg(reinterpret_cast<const uint4 *>(a.cycle_tab) + i);
     __syncthreads();
     // programmatic dependent launch (salp_launch.cuh): the next kernel of the stream may become resident as CTAs of this
@@ -129,22 +179,17 @@ __global__ void __launch_bounds__(FastCfg<F>::warps * 32, FastCfg<F>::minb) salp
     // ---- tile loads.  Full tiles: TMA, one elected lane, every operand warp-uniform.  The last, partial tile of a slab
     //      whose size is not a multiple of 32: each lane copies its own records (bulk copies need 16-byte multiples).
     auto rows_of = [&](unsigned tile) -> unsigned { const unsigned e0 = first + tile * 32u; return end - e0 < 32u ? end - e0 : 32u; };
-    auto load_core = [&](unsigned tile, int st) {
-        unsigned char *sc = ws + L::kOffCore + st * L::kCore;
+    auto load_core = [&](unsigned tile) {
+        unsigned char *sc = ws + L::kOffCore;
         const unsigned e0 = first + tile * 32u;
         if (rows_of(tile) == 32u) {
             if (elect_one_sync()) {
-                uint64_t *bar = bar_core + st;
-                mbar_expect_tx(bar, L::kCore + ((FS == 2) ? L::kFood : 0));
-                bulk_load(sc + L::kC0, a.ctrl + e0, 512, bar);
-                bulk_load(sc + L::kC1, a.ctrl + (size_t)N + e0, 512, bar);
-                bulk_load(sc + L::kB0, g_body + e0, 512, bar);
-                bulk_load(sc + L::kB1, g_body + (size_t)N + e0, 512, bar);
-                if constexpr (FS == 2) {
-                    unsigned char *sf = ws + L::kOffFood + st * L::kFood;
-#pragma unroll
-                    for (int f = 0; f < F; ++f) bulk_load(sf + f * 256, g_food + (size_t)f * N + e0, 256, bar);
-                }
+                mbar_expect_tx(bar_core, L::kCore);
+                bulk_load_hint(sc + L::kC0, a.ctrl + e0, 512, bar_core, pol_state);
+                bulk_load_hint(sc + L::kC1, a.ctrl + (size_t)N + e0, 512, bar_core, pol_state);
+                bulk_load_hint(sc + L::kB0, g_body + e0, 512, bar_core, pol_state);
+                bulk_load_hint(sc + L::kB1, g_body + (size_t)N + e0, 512, bar_core, pol_state);
+                if constexpr (L::kFoodInCore) bulk_load_hint(sc + L::kFoodC, g_food + e0, 256, bar_core, pol_food);
             }
         } else {
             const unsigned e = e0 + lane;
@@ -153,22 +198,18 @@ __global__ void __launch_bounds__(FastCfg<F>::warps * 32, FastCfg<F>::minb) salp
             reinterpret_cast<int4 *>(sc + L::kC1)[lane] = v ? a.ctrl[(size_t)N + e] : make_int4(0, 0, 0, 0);
             reinterpret_cast<float4 *>(sc + L::kB0)[lane] = v ? g_body[e] : make_float4(0.f, 0.f, 0.f, 0.f);
             reinterpret_cast<float4 *>(sc + L::kB1)[lane] = v ? g_body[(size_t)N + e] : make_float4(0.f, 0.f, 0.f, 0.f);
-            if constexpr (FS == 2) {
-                float2 *sf = reinterpret_cast<float2 *>(ws + L::kOffFood + st * L::kFood);
-#pragma unroll
-                for (int f = 0; f < F; ++f) sf[f * 32 + lane] = v ? g_food[(size_t)f * N + e] : make_float2(0.f, 0.f);
-            }
+            if constexpr (L::kFoodInCore) reinterpret_cast<float2 *>(sc + L::kFoodC)[lane] = v ? g_food[e] : make_float2(0.f, 0.f);
             __syncwarp();
         }
     };
-    auto load_food = [&](unsigned tile) {  // FS == 1 only: the single food buffer, its own mbarrier
-        unsigned char *sf = ws + L::kOffFood;
+    auto load_food = [&](unsigned tile, int st) {  // F > 1: one of the two food blocks, its own mbarrier
+        unsigned char *sf = ws + L::kOffFood + st * L::kFood;
         const unsigned e0 = first + tile * 32u;
         if (rows_of(tile) == 32u) {
             if (elect_one_sync()) {
-                mbar_expect_tx(bar_food, L::kFood);
+                mbar_expect_tx(bar_food + st, L::kFood);
 #pragma unroll
-                for (int f = 0; f < F; ++f) bulk_load(sf + f * 256, g_food + (size_t)f * N + e0, 256, bar_food);
+                for (int f = 0; f < F; ++f) bulk_load_hint(sf + f * 256, g_food + (size_t)f * N + e0, 256, bar_food + st, pol_food);
             }
         } else {
             const unsigned e = e0 + lane;
@@ -179,14 +220,14 @@ __global__ void __launch_bounds__(FastCfg<F>::warps * 32, FastCfg<F>::minb) salp
         }
     };
 
-    unsigned ph_core = 0u, ph_food = 0u;  // mbarrier phase parities: bit st of ph_core, bit 0 of ph_food
+    unsigned ph_core = 0u, ph_food = 0u;  // mbarrier phase parities (bit st of ph_food)
     // the two scalars of the state that are not 128-bit records travel in registers, fetched one tile ahead
     float act_nx = 0.f, ep_nx = 0.f;
     if (gw < ntiles) {
-        load_core(gw, 0);
-        if constexpr (FS == 1) load_food(gw);
+        load_core(gw);
+        if constexpr (!L::kFoodInCore) load_food(gw, 0);
         const unsigned e = first + gw * 32u + lane;
-        if (e < end) { act_nx = g_act[e]; ep_nx = g_epret[e]; }
+        if (e < end) { act_nx = ld_hint_f32(g_act + e, pol_out); ep_nx = ld_hint_f32(g_epret + e, pol_state); }
     }
 
     unsigned it = 0;
@@ -198,27 +239,29 @@ __global__ void __launch_bounds__(FastCfg<F>::warps * 32, FastCfg<F>::minb) salp
         const bool full = rows == 32u;
         const bool valid = (unsigned)lane < rows;
         const unsigned nxt = tile + nw;
-        unsigned char *sc = ws + L::kOffCore + st * L::kCore;
-        float2 *sfood = reinterpret_cast<float2 *>(ws + L::kOffFood + (FS == 2 ? st : 0) * L::kFood);
+        unsigned char *sc = ws + L::kOffCore;
+        // F == 1: the tile's food position, private copy (the core stage is refilled below); F > 1: this tile's block
+        float2 *sfood = reinterpret_cast<float2 *>(ws + L::kOffFood + (L::kFoodInCore ? 0 : st * L::kFood));
 
         float act = act_nx, ep_ret = ep_nx;
         if (nxt < ntiles) {
             const unsigned en = first + nxt * 32u + lane;
-            if (en < end) { act_nx = g_act[en]; ep_nx = g_epret[en]; }
+            if (en < end) { act_nx = ld_hint_f32(g_act + en, pol_out); ep_nx = ld_hint_f32(g_epret + en, pol_state); }
         }
-        if (full) { mbar_wait(bar_core + st, (ph_core >> st) & 1u); ph_core ^= 1u << st; }
+        if (full) { mbar_wait(bar_core, ph_core & 1u); ph_core ^= 1u; }
         // ---- state of this lane's env
         const int4 c0 = reinterpret_cast<const int4 *>(sc + L::kC0)[lane];
         const int4 c1 = reinterpret_cast<const int4 *>(sc + L::kC1)[lane];
         const float4 b0 = reinterpret_cast<const float4 *>(sc + L::kB0)[lane];
         const float4 b1 = reinterpret_cast<const float4 *>(sc + L::kB1)[lane];
-        // ---- the other stage is free once the bulk stores issued from it (previous tile) have read it; refill it so the
-        //      loads have this tile's arithmetic to land
-#ifndef SALP_FAST_PREFETCH_LATE
-        if (elect_one_sync()) bulk_wait_read<0>();
+        float2 food1 = make_float2(0.f, 0.f);
+        if constexpr (L::kFoodInCore) food1 = reinterpret_cast<const float2 *>(sc + L::kFoodC)[lane];
+        // ---- every lane holds its records: refill the stage with the next tile, a whole tile of arithmetic ahead of use
         __syncwarp();
-        if (nxt < ntiles) load_core(nxt, st ^ 1);
-#endif
+        if (nxt < ntiles) {
+            load_core(nxt);
+            if constexpr (!L::kFoodInCore) load_food(nxt, st ^ 1);
+        }
 
         float px = b0.x, py = b0.y, vx = b0.z, vy = b0.w;
         float angle = b1.x, omega = b1.y, nozzle = b1.z;
@@ -240,15 +283,10 @@ __global__ void __launch_bounds__(FastCfg<F>::warps * 32, FastCfg<F>::minb) salp
         if constexpr (RNG == 0) jit_row = a.jit_words + (size_t)((a.rows == N) ? e : e % a.rows) * a.jit_len;
 
         for (int k = 0; k < a.K; ++k) {
-            if (k > 0) {  // K fused substeps: later actions come straight from HBM; the observation tile buffer is single
-                act = valid ? g_act[(size_t)k * N + e] : 0.f;
-                if (elect_one_sync()) bulk_wait_read<0>();
-                __syncwarp();
-            }
+            if (k > 0) act = valid ? g_act[(size_t)k * N + e] : 0.f;  // K fused substeps: later actions come straight from HBM
             float *row = s_obs + lane * OBS;
             q = q >= 273 ? 1 : q + 1;
-            const uint4 t0 = reinterpret_cast<const uint4 *>(s_tab + q)[0];
-            const float4 t1 = reinterpret_cast<const float4 *>(s_tab + q)[1];
+            const uint4 t0 = *reinterpret_cast<const uint4 *>(s_tab + q);
             const float radius = __uint_as_float(t0.x), tm = __uint_as_float(t0.y);
             const bool thrust = tm != 0.f;
             // ---- thrust jitter draw (R:311): table mode -- the word for THIS draw came with the state (ctrl rec1.w), fetch
@@ -256,7 +294,11 @@ __global__ void __launch_bounds__(FastCfg<F>::warps * 32, FastCfg<F>::minb) salp
             uint32_t jword = jcache;
             if (thrust) {
                 if constexpr (RNG == 0) jcache = ld_evict_last_u1(jit_row + ((cur_jit + 2u) & a.jit_len_mask));
+#ifdef SALP_FAST_NOJIT
+                else jword = 0x80000000u;
+#else
                 else jword = philox_jitter_pair(a, e, cur_jit).x;
+#endif
             }
             // ---- nozzle slew (R:169-182)
             {
@@ -300,19 +342,12 @@ __global__ void __launch_bounds__(FastCfg<F>::warps * 32, FastCfg<F>::minb) salp
             angle = wrap_pi<float>(angle + omega);
             unsigned clamped = 0u;
             {
-                const float margin = t1.x;
+                const float margin = (float)kc::TANK_MARGIN + radius;
                 if (px < margin) { px = margin; vx = fabsf(vx) * 0.4f; omega *= 0.7f; clamped |= 1u; }
                 else if (px > W - margin) { px = W - margin; vx = -fabsf(vx) * 0.4f; omega *= 0.7f; clamped |= 2u; }
                 if (py < margin) { py = margin; vy = fabsf(vy) * 0.4f; omega *= 0.7f; clamped |= 1u; }
                 else if (py > H - margin) { py = H - margin; vy = -fabsf(vy) * 0.4f; omega *= 0.7f; clamped |= 4u; }
             }
-#ifdef SALP_FAST_PREFETCH_LATE
-            if (k == 0) {
-                if (elect_one_sync()) bulk_wait_read<0>();
-                __syncwarp();
-                if (nxt < ntiles) load_core(nxt, st ^ 1);
-            }
-#endif
             // ---- wall contact (S:219-230): a bounce leaves the robot exactly on the clamp line; whether that registers is
             //      the rounding of (50 + r) - r <= 50 in the reference's doubles -- a table bit per cycle position
             const bool collision = (clamped & (t0.w >> 28)) != 0u;
@@ -341,14 +376,13 @@ __global__ void __launch_bounds__(FastCfg<F>::warps * 32, FastCfg<F>::minb) salp
                     insert_key(alive ? make_key(d, f) : (~kSlotMask | (unsigned)f));
                 }
             };
-            const float reach = t1.y;
+            const float reach = radius + (float)kc::FOOD_R;
             if constexpr (F == 1) {
-                const float2 fv = sfood[lane];
-                dx0 = fv.x - px; dy0 = fv.y - py;
+                dx0 = food1.x - px; dy0 = food1.y - py;
                 dd0 = sqrt_(dx0 * dx0 + dy0 * dy0);
                 if ((mask & 1u) && dd0 < reach) { hit = true; mask &= ~1u; }
             } else {
-                if (FS == 1 && k == 0 && full) { mbar_wait(bar_food, ph_food & 1u); ph_food ^= 1u; }
+                if (k == 0 && full) { mbar_wait(bar_food + st, (ph_food >> st) & 1u); ph_food ^= 1u << st; }
                 unsigned hitbits = 0u;
 #pragma unroll
                 for (int i = 0; i < MU; ++i) key[i] = 0xffffffffu;
@@ -391,7 +425,7 @@ __global__ void __launch_bounds__(FastCfg<F>::warps * 32, FastCfg<F>::minb) salp
                     if (r.slot >= 0) {
                         const float ox = r.x - px, oy = r.y - py;
                         const float d = sqrt_(ox * ox + oy * oy);
-                        if constexpr (F == 1) { dx0 = ox; dy0 = oy; dd0 = d; sfood[lane] = make_float2(r.x, r.y); }
+                        if constexpr (F == 1) { dx0 = ox; dy0 = oy; dd0 = d; food1 = make_float2(r.x, r.y); }
                         else { sfood[r.slot * 32 + lane] = make_float2(ox, oy); dist_sum += d; insert_key(make_key(d, r.slot)); }
                     }
                 }
@@ -408,13 +442,17 @@ __global__ void __launch_bounds__(FastCfg<F>::warps * 32, FastCfg<F>::minb) salp
             const bool done = terminated || truncated;
             if (valid) {
                 const size_t oi = (size_t)k * N + e;
-                g_reward[oi] = reward;
-                a.terminated[oi] = terminated ? 1 : 0;
-                a.truncated[oi] = truncated ? 1 : 0;
-                if (a.events) a.events[oi] = (uint8_t)((terminated ? 1 : 0) | (truncated ? 2 : 0) | (collision ? 4 : 0) | (hit ? 8 : 0));
+                st_hint_f32(g_reward + oi, reward, pol_out);
+                st_hint_u8(a.terminated + oi, terminated ? 1u : 0u, pol_out);
+                st_hint_u8(a.truncated + oi, truncated ? 1u : 0u, pol_out);
+                if (a.events) st_hint_u8(a.events + oi, (terminated ? 1u : 0u) | (truncated ? 2u : 0u) | (collision ? 4u : 0u) | (hit ? 8u : 0u), pol_out);
             }
 
-            float obs6 = t1.z, obs7 = t1.w;
+            float obs6 = radius * (float)(1.0 / kc::BASE_R), obs7 = (float)(t0.w & 3u) * 0.5f;
+            // the observation tile buffer is single: the bulk store of the previous tile / substep must have read it
+            // (it was issued a tile of arithmetic ago)
+            if (elect_one_sync()) bulk_wait_read<0>();
+            __syncwarp();
 #pragma unroll 1
             for (int pass = 0;; ++pass) {
                 // ---- observation (R:377-388 + S:366-428) assembled in registers, written as 128-bit pieces of the row
@@ -437,7 +475,8 @@ __global__ void __launch_bounds__(FastCfg<F>::warps * 32, FastCfg<F>::minb) salp
                 };
                 const float cnt = fminf((float)n_live * 0.1f, 1.0f);
                 float avg = 1.f;
-                if (n_live > 0) avg = ((F == 1 ? dd0 : dist_sum) / (float)n_live) * invDiag;
+                if constexpr (F == 1) { if (n_live > 0) avg = dd0 * invDiag; }
+                else if (n_live > 0) avg = __fdividef(dist_sum, (float)n_live) * invDiag;
                 const float4 e0v = food_entry(0), e1v = food_entry(1), e2v = food_entry(2);
                 float4 *r4 = reinterpret_cast<float4 *>(row);
                 r4[0] = make_float4(px * invW, py * invH, vx * 0.2f, vy * 0.2f);
@@ -483,7 +522,7 @@ __global__ void __launch_bounds__(FastCfg<F>::warps * 32, FastCfg<F>::minb) salp
                         px = W * 0.5f; py = H * 0.5f; vx = 0.f; vy = 0.f; angle = 0.f; omega = 0.f; nozzle = 0.f; wv_now = 0.f;
                         fsm = kPhaseRest | (kShapeReset << 18); q = 0;
                         steps_since_food = 0; food_collected = 0; ep_ret = 0.f; ep_len = 0;
-                        if (a.K > 1) sfood[lane] = g_food[e];  // the next substep reads the food position from the tile buffer
+                        if (a.K > 1) food1 = g_food[e];  // the next substep needs the new food position
                     }
                     break;
                 } else {
@@ -527,8 +566,8 @@ __global__ void __launch_bounds__(FastCfg<F>::warps * 32, FastCfg<F>::minb) salp
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                 __syncwarp();
                 if (elect_one_sync()) {
-                    bulk_store(a.obs + ((size_t)k * N + e0) * OBS, s_obs, L::kObs);
-                    if (k + 1 < a.K) bulk_commit();
+                    bulk_store_hint(a.obs + ((size_t)k * N + e0) * OBS, s_obs, L::kObs, pol_out);
+                    bulk_commit();
                 }
             } else if (valid) {
                 float4 *dst = reinterpret_cast<float4 *>(a.obs + ((size_t)k * N + e) * OBS);
@@ -538,36 +577,14 @@ __global__ void __launch_bounds__(FastCfg<F>::warps * 32, FastCfg<F>::minb) salp
             }
         }  // substeps
 
-        // ---- the food buffer is free (FS == 1): fetch the next tile's foods
-        if constexpr (FS == 1) {
-            __syncwarp();
-            if (nxt < ntiles) load_food(nxt);
-        }
-        // ---- new state over the tile's input slots, stored from there (food records are only written by the slow paths)
-        {
-            const int4 n0 = make_int4(fsm, steps_since_food, food_collected, (int)mask);
-            const int4 n1 = make_int4((int)cur_food, (int)cur_jit, (ep_len < kEpLenMask ? ep_len : kEpLenMask) | (n_food << 26), (int)jcache);
-            if (valid) g_epret[e] = ep_ret;
-            if (full) {
-                reinterpret_cast<int4 *>(sc + L::kC0)[lane] = n0;
-                reinterpret_cast<int4 *>(sc + L::kC1)[lane] = n1;
-                reinterpret_cast<float4 *>(sc + L::kB0)[lane] = make_float4(px, py, vx, vy);
-                reinterpret_cast<float4 *>(sc + L::kB1)[lane] = make_float4(angle, omega, nozzle, wv_now);
-                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-                __syncwarp();
-                if (elect_one_sync()) {
-                    bulk_store(a.ctrl + e0, sc + L::kC0, 512);
-                    bulk_store(a.ctrl + (size_t)N + e0, sc + L::kC1, 512);
-                    bulk_store(reinterpret_cast<float4 *>(a.body) + e0, sc + L::kB0, 512);
-                    bulk_store(reinterpret_cast<float4 *>(a.body) + (size_t)N + e0, sc + L::kB1, 512);
-                    bulk_commit();
-                }
-            } else if (valid) {
-                a.ctrl[e] = n0;
-                a.ctrl[(size_t)N + e] = n1;
-                reinterpret_cast<float4 *>(a.body)[e] = make_float4(px, py, vx, vy);
-                reinterpret_cast<float4 *>(a.body)[(size_t)N + e] = make_float4(angle, omega, nozzle, wv_now);
-            }
+        // ---- write the state back: four coalesced 128-bit stores (a warp writes 512 contiguous bytes each) + ep_return;
+        //      food records are only written by the slow paths
+        if (valid) {
+            st_hint_v4(a.ctrl + e, (uint32_t)fsm, (uint32_t)steps_since_food, (uint32_t)food_collected, mask, pol_state);
+            st_hint_v4(a.ctrl + (size_t)N + e, cur_food, cur_jit, (uint32_t)((ep_len < kEpLenMask ? ep_len : kEpLenMask) | (n_food << 26)), jcache, pol_state);
+            st_hint_v4(reinterpret_cast<float4 *>(a.body) + e, __float_as_uint(px), __float_as_uint(py), __float_as_uint(vx), __float_as_uint(vy), pol_state);
+            st_hint_v4(reinterpret_cast<float4 *>(a.body) + (size_t)N + e, __float_as_uint(angle), __float_as_uint(omega), __float_as_uint(nozzle), __float_as_uint(wv_now), pol_state);
+            st_hint_f32(g_epret + e, ep_ret, pol_state);
         }
     }  // tiles
     if (blockIdx.x == 0 && threadIdx.x == 0 && a.stats) atomicAdd(a.stats + 7, (double)a.count * (double)a.K);
