@@ -448,6 +448,7 @@ class SlabTimer:
     def _graph(self, g):
         if g not in self._graphs:
             self._graphs[g] = self.env.capture_graph([p if self.K > 1 else p[0] for p in self.pool[:g]], self.K)
+            self._graphs[g]()  # the first launch of a captured graph uploads it to the device (~150 us): never inside a timed region
         return self._graphs[g]
 
     def prepare(self, n):

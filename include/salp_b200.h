@@ -236,12 +236,13 @@ int salp_step_slot(SalpHandle *h, int slot, const void *actions, void *cuda_stre
  * Host-buffer convenience path (what a caller holding numpy arrays uses): copies
  * actions host->device (into the caller-owned DEVICE staging buffer `actions_staging`,
  * real [N][act_dim]), runs one step (K=1), copies obs/reward/terminated/truncated
- * device->host, chunked over internal streams so the copies overlap the kernel, and
- * returns after the results are in host memory.  Host pointers should be page-locked.
- * Any output pointer may be NULL.
+ * device->host, in 8 chunks on internal non-blocking streams so the copies overlap the kernel, and
+ * returns after the results are in host memory.  The chunks start after the work already queued
+ * on `caller_stream` (an event is recorded there); work queued on it later runs after the call
+ * has returned.  Host pointers should be page-locked.  Any output pointer may be NULL.
  */
 int salp_step_host(SalpHandle *h, void *actions_staging, const void *actions_host, float *obs_host,
-                   void *reward_host, uint8_t *terminated_host, uint8_t *truncated_host);
+                   void *reward_host, uint8_t *terminated_host, uint8_t *truncated_host, void *caller_stream);
 
 /*
  * Fill `rows` rows of `len` raw MT19937 outputs into HOST memory dst[rows][len]:

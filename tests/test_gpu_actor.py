@@ -193,3 +193,32 @@ def test_fused_gail_reward_matches_torch(salp_lib, n, act_dim, dtype):
         ref = -torch.log(1 - torch.sigmoid(logit) + 1e-8)
     assert (out - ref).abs().max().item() <= 5e-3 * max(1.0, ref.abs().max().item())
     assert (out > 0).all()
+
+
+def test_fused_actor_against_the_true_fp32_actor(salp_lib):
+    """the kernel runs bf16 GEMMs where the reference actor (record_model.py:27-53) is fp32.  Bound,
+    stated and tested: on observations produced by the env itself, with torch's default init AND with weights twice that
+    scale, the deterministic action differs from the fp32 actor's by <= 2e-2 (worst) and <= 2e-3 (mean) -- bf16 keeps 8 bits
+    of mantissa in the inputs of the two hidden GEMMs, accumulation and both epilogues are f32.  (tests/test_reference_networks.py
+    pins TanhGaussianActor itself to the reference class.)"""
+    from underwater_swimmer_rl_b200 import SalpVectorEnv
+    from underwater_swimmer_rl_b200.rollout import FusedActor, TanhGaussianActor
+    env = SalpVectorEnv(32768, dtype="float32", rng="philox", seed=3, num_food_items=12, forced_breathing=True)
+    env.reset()
+    g = torch.Generator(device="cuda")
+    g.manual_seed(0)
+    for _ in range(400):   # observations of moving robots in all breathing phases
+        obs, *_ = env.step(torch.rand(32768, 1, device="cuda", generator=g) * 2 - 1)
+    obs = obs.clone()
+    for scale in (1.0, 2.0):
+        torch.manual_seed(int(scale * 10))
+        actor = TanhGaussianActor(24, 1).cuda()
+        with torch.no_grad():
+            for l in actor.layers:
+                l.weight.mul_(scale)
+        out = torch.empty(32768, 1, device="cuda")
+        FusedActor(actor)(obs, out, deterministic=True)
+        with torch.no_grad():
+            ref = actor(obs, deterministic=True)     # fp32 weights, fp32 activations
+        err = (out - ref).abs()
+        assert err.max().item() <= 2e-2 and err.mean().item() <= 2e-3, (scale, err.max().item(), err.mean().item())

@@ -122,7 +122,7 @@ def load():
     L.salp_forced_cycle.argtypes = [C.POINTER(SalpParams)] + [C.c_void_p] * 5
     L.salp_step.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
     L.salp_step_slot.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
-    L.salp_step_host.argtypes = [C.c_void_p] + [C.c_void_p] * 6
+    L.salp_step_host.argtypes = [C.c_void_p] + [C.c_void_p] * 7
     L.salp_fill_rng_words.argtypes = [C.c_void_p, C.c_int64, C.c_int64, C.c_uint64, C.c_int64, C.c_int, C.c_int]
     L.salp_launch_count.argtypes = [C.c_void_p]
     L.salp_actor_forward.argtypes = [C.POINTER(SalpActorForward), C.c_void_p]

@@ -41,7 +41,7 @@ int cuda_fail(cudaError_t e, const char *what) {
         if (err__ != cudaSuccess) return cuda_fail(err__, #expr); \
     } while (0)
 
-constexpr int kHostChunks = 4;
+constexpr int kHostChunks = 8;  // the last chunk's copy tail is 1/8 of the transfer
 
 int pick_food_slots(int n) {
     const int opts[] = {1, 4, 8, 12, 16, 32};
@@ -124,6 +124,7 @@ struct SalpHandle {
     bool bound;
     int64_t launches;
     cudaStream_t host_streams[kHostChunks];
+    cudaEvent_t host_event;
     bool host_streams_ready;
     salp::CycleEntry *cycle_tab;  // device copy of the forced-breathing cycle table (handle-owned parameter data)
 };
@@ -265,6 +266,7 @@ int salp_destroy(SalpHandle *h) {
     if (h->host_streams_ready) {
         cudaSetDevice(h->device);
         for (auto &s : h->host_streams) cudaStreamDestroy(s);
+        cudaEventDestroy(h->host_event);
     }
     delete h;
     return SALP_OK;
@@ -410,19 +412,21 @@ int salp_step_slot(SalpHandle *h, int slot, const void *actions, void *stream) {
 }
 
 int salp_step_host(SalpHandle *h, void *actions_staging, const void *actions_host, float *obs_host,
-                   void *reward_host, uint8_t *terminated_host, uint8_t *truncated_host) {
+                   void *reward_host, uint8_t *terminated_host, uint8_t *truncated_host, void *caller_stream) {
     if (!h) return fail(SALP_EINVAL, "null handle");
     if (!h->bound) return fail(SALP_EUNBOUND, "salp_bind has not been called");
     if (!actions_staging || !actions_host) return fail(SALP_EINVAL, "actions (device staging and host) must be non-null");
     SALP_CUDA(cudaSetDevice(h->device));
     if (!h->host_streams_ready) {
-        // blocking streams: ordered after earlier work on the legacy default stream
-        for (auto &s : h->host_streams) SALP_CUDA(cudaStreamCreate(&s));
+        for (auto &s : h->host_streams) SALP_CUDA(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+        SALP_CUDA(cudaEventCreateWithFlags(&h->host_event, cudaEventDisableTiming));
         h->host_streams_ready = true;
     }
+    // the chunk streams start after everything already queued on the caller's stream (e.g. the reset, or set_attr copies)
+    SALP_CUDA(cudaEventRecord(h->host_event, (cudaStream_t)caller_stream));
     const int64_t N = h->num_envs;
     const size_t rb = (size_t)h->layout.real_bytes, ad = (size_t)h->layout.act_dim, od = (size_t)h->layout.obs_dim;
-    // chunk boundaries on CTA granularity so every chunk but the last is a whole number of tiles
+    // chunk boundaries on CTA / tile granularity so every chunk but the last is a whole number of tiles
     const int64_t tiles = (N + salp::kHostChunkAlign - 1) / salp::kHostChunkAlign;
     const int chunks = (int)std::min<int64_t>(kHostChunks, tiles);
     int rc = SALP_OK;
@@ -431,6 +435,7 @@ int salp_step_host(SalpHandle *h, void *actions_staging, const void *actions_hos
         const int64_t lo = t0 * salp::kHostChunkAlign, hi = std::min<int64_t>(N, t1 * salp::kHostChunkAlign);
         const size_t n = (size_t)(hi - lo);
         cudaStream_t s = h->host_streams[c];
+        SALP_CUDA(cudaStreamWaitEvent(s, h->host_event, 0));
         SALP_CUDA(cudaMemcpyAsync((char *)actions_staging + lo * ad * rb, (const char *)actions_host + lo * ad * rb,
                                   n * ad * rb, cudaMemcpyHostToDevice, s));
         salp::KernelArgs a = h->base;

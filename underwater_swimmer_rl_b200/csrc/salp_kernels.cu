@@ -26,7 +26,7 @@ template <int F> struct StepCfg {
     static constexpr int store = (F <= 12) ? kStoreTmaBlock : kStoreDirect;
     static constexpr int block = 64;
     static constexpr int prefetch = 0;
-    static constexpr int regs_f32 = F <= 4 ? 64 : (F <= 8 ? 80 : (F <= 12 ? 72 : (F <= 16 ? 128 : 255)));
+    static constexpr int regs_f32 = F <= 4 ? 64 : (F <= 12 ? 80 : (F <= 16 ? 128 : 255));
     static constexpr int regs = SALP_BUILD_F64 ? (2 * regs_f32 > 255 ? 255 : 2 * regs_f32) : regs_f32;
     static constexpr int minb = (65536 / (regs * block)) > 32 ? 32 : (65536 / (regs * block) < 1 ? 1 : 65536 / (regs * block));
 };
@@ -34,8 +34,11 @@ template <int F> struct StepCfg {
 template <int F>
 static cudaError_t launch_step_f(const KernelArgs &a, cudaStream_t s) {
     using C = StepCfg<F>;
-    return a.observed == 3 ? launch_step_variant<real_t, F, 3, C::store, C::block, C::minb, C::prefetch>(a, s)
-                           : launch_step_variant<real_t, F, 8, C::store, C::block, C::minb, C::prefetch>(a, s);
+    if (a.rng_mode)
+        return a.observed == 3 ? launch_step_variant<real_t, F, 3, C::store, C::block, C::minb, C::prefetch, 1>(a, s)
+                               : launch_step_variant<real_t, F, 8, C::store, C::block, C::minb, C::prefetch, 1>(a, s);
+    return a.observed == 3 ? launch_step_variant<real_t, F, 3, C::store, C::block, C::minb, C::prefetch, 0>(a, s)
+                           : launch_step_variant<real_t, F, 8, C::store, C::block, C::minb, C::prefetch, 0>(a, s);
 }
 
 cudaError_t SALP_LAUNCH_STEP(const KernelArgs &a, int food_slots, cudaStream_t s) {

@@ -4,10 +4,10 @@
 
 namespace salp {
 
-template <typename T, int F, int MT, int STORE, int BLOCK, int MINB, int PF>
+template <typename T, int F, int MT, int STORE, int BLOCK, int MINB, int PF, int RNG = 0>
 cudaError_t launch_step_variant(const KernelArgs &a, cudaStream_t s) {
     static_assert(BLOCK % 32 == 0 && BLOCK >= 32 && BLOCK <= 1024, "BLOCK must be a multiple of the warp size");
-    auto kern = salp_step_kernel<T, F, MT, STORE, BLOCK, MINB, PF>;
+    auto kern = salp_step_kernel<T, F, MT, STORE, BLOCK, MINB, PF, RNG>;
     constexpr bool tma = (STORE == kStoreTmaWarp || STORE == kStoreTmaBlock);
     size_t smem;
     if (PF) smem = stage_offset_bytes<STORE, BLOCK>(a.obs_dim) + stage_bytes<T, F, BLOCK>();
@@ -15,25 +15,31 @@ cudaError_t launch_step_variant(const KernelArgs &a, cudaStream_t s) {
         const int nbuf = STORE == kStoreDirect ? 0 : (tma ? ((a.K > 1 || STORE == kStoreTmaWarp) ? 2 : 1) : 1);
         smem = (size_t)nbuf * BLOCK * a.obs_dim * sizeof(float);
     }
-    static size_t smem_set = 0;  // per instantiation
-    static size_t occ_smem = ~(size_t)0;
-    static int occ_blocks = 0, sms = 0;
-    if (smem > 48 * 1024 && smem > smem_set) {
-        cudaError_t err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    // per instantiation AND per device: a process may drive several GPUs through several handles
+    constexpr int kMaxDev = 64;
+    static size_t smem_set[kMaxDev] = {0}, occ_smem[kMaxDev] = {0};
+    static int occ_blocks[kMaxDev] = {0}, sms_[kMaxDev] = {0};
+    int dev = 0;
+    cudaError_t err = cudaGetDevice(&dev);
+    if (err != cudaSuccess) return err;
+    if (dev < 0 || dev >= kMaxDev) return cudaErrorInvalidDevice;
+    if (smem > 48 * 1024 && smem > smem_set[dev]) {
+        err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (err != cudaSuccess) return err;
-        smem_set = smem;
+        smem_set[dev] = smem;
     }
     const unsigned ntiles = (unsigned)((a.count + BLOCK - 1) / BLOCK);
     unsigned grid = ntiles;
-    if (occ_smem != smem) {  // CTAs of this instantiation that fit on the chip at once
-        int dev = 0;
-        cudaError_t err = cudaGetDevice(&dev);
-        if (err == cudaSuccess) err = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        if (err == cudaSuccess) err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_blocks, kern, BLOCK, smem);
+    if (occ_blocks[dev] == 0 || occ_smem[dev] != smem) {  // CTAs of this instantiation that fit on the chip at once
+        err = cudaDeviceGetAttribute(&sms_[dev], cudaDevAttrMultiProcessorCount, dev);
+        if (err == cudaSuccess) err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_blocks[dev], kern, BLOCK, smem);
         if (err != cudaSuccess) return err;
-        occ_smem = smem;
+        if (occ_blocks[dev] < 1) occ_blocks[dev] = 1;
+        occ_smem[dev] = smem;
     }
-    const unsigned resident = (unsigned)(sms * (occ_blocks > 0 ? occ_blocks : 1));
+    const int sms = sms_[dev];
+    const int occ_b = occ_blocks[dev];
+    const unsigned resident = (unsigned)(sms * occ_b);
     if (PF) grid = ntiles < resident ? ntiles : resident;  // persistent
     // Programmatic dependent launch for grids of at least one resident wave: the first CTAs of this launch become resident
     // while the last wave of the previous kernel of the stream drains (they block at griddepcontrol.wait before touching

@@ -490,8 +490,10 @@ template <typename T, int F, int BLOCK> __host__ __device__ constexpr unsigned s
 //   MINB  : CTAs per SM the register allocation must allow (__launch_bounds__)
 //   PF    : 0 one tile per CTA, state loaded straight into registers
 //           1 persistent CTAs, next tile's state prefetched into shared memory with cp.async
+//   RNG   : 0 thrust jitter from the word table, 1 from the in-kernel Philox stream (== a.rng_mode; a template parameter so
+//           that the table-mode kernel carries none of the generator's registers)
 // ---------------------------------------------------------------------------------------------
-template <typename T, int F, int MT, int STORE, int BLOCK, int MINB, int PF>
+template <typename T, int F, int MT, int STORE, int BLOCK, int MINB, int PF, int RNG = 0>
 __global__ void __launch_bounds__(BLOCK, MINB) salp_step_kernel(const __grid_constant__ KernelArgs a) {
     extern __shared__ __align__(128) float s_tile[];  // obs tiles [nbuf][BLOCK][obs_dim], then the PF stage
     const int tid = threadIdx.x;
@@ -612,7 +614,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) salp_step_kernel(const __grid_con
         unsigned jcache = (unsigned)c1.w;  // first word of the jitter pair at cur_jit (see salp_b200.h)
 
         const unsigned trow = (a.rows == N) ? e : e % a.rows;
-        const uint32_t *jit_row = a.rng_mode ? nullptr : a.jit_words + (size_t)trow * a.jit_len;
+        const uint32_t *jit_row = RNG ? nullptr : a.jit_words + (size_t)trow * a.jit_len;
 
         for (int k = 0; k < a.K; ++k, ++gk) {
             // ---- where this thread's observation row goes
@@ -647,7 +649,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) salp_step_kernel(const __grid_con
             uint2 jw = make_uint2(jcache, 0u);
 #ifndef SALP_LAB_NOJIT
             if (thrust) {
-                if (a.rng_mode) jw = philox_jitter_pair(a, e, cur_jit);
+                if constexpr (RNG != 0) jw = philox_jitter_pair(a, e, cur_jit);  // RNG: compile-time copy of a.rng_mode
                 else if constexpr (is_f64<T>::value) jw = ld_evict_last_u2(jit_row + (cur_jit & a.jit_len_mask));
                 else jcache = ld_evict_last_u1(jit_row + ((cur_jit + 2u) & a.jit_len_mask));
             }

@@ -22,6 +22,9 @@ from ._gym_compat import Env
 from .vector_env import PHASE_NAMES, SalpVectorEnv
 
 
+BACKEND = SalpVectorEnv
+
+
 class SalpSnakeEnv(Env):
     metadata = {"render_modes": [], "render_fps": 60}
 
@@ -29,8 +32,10 @@ class SalpSnakeEnv(Env):
                  device="cuda:0", dtype="float64", seed: Optional[int] = None, **kwargs):
         if seed is None:  # the reference draws from unseeded global generators; pick a stream at random
             seed = random.SystemRandom().randrange(1, 2 ** 31)
-        self._v = SalpVectorEnv(1, device=device, dtype=dtype, seed=seed, autoreset=False, food_table_len=4096,
-                                jitter_table_len=16384, render_mode=render_mode, width=width, height=height, **kwargs)
+        # BACKEND is the batched env class; the CPU test of the reference's train.py call sequence swaps in an oracle-backed
+        # stand-in (tests/fake_backend.py) because the build container has no GPU.  The product has exactly one backend.
+        self._v = BACKEND(1, device=device, dtype=dtype, seed=seed, autoreset=False, food_table_len=4096,
+                          jitter_table_len=16384, render_mode=render_mode, width=width, height=height, **kwargs)
         self.render_mode = None
         self.width, self.height = width, height
         self.tank_margin, self.base_radius, self.food_radius, self.min_food_distance = 50, 30, 15, 80

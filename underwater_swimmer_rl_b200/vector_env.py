@@ -305,7 +305,7 @@ class SalpVectorEnv(VectorEnv):
         assert actions_host.dtype == self.real and reward_host.dtype == self.real and obs_host.dtype == torch.float32
         _capi.check(self._L.salp_step_host(self._handle, self.actions.data_ptr(), actions_host.data_ptr(), obs_host.data_ptr(),
                                            reward_host.data_ptr(), terminated_host.data_ptr(),
-                                           truncated_host.data_ptr()))
+                                           truncated_host.data_ptr(), self._stream()))
 
     def capture_graph(self, actions, k_steps: int = 1):
         """Capture step launches into a CUDA graph and return a zero-argument replay function.
