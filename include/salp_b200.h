@@ -245,6 +245,26 @@ int salp_step_host(SalpHandle *h, void *actions_staging, const void *actions_hos
                    void *reward_host, uint8_t *terminated_host, uint8_t *truncated_host, void *caller_stream);
 
 /*
+ * salp_step_host without any allocation.  This entry point has NO counterpart in the reference; it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  Same inputs, outputs and result as salp_step_host, but
+ *   - the device staging buffer the step kernel reads its actions from is not passed in: it is a file-scope
+ *     `static __device__ __align__(256)` array of SALP_NOALLOC_STAGING_BYTES (1 MiB) inside the library, which every
+ *     GPU that loads the library holds until the process exits.  num_envs * act_dim * real_bytes must fit:
+ *     262144 envs (f32, forced breathing) ... 65536 envs (f64, manual breathing); more is rejected with
+ *     SALP_EUNSUPPORTED and a message naming the limit -- use salp_step_host then;
+ *   - everything runs on `caller_stream` alone (one H2D copy, one step kernel, up to four D2H copies, one
+ *     cudaStreamSynchronize): no cudaMalloc / cudaFree, no stream or event creation, no allocating library call.
+ * The first call on a device resolves the array's device address (cudaGetSymbolAddress, once per device).
+ * Every call -- on any handle of the process -- shares the one array per GPU, and it keeps the last call's actions:
+ * nothing in it has to start at zero (the kernel reads exactly the records the call has just copied in), but two
+ * calls whose GPU work overlaps (different streams or threads on the same GPU) race on it.  Not for them.
+ */
+#define SALP_NOALLOC_STAGING_BYTES (1 << 20)
+int salp_step_host_noalloc(SalpHandle *h, const void *actions_host, float *obs_host, void *reward_host,
+                           uint8_t *terminated_host, uint8_t *truncated_host, void *caller_stream);
+
+/*
  * Fill `rows` rows of `len` raw MT19937 outputs into HOST memory dst[rows][len]:
  *   kind 0: the stream of Python's random.seed(seed0 + first_row + r)     (init_by_array)
  *   kind 1: the stream of numpy.random.seed(seed0 + first_row + r)        (init_genrand)

@@ -537,3 +537,76 @@ int salp_fill_rng_words(uint32_t *dst, int64_t rows, int64_t len, uint64_t seed0
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------
+// salp_step_host_noalloc -- the host-buffer step for callers that cannot allocate device memory.
+//
+// salp_step_host needs a caller-owned DEVICE staging buffer for the actions the step kernel reads
+// (actions_staging) and creates eight streams and an event on its first call.  This variant takes that
+// scratch from a file-scope device array instead and works on the caller's stream alone: it calls no
+// cudaMalloc / cudaFree / cudaStreamCreate / cudaEventCreate, so the caller needs no allocator at all.
+// Every GPU that loads the library holds SALP_NOALLOC_STAGING_BYTES (1 MiB) for it until exit.
+//
+// In host code `g_noalloc_staging` is only a host-side stand-in for the device array, NOT a device
+// address: the address the copy engine and the kernel need comes from cudaGetSymbolAddress, asked once
+// per device with that device current (the first call of the entry point on a device is the set-up).
+// ---------------------------------------------------------------------------------------------
+#include <mutex>
+
+static __device__ __align__(256) unsigned char g_noalloc_staging[SALP_NOALLOC_STAGING_BYTES];
+
+namespace {
+
+constexpr int kNoallocMaxDevices = 64;
+std::mutex g_noalloc_mu;
+void *g_noalloc_ptr[kNoallocMaxDevices] = {};
+
+// device address of g_noalloc_staging on `device`, which must be the current device
+int noalloc_staging(int device, void **out) {
+    if (device < 0 || device >= kNoallocMaxDevices) return fail(SALP_EUNSUPPORTED, "device ordinal %d out of range", device);
+    std::lock_guard<std::mutex> lock(g_noalloc_mu);
+    if (!g_noalloc_ptr[device]) {
+        void *p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_staging);
+        if (e != cudaSuccess) return cuda_fail(e, "cudaGetSymbolAddress(static action staging)");
+        if (!p || (uintptr_t)p % 256 != 0) return fail(SALP_ECUDA, "static action staging resolved to a bad device address %p", p);
+        g_noalloc_ptr[device] = p;
+    }
+    *out = g_noalloc_ptr[device];
+    return SALP_OK;
+}
+
+}  // namespace
+
+extern "C" int salp_step_host_noalloc(SalpHandle *h, const void *actions_host, float *obs_host, void *reward_host,
+                                      uint8_t *terminated_host, uint8_t *truncated_host, void *caller_stream) {
+    if (!h) return fail(SALP_EINVAL, "null handle");
+    if (!h->bound) return fail(SALP_EUNBOUND, "salp_bind has not been called");
+    if (!actions_host) return fail(SALP_EINVAL, "actions_host must be non-null");
+    const int64_t N = h->num_envs;
+    const size_t rb = (size_t)h->layout.real_bytes, ad = (size_t)h->layout.act_dim, od = (size_t)h->layout.obs_dim;
+    const size_t need = (size_t)N * ad * rb;
+    if (need > (size_t)SALP_NOALLOC_STAGING_BYTES)
+        return fail(SALP_EUNSUPPORTED,
+                    "salp_step_host_noalloc: %lld envs x %zu-byte action records = %zu bytes exceed the %d-byte static staging "
+                    "array (SALP_NOALLOC_STAGING_BYTES); use salp_step_host with a caller-owned staging buffer",
+                    (long long)N, ad * rb, need, (int)SALP_NOALLOC_STAGING_BYTES);
+    SALP_CUDA(cudaSetDevice(h->device));
+    void *staging = nullptr;
+    if (int rc = noalloc_staging(h->device, &staging)) return rc;
+    cudaStream_t s = (cudaStream_t)caller_stream;
+    // Nothing in the staging array has to start at zero: the kernel reads exactly the N action records written here.
+    SALP_CUDA(cudaMemcpyAsync(staging, actions_host, need, cudaMemcpyHostToDevice, s));
+    salp::KernelArgs a = h->base;
+    a.K = 1;
+    a.actions = staging;
+    if (int rc = launch_step(h, a, s)) return rc;
+    const size_t n = (size_t)N;
+    if (obs_host) SALP_CUDA(cudaMemcpyAsync(obs_host, h->buf.obs, n * od * sizeof(float), cudaMemcpyDeviceToHost, s));
+    if (reward_host) SALP_CUDA(cudaMemcpyAsync(reward_host, h->buf.reward, n * rb, cudaMemcpyDeviceToHost, s));
+    if (terminated_host) SALP_CUDA(cudaMemcpyAsync(terminated_host, h->buf.terminated, n, cudaMemcpyDeviceToHost, s));
+    if (truncated_host) SALP_CUDA(cudaMemcpyAsync(truncated_host, h->buf.truncated, n, cudaMemcpyDeviceToHost, s));
+    cudaError_t e = cudaStreamSynchronize(s);
+    if (e != cudaSuccess) return cuda_fail(e, "salp_step_host_noalloc synchronize");
+    return SALP_OK;
+}

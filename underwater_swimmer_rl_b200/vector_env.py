@@ -307,6 +307,20 @@ class SalpVectorEnv(VectorEnv):
                                            reward_host.data_ptr(), terminated_host.data_ptr(),
                                            truncated_host.data_ptr(), self._stream()))
 
+    def step_host_noalloc(self, actions_host: torch.Tensor, obs_host: torch.Tensor, reward_host: torch.Tensor,
+                          terminated_host: torch.Tensor, truncated_host: torch.Tensor) -> None:
+        """step_host for callers that may not allocate device memory: the action staging lives in a 1 MiB static
+        device array inside the library (salp_step_host_noalloc; num_envs * act_dim * itemsize must fit), the work
+        runs on the current stream alone.  Calls that overlap on one GPU race on that array."""
+        if self._needs_reset:
+            raise RuntimeError("call reset() before step()")
+        for t in (actions_host, obs_host, reward_host, terminated_host, truncated_host):
+            assert t.device.type == "cpu" and t.is_contiguous()
+        assert actions_host.dtype == self.real and reward_host.dtype == self.real and obs_host.dtype == torch.float32
+        _capi.check(self._L.salp_step_host_noalloc(self._handle, actions_host.data_ptr(), obs_host.data_ptr(),
+                                                   reward_host.data_ptr(), terminated_host.data_ptr(),
+                                                   truncated_host.data_ptr(), self._stream()))
+
     def capture_graph(self, actions, k_steps: int = 1):
         """Capture step launches into a CUDA graph and return a zero-argument replay function.
         ``actions``: one tensor (one launch per replay, read in place) or a list of tensors (one launch per
