@@ -183,6 +183,20 @@ __device__ __forceinline__ uint32_t food_word(const KernelArgs &a, unsigned e, u
     ++cur;
     return w;
 }
+// the four words of one (x, y) candidate: in Philox mode they are ONE block whenever the cursor sits on a multiple of 4
+// (always, unless random_food_count's randint has moved it), instead of one block per word
+__device__ __forceinline__ uint4 food_words4(const KernelArgs &a, unsigned e, unsigned &cur) {
+    uint4 w;
+    if (a.rng_mode && (cur & 3u) == 0u) { w = philox_block(a, e, 0u, cur); cur += 4u; }
+    else { w.x = food_word(a, e, cur); w.y = food_word(a, e, cur); w.z = food_word(a, e, cur); w.w = food_word(a, e, cur); }
+    return w;
+}
+// random.uniform(xlo, xhi), random.uniform(ylo, yhi): a + (b - a) * random(), two words per draw
+template <typename T> __device__ __forceinline__ void food_xy(const KernelArgs &a, unsigned e, unsigned &cur, T xlo, T xhi, T ylo, T yhi, T &x, T &y) {
+    const uint4 w = food_words4(a, e, cur);
+    x = xlo + (xhi - xlo) * (T)res53(w.x, w.y);
+    y = ylo + (yhi - ylo) * (T)res53(w.z, w.w);
+}
 template <typename T> __device__ __forceinline__ T food_uniform(const KernelArgs &a, unsigned row, unsigned &cur, T lo, T hi) {
     const uint32_t w0 = food_word(a, row, cur), w1 = food_word(a, row, cur);  // `row` = env index, see food_word
     return lo + (hi - lo) * (T)res53(w0, w1);  // random.uniform: a + (b-a)*random()
@@ -214,8 +228,7 @@ __device__ __noinline__ RespawnResult<T> respawn_slow(const KernelArgs &a, long 
     T x = 0, y = 0;
     bool found = false;
     while (attempts < 50) {
-        x = food_uniform<T>(a, row, cur, xlo, xhi);
-        y = food_uniform<T>(a, row, cur, ylo, yhi);
+        food_xy<T>(a, row, cur, xlo, xhi, ylo, yhi, x, y);
         const T rx = x - px, ry = y - py;
         bool valid = !(sqrt_(rx * rx + ry * ry) < (T)kc::MIN_FOOD_DIST);
 #pragma unroll
@@ -227,15 +240,65 @@ __device__ __noinline__ RespawnResult<T> respawn_slow(const KernelArgs &a, long 
         if (valid) { found = true; break; }
         ++attempts;
     }
-    if (!found) {
-        x = food_uniform<T>(a, row, cur, xlo, xhi);
-        y = food_uniform<T>(a, row, cur, ylo, yhi);
-    }
+    if (!found) food_xy<T>(a, row, cur, xlo, xhi, ylo, yhi, x, y);
     int slot = -1;
     for (int j = 0; j < n_food; ++j)
         if (!((mask >> j) & 1u)) { slot = j; break; }
     if (slot >= 0) {
         food[(size_t)slot * a.N + e] = Vec2<T>{x, y};
+        mask |= 1u << slot;
+    }
+    return RespawnResult<T>{x, y, cur, mask, slot};
+}
+
+// Warp-cooperative S:232-276 _respawn_food for ONE env, run by all 32 lanes of a converged warp (every argument
+// warp-uniform).  The reference draws up to 50 candidates one at a time and keeps the first that is >= 80 px from the robot
+// and from every live food, then draws a 51st unconditionally; here lane L materialises candidate 32 w + L of window w
+// (w = 0, 1) and a ballot picks the first valid one -- the same candidate, the same words consumed, in one pass instead
+// of a serial rejection loop run by a single lane while 31 wait (the slowest lane of a launch sets a small slab's time).
+// Lane 0 writes the new food record; the result is returned in every lane.
+template <typename T, int F>
+__device__ __noinline__ RespawnResult<T> respawn_warp(const KernelArgs &a, unsigned e, T px, T py, unsigned mask, int n_food,
+                                                     unsigned cur, int lane) {
+    constexpr unsigned kFull = 0xffffffffu;
+    Vec2<T> *food = reinterpret_cast<Vec2<T> *>(a.food);
+    const T xlo = (T)(kc::TANK_MARGIN + kc::FOOD_R), xhi = (T)a.W - (T)kc::TANK_MARGIN - (T)kc::FOOD_R;
+    const T ylo = xlo, yhi = (T)a.H - (T)kc::TANK_MARGIN - (T)kc::FOOD_R;
+    Vec2<T> live[F];  // the same address in every lane: one transaction per food, all in flight together
+#pragma unroll
+    for (int j = 0; j < F; ++j)
+        live[j] = (j < n_food && ((mask >> j) & 1u)) ? food[(size_t)j * a.N + e] : Vec2<T>{0, 0};
+    T x = 0, y = 0;
+    int chosen = 50;  // candidate index == rejected attempts before it; candidate 50 is the unconditional draw
+#pragma unroll 1
+    for (int base = 0; base < 64; base += 32) {
+        const int idx = base + lane;
+        unsigned c2 = cur + 4u * (unsigned)idx;
+        T cx, cy;
+        food_xy<T>(a, e, c2, xlo, xhi, ylo, yhi, cx, cy);
+        const T rx = cx - px, ry = cy - py;
+        bool ok = !(sqrt_(rx * rx + ry * ry) < (T)kc::MIN_FOOD_DIST);
+#pragma unroll
+        for (int j = 0; j < F; ++j)
+            if (j < n_food && ((mask >> j) & 1u)) {
+                const T dx = cx - live[j].x, dy = cy - live[j].y;
+                if (sqrt_(dx * dx + dy * dy) < (T)kc::MIN_FOOD_DIST) ok = false;
+            }
+        const unsigned m = __ballot_sync(kFull, ok && idx < 50);
+        const int c = m ? base + __ffs((int)m) - 1 : (base == 32 ? 50 : -1);
+        if (c >= 0) {
+            x = __shfl_sync(kFull, cx, c - base);
+            y = __shfl_sync(kFull, cy, c - base);
+            chosen = c;
+            break;
+        }
+    }
+    cur += 4u * (unsigned)(chosen + 1);
+    int slot = -1;
+    for (int j = 0; j < n_food; ++j)
+        if (!((mask >> j) & 1u)) { slot = j; break; }
+    if (slot >= 0) {
+        if (lane == 0) food[(size_t)slot * a.N + e] = Vec2<T>{x, y};
         mask |= 1u << slot;
     }
     return RespawnResult<T>{x, y, cur, mask, slot};
@@ -264,8 +327,7 @@ __device__ __noinline__ ResetResult reset_slow(const KernelArgs &a, long long e,
         int attempts = 0;
         T x = 0, y = 0;
         while (attempts < 100) {
-            x = food_uniform<T>(a, row, cur, xlo, xhi);
-            y = food_uniform<T>(a, row, cur, ylo, yhi);
+            food_xy<T>(a, row, cur, xlo, xhi, ylo, yhi, x, y);
             bool valid = true;
             for (int j = 0; j < i; ++j) {
                 const Vec2<T> f = food[(size_t)j * a.N + e];
@@ -277,10 +339,7 @@ __device__ __noinline__ ResetResult reset_slow(const KernelArgs &a, long long e,
             if (valid) break;
             ++attempts;
         }
-        if (attempts >= 100) {
-            x = food_uniform<T>(a, row, cur, xlo, xhi);
-            y = food_uniform<T>(a, row, cur, ylo, yhi);
-        }
+        if (attempts >= 100) food_xy<T>(a, row, cur, xlo, xhi, ylo, yhi, x, y);
         food[(size_t)i * a.N + e] = Vec2<T>{x, y};
         const T rx = x - cx, ry = y - cy;
         dist[i] = sqrt_(rx * rx + ry * ry);

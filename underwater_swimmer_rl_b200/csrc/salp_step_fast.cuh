@@ -125,6 +125,15 @@ template <int F> struct FastCfg;
 template <> struct FastCfg<1> { static constexpr int warps = 4, minb = SALP_FAST_F1_MINB; };    // 28 warps/SM, 72 registers
 template <> struct FastCfg<12> { static constexpr int warps = 8, minb = 2; };                    // 16 warps/SM, 128 registers
 
+#ifdef SALP_LAB_CLOCK  // developer builds: per-warp phase timestamps of the first tile (tools/_lab)
+__device__ long long g_lab_clk[24 * 8192];
+#define SALP_LAB_T(i) do { if (it == 0 && lane == 0 && gw < 8192u) g_lab_clk[gw * 24 + (i)] = clock64(); } while (0)
+#define SALP_LAB_V(i, v) do { if (it == 0 && lane == 0 && gw < 8192u) g_lab_clk[gw * 24 + (i)] = (long long)(v); } while (0)
+#else
+#define SALP_LAB_T(i) do { } while (0)
+#define SALP_LAB_V(i, v) do { } while (0)
+#endif
+
 template <int F, int RNG>
 __global__ void __launch_bounds__(FastCfg<F>::warps * 32, FastCfg<F>::minb) salp_step_fast_kernel(const __grid_constant__ KernelArgs a) {
     using Cfg = FastCfg<F>;
@@ -160,6 +169,9 @@ __global__ void __launch_bounds__(FastCfg<F>::warps * 32, FastCfg<F>::minb) salp
     const uint64_t pol_out = (a.l2_mode & 2) ? l2_policy_evict_first() : l2_policy_evict_normal();
     const uint64_t pol_food = (a.l2_mode & 4) ? l2_policy_evict_last() : l2_policy_evict_normal();
 
+#ifdef SALP_LAB_CLOCK
+    { const unsigned it = 0; SALP_LAB_T(0); SALP_LAB_V(15, blockIdx.x); unsigned smid; asm("mov.u32 %0, %%smid;" : "=r"(smid)); SALP_LAB_V(14, smid); }
+#endif
     if (elect_one_sync()) {
         mbar_init(bar_core, 1);
         mbar_init(bar_food + 0, 1);
@@ -220,6 +232,9 @@ __global__ void __launch_bounds__(FastCfg<F>::warps * 32, FastCfg<F>::minb) salp
         }
     };
 
+#ifdef SALP_LAB_CLOCK
+    { const unsigned it = 0; SALP_LAB_T(1); }
+#endif
     unsigned ph_core = 0u, ph_food = 0u;  // mbarrier phase parities (bit st of ph_food)
     // the two scalars of the state that are not 128-bit records travel in registers, fetched one tile ahead
     float act_nx = 0.f, ep_nx = 0.f;
@@ -248,7 +263,9 @@ __global__ void __launch_bounds__(FastCfg<F>::warps * 32, FastCfg<F>::minb) salp
             const unsigned en = first + nxt * 32u + lane;
             if (en < end) { act_nx = ld_hint_f32(g_act + en, pol_out); ep_nx = ld_hint_f32(g_epret + en, pol_state); }
         }
+        SALP_LAB_T(2);
         if (full) { mbar_wait(bar_core, ph_core & 1u); ph_core ^= 1u; }
+        SALP_LAB_T(3);
         // ---- state of this lane's env
         const int4 c0 = reinterpret_cast<const int4 *>(sc + L::kC0)[lane];
         const int4 c1 = reinterpret_cast<const int4 *>(sc + L::kC1)[lane];
@@ -382,7 +399,9 @@ __global__ void __launch_bounds__(FastCfg<F>::warps * 32, FastCfg<F>::minb) salp
                 dd0 = sqrt_(dx0 * dx0 + dy0 * dy0);
                 if ((mask & 1u) && dd0 < reach) { hit = true; mask &= ~1u; }
             } else {
+                SALP_LAB_T(4);
                 if (k == 0 && full) { mbar_wait(bar_food + st, (ph_food >> st) & 1u); ph_food ^= 1u << st; }
+                SALP_LAB_T(5);
                 unsigned hitbits = 0u;
 #pragma unroll
                 for (int i = 0; i < MU; ++i) key[i] = 0xffffffffu;
@@ -400,6 +419,7 @@ __global__ void __launch_bounds__(FastCfg<F>::warps * 32, FastCfg<F>::minb) salp
                 hitbits &= mask;
                 if (hitbits != 0u) { hit = true; mask &= ~(hitbits & (0u - hitbits)); reselect(); }
             }
+            SALP_LAB_T(6);
             // ---- reward (S:278-327)
             float reward = 0.f;
             if (hit) {
@@ -416,17 +436,21 @@ __global__ void __launch_bounds__(FastCfg<F>::warps * 32, FastCfg<F>::minb) salp
             reward += a.f_time_penalty;
             // ---- counters, respawn (S:171-180)
             ++steps_since_food;
-            if (hit) {
-                ++food_collected;
-                steps_since_food = 0;
-                if (a.respawn) {
-                    const RespawnResult<float> r = respawn_slow<float, F>(a, e, px, py, mask, n_food, cur_food);
-                    mask = r.mask; cur_food = r.cur;
-                    if (r.slot >= 0) {
-                        const float ox = r.x - px, oy = r.y - py;
-                        const float d = sqrt_(ox * ox + oy * oy);
-                        if constexpr (F == 1) { dx0 = ox; dy0 = oy; dd0 = d; food1 = make_float2(r.x, r.y); }
-                        else { sfood[r.slot * 32 + lane] = make_float2(ox, oy); dist_sum += d; insert_key(make_key(d, r.slot)); }
+            if (hit) { ++food_collected; steps_since_food = 0; }
+            if (a.respawn) {  // the whole warp finds the new position of each eaten food in turn (respawn_warp)
+                for (unsigned m = __ballot_sync(kFull, hit); m != 0u; m &= m - 1u) {
+                    const int src = __ffs((int)m) - 1;
+                    const RespawnResult<float> r = respawn_warp<float, F>(a, __shfl_sync(kFull, e, src), __shfl_sync(kFull, px, src),
+                        __shfl_sync(kFull, py, src), __shfl_sync(kFull, mask, src), __shfl_sync(kFull, n_food, src),
+                        __shfl_sync(kFull, cur_food, src), lane);
+                    if (lane == src) {
+                        mask = r.mask; cur_food = r.cur;
+                        if (r.slot >= 0) {
+                            const float ox = r.x - px, oy = r.y - py;
+                            const float d = sqrt_(ox * ox + oy * oy);
+                            if constexpr (F == 1) { dx0 = ox; dy0 = oy; dd0 = d; food1 = make_float2(r.x, r.y); }
+                            else { sfood[r.slot * 32 + lane] = make_float2(ox, oy); dist_sum += d; insert_key(make_key(d, r.slot)); }
+                        }
                     }
                 }
             }
@@ -451,8 +475,10 @@ __global__ void __launch_bounds__(FastCfg<F>::warps * 32, FastCfg<F>::minb) salp
             float obs6 = radius * (float)(1.0 / kc::BASE_R), obs7 = (float)(t0.w & 3u) * 0.5f;
             // the observation tile buffer is single: the bulk store of the previous tile / substep must have read it
             // (it was issued a tile of arithmetic ago)
+            SALP_LAB_T(7);
             if (elect_one_sync()) bulk_wait_read<0>();
             __syncwarp();
+            SALP_LAB_V(12, 0);
 #pragma unroll 1
             for (int pass = 0;; ++pass) {
                 // ---- observation (R:377-388 + S:366-428) assembled in registers, written as 128-bit pieces of the row
@@ -488,7 +514,9 @@ __global__ void __launch_bounds__(FastCfg<F>::warps * 32, FastCfg<F>::minb) salp
                 if (pass) break;
                 // ---- episode statistics: warp-shuffle reduction, only in warps where an episode ended
                 const unsigned done_mask = __ballot_sync(kFull, done);
+                SALP_LAB_T(8);
                 if (done_mask == 0u) break;
+                SALP_LAB_V(12, __popc(done_mask));
                 if (a.stats) {
                     const double r = warp_sum(done ? (double)ep_ret : 0.0);
                     const double l = warp_sum(done ? (double)ep_len : 0.0);
@@ -506,6 +534,7 @@ __global__ void __launch_bounds__(FastCfg<F>::warps * 32, FastCfg<F>::minb) salp
                         if (bad_mask) atomicAdd(a.stats + 6, (double)__popc(bad_mask));
                     }
                 }
+                SALP_LAB_T(16);
                 if (done && a.final_info)
                     reinterpret_cast<float4 *>(a.final_info)[(size_t)k * N + e] =
                         make_float4(ep_ret, (float)ep_len, (float)food_collected, (float)steps_since_food);
@@ -515,8 +544,12 @@ __global__ void __launch_bounds__(FastCfg<F>::warps * 32, FastCfg<F>::minb) salp
 #pragma unroll
                     for (int j = 0; j < OBS / 4; ++j) dst[j] = r4[j];
                 }
+                SALP_LAB_T(17);
                 if constexpr (F < 8) {
-                    if (done) {  // few foods: the in-thread reset is cheap and writes the reset observation itself
+                    // few foods: the in-thread reset writes the reset observation itself.  (Measured on B200 against the
+                    // warp-cooperative layout below, which needs the whole warp's state live across the call: 72-register
+                    // budget -> spills in the hot path, 41.8 -> 46.2 us at 1 M envs; with 80 registers no gain at any size.)
+                    if (done) {
                         const ResetResult rr = reset_slow<float>(a, e, cur_food, row);
                         cur_food = rr.cur; mask = rr.mask; n_food = rr.n_food;
                         px = W * 0.5f; py = H * 0.5f; vx = 0.f; vy = 0.f; angle = 0.f; omega = 0.f; nozzle = 0.f; wv_now = 0.f;
@@ -524,6 +557,7 @@ __global__ void __launch_bounds__(FastCfg<F>::warps * 32, FastCfg<F>::minb) salp
                         steps_since_food = 0; food_collected = 0; ep_ret = 0.f; ep_len = 0;
                         if (a.K > 1) food1 = g_food[e];  // the next substep needs the new food position
                     }
+                    SALP_LAB_T(19);
                     break;
                 } else {
                     // ---- auto-reset (S:133-155): the whole warp lays out the food of each finished env in turn
@@ -531,28 +565,31 @@ __global__ void __launch_bounds__(FastCfg<F>::warps * 32, FastCfg<F>::minb) salp
                         const int src = __ffs((int)m) - 1;
                         const unsigned e_src = __shfl_sync(kFull, e, src);
                         const LayoutResult<float> Lr = layout_warp<float>(a, e_src, __shfl_sync(kFull, cur_food, src), lane);
-                        if (lane < Lr.n_food) reinterpret_cast<float2 *>(a.food)[(size_t)lane * N + e_src] = make_float2(Lr.x, Lr.y);
+                        if (lane < Lr.n_food) {
+                            reinterpret_cast<float2 *>(a.food)[(size_t)lane * N + e_src] = make_float2(Lr.x, Lr.y);
+                            // food `lane` of env `src`, as the offset from the reset position, straight into that env's
+                            // column of the scratch (slots >= n_food keep stale offsets; their mask bits are clear)
+                            sfood[lane * 32 + src] = make_float2(Lr.x - W * 0.5f, Lr.y - H * 0.5f);
+                        }
                         if (lane == src) {
                             cur_food = Lr.cur; n_food = Lr.n_food;
                             mask = Lr.n_food >= 32 ? 0xffffffffu : ((1u << Lr.n_food) - 1u);
                         }
                     }
                     __syncwarp();
+                    SALP_LAB_T(18);
                     if (done) {
                         px = W * 0.5f; py = H * 0.5f; vx = 0.f; vy = 0.f; angle = 0.f; omega = 0.f; nozzle = 0.f; wv_now = 0.f;
                         fsm = kPhaseRest | (kShapeReset << 18); q = 0;
                         steps_since_food = 0; food_collected = 0; ep_ret = 0.f; ep_len = 0;
                         obs6 = 1.0f; obs7 = 0.f;
                         hit = true;  // the bearing computed for the reward belongs to the finished episode
-#pragma unroll 1
-                        for (int f = 0; f < F; ++f) {  // offsets of the new foods from the new position (HBM: other lanes wrote them)
-                            const float2 nf = g_food[(size_t)f * N + e];
-                            sfood[f * 32 + lane] = make_float2(nf.x - px, nf.y - py);
-                        }
-                        reselect();
+                        reselect();  // the new foods' offsets are in the scratch already (written by the lanes that placed them)
                     }
+                    SALP_LAB_T(19);
                 }
             }  // pass
+            SALP_LAB_T(9);
             if constexpr (F > 1) {
                 // K > 1: the next substep expects positions in the buffer again; re-read them from HBM (L1/L2 hits;
                 // foods change only through the slow paths, which write HBM)
@@ -586,7 +623,11 @@ __global__ void __launch_bounds__(FastCfg<F>::warps * 32, FastCfg<F>::minb) salp
             st_hint_v4(reinterpret_cast<float4 *>(a.body) + (size_t)N + e, __float_as_uint(angle), __float_as_uint(omega), __float_as_uint(nozzle), __float_as_uint(wv_now), pol_state);
             st_hint_f32(g_epret + e, ep_ret, pol_state);
         }
+        SALP_LAB_T(10);
     }  // tiles
+#ifdef SALP_LAB_CLOCK
+    { const unsigned it = 0; SALP_LAB_T(11); }
+#endif
     if (blockIdx.x == 0 && threadIdx.x == 0 && a.stats) atomicAdd(a.stats + 7, (double)a.count * (double)a.K);
     if (elect_one_sync()) bulk_wait_read<0>();  // shared memory must stay allocated until the last bulk store has read it
 }
