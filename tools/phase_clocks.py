@@ -53,6 +53,13 @@ def main():
         torch.cuda.synchronize()
         assert lib.salp_lab_read_clocks(buf.ctypes.data, buf.size, 0) == 0
         rows.append(buf[:warps].copy())
+    lay = np.zeros(8, dtype=np.uint64)
+    lib.salp_lab_read_layout.argtypes = [C.c_void_p, C.c_int]
+    if lib.salp_lab_read_layout(lay.ctypes.data, 0) == 0 and lay[0] > 0:
+        c = float(lay[0])
+        print(f"layout_warp: {int(lay[0])} calls, {lay[5] / c:.2f} windows per call; cycles per call: total {lay[4] / c:.0f} = "
+              f"words+uniform {lay[1] / c:.0f} + placed-food checks {lay[2] / c:.0f} + conflict mask {lay[3] / c:.0f} + "
+              f"placements/rest {(float(lay[4]) - float(lay[1]) - float(lay[2]) - float(lay[3])) / c:.0f}")
     ghz = 1.0
     try:
         import pynvml

@@ -63,6 +63,15 @@ cudaError_t launch_step_fast_f32(const KernelArgs &a, int food_slots, cudaStream
 }  // namespace salp
 
 #ifdef SALP_LAB_CLOCK
+extern "C" int salp_lab_read_layout(unsigned long long *dst, int clear) {
+    cudaError_t e = cudaMemcpyFromSymbol(dst, salp::g_lab_lay, sizeof(salp::g_lab_lay));
+    if (e == cudaSuccess && clear) {
+        void *p = nullptr;
+        e = cudaGetSymbolAddress(&p, salp::g_lab_lay);
+        if (e == cudaSuccess) e = cudaMemset(p, 0, sizeof(salp::g_lab_lay));
+    }
+    return (int)e;
+}
 extern "C" int salp_lab_read_clocks(long long *dst, int n, int clear) {
     cudaError_t e = cudaMemcpyFromSymbol(dst, salp::g_lab_clk, (size_t)n * sizeof(long long));
     if (e == cudaSuccess && clear) {

@@ -381,15 +381,79 @@ __device__ __noinline__ ResetResult reset_slow(const KernelArgs &a, long long e,
     return ResetResult{cur, mask, n_food};
 }
 
+// reset_slow for the f32 build with at most ONE food (SalpLayout.food_slots == 1): no arrays, no sort, no divisions --
+// the reset observation in closed form with the host's reciprocals, as the step's own observation code computes it.
+// A finished episode is rare per env but present in some tile of every launch, and a lone lane runs dependent
+// instructions at ~5 cycles each: the length of this routine is the tail of a small slab's step.
+static __device__ __noinline__ ResetResult reset_single_f32(const KernelArgs &a, unsigned e, unsigned cur, float *obs_row) {
+    float2 *food = reinterpret_cast<float2 *>(a.food);
+    int n_food = a.num_food;
+    if (a.random_food_count) {  // random.randint(1, 1): _randbelow(1) still consumes words (k = 1 bit, until the bit is 0)
+        uint32_t r;
+        do { r = food_word(a, e, cur) >> 31; } while (r >= 1u);
+        n_food = 1;
+    }
+    const float xlo = (float)(kc::TANK_MARGIN + kc::FOOD_R), xhi = a.fW - (float)kc::TANK_MARGIN - (float)kc::FOOD_R;
+    const float ylo = xlo, yhi = a.fH - (float)kc::TANK_MARGIN - (float)kc::FOOD_R;
+    const float cx = a.fW * 0.5f, cy = a.fH * 0.5f;
+    float rx = 0.f, ry = 0.f, d = 0.f;
+    if (n_food > 0) {
+        float x = 0.f, y = 0.f;
+        int attempts = 0;
+        for (;;) {  // S:96-117: up to 100 candidates at least 80 px from the robot, then one unconditional draw
+            food_xy<float>(a, e, cur, xlo, xhi, ylo, yhi, x, y);
+            rx = x - cx; ry = y - cy;
+            d = sqrt_(rx * rx + ry * ry);
+            if (attempts >= 100 || !(d < (float)kc::MIN_FOOD_DIST)) break;
+            ++attempts;
+        }
+        food[e] = make_float2(x, y);
+    }
+    if (obs_row != nullptr) {
+        float4 ent = make_float4(0.f, 0.f, 1.f, 0.f);  // S:412 padding
+        float avg = 1.f;
+        if (n_food > 0) {
+            ent = make_float4(rx * a.f_inv_w, ry * a.f_inv_h, d * a.f_inv_diag, wrap_pi<float>(atan2_(ry, rx) - 0.f) * (float)(1.0 / kc::PI));
+            avg = d * a.f_inv_diag;
+        }
+        float4 *r4 = reinterpret_cast<float4 *>(obs_row);
+        r4[0] = make_float4(cx * a.f_inv_w, cy * a.f_inv_h, 0.f, 0.f);
+        r4[1] = make_float4(0.f, 0.f, 1.0f, 0.f);
+        r4[2] = make_float4(0.f, 0.f, ent.x, ent.y);
+        r4[3] = make_float4(ent.z, ent.w, 0.f, 0.f);
+        r4[4] = make_float4(1.f, 0.f, 0.f, 0.f);
+        r4[5] = make_float4(1.f, 0.f, fminf((float)n_food * 0.1f, 1.0f), avg);
+    }
+    return ResetResult{cur, n_food > 0 ? 1u : 0u, n_food};
+}
+
 // Warp-cooperative S:92-131 _generate_food_positions (+ S:144-148 food count) for ONE env, run by all
-// 32 lanes of a converged warp (e, cur warp-uniform).  The reference draws candidates one at a time and
-// tests each against the tank centre and the foods placed so far; here lane L materialises candidate L
-// of a 32-candidate window of the env's `random` stream (4 words each) and keeps a running verdict
-// `ok` that is updated once per newly placed food, so placing a food is a ballot + ffs instead of a
-// serial rejection loop with dependent HBM reads.  Candidate order, the 100-attempt cap and its
-// unconditional 101st draw, and the words consumed are exactly the reference's.
+// 32 lanes of a converged warp (e, cur warp-uniform).
+//
+// The reference draws candidates one at a time and keeps a candidate iff it is >= 80 px from the tank centre and
+// from every food kept so far: a greedy scan in stream order.  Here lane L materialises candidate L of a
+// 32-candidate window of the env's `random` stream (4 words each), tests it against the centre and the foods kept
+// from earlier windows, and computes once which other candidates of the window lie within 80 px of it (31
+// independent distance tests).  Which candidates the greedy scan keeps is then decided for the whole window in a
+// few rounds of two ballots: an undecided candidate with no undecided conflicting predecessor is kept, and every
+// undecided successor in conflict with a kept one is dropped -- the same set as the serial scan, because its
+// decision for a candidate depends only on earlier candidates.  Lane i then fetches the (i+1)-th kept candidate.
+// (A lone warp runs dependent instructions at ~5-10 cycles each; the serial scan was ~45 dependent instructions
+// per food, 3 300 cycles for twelve, and the slowest reset sets the time of a small slab.)
+// The 100-attempt cap with its unconditional 101st draw (S:100-117) can only bind for the first food sought in a
+// window (the rejections carried over from earlier windows); that food alone takes the serial path.  Candidate
+// order, distance arithmetic and the words consumed are exactly the reference's.
 // Returns food j's position in lane j (j < n_food), plus the new cursor and n_food in every lane.
 template <typename T> struct LayoutResult { T x, y; unsigned cur; int n_food; };
+
+#ifdef SALP_LAB_CLOCK
+static __device__ unsigned long long g_lab_lay[8];  // [0] calls; cycles: [1] window words+uniform [2] kept-food checks [3] conflict mask [4] total; [5] windows
+#define SALP_LAY_T(v) const long long v = clock64()
+#define SALP_LAY_ADD(i, d) do { if (lane == 0) atomicAdd(&g_lab_lay[i], (unsigned long long)(d)); } while (0)
+#else
+#define SALP_LAY_T(v) do { } while (0)
+#define SALP_LAY_ADD(i, d) do { } while (0)
+#endif
 
 template <typename T>
 __device__ __noinline__ LayoutResult<T> layout_warp(const KernelArgs &a, unsigned e, unsigned cur, int lane) {
@@ -407,54 +471,93 @@ __device__ __noinline__ LayoutResult<T> layout_warp(const KernelArgs &a, unsigne
     const T xlo = (T)(kc::TANK_MARGIN + kc::FOOD_R), xhi = (T)a.W - (T)kc::TANK_MARGIN - (T)kc::FOOD_R;
     const T ylo = xlo, yhi = (T)a.H - (T)kc::TANK_MARGIN - (T)kc::FOOD_R;
     const T cx = (T)a.W / 2, cy = (T)a.H / 2;
-    T myx = 0, myy = 0;       // position of food `lane`
-    T candx = 0, candy = 0;   // candidate `lane` of the current window
-    bool ok = false;          // candidate is >= 80 px from the centre and from every food placed so far
-    int ptr = 32;             // next untested candidate of the window (32 = window exhausted / not loaded)
-    unsigned base = cur;      // stream position of candidate 0 of the next window
-    for (int i = 0; i < n_food; ++i) {
-        int attempts = 0, chosen;
-        for (;;) {
-            if (ptr == 32) {
-                const unsigned w = base + 4u * (unsigned)lane;
-                uint32_t w0, w1, w2, w3;
-                if (a.rng_mode) {
-                    if ((w & 3u) == 0u) {  // a candidate's four words are one Philox block unless randint moved the cursor off 4
-                        const uint4 r = philox_block(a, e, 0u, w);
-                        w0 = r.x; w1 = r.y; w2 = r.z; w3 = r.w;
-                    } else {
-                        unsigned c2 = w;
-                        w0 = food_word(a, e, c2); w1 = food_word(a, e, c2); w2 = food_word(a, e, c2); w3 = food_word(a, e, c2);
-                    }
-                } else {
-                    w0 = words[w & a.food_len_mask]; w1 = words[(w + 1) & a.food_len_mask];
-                    w2 = words[(w + 2) & a.food_len_mask]; w3 = words[(w + 3) & a.food_len_mask];
-                }
-                candx = xlo + (xhi - xlo) * (T)res53(w0, w1);  // random.uniform: a + (b-a)*random()
-                candy = ylo + (yhi - ylo) * (T)res53(w2, w3);
-                const T rx = candx - cx, ry = candy - cy;
-                ok = !(sqrt_(rx * rx + ry * ry) < (T)kc::MIN_FOOD_DIST);
-                for (int j = 0; j < i; ++j) {
-                    const T dx = candx - __shfl_sync(kFull, myx, j), dy = candy - __shfl_sync(kFull, myy, j);
-                    if (sqrt_(dx * dx + dy * dy) < (T)kc::MIN_FOOD_DIST) ok = false;
-                }
-                base += 128u;
-                ptr = 0;
+    const unsigned below = (1u << lane) - 1u;  // the candidates before `lane`
+    T myx = 0, myy = 0;    // position of food `lane`
+    int placed = 0;        // foods kept so far
+    int attempts = 0;      // candidates rejected so far for food `placed` (S:100 caps them at 100)
+    int ptr = 0;           // next untested candidate of the current window
+    unsigned base = cur;   // stream position of candidate 0 of the next window
+    SALP_LAY_T(t_begin);
+    SALP_LAY_ADD(0, 1);
+    while (placed < n_food) {
+        // ---- a window of 32 candidates
+        SALP_LAY_T(t0);
+        const unsigned w = base + 4u * (unsigned)lane;
+        uint32_t w0, w1, w2, w3;
+        if (a.rng_mode) {
+            if ((w & 3u) == 0u) {  // a candidate's four words are one Philox block unless randint moved the cursor off 4
+                const uint4 r = philox_block(a, e, 0u, w);
+                w0 = r.x; w1 = r.y; w2 = r.z; w3 = r.w;
+            } else {
+                unsigned c2 = w;
+                w0 = food_word(a, e, c2); w1 = food_word(a, e, c2); w2 = food_word(a, e, c2); w3 = food_word(a, e, c2);
             }
-            const unsigned m = __ballot_sync(kFull, ok) & (kFull << ptr);
+        } else {
+            w0 = words[w & a.food_len_mask]; w1 = words[(w + 1) & a.food_len_mask];
+            w2 = words[(w + 2) & a.food_len_mask]; w3 = words[(w + 3) & a.food_len_mask];
+        }
+        const T candx = xlo + (xhi - xlo) * (T)res53(w0, w1);  // random.uniform: a + (b-a)*random()
+        const T candy = ylo + (yhi - ylo) * (T)res53(w2, w3);
+        const T rx = candx - cx, ry = candy - cy;
+        bool base_ok = !(sqrt_(rx * rx + ry * ry) < (T)kc::MIN_FOOD_DIST);
+        SALP_LAY_T(t1);
+        for (int j = 0; j < placed; ++j) {  // foods kept from earlier windows
+            const T dx = candx - __shfl_sync(kFull, myx, j), dy = candy - __shfl_sync(kFull, myy, j);
+            if (sqrt_(dx * dx + dy * dy) < (T)kc::MIN_FOOD_DIST) base_ok = false;
+        }
+        SALP_LAY_T(t2);
+        unsigned conf = 0u;  // bit j: candidate j of this window is within 80 px of candidate `lane`
+#pragma unroll 8
+        for (int j = 0; j < 32; ++j) {
+            const T dx = candx - __shfl_sync(kFull, candx, j), dy = candy - __shfl_sync(kFull, candy, j);
+            if (sqrt_(dx * dx + dy * dy) < (T)kc::MIN_FOOD_DIST) conf |= 1u << j;
+        }
+        conf &= ~(1u << lane);
+        const unsigned earlier = conf & below;
+        unsigned ok = __ballot_sync(kFull, base_ok);  // candidates that are still valid (warp-uniform)
+        SALP_LAY_T(t3);
+        SALP_LAY_ADD(1, t1 - t0); SALP_LAY_ADD(2, t2 - t1); SALP_LAY_ADD(3, t3 - t2); SALP_LAY_ADD(5, 1);
+        base += 128u;
+        ptr = 0;
+        // ---- serial path, one food at a time, while the 100-attempt cap could bind inside this window
+        while (placed < n_food && ptr < 32 && attempts > 68 + ptr) {
+            const unsigned m = ok & (kFull << ptr);
             const int first = m ? __ffs((int)m) - 1 : 32;
             const int limit = ptr + (100 - attempts);  // after 100 rejects the next draw is taken unconditionally
             const int c = first < limit ? first : limit;
-            if (c < 32) { chosen = c; break; }
-            attempts += 32 - ptr;
-            ptr = 32;
+            if (c >= 32) { attempts += 32 - ptr; ptr = 32; break; }
+            const T x = __shfl_sync(kFull, candx, c), y = __shfl_sync(kFull, candy, c);
+            if (lane == placed) { myx = x; myy = y; }
+            ok &= ~__shfl_sync(kFull, conf, c);  // candidates within 80 px of the new food are out
+            ptr = c + 1;
+            attempts = 0;
+            ++placed;
         }
-        const T x = __shfl_sync(kFull, candx, chosen), y = __shfl_sync(kFull, candy, chosen);
-        if (lane == i) { myx = x; myy = y; }
-        ptr = chosen + 1;
-        const T dx = candx - x, dy = candy - y;
-        if (sqrt_(dx * dx + dy * dy) < (T)kc::MIN_FOOD_DIST) ok = false;
+        // ---- the rest of the window at once: the cap cannot bind (attempts <= 68 + ptr, and 0 after a food is kept)
+        if (placed < n_food && ptr < 32) {
+            unsigned und = ok & (kFull << ptr);  // undecided candidates
+            unsigned kept = 0u;
+            while (und != 0u) {
+                const bool u = (und >> lane) & 1u;
+                const unsigned s = __ballot_sync(kFull, u && (earlier & und) == 0u);   // no undecided conflicting predecessor: kept
+                const unsigned d = __ballot_sync(kFull, u && (earlier & s) != 0u);     // in conflict with a kept predecessor: dropped
+                kept |= s;
+                und &= ~(s | d);
+            }
+            const int n_kept = __popc(kept);
+            const int take = n_kept < n_food - placed ? n_kept : n_food - placed;
+            const int r = lane - placed;  // food `lane` is the (r + 1)-th kept candidate
+            const bool get = r >= 0 && r < take;
+            const unsigned src = get ? __fns(kept, 0u, r + 1) : 0u;
+            const T sx = __shfl_sync(kFull, candx, (int)src), sy = __shfl_sync(kFull, candy, (int)src);
+            if (get) { myx = sx; myy = sy; }
+            if (take > 0) { ptr = (int)__fns(kept, 0u, take) + 1; attempts = 0; }
+            placed += take;
+            if (placed < n_food) { attempts += 32 - ptr; ptr = 32; }  // window exhausted, the remaining candidates are rejects
+        }
     }
+    SALP_LAY_T(t_end);
+    SALP_LAY_ADD(4, t_end - t_begin);
     if (n_food > 0) cur = base - 128u + 4u * (unsigned)ptr;
     return LayoutResult<T>{myx, myy, cur, n_food};
 }

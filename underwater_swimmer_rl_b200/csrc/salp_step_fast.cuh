@@ -517,27 +517,30 @@ __global__ void __launch_bounds__(FastCfg<F>::warps * 32, FastCfg<F>::minb) salp
                 SALP_LAB_T(8);
                 if (done_mask == 0u) break;
                 SALP_LAB_V(12, __popc(done_mask));
+#ifdef SALP_LAB_NO_STATS
+                if (false) {
+#else
                 if (a.stats) {
-                    const double r = warp_sum(done ? (double)ep_ret : 0.0);
-                    const double l = warp_sum(done ? (double)ep_len : 0.0);
-                    const double fc = warp_sum(done ? (double)food_collected : 0.0);
-                    const unsigned coll_mask = __ballot_sync(kFull, done && collision);
-                    const unsigned trunc_mask = __ballot_sync(kFull, done && truncated);
-                    const unsigned bad_mask = __ballot_sync(kFull, done && !(isfinite(px) && isfinite(py)));
-                    if (lane == 0) {
-                        atomicAdd(a.stats + 0, (double)__popc(done_mask));
-                        atomicAdd(a.stats + 1, r);
-                        atomicAdd(a.stats + 2, l);
-                        atomicAdd(a.stats + 3, fc);
-                        if (coll_mask) atomicAdd(a.stats + 4, (double)__popc(coll_mask));
-                        if (trunc_mask) atomicAdd(a.stats + 5, (double)__popc(trunc_mask));
-                        if (bad_mask) atomicAdd(a.stats + 6, (double)__popc(bad_mask));
+#endif
+                    // ---- episode statistics: the (rare) finished lanes add their own episode -- reductions without a
+                    //      return value, nothing on the warp's dependent chain (a shuffle tree of doubles was ~1 300 cycles)
+                    if (done) {
+                        atomicAdd(a.stats + 0, 1.0);
+                        atomicAdd(a.stats + 1, (double)ep_ret);
+                        atomicAdd(a.stats + 2, (double)ep_len);
+                        atomicAdd(a.stats + 3, (double)food_collected);
+                        if (collision) atomicAdd(a.stats + 4, 1.0);
+                        if (truncated) atomicAdd(a.stats + 5, 1.0);
+                        if (!(isfinite(px) && isfinite(py))) atomicAdd(a.stats + 6, 1.0);
                     }
                 }
                 SALP_LAB_T(16);
                 if (done && a.final_info)
                     reinterpret_cast<float4 *>(a.final_info)[(size_t)k * N + e] =
                         make_float4(ep_ret, (float)ep_len, (float)food_collected, (float)steps_since_food);
+#ifdef SALP_LAB_NO_RESET
+                break;
+#endif
                 if (!a.autoreset) break;
                 if (done && a.final_obs) {  // terminal observation (gymnasium "final_observation")
                     float4 *dst = reinterpret_cast<float4 *>(a.final_obs + ((size_t)k * N + e) * OBS);
@@ -550,7 +553,7 @@ __global__ void __launch_bounds__(FastCfg<F>::warps * 32, FastCfg<F>::minb) salp
                     // warp-cooperative layout below, which needs the whole warp's state live across the call: 72-register
                     // budget -> spills in the hot path, 41.8 -> 46.2 us at 1 M envs; with 80 registers no gain at any size.)
                     if (done) {
-                        const ResetResult rr = reset_slow<float>(a, e, cur_food, row);
+                        const ResetResult rr = F == 1 ? reset_single_f32(a, e, cur_food, row) : reset_slow<float>(a, e, cur_food, row);
                         cur_food = rr.cur; mask = rr.mask; n_food = rr.n_food;
                         px = W * 0.5f; py = H * 0.5f; vx = 0.f; vy = 0.f; angle = 0.f; omega = 0.f; nozzle = 0.f; wv_now = 0.f;
                         fsm = kPhaseRest | (kShapeReset << 18); q = 0;
@@ -561,7 +564,11 @@ __global__ void __launch_bounds__(FastCfg<F>::warps * 32, FastCfg<F>::minb) salp
                     break;
                 } else {
                     // ---- auto-reset (S:133-155): the whole warp lays out the food of each finished env in turn
+#ifdef SALP_LAB_NO_LAYOUT
+                    for (unsigned m = 0u; m != 0u; m &= m - 1u) {
+#else
                     for (unsigned m = done_mask; m != 0u; m &= m - 1u) {
+#endif
                         const int src = __ffs((int)m) - 1;
                         const unsigned e_src = __shfl_sync(kFull, e, src);
                         const LayoutResult<float> Lr = layout_warp<float>(a, e_src, __shfl_sync(kFull, cur_food, src), lane);
@@ -571,9 +578,23 @@ __global__ void __launch_bounds__(FastCfg<F>::warps * 32, FastCfg<F>::minb) salp
                             // column of the scratch (slots >= n_food keep stale offsets; their mask bits are clear)
                             sfood[lane * 32 + src] = make_float2(Lr.x - W * 0.5f, Lr.y - H * 0.5f);
                         }
+                        // distances and selection keys of the new foods, one per lane: the MU nearest by MU warp-wide minima,
+                        // the distance sum in slot order (the order `reselect` adds them in)
+                        const float ox = Lr.x - W * 0.5f, oy = Lr.y - H * 0.5f;
+                        const float dj = sqrt_(ox * ox + oy * oy);
+                        unsigned kj = lane < Lr.n_food ? make_key(dj, lane) : (lane < F ? (~kSlotMask | (unsigned)lane) : 0xffffffffu);
+                        unsigned kmin[MU];
+#pragma unroll
+                        for (int i = 0; i < MU; ++i) { kmin[i] = __reduce_min_sync(kFull, kj); if (kj == kmin[i]) kj = 0xffffffffu; }
+                        float ds = 0.f;
+#pragma unroll
+                        for (int f = 0; f < F; ++f) { const float df = __shfl_sync(kFull, dj, f); if (f < Lr.n_food) ds += df; }
                         if (lane == src) {
                             cur_food = Lr.cur; n_food = Lr.n_food;
                             mask = Lr.n_food >= 32 ? 0xffffffffu : ((1u << Lr.n_food) - 1u);
+#pragma unroll
+                            for (int i = 0; i < MU; ++i) key[i] = kmin[i];
+                            dist_sum = ds;
                         }
                     }
                     __syncwarp();
@@ -584,7 +605,6 @@ __global__ void __launch_bounds__(FastCfg<F>::warps * 32, FastCfg<F>::minb) salp
                         steps_since_food = 0; food_collected = 0; ep_ret = 0.f; ep_len = 0;
                         obs6 = 1.0f; obs7 = 0.f;
                         hit = true;  // the bearing computed for the reward belongs to the finished episode
-                        reselect();  // the new foods' offsets are in the scratch already (written by the lanes that placed them)
                     }
                     SALP_LAB_T(19);
                 }
