@@ -650,6 +650,21 @@ def main():
     e2e_value = world * N * args.e2e_steps / e2e_max
     h2d = N * env.act_dim * rb
     d2h = N * (env.obs_dim * 4 + rb + 2)
+    # the ceiling the box puts on that call: every rank copies its observation rows device -> pinned host memory at the same
+    # time, no kernel (what the PCIe links / switches and the host memory sustain with `world` GPUs copying together)
+    obs_dev = env.obs[0]
+    for _ in range(2):
+        o_h.copy_(obs_dev, non_blocking=True)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    t0 = time.perf_counter()
+    for _ in range(10):
+        o_h.copy_(obs_dev, non_blocking=True)
+    torch.cuda.synchronize()
+    copy_s = time.perf_counter() - t0
+    copy_max, _ = rank_max_min(torch, dist, dev, copy_s, world)
+    d2h_copy_only_gbs = 10 * obs_dev.numel() * 4 / copy_max / 1e9
 
     stats = env.episode_stats()  # NCCL all-reduce (SUM) of the 8-double stats vector when world > 1
     obs_dim, act_dim = env.obs_dim, env.act_dim
@@ -721,7 +736,10 @@ def main():
             "per_rank_ms_per_step": {"min": ms_min / args.steps, "max": ms_max / args.steps},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "steps": args.e2e_steps, "api": "SalpVectorEnv.step_host -> salp_step_host (pinned host buffers)",
-                    "d2h_gbs_per_gpu": d2h * args.e2e_steps / e2e_max / 1e9, "per_rank_s": {"min": e2e_min, "max": e2e_max}},
+                    "d2h_gbs_per_gpu": d2h * args.e2e_steps / e2e_max / 1e9, "per_rank_s": {"min": e2e_min, "max": e2e_max},
+                    "d2h_copy_only_gbs_per_gpu": d2h_copy_only_gbs,
+                    "d2h_copy_only_note": "all %d ranks copying their observation rows to pinned host memory at once, no kernel: the "
+                                          "box's ceiling for this call (slowest rank)" % world},
             "gpu_launches": launches, "clocks": clocks,
             "episode_stats": {k: stats[k] for k in ("episodes", "mean_return", "mean_length", "collisions", "truncations", "env_steps")},
         }

@@ -72,3 +72,23 @@ def test_wall_touch_bits_are_the_reference_rounding(salp_lib):
         assert ((t["touch"] & 2) != 0).tolist() == right.tolist()
         assert ((t["touch"] & 4) != 0).tolist() == bottom.tolist()
         assert 0 < lo.sum() < 274  # both outcomes occur (~5 % of the touches bounce and survive)
+
+
+def test_sqrt_free_min_food_distance_threshold():
+    """csrc/salp_step.cuh closer_than_min_food_dist<double>: sqrt(x) < 80 == x < 6400 - 2^-40 for every double (correctly rounded
+    sqrt), so the fp64 build's pair tests of the food layout need no square root and keep the reference's verdicts."""
+    t = float.fromhex("0x1.8ffffffffffffp+12")
+    assert t == np.nextafter(6400.0, 0.0)
+    x = np.float64(6400.0)
+    near = [x]
+    for _ in range(64):
+        x = np.nextafter(x, 0.0)
+        near.append(x)
+    x = np.float64(6400.0)
+    for _ in range(64):
+        x = np.nextafter(x, np.inf)
+        near.append(x)
+    rng = np.random.default_rng(7)
+    v = np.concatenate([np.array(near), rng.uniform(0.0, 1.0e6, 1_000_000), 6400.0 + rng.uniform(-1e-8, 1e-8, 1_000_000),
+                        np.array([0.0, 5e-324, 1e-300, 1e300])])
+    assert ((np.sqrt(v) < 80.0) == (v < t)).all()

@@ -22,7 +22,7 @@ import sys
 from concurrent.futures import ThreadPoolExecutor
 
 PKG = os.path.dirname(os.path.abspath(__file__))
-CSRC = os.path.join(PKG, "csrc")
+CSRC = os.environ.get("SALP_CSRC") or os.path.join(PKG, "csrc")  # SALP_CSRC: developer A/B builds from another source tree
 # developer A/B builds: SALP_LIB_TAG=x builds libsalp_b200_x.so from objects in _build_x/ (and _capi loads that one)
 TAG = os.environ.get("SALP_LIB_TAG", "")
 OBJ = os.path.join(PKG, "_build" + ("_" + TAG if TAG else ""))

@@ -21,6 +21,7 @@
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
 
 #include "../../include/salp_b200.h"
 
@@ -298,6 +299,13 @@ __global__ void __launch_bounds__(kThreads, 1) salp_actor_kernel(const __grid_co
     };
     const long long n_tiles = (a.n + kTileM - 1) / kTileM;
     long long tile = blockIdx.x;
+    // Programmatic dependent launch: everything above reads parameter data only (weights, biases -- never written by the
+    // kernels that trigger early, the env step kernels), so a CTA may do it while the previous kernel of the stream -- the
+    // env step whose observations it is about to read -- is still draining.  Observations, noise, the RNG state and the
+    // action buffer are touched only after the wait.  The kernel after this one (an env step: small CTAs) may start its own
+    // prologue as soon as this CTA's resources free up.
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
     // ---- prologue: first observation tile -> A1, GEMM 1 of it in flight, second tile's obs in registers
     store_obs_chunk(load_obs_chunk(a, tile * kTileM + lrow, lchunk));
     fence_async_smem();  // weights and A1 were written with generic-proxy stores, the MMA reads through the async proxy
@@ -678,8 +686,14 @@ extern "C" int salp_actor_forward(const SalpActorForward *p, void *cuda_stream) 
     else if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && cached) sm_count[dev] = sms;
     const long long n_tiles = (a.n + kTileM - 1) / kTileM;
     const unsigned grid = (unsigned)(n_tiles < sms ? n_tiles : sms);  // persistent: one CTA per SM
-    kern<<<grid, kThreads, kSmemBytes, (cudaStream_t)cuda_stream>>>(a);
-    cudaError_t e = cudaGetLastError();
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(kThreads); cfg.dynamicSmemBytes = kSmemBytes; cfg.stream = (cudaStream_t)cuda_stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = getenv("SALP_NO_PDL") ? 0 : 1;
+    cudaError_t e = cudaLaunchKernelEx(&cfg, kern, a);
+    if (e == cudaSuccess) e = cudaGetLastError();
     if (e != cudaSuccess) return salp::set_error(SALP_ECUDA, cudaGetErrorString(e));
     return SALP_OK;
 }

@@ -381,6 +381,17 @@ __device__ __noinline__ ResetResult reset_slow(const KernelArgs &a, long long e,
     return ResetResult{cur, mask, n_food};
 }
 
+// "sqrt(d2) < 80" (S:113, S:252: distance below MIN_FOOD_DIST) without the square root, for the many pair tests of
+// layout_warp.  In IEEE doubles with a correctly rounded sqrt (CUDA's sqrt.rn.f64, glibc's sqrt in the oracle, CPython's
+// math.sqrt) sqrt(x) rounds to 80 exactly for x = 6400 - 2^-40, the double just below 6400, and below 80 for every smaller x,
+// so the test is x < 6400 - 2^-40 -- the same verdict for every double (tests/test_forced_cycle.py checks the neighbourhood
+// with numpy; the fp64 parity tests check the layouts bit for bit).  The f32 build keeps its approximate square root.
+template <typename T> __device__ __forceinline__ bool closer_than_min_food_dist(T d2) {
+    static_assert(kc::MIN_FOOD_DIST == 80.0, "the threshold below is sqrt_rn's preimage of [0, 80)");
+    if constexpr (is_f64<T>::value) return d2 < 0x1.8ffffffffffffp+12;
+    else return sqrt_(d2) < (T)kc::MIN_FOOD_DIST;
+}
+
 // reset_slow for the f32 build with at most ONE food (SalpLayout.food_slots == 1): no arrays, no sort, no divisions --
 // the reset observation in closed form with the host's reciprocals, as the step's own observation code computes it.
 // A finished episode is rare per env but present in some tile of every launch, and a lone lane runs dependent
@@ -510,7 +521,7 @@ __device__ __noinline__ LayoutResult<T> layout_warp(const KernelArgs &a, unsigne
 #pragma unroll 8
         for (int j = 0; j < 32; ++j) {
             const T dx = candx - __shfl_sync(kFull, candx, j), dy = candy - __shfl_sync(kFull, candy, j);
-            if (sqrt_(dx * dx + dy * dy) < (T)kc::MIN_FOOD_DIST) conf |= 1u << j;
+            if (closer_than_min_food_dist<T>(dx * dx + dy * dy)) conf |= 1u << j;
         }
         conf &= ~(1u << lane);
         const unsigned earlier = conf & below;
