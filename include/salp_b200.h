@@ -38,7 +38,8 @@ enum { SALP_OK = 0, SALP_EINVAL = -1, SALP_ECUDA = -2, SALP_EUNBOUND = -3, SALP_
 
 /* arithmetic type of the integrator ("dtype" of the build, not a precision claim) */
 enum { SALP_F32 = 0, /* throughput build: float state/actions/reward                      */
-       SALP_F64 = 1  /* validation build: double, reference operation order, no FMA fusion */ };
+       SALP_F64 = 1  /* validation build: double, reference operation order, no FMA fusion (the float32 observation
+                        columns are scaled with reciprocals: <= 1 ulp(double) before the cast)              */ };
 
 enum { SALP_MAX_FOOD = 32, SALP_MAX_OBSERVED_FOOD = 8 };
 
