@@ -418,6 +418,16 @@ int salp_cycle_reset(const SalpCycleParams *p, const SalpCycleBuffers *b, const 
 /* step: one breathing cycle per env for actions real [n][3]. */
 int salp_cycle_step(const SalpCycleParams *p, const SalpCycleBuffers *b, const void *actions, void *cuda_stream);
 
+/*
+ * Replaces the per-episode bookkeeping of the reference's loops -- score, steps and food of every finished episode
+ * (src/salp/training/continuous_trainer.py:287-327, evaluation :343-372) -- in aggregate: copies the eight doubles the
+ * step kernels accumulate in SalpBuffers.stats (episodes, sum return, sum length, sum food, collisions, truncations,
+ * non-finite lanes, env-steps) to HOST memory `out8_host`, after the work already queued on `cuda_stream`, and returns
+ * when they are there (it synchronises that stream; the only entry point besides the *_host steps that does).
+ * reset != 0 zeroes the device vector afterwards.  SALP_EUNBOUND when no stats buffer is bound.  
+ */
+int salp_stats(SalpHandle *h, double *out8_host, int reset, void *cuda_stream);
+
 /* Number of kernels this library has launched on behalf of `h` (bench "gpu_launches"). */
 int64_t salp_launch_count(const SalpHandle *h);
 

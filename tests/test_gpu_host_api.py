@@ -148,3 +148,34 @@ def test_full_size_properties_1m_envs(salp_lib):
     env.reset(mask=mask)
     assert torch.equal(env.body[:, ~mask], before[:, ~mask])
     assert (env.robot_pos[mask] == torch.tensor([400.0, 300.0], device="cuda")).all() and (env.episode_length[mask] == 0).all()
+
+
+def test_salp_stats_entry_point_matches_the_bound_vector(salp_lib):
+    """salp_stats (SURVEY 8(b)): the eight accumulators copied to host memory through the C ABI equal the bound device vector;
+    reset zeroes it; a handle without a stats buffer is refused."""
+    import ctypes as C
+    from underwater_swimmer_rl_b200 import SalpVectorEnv, _capi
+    env = SalpVectorEnv(4096, device="cuda:0", dtype="float32", rng="philox", max_steps_without_food=40, **{
+        k: v for k, v in CONFIGS["single_food"].items() if k != "max_steps_without_food"})
+    env.reset()
+    g = torch.Generator(device="cuda")
+    g.manual_seed(3)
+    for _ in range(120):
+        env.step(torch.rand(4096, 1, device="cuda", generator=g) * 2 - 1)
+    want = env.stats.cpu().numpy().copy()
+    got = env.stats_host()
+    assert want[0] > 0 and want[7] == 4096 * 120            # episodes ended (timeouts after 40 steps); env-steps counted
+    assert list(got.values()) == want.tolist()
+    again = env.stats_host(reset=True)
+    assert list(again.values()) == want.tolist()
+    assert float(env.stats.abs().sum()) == 0.0
+    env.step(torch.zeros(4096, 1, device="cuda"))
+    assert env.stats_host()["env_steps"] == 4096.0
+    # no stats buffer bound -> SALP_EUNBOUND
+    env._bind(omit=("stats",))
+    out = (C.c_double * 8)()
+    assert salp_lib.salp_stats(env._handle, out, 0, None) == _capi.SALP_EUNBOUND
+    assert "stats" in salp_lib.salp_last_error().decode()
+    env.step(torch.zeros(4096, 1, device="cuda"))     # stepping without a stats buffer is fine
+    env._bind()
+    assert env.stats_host()["env_steps"] == 4096.0   # the unbound step was not counted

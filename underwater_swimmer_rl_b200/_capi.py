@@ -21,7 +21,7 @@ EV_TERMINATED, EV_TRUNCATED, EV_COLLISION, EV_FOOD = 1, 2, 4, 8
 # every symbol include/salp_b200.h declares (tests/test_capi_symbols.py parses the header too)
 EXPORTED_SYMBOLS = (
     "salp_abi_version", "salp_last_error", "salp_query_layout", "salp_create", "salp_destroy", "salp_bind",
-    "salp_reset", "salp_refresh_rng", "salp_observe", "salp_set_num_food_items", "salp_set_rng_seed", "salp_forced_cycle", "salp_step", "salp_step_slot", "salp_step_host", "salp_step_host_noalloc", "salp_fill_rng_words", "salp_launch_count", "salp_replay_append", "salp_actor_forward",
+    "salp_reset", "salp_refresh_rng", "salp_observe", "salp_set_num_food_items", "salp_set_rng_seed", "salp_forced_cycle", "salp_step", "salp_step_slot", "salp_step_host", "salp_step_host_noalloc", "salp_fill_rng_words", "salp_launch_count", "salp_stats", "salp_replay_append", "salp_actor_forward",
     "salp_cycle_reset", "salp_cycle_step",
 )
 SALP_CYCLE_AUTORESET = 1
@@ -127,6 +127,7 @@ def load():
     L.salp_step_host_noalloc.argtypes = [C.c_void_p] + [C.c_void_p] * 6
     L.salp_fill_rng_words.argtypes = [C.c_void_p, C.c_int64, C.c_int64, C.c_uint64, C.c_int64, C.c_int, C.c_int]
     L.salp_launch_count.argtypes = [C.c_void_p]
+    L.salp_stats.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
     L.salp_actor_forward.argtypes = [C.POINTER(SalpActorForward), C.c_void_p]
     L.salp_replay_append.argtypes = [C.POINTER(SalpReplayAppend), C.c_void_p]
     L.salp_launch_count.restype = C.c_int64

@@ -463,6 +463,18 @@ int salp_step_host(SalpHandle *h, void *actions_staging, const void *actions_hos
 
 int64_t salp_launch_count(const SalpHandle *h) { return h ? h->launches : 0; }
 
+int salp_stats(SalpHandle *h, double *out8_host, int reset, void *stream) {
+    if (!h || !out8_host) return fail(SALP_EINVAL, "null argument");
+    if (!h->bound) return fail(SALP_EUNBOUND, "salp_bind has not been called");
+    if (!h->buf.stats) return fail(SALP_EUNBOUND, "no stats buffer is bound (SalpBuffers.stats is NULL)");
+    SALP_CUDA(cudaSetDevice(h->device));
+    cudaStream_t s = (cudaStream_t)stream;
+    SALP_CUDA(cudaMemcpyAsync(out8_host, h->buf.stats, salp::kStatsLen * sizeof(double), cudaMemcpyDeviceToHost, s));
+    if (reset) SALP_CUDA(cudaMemsetAsync(h->buf.stats, 0, salp::kStatsLen * sizeof(double), s));
+    SALP_CUDA(cudaStreamSynchronize(s));
+    return SALP_OK;
+}
+
 // ---------------------------------------------------------------------------------------------
 // MT19937 word streams (host).  Reproduces CPython's random.seed(int) and numpy's legacy
 // np.random.seed(int) so the tables hold exactly the words the reference would consume.

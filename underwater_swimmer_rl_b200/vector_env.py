@@ -183,11 +183,12 @@ class SalpVectorEnv(VectorEnv):
         self.jit_words = torch.from_numpy(jw.view(np.int32)).to(self.device)
         self._bind()
 
-    def _bind(self) -> None:
+    def _bind(self, omit=()) -> None:
+        """(Re-)attach the tensors to the handle; ``omit`` names optional buffers to leave unbound (NULL) -- tests."""
         b = _capi.SalpBuffers()
         for name in ("body", "ctrl", "ep_return", "food", "obs", "reward", "terminated", "truncated",
                      "events", "final_obs", "final_info", "stats", "food_words", "jit_words"):
-            setattr(b, name, getattr(self, name).data_ptr())
+            setattr(b, name, None if name in omit else getattr(self, name).data_ptr())
         b.table_rows, b.food_len, b.jit_len = self.table_rows, self.food_table_len, self.jitter_table_len
         b.max_substeps = self.max_substeps
         _capi.check(self._L.salp_bind(self._handle, C.byref(b)))
@@ -378,6 +379,16 @@ class SalpVectorEnv(VectorEnv):
         if reset:
             self.stats.zero_()
         return out
+
+    def stats_host(self, reset: bool = False) -> dict:
+        """The same eight accumulators through the C ABI (salp_stats): copied to host memory after the work queued on the
+        current stream; this rank only (episode_stats all-reduces over ranks)."""
+        import numpy as np
+        from .sharding import STATS_KEYS
+        out = np.zeros(8, dtype=np.float64)
+        with torch.cuda.device(self.device):
+            _capi.check(self._L.salp_stats(self._handle, out.ctypes.data, 1 if reset else 0, self._stream()))
+        return dict(zip(STATS_KEYS, out.tolist()))
 
     # ------------------------------------------------------------------ state access (tensor views)
     # The reference's callers read and poke these attributes directly
