@@ -61,7 +61,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
     jobs = [
         (os.path.join(OBJ, "salp_kernels_f32.o"), [NVCC, "-c", kern, "-DSALP_BUILD_F64=0"] + COMMON + vflag + step_defs, [kern] + hdrs),
         (os.path.join(OBJ, "salp_kernels_fast.o"), [NVCC, "-c", fast] + COMMON + vflag + step_defs, [fast] + hdrs),
-        (os.path.join(OBJ, "salp_kernels_f64.o"), [NVCC, "-c", kern, "-DSALP_BUILD_F64=1", "-fmad=false"] + COMMON + vflag, [kern] + hdrs),
+        (os.path.join(OBJ, "salp_kernels_f64.o"), [NVCC, "-c", kern, "-DSALP_BUILD_F64=1", "-fmad=false"] + COMMON + vflag + os.environ.get("SALP_F64_DEFS", "").split(), [kern] + hdrs),
         (os.path.join(OBJ, "salp_capi.o"), [NVCC, "-c", capi] + COMMON, [capi] + hdrs),
         (os.path.join(OBJ, "salp_replay.o"), [NVCC, "-c", replay] + COMMON, [replay] + hdrs),
         (os.path.join(OBJ, "salp_actor.o"), [NVCC, "-c", actor] + COMMON + vflag + actor_defs, [actor] + hdrs),

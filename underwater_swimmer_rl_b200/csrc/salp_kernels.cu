@@ -27,7 +27,15 @@ template <int F> struct StepCfg {
     static constexpr int block = 64;
     static constexpr int prefetch = 0;
     static constexpr int regs_f32 = F <= 4 ? 64 : (F <= 12 ? 80 : (F <= 16 ? 128 : 255));
-    static constexpr int regs = SALP_BUILD_F64 ? (2 * regs_f32 > 255 ? 255 : 2 * regs_f32) : regs_f32;
+    // validation build: twice the f32 budget, except that up to four food slots run best at 96 (20 warps/SM, 12-20 bytes of
+    // spill: 1 M single-food envs 90.4 us at 128 registers, 80.7 at 96, 84.8 at 80 -- measured on B200)
+#ifndef SALP_F64_REGS_SMALLF
+#define SALP_F64_REGS_SMALLF 96
+#endif
+#ifndef SALP_F64_REGS_F12
+#define SALP_F64_REGS_F12 160
+#endif
+    static constexpr int regs = SALP_BUILD_F64 ? (F <= 4 ? SALP_F64_REGS_SMALLF : (F <= 12 ? SALP_F64_REGS_F12 : (2 * regs_f32 > 255 ? 255 : 2 * regs_f32))) : regs_f32;
     static constexpr int minb = (65536 / (regs * block)) > 32 ? 32 : (65536 / (regs * block) < 1 ? 1 : 65536 / (regs * block));
 };
 
