@@ -306,6 +306,9 @@ EDGE_CASES = {
     "crowded_no_respawn_random_count": dict(num_food_items=12, respawn_food=False, random_food_count=True,
                                             max_steps_without_food=500, efficiency_bonus=0.5, proximity_reward_weight=1.0),
     "timeout_zero": dict(num_food_items=1, max_steps_without_food=0),
+    # twelve foods cannot keep 80 px apart in a 460 x 380 tank: the reset layout runs into the 100-attempt cap (S:100-117) and
+    # spans several 32-candidate windows, respawns reject most candidates and some take the unconditional 51st draw (S:232-276)
+    "crowded_tank_twelve": dict(width=460, height=380, num_food_items=12, max_steps_without_food=200, efficiency_bonus=0.5),
 }
 
 

@@ -165,6 +165,22 @@ def test_fp32_teacher_forced_through_every_event(cfg, N, T, autoreset, seed0, ex
     assert st["swaps"] <= max(3, n_steps // 100_000) and st["reset_flips"] <= 2, st
 
 
+def test_fp32_crowded_tank_takes_the_capped_layout_and_respawn_paths(oracle_lib, salp_lib):
+    """Twelve foods cannot keep 80 px apart in a 460 x 380 tank: every reset layout runs into the 100-attempt cap (S:100-117)
+    and spans several 32-candidate windows, respawns reject most candidates and some take the unconditional 51st draw
+    (S:232-276) -- the paths of layout_warp / respawn_warp that the 800 x 600 tank almost never walks.  The fp32 forced-breathing
+    kernel (salp_step_fast_kernel<12, 0>), teacher-forced against the oracle: cursors equal word for word after every respawn
+    and reset, food layouts within 1e-3 px."""
+    N, T = 256, 1100
+    st = _teacher_forced(oracle_lib, "defaults", N, T, True, 71_000, dict(width=460, height=380, max_steps_without_food=200), False)
+    print(f"\n[fp32 parity] crowded tank: {st}")
+    assert st["hits"] > 100 and st["resets"] > 100, st
+    assert st["obs"] <= OBS_BAR and st["rew"] <= REWARD_BAR and st["reset_obs"] <= OBS_BAR and st["food"] <= FOOD_BAR, st
+    assert st["unexplained"] == 0, st
+    # far more 80-px rejection tests per reset than in the big tank (hundreds): a few may sit on an fp32 rounding
+    assert st["flips"] <= 5 and st["reset_flips"] <= 5 and st["swaps"] <= 10, st
+
+
 def test_fp32_free_running_long_horizon_65536(oracle_lib, salp_lib):
     """BASELINE configs[2]: single_food_long_horizon, 65 536 envs, fp32, 5 000 steps, NOT teacher-forced, against
     the OpenMP oracle on the same seeds and open-loop actions.  fp32 and fp64 trajectories separate (positions are
