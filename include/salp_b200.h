@@ -237,7 +237,8 @@ int salp_step_slot(SalpHandle *h, int slot, const void *actions, void *cuda_stre
  * Host-buffer convenience path (what a caller holding numpy arrays uses): copies
  * actions host->device (into the caller-owned DEVICE staging buffer `actions_staging`,
  * real [N][act_dim]), runs one step (K=1), copies obs/reward/terminated/truncated
- * device->host, in 8 chunks on internal non-blocking streams so the copies overlap the kernel, and
+ * device->host -- the observation rows in 8 chunks on internal non-blocking streams so that the copies overlap the
+ * kernels of the later chunks, rewards and flags as one copy per array once every chunk has run -- and
  * returns after the results are in host memory.  The chunks start after the work already queued
  * on `caller_stream` (an event is recorded there); work queued on it later runs after the call
  * has returned.  Host pointers should be page-locked.  Any output pointer may be NULL.

@@ -41,7 +41,19 @@ int cuda_fail(cudaError_t e, const char *what) {
         if (err__ != cudaSuccess) return cuda_fail(err__, #expr); \
     } while (0)
 
-constexpr int kHostChunks = 8;  // the last chunk's copy tail is 1/8 of the transfer
+constexpr int kHostChunks = 16;  // streams available to salp_step_host; it uses host_chunks() of them
+
+// chunks of one salp_step_host call: enough that the first chunk's copy-in + kernel (the only part of the step that does not
+// overlap a device->host copy) is short, few enough that the per-copy overhead stays small.  SALP_HOST_CHUNKS overrides.
+int host_chunks() {
+    static int n = 0;
+    if (n == 0) {
+        int v = 8;
+        if (const char *ev = getenv("SALP_HOST_CHUNKS")) v = atoi(ev);
+        n = v < 1 ? 1 : (v > kHostChunks ? kHostChunks : v);
+    }
+    return n;
+}
 
 int pick_food_slots(int n) {
     const int opts[] = {1, 4, 8, 12, 16, 32};
@@ -125,6 +137,7 @@ struct SalpHandle {
     int64_t launches;
     cudaStream_t host_streams[kHostChunks];
     cudaEvent_t host_event;
+    cudaEvent_t chunk_done[kHostChunks];  // step_host: "the step kernel of chunk c has run"
     bool host_streams_ready;
     salp::CycleEntry *cycle_tab;  // device copy of the forced-breathing cycle table (handle-owned parameter data)
 };
@@ -267,6 +280,7 @@ int salp_destroy(SalpHandle *h) {
         cudaSetDevice(h->device);
         for (auto &s : h->host_streams) cudaStreamDestroy(s);
         cudaEventDestroy(h->host_event);
+        for (auto &ev : h->chunk_done) cudaEventDestroy(ev);
     }
     delete h;
     return SALP_OK;
@@ -420,6 +434,7 @@ int salp_step_host(SalpHandle *h, void *actions_staging, const void *actions_hos
     if (!h->host_streams_ready) {
         for (auto &s : h->host_streams) SALP_CUDA(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
         SALP_CUDA(cudaEventCreateWithFlags(&h->host_event, cudaEventDisableTiming));
+        for (auto &ev : h->chunk_done) SALP_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
         h->host_streams_ready = true;
     }
     // the chunk streams start after everything already queued on the caller's stream (e.g. the reset, or set_attr copies)
@@ -428,7 +443,7 @@ int salp_step_host(SalpHandle *h, void *actions_staging, const void *actions_hos
     const size_t rb = (size_t)h->layout.real_bytes, ad = (size_t)h->layout.act_dim, od = (size_t)h->layout.obs_dim;
     // chunk boundaries on CTA / tile granularity so every chunk but the last is a whole number of tiles
     const int64_t tiles = (N + salp::kHostChunkAlign - 1) / salp::kHostChunkAlign;
-    const int chunks = (int)std::min<int64_t>(kHostChunks, tiles);
+    const int chunks = (int)std::min<int64_t>(host_chunks(), tiles);
     int rc = SALP_OK;
     for (int c = 0; c < chunks && rc == SALP_OK; ++c) {
         const int64_t t0 = tiles * c / chunks, t1 = tiles * (c + 1) / chunks;
@@ -445,14 +460,19 @@ int salp_step_host(SalpHandle *h, void *actions_staging, const void *actions_hos
         a.count = hi - lo;
         rc = launch_step(h, a, s);
         if (rc != SALP_OK) break;
+        SALP_CUDA(cudaEventRecord(h->chunk_done[c], s));
+        // the observation rows (94 % of the bytes) leave chunk by chunk, overlapping the later chunks' kernels
         if (obs_host)
             SALP_CUDA(cudaMemcpyAsync(obs_host + lo * od, h->buf.obs + lo * od, n * od * sizeof(float), cudaMemcpyDeviceToHost, s));
-        if (reward_host)
-            SALP_CUDA(cudaMemcpyAsync((char *)reward_host + lo * rb, (char *)h->buf.reward + lo * rb, n * rb, cudaMemcpyDeviceToHost, s));
-        if (terminated_host)
-            SALP_CUDA(cudaMemcpyAsync(terminated_host + lo, h->buf.terminated + lo, n, cudaMemcpyDeviceToHost, s));
-        if (truncated_host)
-            SALP_CUDA(cudaMemcpyAsync(truncated_host + lo, h->buf.truncated + lo, n, cudaMemcpyDeviceToHost, s));
+    }
+    if (rc == SALP_OK && chunks > 0) {
+        // rewards and flags (6 bytes per env) as ONE copy per array once every chunk's kernel has run: 3 copies at full link
+        // rate instead of 24 short ones (a 128 KB copy costs ~5 us of link time whatever its size)
+        cudaStream_t s = h->host_streams[chunks - 1];
+        for (int c = 0; c + 1 < chunks; ++c) SALP_CUDA(cudaStreamWaitEvent(s, h->chunk_done[c], 0));
+        if (reward_host) SALP_CUDA(cudaMemcpyAsync(reward_host, h->buf.reward, (size_t)N * rb, cudaMemcpyDeviceToHost, s));
+        if (terminated_host) SALP_CUDA(cudaMemcpyAsync(terminated_host, h->buf.terminated, (size_t)N, cudaMemcpyDeviceToHost, s));
+        if (truncated_host) SALP_CUDA(cudaMemcpyAsync(truncated_host, h->buf.truncated, (size_t)N, cudaMemcpyDeviceToHost, s));
     }
     for (int c = 0; c < chunks; ++c) {
         cudaError_t e = cudaStreamSynchronize(h->host_streams[c]);
