@@ -517,11 +517,7 @@ __global__ void __launch_bounds__(FastCfg<F>::warps * 32, FastCfg<F>::minb) salp
                 SALP_LAB_T(8);
                 if (done_mask == 0u) break;
                 SALP_LAB_V(12, __popc(done_mask));
-#ifdef SALP_LAB_NO_STATS
-                if (false) {
-#else
                 if (a.stats) {
-#endif
                     // ---- episode statistics: the (rare) finished lanes add their own episode -- reductions without a
                     //      return value, nothing on the warp's dependent chain (a shuffle tree of doubles was ~1 300 cycles)
                     if (done) {
@@ -538,9 +534,6 @@ __global__ void __launch_bounds__(FastCfg<F>::warps * 32, FastCfg<F>::minb) salp
                 if (done && a.final_info)
                     reinterpret_cast<float4 *>(a.final_info)[(size_t)k * N + e] =
                         make_float4(ep_ret, (float)ep_len, (float)food_collected, (float)steps_since_food);
-#ifdef SALP_LAB_NO_RESET
-                break;
-#endif
                 if (!a.autoreset) break;
                 if (done && a.final_obs) {  // terminal observation (gymnasium "final_observation")
                     float4 *dst = reinterpret_cast<float4 *>(a.final_obs + ((size_t)k * N + e) * OBS);
@@ -564,11 +557,7 @@ __global__ void __launch_bounds__(FastCfg<F>::warps * 32, FastCfg<F>::minb) salp
                     break;
                 } else {
                     // ---- auto-reset (S:133-155): the whole warp lays out the food of each finished env in turn
-#ifdef SALP_LAB_NO_LAYOUT
-                    for (unsigned m = 0u; m != 0u; m &= m - 1u) {
-#else
                     for (unsigned m = done_mask; m != 0u; m &= m - 1u) {
-#endif
                         const int src = __ffs((int)m) - 1;
                         const unsigned e_src = __shfl_sync(kFull, e, src);
                         const LayoutResult<float> Lr = layout_warp<float>(a, e_src, __shfl_sync(kFull, cur_food, src), lane);
