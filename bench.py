@@ -703,6 +703,22 @@ def main():
             strong[name] = {"ms_per_step_per_gpu": ms3_max, "value": n_s * world / (ms3_max * 1e-3), "achieved_gbs_per_gpu": ach,
                             "frac": ach / peak, "algorithmic_bytes_per_env_step": b3}
         extras["strong"] = strong
+        if wl["dtype"] == "float32":
+            # the fp64 validation build (bit-exact discrete trajectories against the reference) on the same workload,
+            # same protocol: north_star couples ">= 60 % of the HBM roofline" with bit-exact discrete state
+            s4 = SlabTimer(torch, wl["params"], N, dev, "float64", rank * N, args.rng, 1, args.graph == "on", 1234 + rank)
+            n4 = max(min(args.steps, 400), 64)
+            ms4, _ = s4.time(n4, args.warmup, args.prime_steps, dist, world)
+            ms4_max, _ = rank_max_min(torch, dist, dev, ms4 / n4, world)
+            s4.close()
+            del s4
+            torch.cuda.empty_cache()
+            b4 = algorithmic_bytes_per_env_step(nf, 8, 1, act_dim, obs_dim)
+            ach4 = b4 * N / (ms4_max * 1e-3) / 1e9
+            extras["fp64_validation_build"] = {"ms_per_step": ms4_max, "value": world * N / (ms4_max * 1e-3), "steps": n4,
+                                               "algorithmic_bytes_per_env_step": b4, "achieved_gbs_per_gpu": ach4, "frac": ach4 / peak,
+                                               "note": "dtype f64, reference operation order, discrete trajectories bit-exact vs the oracle "
+                                                       "(tests/test_gpu_parity.py); same workload, slab size and timing protocol as `value`"}
 
     if rank == 0:
         bpe = algorithmic_bytes_per_env_step(nf, rb, K, act_dim, obs_dim)
